@@ -1,0 +1,204 @@
+/* orlg.h — C-ABI of the B200-native batched stepping engine for the QoT-aware
+ * Optical RL-Gym environments (RMSA-v0, DeepRMSA-v0, RMCSA-v0, PhyRMSA-v0).
+ *
+ * The reference (pure Python) has no FFI; the boundary this ABI replaces is the
+ * gym.Env protocol of its envs:
+ *   orlg_create      <- RMSAEnv.__init__       optical_rl_gym/envs/rmsa_env.py:29-220
+ *                       DeepRMSAEnv.__init__   optical_rl_gym/envs/deeprmsa_env.py:10-46
+ *                       RMCSAEnv.__init__      optical_rl_gym/envs/rmcsa_env.py:29-207
+ *   orlg_reset       <- RMSAEnv.reset          rmsa_env.py:343-457 (full / counters-only)
+ *   orlg_step        <- RMSAEnv.step           rmsa_env.py:222-341
+ *                       DeepRMSAEnv.step       deeprmsa_env.py:48-58
+ *                       RMCSAEnv.step          rmcsa_env.py:209-339
+ *   orlg_observation <- DeepRMSAEnv.observation deeprmsa_env.py:60-121,
+ *                       SimpleMatrixObservation rmsa_env.py:940-971
+ *   orlg_heuristic   <- shortest_path_first_fit rmsa_env.py:854-871,
+ *                       shortest_available_path_first_fit rmsa_env.py:901-913,
+ *                       least_loaded_path_first_fit rmsa_env.py:916-937,
+ *                       deeprmsa_env.py:135-155, rmcsa_env.py:882-911
+ *   orlg_rollout     <- utils.evaluate_heuristic utils.py:124-162 (heuristic+step loop)
+ *   orlg_load_trace  <- the five rng draws of _next_service rmsa_env.py:646-659
+ *   orlg_get_counters<- the counters behind the info dict rmsa_env.py:293-307
+ *   orlg_export_state<- topology.graph["available_slots"] rmsa_env.py:396-398
+ *   orlg_gsnr        <- calculate_osnr examples/calculate_osnr.py:9-56
+ *
+ * All pointers named dev_* are CUDA device pointers owned by the caller; the
+ * engine owns its internal state.  Functions return 0 or a negative ORLG_E*.
+ * Work is asynchronous on the given stream (a cudaStream_t passed as void*).
+ * No C++ exceptions and no torch types cross this boundary.
+ */
+#ifndef ORLG_H
+#define ORLG_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORLG_ABI_VERSION 1
+
+enum {
+  ORLG_OK = 0,
+  ORLG_EINVAL = -1,   /* bad config / argument */
+  ORLG_ENOMEM = -2,   /* device or host allocation failed */
+  ORLG_ECUDA = -3,    /* CUDA runtime error (see orlg_last_error) */
+  ORLG_ESTATE = -4,   /* call not valid in this state (e.g. replay without trace) */
+  ORLG_EFAULT = -5    /* device-side sticky fault (heap overflow ...) */
+};
+
+enum { ORLG_ENV_RMSA = 0, ORLG_ENV_DEEPRMSA = 1, ORLG_ENV_RMCSA = 2, ORLG_ENV_PHYRMSA = 3 };
+
+enum { ORLG_SRC_REPLAY = 0, ORLG_SRC_PHILOX = 1 };
+
+/* heuristic ids (orlg_heuristic / orlg_rollout) */
+enum {
+  ORLG_H_SP_FF = 0,    /* rmsa_env.py:854-871 ; DeepRMSA: deeprmsa_env.py:135-143 */
+  ORLG_H_SAP_FF = 1,   /* rmsa_env.py:901-913 ; DeepRMSA: deeprmsa_env.py:146-155 */
+  ORLG_H_LLP_FF = 2,   /* rmsa_env.py:916-937 */
+  ORLG_H_SAP_BM_FC_FF = 3, /* rmcsa_env.py:882-911 */
+  ORLG_H_RANDOM = 4    /* uniform action from the env's Philox stream */
+};
+
+enum { ORLG_OBS_NONE = 0, ORLG_OBS_F64 = 1, ORLG_OBS_F32 = 2, ORLG_OBS_MATRIX_U8 = 3 };
+
+/* One request as drawn by _next_service (rmsa_env.py:646-659).  `arrival` is the
+ * absolute clock value after the draw (current_time + expovariate), `holding`
+ * the holding time; both raw f64 so that replay is bit-exact. */
+typedef struct orlg_request {
+  double arrival;
+  double holding;
+  int32_t bit_rate;
+  int16_t src; /* node ids in graph["node_indices"] order */
+  int16_t dst;
+} orlg_request; /* 24 bytes */
+
+typedef struct orlg_config {
+  int32_t abi_version; /* = ORLG_ABI_VERSION */
+  int32_t env_kind;    /* ORLG_ENV_* */
+  int32_t device;      /* CUDA device ordinal */
+  int32_t num_envs;    /* envs held by this engine (this GPU's shard) */
+  int64_t global_env_offset; /* global id of local env 0 (Philox key, trace rows) */
+
+  /* topology tables, host pointers, copied by orlg_create */
+  int32_t n_nodes, n_edges, k_paths, max_hops;
+  const int16_t* path_links;       /* [n_nodes*n_nodes][k_paths][max_hops], -1 padded, by edge "index" */
+  const int16_t* path_links_by_id; /* same through edge "id" (rmsa_env.py:750, F9) or NULL = path_links */
+  const int32_t* path_hops;        /* [n_nodes*n_nodes][k_paths], 0 = absent */
+  const double* path_length;       /* [n_nodes*n_nodes][k_paths] km */
+  const int32_t* path_se;          /* spectral efficiency of best_modulation */
+  int32_t n_mods;
+  const int32_t* mod_se;           /* [n_mods] */
+  const double* mod_max_length;    /* [n_mods] */
+  const double* mod_reach;         /* RMCSA: [n_mods] lmax_xt (rmcsa_env.py:377-379), host-evaluated */
+  const double* mod_snr_coeff;     /* RMCSA: [n_mods] SNR_min*h*f*G*NF prefix product (rmcsa_env.py:366-374) */
+
+  /* env parameters (constructor kwargs of the reference) */
+  int32_t num_slots;     /* num_spectrum_resources */
+  int32_t num_cores;     /* num_spatial_resources (RMCSA), else 1 */
+  int32_t j;             /* DeepRMSA blocks per path */
+  int32_t episode_length;
+  int32_t allow_rejection;
+  int32_t auto_reset;    /* VecEnv semantics: counters-only reset in-kernel when done */
+  double channel_width;  /* GHz per slot (12.5) */
+  double mean_iat;       /* mean_service_inter_arrival_time (optical_network_env.py:127-129) */
+  double mean_holding;   /* mean_service_holding_time */
+
+  /* request source */
+  int32_t request_source; /* ORLG_SRC_* */
+  int32_t n_bit_rates;    /* discrete table size, 0 = continuous randint(lo, hi) */
+  uint64_t seed;          /* Philox key */
+  const int32_t* bit_rates;     /* [n_bit_rates] */
+  const double* bit_rate_cum;   /* [n_bit_rates] cumulative weights (random.choices) */
+  int32_t bit_rate_lo, bit_rate_hi;
+  const double* src_cum;        /* [n_nodes] cumulative node weights */
+  const double* dst_cum;        /* [n_nodes][n_nodes] cumulative weights given src (optical_network_env.py:201-206) */
+
+  int32_t heap_capacity;  /* release-queue entries per env; 0 = provable bound */
+  int32_t obs_kind;       /* ORLG_OBS_* written by orlg_step */
+  int32_t reserved[6];
+} orlg_config;
+
+typedef struct orlg_engine orlg_engine;
+
+/* counters exported per env by orlg_get_counters, int64 each */
+enum {
+  ORLG_C_SERVICES_PROCESSED = 0,
+  ORLG_C_SERVICES_ACCEPTED = 1,
+  ORLG_C_EP_SERVICES_PROCESSED = 2,
+  ORLG_C_EP_SERVICES_ACCEPTED = 3,
+  ORLG_C_BIT_RATE_REQUESTED = 4,
+  ORLG_C_BIT_RATE_PROVISIONED = 5,
+  ORLG_C_EP_BIT_RATE_REQUESTED = 6,
+  ORLG_C_EP_BIT_RATE_PROVISIONED = 7,
+  ORLG_C_REQUESTS_DRAWN = 8,   /* number of _next_service draws so far */
+  ORLG_C_QUEUE_LEN = 9,        /* live entries of the release heap */
+  ORLG_C_FAULT = 10,           /* sticky fault bits */
+  ORLG_C_EPISODES = 11,        /* completed episodes */
+  ORLG_NUM_COUNTERS = 12
+};
+
+int orlg_abi_version(void);
+const char* orlg_build_info(void);
+
+int orlg_create(const orlg_config* cfg, orlg_engine** out);
+int orlg_destroy(orlg_engine* e);
+const char* orlg_last_error(const orlg_engine* e);
+
+/* Geometry helpers so callers can size their buffers. */
+int orlg_action_dim(const orlg_engine* e);
+int orlg_obs_dim(const orlg_engine* e);        /* elements per env of the configured obs */
+int64_t orlg_state_words(const orlg_engine* e); /* uint32 words per env of the packed occupancy */
+int64_t orlg_hbm_bytes(const orlg_engine* e);   /* device bytes owned by the engine */
+
+/* Replay source: dev_trace is [n_requests][num_envs] orlg_request (request r of
+ * local env i at dev_trace[r*num_envs + i]); the engine keeps the pointer (caller
+ * keeps the buffer alive).  Request 0 is consumed by orlg_reset(full=1). */
+int orlg_load_trace(orlg_engine* e, const orlg_request* dev_trace, int64_t n_requests);
+
+/* full=1: constructor-time reset (rmsa_env.py:391-457) incl. drawing the first
+ * request; full=0: per-episode counters only (rmsa_env.py:344-389). */
+int orlg_reset(orlg_engine* e, int full, void* stream);
+
+/* One env step for every env.  dev_actions: int32 [num_envs][action_dim].
+ * Outputs (any may be NULL): dev_reward int32[num_envs], dev_done uint8[num_envs],
+ * dev_obs [num_envs][obs_dim] of the configured obs type, dev_alloc int32
+ * [num_envs][4] = (accepted, path, initial_slot, n_slots) of the decision taken
+ * (core in bits 16.. of path for RMCSA). */
+int orlg_step(orlg_engine* e, const int32_t* dev_actions, int32_t* dev_reward,
+              uint8_t* dev_done, void* dev_obs, int32_t* dev_alloc, void* stream);
+
+/* Same, with HOST buffers: copies actions H2D, steps, copies outputs D2H and
+ * synchronises the stream (the end-to-end path measured by bench.py "e2e"). */
+int orlg_step_host(orlg_engine* e, const int32_t* host_actions, int32_t* host_reward,
+                   uint8_t* host_done, void* host_obs, int32_t* host_alloc, void* stream);
+
+/* Observation of the pending request without stepping. */
+int orlg_observation(orlg_engine* e, int obs_kind, void* dev_obs, void* stream);
+
+/* Device-side heuristic: writes the action the reference heuristic would return. */
+int orlg_heuristic(orlg_engine* e, int heuristic_id, int32_t* dev_actions, void* stream);
+
+/* nsteps x (heuristic -> step) in one launch, state staged on chip between steps.
+ * dev_reward_sum (optional) int64[num_envs] accumulates rewards. */
+int orlg_rollout(orlg_engine* e, int heuristic_id, int nsteps, int64_t* dev_reward_sum,
+                 void* stream);
+
+int orlg_get_counters(orlg_engine* e, int64_t* dev_out /* [num_envs][ORLG_NUM_COUNTERS] */,
+                      void* stream);
+
+/* Unpacked occupancy: uint8 [num_envs][num_cores][n_edges][num_slots], 1 = free,
+ * i.e. topology.graph["available_slots"] of every env. */
+int orlg_export_state(orlg_engine* e, uint8_t* dev_out, void* stream);
+
+/* Pending request of every env (current_service). */
+int orlg_get_requests(orlg_engine* e, orlg_request* dev_out, void* stream);
+
+/* kernels launched by this engine so far (bench.py "gpu_launches") */
+int64_t orlg_launch_count(const orlg_engine* e);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORLG_H */

@@ -1,0 +1,210 @@
+"""Host-side flattening of the reference's constructor kwargs into one POD spec.
+
+``EnvSpec`` carries exactly what ``orlg_config`` (include/orlg.h) needs: the
+flat topology tables plus the scalar env parameters, evaluated on the host with
+the reference's own expressions so that every value the device compares against
+is bit-identical to what the Python reference would have computed:
+
+* ``mean_iat = 1 / (load / holding)``        optical_network_env.py:127-129
+* default bit rates 200..1200 step 50        rmsa_env.py:37-38
+* cumulative weights of ``random.choices``   optical_network_env.py:197-206
+* RMCSA QoT factors (10**x terms)            rmcsa_env.py:341-384, +4 dB rmcsa_env.py:127-129
+"""
+from __future__ import annotations
+
+import itertools
+from dataclasses import dataclass, field
+from typing import Optional, Sequence
+
+import numpy as np
+
+from .tables import TopologyTables
+
+ENV_RMSA, ENV_DEEPRMSA, ENV_RMCSA, ENV_PHYRMSA = 0, 1, 2, 3
+SRC_REPLAY, SRC_PHILOX = 0, 1
+OBS_NONE, OBS_F64, OBS_F32, OBS_MATRIX_U8 = 0, 1, 2, 3
+H_SP_FF, H_SAP_FF, H_LLP_FF, H_SAP_BM_FC_FF, H_RANDOM = 0, 1, 2, 3, 4
+
+ENV_IDS = {
+    "RMSA-v0": ENV_RMSA,
+    "DeepRMSA-v0": ENV_DEEPRMSA,
+    "RMCSA-v0": ENV_RMCSA,
+    "RMCSA": ENV_RMCSA,
+    "PhyRMSA-v0": ENV_PHYRMSA,
+}
+
+DEFAULT_BIT_RATES = tuple(range(200, 1201, 50))  # rmsa_env.py:37-38
+WORST_XT_BY_CORE = {7: -84.7, 12: -61.9, 19: -54.8}  # rmcsa_env.py:63-67
+
+
+def _cum(weights) -> np.ndarray:
+    # random.choices: cum_weights = list(itertools.accumulate(weights))
+    return np.array(list(itertools.accumulate(float(w) for w in weights)), np.float64)
+
+
+@dataclass
+class EnvSpec:
+    env_kind: int
+    tables: TopologyTables
+    num_slots: int = 100
+    num_cores: int = 1
+    j: int = 1
+    episode_length: int = 1000
+    allow_rejection: bool = False
+    auto_reset: bool = False
+    channel_width: float = 12.5
+    mean_holding: float = 10800.0
+    mean_iat: float = 1080.0
+    load: float = 10.0
+    bit_rates: Optional[np.ndarray] = None  # None => continuous randint(lo, hi)
+    bit_rate_cum: Optional[np.ndarray] = None
+    bit_rate_lo: int = 25
+    bit_rate_hi: int = 100
+    node_probs: np.ndarray = field(default_factory=lambda: np.zeros(0))
+    src_cum: np.ndarray = field(default_factory=lambda: np.zeros(0))
+    dst_cum: np.ndarray = field(default_factory=lambda: np.zeros(0))
+    mod_reach: Optional[np.ndarray] = None
+    mod_snr_coeff: Optional[np.ndarray] = None
+    worst_xt: Optional[float] = None
+    seed: int = 41
+    request_source: int = SRC_PHILOX
+    obs_kind: int = OBS_NONE
+
+    @property
+    def action_dim(self) -> int:
+        return {ENV_RMSA: 2, ENV_DEEPRMSA: 1, ENV_RMCSA: 4}.get(self.env_kind, 2)
+
+    @property
+    def obs_dim(self) -> int:
+        t = self.tables
+        if self.obs_kind in (OBS_F64, OBS_F32):
+            return 1 + 2 * t.n_nodes + (2 * self.j + 3) * t.k_paths  # deeprmsa_env.py:35-37
+        if self.obs_kind == OBS_MATRIX_U8:
+            return 2 * t.n_nodes + self.num_cores * t.n_edges * self.num_slots  # rmsa_env.py:943-946
+        return 0
+
+    @property
+    def reject_action(self):
+        t = self.tables
+        if self.env_kind == ENV_RMSA:
+            return (t.k_paths, self.num_slots)
+        if self.env_kind == ENV_DEEPRMSA:
+            return (t.k_paths * self.j,)
+        return (t.k_paths, len(t.mod_names), self.num_cores, self.num_slots)
+
+
+def rmcsa_qot_factors(tables: TopologyTables, worst_xt: float):
+    """Modulation-only factors of ``_crosstalk_is_acceptable`` (rmcsa_env.py:341-384),
+    evaluated with the reference's expression order.  ``worst_xt`` is the user
+    value; the +4 dB the constructor adds to it and to every ``inband_xt``
+    (rmcsa_env.py:127-129) is applied here."""
+    nf = 10.0 ** (5.5 / 10.0)
+    amp_gain = 10.0 ** (20 / 10.0)
+    h = 6.626068e-34
+    f_hz = 2.99e8 / (1550 * 1e-9)
+    wxt = worst_xt + 4
+    coeff, reach = [], []
+    for m in range(len(tables.mod_names)):
+        snr_min = 10 ** ((float(tables.mod_min_osnr[m]) + 2) / 10)
+        coeff.append(snr_min * h * f_hz * amp_gain * nf)
+        inband = float(tables.mod_inband_xt[m]) + 4
+        reach.append(10 ** ((inband - wxt - 4) / 10))
+    return np.array(coeff, np.float64), np.array(reach, np.float64)
+
+
+def make_spec(
+    env_id,
+    tables: TopologyTables,
+    *,
+    episode_length: int = 1000,
+    load: float = 10.0,
+    mean_service_holding_time: Optional[float] = None,
+    mean_service_inter_arrival_time: Optional[float] = None,
+    num_spectrum_resources: int = 100,
+    num_spatial_resources: int = 7,
+    j: int = 1,
+    bit_rate_selection: Optional[str] = None,
+    bit_rates: Optional[Sequence[int]] = None,
+    bit_rate_probabilities=None,
+    bit_rate_lower_bound: int = 25,
+    bit_rate_higher_bound: int = 100,
+    node_request_probabilities=None,
+    worst_xt: Optional[float] = None,
+    seed: Optional[int] = None,
+    allow_rejection: bool = False,
+    channel_width: float = 12.5,
+    auto_reset: bool = False,
+    request_source: int = SRC_PHILOX,
+    obs_kind: Optional[int] = None,
+) -> EnvSpec:
+    kind = ENV_IDS[env_id] if isinstance(env_id, str) else int(env_id)
+    n = tables.n_nodes
+    if kind == ENV_DEEPRMSA:
+        # deeprmsa_env.py:10-32: load = holding / inter-arrival
+        holding = 25.0 if mean_service_holding_time is None else mean_service_holding_time
+        iat_in = 0.1 if mean_service_inter_arrival_time is None else mean_service_inter_arrival_time
+        load = holding / iat_in
+    else:
+        holding = 10800.0 if mean_service_holding_time is None else mean_service_holding_time
+    mean_iat = 1 / float(load / float(holding))  # optical_network_env.py:127-129
+
+    if bit_rate_selection is None:
+        bit_rate_selection = "continuous" if kind == ENV_RMCSA else "discrete"
+    assert bit_rate_selection in ("continuous", "discrete")
+    br = cum = None
+    if bit_rate_selection == "discrete":
+        if bit_rates is None:
+            bit_rates = (10, 40, 100) if kind == ENV_RMCSA else DEFAULT_BIT_RATES
+        if bit_rate_probabilities is None:
+            bit_rate_probabilities = [1.0 / len(bit_rates) for _ in bit_rates]  # rmsa_env.py:104-107
+        assert len(bit_rates) == len(bit_rate_probabilities)
+        br = np.array(bit_rates, np.int32)
+        cum = _cum(bit_rate_probabilities)
+
+    if node_request_probabilities is None:
+        p = np.full(n, fill_value=1.0 / n)  # optical_network_env.py:106-109
+    else:
+        p = np.asarray(node_request_probabilities, np.float64)
+        assert len(p) == n
+    src_cum = _cum(p)
+    dst_cum = np.zeros((n, n), np.float64)
+    for s in range(n):  # optical_network_env.py:201-203
+        q = np.copy(p)
+        q[s] = 0.0
+        q = q / np.sum(q)
+        dst_cum[s] = _cum(q)
+
+    spec = EnvSpec(
+        env_kind=kind,
+        tables=tables,
+        num_slots=int(num_spectrum_resources),
+        num_cores=int(num_spatial_resources) if kind == ENV_RMCSA else 1,
+        j=int(j) if kind == ENV_DEEPRMSA else 1,
+        episode_length=int(episode_length),
+        allow_rejection=bool(allow_rejection),
+        auto_reset=bool(auto_reset),
+        channel_width=float(channel_width),
+        mean_holding=float(holding),
+        mean_iat=float(mean_iat),
+        load=float(load),
+        bit_rates=br,
+        bit_rate_cum=cum,
+        bit_rate_lo=int(bit_rate_lower_bound),
+        bit_rate_hi=int(bit_rate_higher_bound),
+        node_probs=p,
+        src_cum=src_cum,
+        dst_cum=dst_cum,
+        seed=41 if seed is None else int(seed),  # optical_network_env.py:266-271
+        request_source=request_source,
+    )
+    if kind == ENV_RMCSA:
+        wxt = WORST_XT_BY_CORE.get(spec.num_cores) if worst_xt is None else worst_xt
+        if wxt is None:
+            raise ValueError("worst_xt must be given for this number of cores")
+        spec.worst_xt = float(wxt)
+        spec.mod_snr_coeff, spec.mod_reach = rmcsa_qot_factors(tables, float(wxt))
+    if obs_kind is None:
+        obs_kind = OBS_F64 if kind == ENV_DEEPRMSA else OBS_NONE
+    spec.obs_kind = obs_kind
+    assert spec.num_slots <= 1024 and tables.n_edges <= 128
+    return spec

@@ -1,0 +1,642 @@
+/* orlg_oracle.c — CPU restatement of the reference env stepping path.
+ * TEST INFRASTRUCTURE ONLY (see orlg_oracle.h for the rules and parity status).
+ *
+ * Every function cites the reference lines it follows; paths are relative to
+ * /root/reference/optical_rl_gym/envs/.
+ */
+#include "orlg_oracle.h"
+
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+#include <pthread.h>
+
+/* ------------------------------------------------------------------ RNG -- */
+/* Philox4x32-10 (Salmon et al., SC'11).  Used only by the "philox" request
+ * source, which replaces CPython's MT19937 stream. */
+void oracle_philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                       uint32_t k1, uint32_t out[4]) {
+  for (int r = 0; r < 10; r++) {
+    uint64_t p0 = (uint64_t)0xD2511F53u * c0;
+    uint64_t p1 = (uint64_t)0xCD9E8D57u * c2;
+    uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
+    uint32_t n1 = (uint32_t)p1;
+    uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+    uint32_t n3 = (uint32_t)p0;
+    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+/* Natural log built from IEEE add/mul/div only (fdlibm e_log.c scheme, no FMA)
+ * so that the CUDA engine and this oracle agree bit for bit in philox mode. */
+double oracle_dlog(double x) {
+  static const double ln2_hi = 6.93147180369123816490e-01, ln2_lo = 1.90821492927058770002e-10,
+                      Lg1 = 6.666666666666735130e-01, Lg2 = 3.999999999940941908e-01,
+                      Lg3 = 2.857142874366239149e-01, Lg4 = 2.222219843214978396e-01,
+                      Lg5 = 1.818357216161805012e-01, Lg6 = 1.531383769920937332e-01,
+                      Lg7 = 1.479819860511658591e-01;
+  uint64_t bits;
+  memcpy(&bits, &x, 8);
+  int k = 0;
+  if ((bits >> 52) == 0) { /* subnormal or zero: scale up (never hit for 1-u, u<1) */
+    x *= 18014398509481984.0; /* 2^54 */
+    memcpy(&bits, &x, 8);
+    k = -54;
+  }
+  k += (int)(bits >> 52) - 1023;
+  uint64_t mant = bits & 0x000FFFFFFFFFFFFFull;
+  /* bring m into [sqrt(1/2), sqrt(2)) */
+  if (mant >= 0x6A09E667F3BCDull) {
+    k += 1;
+    bits = mant | 0x3FE0000000000000ull;
+  } else {
+    bits = mant | 0x3FF0000000000000ull;
+  }
+  double m;
+  memcpy(&m, &bits, 8);
+  double f = m - 1.0;
+  double s = f / (2.0 + f);
+  double z = s * s;
+  double w = z * z;
+  double t1 = w * (Lg2 + w * (Lg4 + w * Lg6));
+  double t2 = z * (Lg1 + w * (Lg3 + w * (Lg5 + w * Lg7)));
+  double R = t2 + t1;
+  double hfsq = 0.5 * f * f;
+  double dk = (double)k;
+  return dk * ln2_hi - ((hfsq - (s * (hfsq + R) + dk * ln2_lo)) - f);
+}
+
+static double res53(uint32_t a, uint32_t b) { /* MT genrand_res53 form */
+  return ((double)(a >> 5) * 67108864.0 + (double)(b >> 6)) / 9007199254740992.0;
+}
+
+/* bisect.bisect_right(cum, x, 0, hi) as used by random.choices */
+static int bisect_right(const double* cum, double x, int hi) {
+  int lo = 0;
+  while (lo < hi) {
+    int mid = (lo + hi) / 2;
+    if (x < cum[mid]) hi = mid; else lo = mid + 1;
+  }
+  return lo;
+}
+
+/* The five draws of _next_service (rmsa_env.py:646-659; _get_node_pair
+ * optical_network_env.py:191-208) on the Philox stream of one env. */
+void oracle_philox_request(const oracle_config* c, int64_t genv, int64_t r, double now,
+                           oracle_request* out) {
+  uint32_t R0[4], R1[4];
+  uint32_t k0 = (uint32_t)c->seed, k1 = (uint32_t)(c->seed >> 32);
+  oracle_philox4x32((uint32_t)r, (uint32_t)((uint64_t)r >> 32), (uint32_t)genv, 0u, k0, k1, R0);
+  oracle_philox4x32((uint32_t)r, (uint32_t)((uint64_t)r >> 32), (uint32_t)genv, 1u, k0, k1, R1);
+  double u_at = res53(R0[0], R0[1]), u_ht = res53(R0[2], R0[3]);
+  double lam_a = 1.0 / c->mean_iat, lam_h = 1.0 / c->mean_holding;
+  out->arrival = now + (-oracle_dlog(1.0 - u_at) / lam_a);
+  out->holding = -oracle_dlog(1.0 - u_ht) / lam_h;
+  double us = (double)R1[0] * (1.0 / 4294967296.0);
+  double ud = (double)R1[1] * (1.0 / 4294967296.0);
+  double ub = (double)R1[2] * (1.0 / 4294967296.0);
+  int n = c->n_nodes;
+  int src = bisect_right(c->src_cum, us * c->src_cum[n - 1], n - 1);
+  const double* dc = c->dst_cum + (size_t)src * n;
+  int dst = bisect_right(dc, ud * dc[n - 1], n - 1);
+  out->src = (int16_t)src;
+  out->dst = (int16_t)dst;
+  if (c->n_bit_rates > 0) {
+    int nb = c->n_bit_rates;
+    out->bit_rate = c->bit_rates[bisect_right(c->bit_rate_cum, ub * c->bit_rate_cum[nb - 1], nb - 1)];
+  } else {
+    out->bit_rate = c->bit_rate_lo + (int32_t)floor(ub * (double)(c->bit_rate_hi - c->bit_rate_lo + 1));
+  }
+}
+
+/* ------------------------------------------------------------ env state -- */
+typedef struct svc { /* a provisioned Service (utils.py:56-80), what release needs */
+  double release_time;
+  int32_t pair, path, core, initial_slot, number_slots;
+} svc;
+
+struct oracle_env {
+  oracle_config c;
+  int64_t genv;
+  uint8_t* avail; /* [cores][E][S], 1 = free: topology.graph["available_slots"] */
+  svc* heap;      /* heapq list of (release_time, service) */
+  int64_t heap_len, heap_cap;
+  double now;     /* current_time */
+  oracle_request cur;
+  int new_service; /* _new_service */
+  int64_t services_processed, services_accepted, ep_processed, ep_accepted;
+  int64_t br_requested, br_provisioned, ep_br_requested, ep_br_provisioned;
+  int64_t requests_drawn, episodes;
+  const oracle_request* trace;
+  int64_t trace_len, trace_stride;
+};
+
+#define AV(e, core, link) ((e)->avail + ((size_t)(core) * (e)->c.n_edges + (link)) * (e)->c.num_slots)
+
+oracle_env* oracle_create(const oracle_config* cfg, int64_t genv) {
+  oracle_env* e = (oracle_env*)calloc(1, sizeof(*e));
+  e->c = *cfg;
+  if (e->c.num_cores < 1) e->c.num_cores = 1;
+  if (e->c.j < 1) e->c.j = 1;
+  e->genv = genv;
+  e->avail = (uint8_t*)malloc((size_t)e->c.num_cores * e->c.n_edges * e->c.num_slots);
+  e->heap_cap = 64;
+  e->heap = (svc*)malloc(sizeof(svc) * e->heap_cap);
+  return e;
+}
+
+void oracle_destroy(oracle_env* e) {
+  if (!e) return;
+  free(e->avail);
+  free(e->heap);
+  free(e);
+}
+
+void oracle_set_trace(oracle_env* e, const oracle_request* t, int64_t n, int64_t stride) {
+  e->trace = t;
+  e->trace_len = n;
+  e->trace_stride = stride;
+}
+
+int oracle_action_dim(const oracle_env* e) {
+  return e->c.env_kind == 0 ? 2 : e->c.env_kind == 1 ? 1 : 4;
+}
+int oracle_obs_dim(const oracle_env* e) { /* deeprmsa_env.py:35-37 */
+  return 1 + 2 * e->c.n_nodes + (2 * e->c.j + 3) * e->c.k_paths;
+}
+
+/* --------------------------------------------------------------- heapq -- */
+/* heapq.heappush / heappop on (release_time, service): _add_release
+ * optical_network_env.py:178-189, consumer rmsa_env.py:689-695. */
+static void heap_push(oracle_env* e, svc item) {
+  if (e->heap_len == e->heap_cap) {
+    e->heap_cap *= 2;
+    e->heap = (svc*)realloc(e->heap, sizeof(svc) * e->heap_cap);
+  }
+  int64_t pos = e->heap_len++;
+  while (pos > 0) { /* _siftdown */
+    int64_t parent = (pos - 1) >> 1;
+    if (item.release_time < e->heap[parent].release_time) {
+      e->heap[pos] = e->heap[parent];
+      pos = parent;
+    } else break;
+  }
+  e->heap[pos] = item;
+}
+
+static svc heap_pop(oracle_env* e) {
+  svc last = e->heap[--e->heap_len];
+  if (e->heap_len == 0) return last;
+  svc ret = e->heap[0];
+  /* _siftup: bubble the smaller child up to a leaf, then sift `last` down */
+  int64_t pos = 0, end = e->heap_len, child = 1;
+  while (child < end) {
+    int64_t right = child + 1;
+    if (right < end && !(e->heap[child].release_time < e->heap[right].release_time)) child = right;
+    e->heap[pos] = e->heap[child];
+    pos = child;
+    child = 2 * pos + 1;
+  }
+  while (pos > 0) {
+    int64_t parent = (pos - 1) >> 1;
+    if (last.release_time < e->heap[parent].release_time) {
+      e->heap[pos] = e->heap[parent];
+      pos = parent;
+    } else break;
+  }
+  e->heap[pos] = last;
+  return ret;
+}
+
+/* ------------------------------------------------------------ core ops -- */
+static const int16_t* links_of(const oracle_env* e, int pair, int path, int by_id) {
+  const int16_t* t = (by_id && e->c.path_links_by_id) ? e->c.path_links_by_id : e->c.path_links;
+  return t + ((size_t)pair * e->c.k_paths + path) * e->c.max_hops;
+}
+static int hops_of(const oracle_env* e, int pair, int path) {
+  return e->c.path_hops[(size_t)pair * e->c.k_paths + path];
+}
+static int cur_pair(const oracle_env* e) { return e->cur.src * e->c.n_nodes + e->cur.dst; }
+
+/* get_number_slots rmsa_env.py:708-719 / rmcsa_env.py:753-765 */
+static int number_slots(const oracle_env* e, int se) {
+  return (int)ceil((double)e->cur.bit_rate / ((double)se * e->c.channel_width)) + 1;
+}
+
+/* is_path_free rmsa_env.py:721-734 / rmcsa_env.py:767-794 */
+static int is_path_free(const oracle_env* e, int pair, int path, int core, int start, int n) {
+  if (start + n > e->c.num_slots) return 0;
+  const int16_t* L = links_of(e, pair, path, 0);
+  int h = hops_of(e, pair, path);
+  for (int i = 0; i < h; i++) {
+    const uint8_t* row = AV(e, core, L[i]);
+    for (int s = start; s < start + n; s++)
+      if (row[s] == 0) return 0;
+  }
+  return 1;
+}
+
+/* _provision_path rmsa_env.py:462-513 / rmcsa_env.py:488-534 (state + counters;
+ * the info-only link/network statistics are out of scope) */
+static void provision_path(oracle_env* e, int pair, int path, int core, int start, int n) {
+  const int16_t* L = links_of(e, pair, path, 0);
+  int h = hops_of(e, pair, path);
+  for (int i = 0; i < h; i++) memset(AV(e, core, L[i]) + start, 0, (size_t)n);
+  e->services_accepted++;
+  e->ep_accepted++;
+  e->br_provisioned += e->cur.bit_rate;
+  e->ep_br_provisioned += e->cur.bit_rate;
+}
+
+/* _release_path rmsa_env.py:515-535 / rmcsa_env.py:536-558 */
+static void release_path(oracle_env* e, const svc* s) {
+  const int16_t* L = links_of(e, s->pair, s->path, 0);
+  int h = hops_of(e, s->pair, s->path);
+  for (int i = 0; i < h; i++) memset(AV(e, s->core, L[i]) + s->initial_slot, 1, (size_t)s->number_slots);
+}
+
+/* get_available_slots rmsa_env.py:745-756 (rows by edge "id", F9); core 0 plane
+ * as in rmcsa_env.py:796-807 is not used by any in-scope caller. */
+static void available_slots(const oracle_env* e, int pair, int path, uint8_t* out) {
+  const int16_t* L = links_of(e, pair, path, 1);
+  int h = hops_of(e, pair, path), S = e->c.num_slots;
+  memset(out, 1, (size_t)S);
+  for (int i = 0; i < h; i++) {
+    const uint8_t* row = AV(e, 0, L[i]);
+    for (int s = 0; s < S; s++) out[s] = (uint8_t)(out[s] * row[s]);
+  }
+}
+
+/* rle rmsa_env.py:758-772: returns number of runs */
+static int rle(const uint8_t* a, int n, int* pos, uint8_t* val, int* len) {
+  int r = 0, start = 0;
+  for (int i = 1; i <= n; i++) {
+    if (i == n || a[i] != a[i - 1]) {
+      pos[r] = start; val[r] = a[start]; len[r] = i - start;
+      r++; start = i;
+    }
+  }
+  return r;
+}
+
+/* get_available_blocks rmsa_env.py:774-804: first j runs of ones with length>=slots */
+static int available_blocks(const oracle_env* e, int pair, int path, int slots, int* starts, int* lens) {
+  int S = e->c.num_slots;
+  uint8_t av[1024], val[1024];
+  int pos[1024], len[1024];
+  available_slots(e, pair, path, av);
+  int r = rle(av, S, pos, val, len), nb = 0;
+  for (int i = 0; i < r && nb < e->c.j; i++)
+    if (val[i] == 1 && len[i] >= slots) { starts[nb] = pos[i]; lens[nb] = len[i]; nb++; }
+  return nb;
+}
+
+/* _next_service rmsa_env.py:643-695 ; rmcsa_env.py:690-739 */
+static void next_service(oracle_env* e) {
+  if (e->new_service) return;
+  oracle_request rq;
+  if (e->c.request_source == 0) {
+    int64_t r = e->requests_drawn < e->trace_len ? e->requests_drawn : e->trace_len - 1;
+    rq = e->trace[r * e->trace_stride];
+  } else {
+    oracle_philox_request(&e->c, e->genv, e->requests_drawn, e->now, &rq);
+  }
+  e->requests_drawn++;
+  e->now = rq.arrival; /* at = current_time + expovariate(...); current_time = at */
+  e->cur = rq;
+  e->new_service = 1;
+  if (e->c.env_kind != 2) { /* rmsa_env.py:673-678 */
+    e->services_processed++;
+    e->ep_processed++;
+  }
+  e->br_requested += rq.bit_rate; /* rmsa_env.py:677-678 ; rmcsa_env.py:730-731 */
+  e->ep_br_requested += rq.bit_rate;
+  while (e->heap_len > 0) { /* rmsa_env.py:689-695 */
+    if (e->heap[0].release_time <= e->now) {
+      svc s = heap_pop(e);
+      release_path(e, &s);
+    } else break; /* pop + push back of the same item leaves the heap's content unchanged */
+  }
+}
+
+/* reset rmsa_env.py:343-457 / rmcsa_env.py:386-483 */
+void oracle_reset(oracle_env* e, int full) {
+  e->ep_br_requested = e->ep_br_provisioned = 0;
+  e->ep_processed = e->ep_accepted = 0;
+  if (!full) {
+    if (e->new_service) { /* pending service is re-counted, rmsa_env.py:370-374 */
+      e->ep_processed++;
+      e->ep_br_requested += e->cur.bit_rate;
+    }
+    return;
+  }
+  e->heap_len = 0; /* OpticalNetworkEnv.reset optical_network_env.py:216-222 */
+  e->now = 0.0;
+  e->services_processed = e->services_accepted = 0;
+  e->br_requested = e->br_provisioned = 0;
+  e->requests_drawn = 0;
+  e->episodes = 0;
+  memset(e->avail, 1, (size_t)e->c.num_cores * e->c.n_edges * e->c.num_slots);
+  e->new_service = 0;
+  next_service(e);
+}
+
+/* ------------------------------------------------------------- stepping -- */
+/* _crosstalk_is_acceptable rmcsa_env.py:341-384.  The modulation-only factors
+ * (10**x terms) are evaluated by the caller in Python with the reference's own
+ * expression order and arrive as mod_snr_coeff / mod_reach. */
+static int crosstalk_ok(const oracle_env* e, int mod, double path_length) {
+  double denom = e->c.mod_snr_coeff[mod] * ((double)e->cur.bit_rate / (double)e->c.mod_se[mod]);
+  denom = denom * 1e9;
+  double lmax_snr = 100.0 / denom;
+  lmax_snr = lmax_snr / 1000.0;
+  double lmax_xt = e->c.mod_reach[mod];
+  return path_length < lmax_xt && path_length < lmax_snr;
+}
+
+static void finish_step(oracle_env* e, int accepted, int32_t* reward, uint8_t* done) {
+  if (e->c.env_kind == 2) { /* rmcsa_env.py:292-295 (bit rate counted a second time) */
+    e->services_processed++;
+    e->ep_processed++;
+    e->br_requested += e->cur.bit_rate;
+    e->ep_br_requested += e->cur.bit_rate;
+  }
+  /* reward: optical_network_env.py:213-214 ; deeprmsa_env.py:123-124 */
+  int r = e->c.env_kind == 1 ? (accepted ? 1 : -1) : (accepted ? 1 : 0);
+  e->new_service = 0;
+  next_service(e);
+  int d = e->ep_processed == e->c.episode_length; /* rmsa_env.py:339 */
+  if (d) {
+    e->episodes++;
+    if (e->c.auto_reset) oracle_reset(e, 0);
+  }
+  if (reward) *reward = r;
+  if (done) *done = (uint8_t)d;
+}
+
+/* RMSAEnv.step rmsa_env.py:222-341 (decision part) */
+static int rmsa_decide(oracle_env* e, int path, int slot, int32_t* alloc) {
+  int pair = cur_pair(e), accepted = 0, n = 0;
+  if (path >= 0 && slot >= 0 && path < e->c.k_paths && slot < e->c.num_slots &&
+      hops_of(e, pair, path) > 0) {
+    n = number_slots(e, e->c.path_se[(size_t)pair * e->c.k_paths + path]);
+    if (is_path_free(e, pair, path, 0, slot, n)) {
+      provision_path(e, pair, path, 0, slot, n);
+      accepted = 1;
+      svc s = {e->cur.arrival + e->cur.holding, pair, path, 0, slot, n};
+      heap_push(e, s); /* _add_release */
+    }
+  }
+  if (alloc) {
+    alloc[0] = accepted;
+    alloc[1] = accepted ? path : -1;
+    alloc[2] = accepted ? slot : -1;
+    alloc[3] = accepted ? n : 0;
+  }
+  return accepted;
+}
+
+void oracle_step(oracle_env* e, const int32_t* a, int32_t* reward, uint8_t* done, double* obs,
+                 int32_t* alloc) {
+  int accepted = 0;
+  int k = e->c.k_paths, S = e->c.num_slots;
+  if (e->c.env_kind == 0) {
+    accepted = rmsa_decide(e, a[0], a[1], alloc);
+  } else if (e->c.env_kind == 1) { /* DeepRMSAEnv.step deeprmsa_env.py:48-58 */
+    int act = a[0], path = k, slot = S;
+    int pair = cur_pair(e);
+    if (act >= 0 && act < k * e->c.j) {
+      int route = act / e->c.j, block = act % e->c.j;
+      if (hops_of(e, pair, route) > 0) {
+        int starts[64], lens[64];
+        int n = number_slots(e, e->c.path_se[(size_t)pair * k + route]);
+        int nb = available_blocks(e, pair, route, n, starts, lens);
+        if (block < nb) { path = route; slot = starts[block]; }
+      }
+    }
+    accepted = rmsa_decide(e, path, slot, alloc);
+  } else { /* RMCSAEnv.step rmcsa_env.py:209-339 */
+    int path = a[0], mod = a[1], core = a[2], slot = a[3], n = 0;
+    int pair = cur_pair(e);
+    if (path >= 0 && mod >= 0 && core >= 0 && slot >= 0 && path < k && mod < e->c.n_mods &&
+        core < e->c.num_cores && slot < S && hops_of(e, pair, path) > 0) {
+      n = number_slots(e, e->c.mod_se[mod]);
+      if (is_path_free(e, pair, path, core, slot, n) &&
+          crosstalk_ok(e, mod, e->c.path_length[(size_t)pair * k + path])) {
+        provision_path(e, pair, path, core, slot, n);
+        accepted = 1;
+        svc s = {e->cur.arrival + e->cur.holding, pair, path, core, slot, n};
+        heap_push(e, s);
+      }
+    }
+    if (alloc) {
+      alloc[0] = accepted;
+      alloc[1] = accepted ? (path | (core << 16)) : -1;
+      alloc[2] = accepted ? slot : -1;
+      alloc[3] = accepted ? n : 0;
+    }
+  }
+  finish_step(e, accepted, reward, done);
+  if (obs && e->c.env_kind == 1) oracle_observation(e, obs);
+}
+
+/* DeepRMSAEnv.observation deeprmsa_env.py:60-121 */
+void oracle_observation(oracle_env* e, double* obs) {
+  int N = e->c.n_nodes, k = e->c.k_paths, j = e->c.j, S = e->c.num_slots;
+  int dim = oracle_obs_dim(e), pair = cur_pair(e);
+  double* tau = obs + 1;
+  double* sp = obs + 1 + 2 * N;
+  for (int i = 0; i < dim; i++) obs[i] = 0.0;
+  obs[0] = (double)e->cur.bit_rate / 100.0;
+  int mn = e->cur.src < e->cur.dst ? e->cur.src : e->cur.dst;
+  int mx = e->cur.src < e->cur.dst ? e->cur.dst : e->cur.src;
+  tau[mn] = 1.0;
+  tau[N + mx] = 1.0;
+  for (int i = 0; i < k * (2 * j + 3); i++) sp[i] = -1.0;
+  uint8_t av[1024], val[1024];
+  int pos[1024], len[1024], starts[64], lens[64];
+  for (int p = 0; p < k; p++) {
+    if (hops_of(e, pair, p) <= 0) continue;
+    double* row = sp + (size_t)p * (2 * j + 3);
+    available_slots(e, pair, p, av);
+    int n = number_slots(e, e->c.path_se[(size_t)pair * k + p]);
+    int nb = available_blocks(e, pair, p, n, starts, lens);
+    for (int b = 0; b < nb; b++) {
+      row[2 * b] = 2.0 * ((double)starts[b] - 0.5 * (double)S) / (double)S;
+      row[2 * b + 1] = ((double)lens[b] - 8.0) / 8.0;
+    }
+    row[2 * j] = ((double)n - 5.5) / 3.5;
+    int r = rle(av, S, pos, val, len);
+    long tot = 0, cnt = 0, sumlen = 0;
+    for (int s = 0; s < S; s++) tot += av[s];
+    row[2 * j + 1] = 2.0 * ((double)tot - 0.5 * (double)S) / (double)S;
+    for (int i = 0; i < r; i++)
+      if (val[i] == 1) { cnt++; sumlen += len[i]; }
+    if (cnt > 0) row[2 * j + 2] = ((double)sumlen / (double)cnt - 4.0) / 4.0; /* np.mean */
+  }
+}
+
+/* SimpleMatrixObservation rmsa_env.py:940-971 / rmcsa_env.py:914-947 */
+void oracle_matrix_observation(oracle_env* e, uint8_t* obs) {
+  int N = e->c.n_nodes;
+  size_t cells = (size_t)e->c.num_cores * e->c.n_edges * e->c.num_slots;
+  memset(obs, 0, 2 * (size_t)N);
+  int mn = e->cur.src < e->cur.dst ? e->cur.src : e->cur.dst;
+  int mx = e->cur.src < e->cur.dst ? e->cur.dst : e->cur.src;
+  obs[mn] = 1;
+  obs[N + mx] = 1;
+  memcpy(obs + 2 * N, e->avail, cells);
+}
+
+/* first fit with the reference's exclusive upper bound range(0, S - n) (F8) */
+static int first_fit(const oracle_env* e, int pair, int path, int core, int n) {
+  for (int s = 0; s < e->c.num_slots - n; s++)
+    if (is_path_free(e, pair, path, core, s, n)) return s;
+  return -1;
+}
+
+void oracle_heuristic(oracle_env* e, int hid, int32_t* a) {
+  int k = e->c.k_paths, S = e->c.num_slots, pair = cur_pair(e);
+  if (e->c.env_kind == 0) {
+    a[0] = k; a[1] = S;
+    if (hid == 0) { /* shortest_path_first_fit rmsa_env.py:854-871 */
+      if (hops_of(e, pair, 0) > 0) {
+        int s = first_fit(e, pair, 0, 0, number_slots(e, e->c.path_se[(size_t)pair * k]));
+        if (s >= 0) { a[0] = 0; a[1] = s; }
+      }
+    } else if (hid == 1) { /* shortest_available_path_first_fit rmsa_env.py:901-913 */
+      for (int p = 0; p < k; p++) {
+        if (hops_of(e, pair, p) <= 0) continue;
+        int s = first_fit(e, pair, p, 0, number_slots(e, e->c.path_se[(size_t)pair * k + p]));
+        if (s >= 0) { a[0] = p; a[1] = s; return; }
+      }
+    } else if (hid == 2) { /* least_loaded_path_first_fit rmsa_env.py:916-937 */
+      long max_free = 0;
+      uint8_t av[1024];
+      for (int p = 0; p < k; p++) {
+        if (hops_of(e, pair, p) <= 0) continue;
+        int s = first_fit(e, pair, p, 0, number_slots(e, e->c.path_se[(size_t)pair * k + p]));
+        if (s >= 0) {
+          available_slots(e, pair, p, av);
+          long fr = 0;
+          for (int i = 0; i < S; i++) fr += av[i];
+          if (fr > max_free) { a[0] = p; a[1] = s; max_free = fr; }
+        }
+      }
+    }
+  } else if (e->c.env_kind == 1) {
+    int starts[64], lens[64];
+    if (hid == 0) { /* deeprmsa_env.py:135-143 */
+      a[0] = 0;
+      if (e->c.allow_rejection) {
+        int nb = hops_of(e, pair, 0) > 0
+                     ? available_blocks(e, pair, 0, number_slots(e, e->c.path_se[(size_t)pair * k]), starts, lens)
+                     : 0;
+        a[0] = nb > 0 ? 0 : k * e->c.j;
+      }
+    } else { /* deeprmsa_env.py:146-155 */
+      a[0] = k * e->c.j;
+      for (int p = 0; p < k; p++) {
+        if (hops_of(e, pair, p) <= 0) continue;
+        int nb = available_blocks(e, pair, p, number_slots(e, e->c.path_se[(size_t)pair * k + p]), starts, lens);
+        if (nb > 0) { a[0] = p * e->c.j; return; }
+      }
+    }
+  } else { /* shortest_available_path_best_modulation_first_core_first_fit rmcsa_env.py:882-911 */
+    a[0] = k; a[1] = e->c.n_mods; a[2] = e->c.num_cores; a[3] = S;
+    for (int p = 0; p < k; p++) {
+      if (hops_of(e, pair, p) <= 0) continue;
+      double len = e->c.path_length[(size_t)pair * k + p];
+      /* get_best_modulation_format utils.py:105-117: highest SE first (stable), first that reaches */
+      int best = -1;
+      for (int se_rank = 0; se_rank < e->c.n_mods && best < 0; se_rank++) {
+        /* pick the se_rank-th modulation in (SE desc, original order) */
+        int chosen = -1, seen = 0;
+        for (int pass_se = 1 << 30; chosen < 0;) {
+          int top = -1;
+          for (int m = 0; m < e->c.n_mods; m++)
+            if (e->c.mod_se[m] < pass_se && (top < 0 || e->c.mod_se[m] > e->c.mod_se[top])) top = m;
+          if (top < 0) break;
+          int se = e->c.mod_se[top];
+          for (int m = 0; m < e->c.n_mods; m++)
+            if (e->c.mod_se[m] == se) { if (seen == se_rank) { chosen = m; break; } seen++; }
+          pass_se = se;
+        }
+        if (chosen >= 0 && len <= e->c.mod_max_length[chosen]) best = chosen;
+      }
+      if (best < 0) continue;
+      int n = number_slots(e, e->c.mod_se[best]);
+      for (int core = 0; core < e->c.num_cores; core++) {
+        int s = first_fit(e, pair, p, core, n);
+        if (s >= 0) { a[0] = p; a[1] = best; a[2] = core; a[3] = s; return; }
+      }
+    }
+  }
+}
+
+void oracle_counters(const oracle_env* e, int64_t* o) {
+  o[0] = e->services_processed; o[1] = e->services_accepted;
+  o[2] = e->ep_processed; o[3] = e->ep_accepted;
+  o[4] = e->br_requested; o[5] = e->br_provisioned;
+  o[6] = e->ep_br_requested; o[7] = e->ep_br_provisioned;
+  o[8] = e->requests_drawn; o[9] = e->heap_len; o[10] = 0; o[11] = e->episodes;
+}
+
+void oracle_state(const oracle_env* e, uint8_t* out) {
+  memcpy(out, e->avail, (size_t)e->c.num_cores * e->c.n_edges * e->c.num_slots);
+}
+
+void oracle_request_now(const oracle_env* e, oracle_request* out) { *out = e->cur; }
+
+/* ---- timed CPU baseline: independent envs spread over host threads ---- */
+typedef struct rollout_job {
+  const oracle_config* cfg;
+  int64_t env0, n_envs;
+  int nsteps, hid;
+  int64_t* counters_out;
+  uint8_t* state_out;
+  int64_t* reward_sum_out;
+  int64_t next; /* shared work counter (atomic) */
+} rollout_job;
+
+static void* rollout_worker(void* arg) {
+  rollout_job* jb = (rollout_job*)arg;
+  const oracle_config* cfg = jb->cfg;
+  size_t cells = (size_t)(cfg->num_cores < 1 ? 1 : cfg->num_cores) * cfg->n_edges * cfg->num_slots;
+  for (;;) {
+    int64_t i = __atomic_fetch_add(&jb->next, 1, __ATOMIC_RELAXED);
+    if (i >= jb->n_envs) break;
+    oracle_env* e = oracle_create(cfg, jb->env0 + i);
+    oracle_reset(e, 1);
+    int32_t a[4], r;
+    uint8_t d;
+    int64_t rs = 0;
+    double obs[1024];
+    for (int t = 0; t < jb->nsteps; t++) {
+      oracle_heuristic(e, jb->hid, a);
+      oracle_step(e, a, &r, &d, cfg->env_kind == 1 ? obs : NULL, NULL);
+      rs += r;
+    }
+    if (jb->counters_out) oracle_counters(e, jb->counters_out + i * 12);
+    if (jb->state_out) oracle_state(e, jb->state_out + (size_t)i * cells);
+    if (jb->reward_sum_out) jb->reward_sum_out[i] = rs;
+    oracle_destroy(e);
+  }
+  return NULL;
+}
+
+int64_t oracle_rollout_many(const oracle_config* cfg, int64_t env0, int64_t n_envs, int nsteps,
+                            int hid, int threads, int64_t* counters_out, uint8_t* state_out,
+                            int64_t* reward_sum_out) {
+  rollout_job jb = {cfg, env0, n_envs, nsteps, hid, counters_out, state_out, reward_sum_out, 0};
+  if (threads < 1) threads = 1;
+  if (threads > 256) threads = 256;
+  pthread_t th[256];
+  for (int t = 1; t < threads; t++) pthread_create(&th[t], NULL, rollout_worker, &jb);
+  rollout_worker(&jb);
+  for (int t = 1; t < threads; t++) pthread_join(th[t], NULL);
+  return n_envs * (int64_t)nsteps;
+}

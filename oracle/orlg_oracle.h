@@ -1,0 +1,96 @@
+/* orlg_oracle.h — CPU restatement of the reference's env stepping path.
+ *
+ * TEST INFRASTRUCTURE.  Only tests/, __graft_entry__.smoke() and bench.py's
+ * cpu_baseline / --impl reference legs may build, load or call this.  The
+ * product (optical_rl_gym_qot_aware_b200/, include/orlg.h) never links it.
+ *
+ * Parity status: PINNED for RMSA-v0 / DeepRMSA-v0 / RMCSA-v0 against golden
+ * traces exported from the unmodified reference run in the build container
+ * (oracle/refharness/gen_golden.py -> tests/golden/ (npz files), checked by
+ * tests/test_oracle_golden.py).  The reference itself holds no golden vectors
+ * (SURVEY.md F13).  GN-model GSNR (examples/calculate_osnr.py) is "parity
+ * unpinned": the reference function is not importable.
+ *
+ * Deliberately literal: one byte per (core, link, slot) like the reference's
+ * numpy int arrays, run-length encoding by scanning, heap as in heapq.  It
+ * shares no code with the CUDA engine.
+ */
+#ifndef ORLG_ORACLE_H
+#define ORLG_ORACLE_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct oracle_request { /* same layout as orlg_request */
+  double arrival;
+  double holding;
+  int32_t bit_rate;
+  int16_t src;
+  int16_t dst;
+} oracle_request;
+
+typedef struct oracle_config {
+  int32_t env_kind; /* 0 RMSA, 1 DeepRMSA, 2 RMCSA */
+  int32_t n_nodes, n_edges, k_paths, max_hops;
+  const int16_t* path_links;
+  const int16_t* path_links_by_id; /* may be NULL */
+  const int32_t* path_hops;
+  const double* path_length;
+  const int32_t* path_se;
+  int32_t n_mods;
+  const int32_t* mod_se;
+  const double* mod_max_length;
+  const double* mod_reach;
+  const double* mod_snr_coeff;
+  int32_t num_slots, num_cores, j, episode_length, allow_rejection, auto_reset;
+  double channel_width, mean_iat, mean_holding;
+  int32_t request_source; /* 0 replay, 1 philox */
+  int32_t n_bit_rates;
+  uint64_t seed;
+  const int32_t* bit_rates;
+  const double* bit_rate_cum;
+  int32_t bit_rate_lo, bit_rate_hi;
+  const double* src_cum;
+  const double* dst_cum;
+} oracle_config;
+
+typedef struct oracle_env oracle_env;
+
+oracle_env* oracle_create(const oracle_config* cfg, int64_t global_env_id);
+void oracle_destroy(oracle_env* e);
+/* per-env contiguous trace; stride in requests between consecutive requests */
+void oracle_set_trace(oracle_env* e, const oracle_request* trace, int64_t n, int64_t stride);
+void oracle_reset(oracle_env* e, int full);
+int oracle_action_dim(const oracle_env* e);
+int oracle_obs_dim(const oracle_env* e);
+/* alloc[4] = accepted, path (| core<<16), initial_slot, n_slots */
+void oracle_step(oracle_env* e, const int32_t* action, int32_t* reward, uint8_t* done,
+                 double* obs, int32_t* alloc);
+void oracle_observation(oracle_env* e, double* obs);
+void oracle_matrix_observation(oracle_env* e, uint8_t* obs);
+void oracle_heuristic(oracle_env* e, int heuristic_id, int32_t* action);
+void oracle_counters(const oracle_env* e, int64_t* out12);
+void oracle_state(const oracle_env* e, uint8_t* out); /* [cores][E][S] */
+void oracle_request_now(const oracle_env* e, oracle_request* out);
+
+/* n_envs independent envs, nsteps of heuristic+step each, on `threads` host
+ * threads; returns total steps.  Used as the timed CPU baseline. */
+int64_t oracle_rollout_many(const oracle_config* cfg, int64_t env0, int64_t n_envs,
+                            int nsteps, int heuristic_id, int threads,
+                            int64_t* counters_out /* [n_envs][12] or NULL */,
+                            uint8_t* state_out /* [n_envs][cores*E*S] or NULL */,
+                            int64_t* reward_sum_out /* [n_envs] or NULL */);
+
+/* deterministic RNG pieces, exposed for tests */
+void oracle_philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                       uint32_t k1, uint32_t out[4]);
+double oracle_dlog(double x);
+void oracle_philox_request(const oracle_config* cfg, int64_t global_env_id, int64_t req_index,
+                           double now, oracle_request* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

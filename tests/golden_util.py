@@ -1,0 +1,42 @@
+"""Helpers shared by the golden-vector tests: load a case and rebuild its EnvSpec."""
+import os
+
+import numpy as np
+
+from optical_rl_gym_qot_aware_b200 import spec as S
+from optical_rl_gym_qot_aware_b200.tables import TopologyTables
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+TOPO_SHORT = {
+    "nsfnet_chen_5-paths_6-modulations.h5": "nsfnet",
+    "us14_3-paths_6-modulations.h5": "us14",
+    "jpn12_5-paths_6-modulations.h5": "jpn12_k5",
+    "jpn12_3-paths_6-modulations.h5": "jpn12_k3",
+    "spn_3-paths_6-modulations.h5": "spn",
+    "germany50_5-paths_6-modulations.h5": "germany50",
+}
+
+CASES = sorted(f[:-4] for f in os.listdir(GOLDEN) if f.endswith(".npz") and not f.startswith("topology_"))
+ENV_NAME = {0: "RMSA-v0", 1: "DeepRMSA-v0", 2: "RMCSA-v0"}
+
+
+def topology(short: str) -> TopologyTables:
+    return TopologyTables.load(os.path.join(GOLDEN, f"topology_{short}.npz"))
+
+
+def load_case(name: str):
+    z = np.load(os.path.join(GOLDEN, name + ".npz"), allow_pickle=False)
+    g = {k: z[k] for k in z.files}
+    kw = {}
+    for k in g["kwargs_keys"]:
+        v = g["kw_" + str(k)]
+        if v.dtype == object or (v.ndim == 0 and str(v) == "None"):
+            kw[str(k)] = None
+        elif v.ndim == 0:
+            kw[str(k)] = v.item()
+        else:
+            kw[str(k)] = v
+    tables = topology(TOPO_SHORT[str(g["topo_file"])])
+    spec = S.make_spec(ENV_NAME[int(g["env_kind"])], tables, request_source=S.SRC_REPLAY, **kw)
+    return g, spec
