@@ -174,6 +174,12 @@ int orlg_step(orlg_engine* e, const int32_t* dev_actions, int32_t* dev_reward,
 int orlg_step_host(orlg_engine* e, const int32_t* host_actions, int32_t* host_reward,
                    uint8_t* host_done, void* host_obs, int32_t* host_alloc, void* stream);
 
+/* Layout of dev_obs for orlg_step / orlg_observation, in elements: feature f of
+ * env i is written at dev_obs[i*env_stride + f*feat_stride].  Default (obs_dim, 1)
+ * = row-major [num_envs][obs_dim]; (1, num_envs) = feature-major, which makes the
+ * kernel's stores coalesced (the Python wrapper exposes it as a transposed view). */
+int orlg_set_obs_layout(orlg_engine* e, int64_t env_stride, int64_t feat_stride);
+
 /* Observation of the pending request without stepping. */
 int orlg_observation(orlg_engine* e, int obs_kind, void* dev_obs, void* stream);
 

@@ -1,0 +1,169 @@
+// engine.cuh — device-side env stepping for RMSA-v0 / DeepRMSA-v0 / RMCSA-v0.
+//
+// Execution model: one thread owns one env for the whole launch (a warp owns 32
+// envs).  A CTA of BD threads owns the tile of BD consecutive envs; the tile's
+// packed occupancy lives in HBM as occ[tile][plane][BD] (plane = (core*E+link)*W
+// + word), i.e. exactly the shared-memory image, so one TMA bulk copy
+// (cp.async.bulk, mbarrier completion) stages it and one bulk copy writes it
+// back.  In shared memory word (plane, tid) sits at plane*BD+tid: lanes hit
+// consecutive banks whatever plane each lane addresses, so the per-env gathers
+// over path links are conflict free.
+//
+// Reference functions restated here (paths under optical_rl_gym/envs/):
+//   is_path_free            rmsa_env.py:721-734, rmcsa_env.py:767-794
+//   get_number_slots        rmsa_env.py:708-719, rmcsa_env.py:753-765
+//   _provision/_release     rmsa_env.py:462-535, rmcsa_env.py:488-558
+//   get_available_blocks    rmsa_env.py:774-804
+//   _next_service           rmsa_env.py:643-695, rmcsa_env.py:690-739
+//   step                    rmsa_env.py:222-341, deeprmsa_env.py:48-58, rmcsa_env.py:209-339
+//   observation             deeprmsa_env.py:60-121
+//   heuristics              rmsa_env.py:854-937, deeprmsa_env.py:135-155, rmcsa_env.py:882-911
+#pragma once
+#include <cstdint>
+
+#include "../../include/orlg.h"
+#include "bitrow.cuh"
+#include "rng.cuh"
+
+namespace orlg {
+
+enum Mode {
+  MODE_STEP = 0,        // actions from a device tensor (gym / VecEnv step)
+  MODE_HEURISTIC = 1,   // only compute the heuristic's action
+  MODE_ROLLOUT = 2,     // nsteps x (heuristic -> step) with state kept on chip
+  MODE_OBS = 3,         // only write the observation
+  MODE_RESET_FULL = 4,  // constructor-time reset
+  MODE_RESET_EPISODE = 5
+};
+
+// internal per-env counters, SoA [CNT_N][NP]
+enum { CNT_PROC = 0, CNT_ACC, CNT_EP_PROC, CNT_EP_ACC, CNT_BR_REQ, CNT_BR_PROV, CNT_EP_BR_REQ,
+       CNT_EP_BR_PROV, CNT_DRAWN, CNT_EPISODES, CNT_FAULT, CNT_N };
+
+struct Params {
+  int kind, num_envs, NP, n_nodes, E, k, S, cores, j, n_mods;
+  int planes, rec_u4, episode_length, allow_rejection, auto_reset, request_source;
+  int n_bit_rates, br_lo, br_hi, heap_cap, heap_stride, action_dim;
+  double cw, mean_iat, mean_holding;
+  unsigned long long seed;
+  long long genv0;
+  const uint4* path_rec;  // [N*N*k][rec_u4]: byte0 hops, 1 se, 2 best modulation, 3.. link index per hop
+  const double* path_length;
+  const int* mod_se;
+  const double* mod_reach;
+  const double* mod_coeff;
+  const int* bit_rates;
+  const double* br_cum;
+  const double* src_cum;
+  const double* dst_cum;
+  uint32_t* occ;
+  double* now;
+  double* holding;
+  uint32_t* meta;  // bit_rate | src << 16 | dst << 24
+  double* next_rel;
+  int* heap_len;
+  ulonglong2* heap;  // [NP][heap_stride] {key bits, payload}
+  long long* counters;
+  const orlg_request* trace;
+  long long trace_len;
+};
+
+struct StepIO {
+  int mode, heuristic, nsteps, obs_kind;
+  const int* actions;
+  int* actions_out;
+  int* reward;
+  unsigned char* done;
+  void* obs;
+  long long obs_es, obs_fs;  // element strides: env, feature
+  int* alloc;
+  long long* reward_sum;
+};
+
+// ---- path records ----------------------------------------------------------
+struct PathRec {
+  unsigned long long q[4];
+  __device__ __forceinline__ int byte_at(int i) const {
+    unsigned long long v = (i < 8) ? q[0] : (i < 16) ? q[1] : (i < 24) ? q[2] : q[3];
+    return (int)((v >> ((i & 7) * 8)) & 0xFFull);
+  }
+  __device__ __forceinline__ int hops() const { return (int)(q[0] & 0xFF); }
+  __device__ __forceinline__ int se() const { return (int)((q[0] >> 8) & 0xFF); }
+  __device__ __forceinline__ int best_mod() const { return (int)((q[0] >> 16) & 0xFF); }
+  __device__ __forceinline__ int link(int h) const { return byte_at(h + 3); }
+};
+
+__device__ __forceinline__ PathRec load_path(const Params& p, int pair, int path) {
+  const uint4* a = p.path_rec + ((size_t)pair * p.k + path) * p.rec_u4;
+  PathRec r;
+  uint4 v = __ldg(a);
+  r.q[0] = ((unsigned long long)v.y << 32) | v.x;
+  r.q[1] = ((unsigned long long)v.w << 32) | v.z;
+  r.q[2] = r.q[3] = 0ull;
+  if (p.rec_u4 > 1) {
+    uint4 u = __ldg(a + 1);
+    r.q[2] = ((unsigned long long)u.y << 32) | u.x;
+    r.q[3] = ((unsigned long long)u.w << 32) | u.z;
+  }
+  return r;
+}
+
+// ---- occupancy tile in shared memory ----------------------------------------
+template <int W, int BD>
+struct Tile {
+  uint32_t* s;  // [planes][BD]
+  int tid, E;
+  __device__ __forceinline__ uint32_t& word(int core, int link, int wi) {
+    return s[(((core * E) + link) * W + wi) * BD + tid];
+  }
+  // AND of the rows of every link of the path (core plane `core`)
+  __device__ __forceinline__ Row<W> path_avail(const PathRec& r, int core) {
+    Row<W> a = row_ones<W>();
+    int h = r.hops();
+    for (int i = 0; i < h; i++) {
+      int l = r.link(i);
+#pragma unroll
+      for (int wi = 0; wi < W; wi++) a.w[wi] &= word(core, l, wi);
+    }
+    return a;
+  }
+  __device__ __forceinline__ void clear_range(const PathRec& r, int core, int start, int n) {
+    int h = r.hops();
+    for (int i = 0; i < h; i++) {
+      int l = r.link(i);
+#pragma unroll
+      for (int wi = 0; wi < W; wi++) {
+        uint32_t m = mask_word(wi, start, start + n);
+        if (m) word(core, l, wi) &= ~m;
+      }
+    }
+  }
+  __device__ __forceinline__ void set_range(const PathRec& r, int core, int start, int n) {
+    int h = r.hops();
+    for (int i = 0; i < h; i++) {
+      int l = r.link(i);
+#pragma unroll
+      for (int wi = 0; wi < W; wi++) {
+        uint32_t m = mask_word(wi, start, start + n);
+        if (m) word(core, l, wi) |= m;
+      }
+    }
+  }
+};
+
+// get_number_slots: ceil(bit_rate / (SE * channel_width)) + 1, f64 like Python
+__device__ __forceinline__ int number_slots(int bit_rate, int se, double cw) {
+  return (int)ceil((double)bit_rate / ((double)se * cw)) + 1;
+}
+
+// first start in [0, S - n) with n free slots (exclusive bound: SURVEY.md F8), -1 if none
+template <int W>
+__device__ __forceinline__ int first_fit(const Row<W>& avail, int n, int S) {
+  if (n >= S) return -1;
+  Row<W> b = window_starts<W>(avail, n);
+#pragma unroll
+  for (int i = 0; i < W; i++) b.w[i] &= mask_word(i, 0, S - n);
+  return lowest_set<W>(b);
+}
+
+}  // namespace orlg

@@ -1,0 +1,439 @@
+// orlg.cu — C-ABI (include/orlg.h) over the sm_100a stepping kernels.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo --fmad=false -shared -Xcompiler -fPIC
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "engine_kernel.cuh"
+
+using namespace orlg;
+
+struct orlg_engine {
+  Params p{};
+  orlg_config cfg{};
+  int W = 0, BD = 0, device = 0;
+  size_t smem_bytes = 0;
+  int obs_kind = 0, obs_dim = 0;
+  std::vector<void*> allocs;
+  size_t hbm_bytes = 0;
+  long long launches = 0;
+  std::string err;
+  // pinned/device staging for orlg_step_host
+  int* d_actions = nullptr;
+  int* d_reward = nullptr;
+  unsigned char* d_done = nullptr;
+  void* d_obs = nullptr;
+  int* d_alloc = nullptr;
+  size_t obs_elem = 0;
+  long long obs_es = 0, obs_fs = 1;  // 0 = row-major default
+};
+
+static thread_local std::string g_create_error;
+
+#define CK(call)                                                                          \
+  do {                                                                                    \
+    cudaError_t _e = (call);                                                              \
+    if (_e != cudaSuccess) {                                                              \
+      e->err = std::string(#call) + ": " + cudaGetErrorString(_e);                        \
+      return ORLG_ECUDA;                                                                  \
+    }                                                                                     \
+  } while (0)
+
+template <typename T>
+static int dev_alloc(orlg_engine* e, T** out, size_t count, bool zero = true) {
+  void* ptr = nullptr;
+  size_t bytes = count * sizeof(T);
+  if (bytes == 0) bytes = 16;
+  if (cudaMalloc(&ptr, bytes) != cudaSuccess) {
+    e->err = "cudaMalloc failed for " + std::to_string(bytes) + " bytes";
+    return ORLG_ENOMEM;
+  }
+  if (zero) cudaMemset(ptr, 0, bytes);
+  e->allocs.push_back(ptr);
+  e->hbm_bytes += bytes;
+  *out = (T*)ptr;
+  return ORLG_OK;
+}
+
+template <typename T>
+static int dev_upload(orlg_engine* e, const T** out, const T* host, size_t count) {
+  T* d = nullptr;
+  int rc = dev_alloc(e, &d, count, false);
+  if (rc) return rc;
+  if (count && cudaMemcpy(d, host, count * sizeof(T), cudaMemcpyHostToDevice) != cudaSuccess) {
+    e->err = "cudaMemcpy H2D failed";
+    return ORLG_ECUDA;
+  }
+  *out = d;
+  return ORLG_OK;
+}
+
+extern "C" int orlg_abi_version(void) { return ORLG_ABI_VERSION; }
+extern "C" const char* orlg_build_info(void) {
+  return "orlg sm_100a engine: TMA-staged tiles, thread-per-env, W in {2,4,10}, BD in {32,64,128}";
+}
+extern "C" const char* orlg_last_error(const orlg_engine* e) {
+  return e ? e->err.c_str() : g_create_error.c_str();
+}
+
+template <int W, int BD>
+static cudaError_t launch_t(orlg_engine* e, const StepIO& io, cudaStream_t st) {
+  static size_t configured[64] = {};  // largest dynamic smem opted into, per device
+  if (e->smem_bytes > 48 * 1024 && configured[e->device & 63] < e->smem_bytes) {
+    cudaError_t rc = cudaFuncSetAttribute(env_kernel<W, BD>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)e->smem_bytes);
+    if (rc != cudaSuccess) return rc;
+    configured[e->device & 63] = e->smem_bytes;
+  }
+  env_kernel<W, BD><<<e->p.NP / BD, BD, e->smem_bytes, st>>>(e->p, io);
+  return cudaGetLastError();
+}
+
+template <int W>
+static cudaError_t launch_w(orlg_engine* e, const StepIO& io, cudaStream_t st) {
+  switch (e->BD) {
+    case 32: return launch_t<W, 32>(e, io, st);
+    case 64: return launch_t<W, 64>(e, io, st);
+    default: return launch_t<W, 128>(e, io, st);
+  }
+}
+
+static int launch(orlg_engine* e, const StepIO& io, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t rc;
+  switch (e->W) {
+    case 2: rc = launch_w<2>(e, io, st); break;
+    case 4: rc = launch_w<4>(e, io, st); break;
+    default: rc = launch_w<10>(e, io, st); break;
+  }
+  if (rc != cudaSuccess) {
+    e->err = std::string("kernel launch: ") + cudaGetErrorString(rc);
+    return ORLG_ECUDA;
+  }
+  e->launches++;
+  return ORLG_OK;
+}
+
+static int fail_create(orlg_engine* e, int code, const std::string& msg) {
+  g_create_error = msg;
+  if (e) {
+    for (void* a : e->allocs) cudaFree(a);
+    delete e;
+  }
+  return code;
+}
+
+extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
+  if (!c || !out) return fail_create(nullptr, ORLG_EINVAL, "null argument");
+  *out = nullptr;
+  if (c->abi_version != ORLG_ABI_VERSION) return fail_create(nullptr, ORLG_EINVAL, "abi_version mismatch");
+  if (c->env_kind < ORLG_ENV_RMSA || c->env_kind > ORLG_ENV_RMCSA)
+    return fail_create(nullptr, ORLG_EINVAL, "env_kind not supported by this build");
+  if (c->num_envs < 1 || c->n_nodes < 2 || c->n_nodes > 255 || c->n_edges < 1 || c->n_edges > 255 ||
+      c->k_paths < 1 || c->k_paths > 15 || c->max_hops < 1 || c->max_hops > 29 || c->num_slots < 2 ||
+      c->num_slots > 320 || c->episode_length < 1)
+    return fail_create(nullptr, ORLG_EINVAL, "config out of range (nodes/edges<=255, k<=15, hops<=29, slots<=320)");
+  if (!c->path_links || !c->path_hops || !c->path_se || !c->path_length)
+    return fail_create(nullptr, ORLG_EINVAL, "missing topology tables");
+  if (!(c->mean_iat > 0) || !(c->mean_holding > 0) || !(c->channel_width > 0))
+    return fail_create(nullptr, ORLG_EINVAL, "mean_iat, mean_holding, channel_width must be > 0");
+  const int cores = c->env_kind == ORLG_ENV_RMCSA ? c->num_cores : 1;
+  if (cores < 1 || cores > 32) return fail_create(nullptr, ORLG_EINVAL, "num_cores out of range");
+  if (c->env_kind == ORLG_ENV_RMCSA && (!c->mod_reach || !c->mod_snr_coeff || !c->mod_se || c->n_mods < 1))
+    return fail_create(nullptr, ORLG_EINVAL, "RMCSA needs modulation tables");
+  if (c->request_source == ORLG_SRC_PHILOX &&
+      (!c->src_cum || !c->dst_cum || (c->n_bit_rates > 0 && (!c->bit_rates || !c->bit_rate_cum))))
+    return fail_create(nullptr, ORLG_EINVAL, "philox source needs src_cum/dst_cum/bit-rate tables");
+  const size_t npairs = (size_t)c->n_nodes * c->n_nodes, npaths = npairs * c->k_paths;
+  if (c->path_links_by_id &&
+      memcmp(c->path_links_by_id, c->path_links, npaths * c->max_hops * sizeof(int16_t)) != 0)
+    return fail_create(nullptr, ORLG_EINVAL, "edge 'id' != 'index' (SURVEY F9) is not supported");
+
+  if (cudaSetDevice(c->device) != cudaSuccess) return fail_create(nullptr, ORLG_ECUDA, "cudaSetDevice failed");
+  orlg_engine* e = new orlg_engine();
+  e->cfg = *c;
+  e->device = c->device;
+  Params& p = e->p;
+  e->W = c->num_slots <= 64 ? 2 : c->num_slots <= 128 ? 4 : 10;
+  p.kind = c->env_kind;
+  p.num_envs = c->num_envs;
+  p.n_nodes = c->n_nodes;
+  p.E = c->n_edges;
+  p.k = c->k_paths;
+  p.S = c->num_slots;
+  p.cores = cores;
+  p.j = c->env_kind == ORLG_ENV_DEEPRMSA ? (c->j < 1 ? 1 : c->j) : 1;
+  p.n_mods = c->n_mods;
+  p.planes = cores * p.E * e->W;
+  p.episode_length = c->episode_length;
+  p.allow_rejection = c->allow_rejection;
+  p.auto_reset = c->auto_reset;
+  p.request_source = c->request_source;
+  p.n_bit_rates = c->n_bit_rates;
+  p.br_lo = c->bit_rate_lo;
+  p.br_hi = c->bit_rate_hi;
+  p.action_dim = c->env_kind == ORLG_ENV_RMSA ? 2 : c->env_kind == ORLG_ENV_DEEPRMSA ? 1 : 4;
+  p.cw = c->channel_width;
+  p.mean_iat = c->mean_iat;
+  p.mean_holding = c->mean_holding;
+  p.seed = c->seed;
+  p.genv0 = c->global_env_offset;
+
+  // tile geometry: as many envs per CTA as keep >= 3 CTAs resident per SM
+  const size_t bytes_per_env = (size_t)p.planes * 4;
+  int bd = 128;
+  while (bd > 32 && bytes_per_env * bd > 72 * 1024) bd >>= 1;
+  if (const char* s = getenv("ORLG_BD")) {
+    int v = atoi(s);
+    if (v == 32 || v == 64 || v == 128) bd = v;
+  }
+  if (bytes_per_env * bd > 220 * 1024)
+    return fail_create(e, ORLG_EINVAL, "occupancy of one tile exceeds shared memory (cores*edges*slots too large)");
+  e->BD = bd;
+  e->smem_bytes = bytes_per_env * bd;
+  p.NP = (c->num_envs + bd - 1) / bd * bd;
+
+  // path records
+  p.rec_u4 = c->max_hops <= 13 ? 1 : 2;
+  std::vector<unsigned char> rec(npaths * 16 * p.rec_u4, 0);
+  int max_se = 1;
+  for (size_t i = 0; i < npaths; i++) {
+    unsigned char* r = rec.data() + i * 16 * p.rec_u4;
+    int h = c->path_hops[i];
+    if (h < 0 || h > c->max_hops) return fail_create(e, ORLG_EINVAL, "path_hops out of range");
+    r[0] = (unsigned char)h;
+    r[1] = (unsigned char)c->path_se[i];
+    r[2] = 255;
+    if (h > 0 && c->path_se[i] < 1) return fail_create(e, ORLG_EINVAL, "path_se must be >= 1");
+    if (h > 0 && c->path_se[i] > max_se) max_se = c->path_se[i];
+    if (c->n_mods > 0 && c->mod_se && c->mod_max_length && h > 0) {
+      // get_best_modulation_format utils.py:105-117: highest SE first (stable), first that reaches
+      int best = -1;
+      std::vector<int> order(c->n_mods);
+      for (int m = 0; m < c->n_mods; m++) order[m] = m;
+      for (int a = 1; a < c->n_mods; a++)  // stable insertion sort by SE descending
+        for (int b = a; b > 0 && c->mod_se[order[b]] > c->mod_se[order[b - 1]]; b--) std::swap(order[b], order[b - 1]);
+      for (int m = 0; m < c->n_mods && best < 0; m++)
+        if (c->path_length[i] <= c->mod_max_length[order[m]]) best = order[m];
+      if (best >= 0) r[2] = (unsigned char)best;
+    }
+    for (int k = 0; k < h; k++) {
+      int l = c->path_links[i * c->max_hops + k];
+      if (l < 0 || l >= c->n_edges) return fail_create(e, ORLG_EINVAL, "path_links out of range");
+      r[3 + k] = (unsigned char)l;
+    }
+  }
+  if (c->mod_se)
+    for (int m = 0; m < c->n_mods; m++) max_se = c->mod_se[m] > max_se ? c->mod_se[m] : max_se;
+
+  // release-queue capacity: every live service holds >= min_slots slots on >= 1 link
+  int min_br = c->bit_rate_lo;
+  if (c->n_bit_rates > 0 && c->bit_rates) {
+    min_br = c->bit_rates[0];
+    for (int i = 1; i < c->n_bit_rates; i++) min_br = c->bit_rates[i] < min_br ? c->bit_rates[i] : min_br;
+  }
+  if (c->request_source == ORLG_SRC_REPLAY || min_br < 1) min_br = 1;
+  int min_slots = (int)std::ceil((double)min_br / ((double)max_se * c->channel_width)) + 1;
+  long long bound = (long long)cores * p.E * (p.S / min_slots);
+  p.heap_cap = c->heap_capacity > 0 ? c->heap_capacity : (int)(bound < 16 ? 16 : bound);
+  p.heap_stride = (p.heap_cap + HEAP_PAD + 3) & ~3;
+
+  int rc = 0;
+  const uint4* drec = nullptr;
+  if ((rc = dev_upload(e, &drec, (const uint4*)rec.data(), npaths * p.rec_u4))) return fail_create(e, rc, e->err);
+  p.path_rec = drec;
+  if ((rc = dev_upload(e, &p.path_length, c->path_length, npaths))) return fail_create(e, rc, e->err);
+  if (c->mod_se && (rc = dev_upload(e, &p.mod_se, c->mod_se, c->n_mods))) return fail_create(e, rc, e->err);
+  if (c->mod_reach && (rc = dev_upload(e, &p.mod_reach, c->mod_reach, c->n_mods))) return fail_create(e, rc, e->err);
+  if (c->mod_snr_coeff && (rc = dev_upload(e, &p.mod_coeff, c->mod_snr_coeff, c->n_mods))) return fail_create(e, rc, e->err);
+  if (c->bit_rates && c->n_bit_rates > 0) {
+    if ((rc = dev_upload(e, &p.bit_rates, c->bit_rates, c->n_bit_rates))) return fail_create(e, rc, e->err);
+    if ((rc = dev_upload(e, &p.br_cum, c->bit_rate_cum, c->n_bit_rates))) return fail_create(e, rc, e->err);
+  }
+  if (c->src_cum && (rc = dev_upload(e, &p.src_cum, c->src_cum, c->n_nodes))) return fail_create(e, rc, e->err);
+  if (c->dst_cum && (rc = dev_upload(e, &p.dst_cum, c->dst_cum, npairs))) return fail_create(e, rc, e->err);
+
+  const size_t NP = p.NP;
+  if ((rc = dev_alloc(e, &p.occ, (size_t)p.planes * NP)) || (rc = dev_alloc(e, &p.now, NP)) ||
+      (rc = dev_alloc(e, &p.holding, NP)) || (rc = dev_alloc(e, &p.meta, NP)) ||
+      (rc = dev_alloc(e, &p.next_rel, NP)) || (rc = dev_alloc(e, &p.heap_len, NP)) ||
+      (rc = dev_alloc(e, &p.heap, NP * p.heap_stride, false)) ||
+      (rc = dev_alloc(e, &p.counters, (size_t)CNT_N * NP)))
+    return fail_create(e, rc, e->err);
+
+  e->obs_kind = c->obs_kind;
+  if (c->obs_kind == ORLG_OBS_F64 || c->obs_kind == ORLG_OBS_F32) {
+    e->obs_dim = 1 + 2 * p.n_nodes + (2 * p.j + 3) * p.k;
+    e->obs_elem = c->obs_kind == ORLG_OBS_F64 ? 8 : 4;
+  } else if (c->obs_kind == ORLG_OBS_MATRIX_U8) {
+    e->obs_dim = 2 * p.n_nodes + cores * p.E * p.S;
+    e->obs_elem = 1;
+  }
+  *out = e;
+  return ORLG_OK;
+}
+
+extern "C" int orlg_destroy(orlg_engine* e) {
+  if (!e) return ORLG_EINVAL;
+  cudaSetDevice(e->device);
+  for (void* a : e->allocs) cudaFree(a);
+  delete e;
+  return ORLG_OK;
+}
+
+extern "C" int orlg_action_dim(const orlg_engine* e) { return e ? e->p.action_dim : ORLG_EINVAL; }
+extern "C" int orlg_obs_dim(const orlg_engine* e) { return e ? e->obs_dim : ORLG_EINVAL; }
+extern "C" int64_t orlg_state_words(const orlg_engine* e) { return e ? e->p.planes : ORLG_EINVAL; }
+extern "C" int64_t orlg_hbm_bytes(const orlg_engine* e) { return e ? (int64_t)e->hbm_bytes : ORLG_EINVAL; }
+extern "C" int64_t orlg_launch_count(const orlg_engine* e) { return e ? e->launches : ORLG_EINVAL; }
+
+extern "C" int orlg_set_obs_layout(orlg_engine* e, int64_t env_stride, int64_t feat_stride) {
+  if (!e || env_stride < 1 || feat_stride < 1) return ORLG_EINVAL;
+  e->obs_es = env_stride;
+  e->obs_fs = feat_stride;
+  return ORLG_OK;
+}
+
+extern "C" int orlg_load_trace(orlg_engine* e, const orlg_request* dev_trace, int64_t n) {
+  if (!e || !dev_trace || n < 1) return ORLG_EINVAL;
+  e->p.trace = dev_trace;
+  e->p.trace_len = n;
+  return ORLG_OK;
+}
+
+static int check_source(orlg_engine* e) {
+  if (e->p.request_source == ORLG_SRC_REPLAY && !e->p.trace) {
+    e->err = "replay source without a trace (call orlg_load_trace)";
+    return ORLG_ESTATE;
+  }
+  return ORLG_OK;
+}
+
+static StepIO make_io(orlg_engine* e, int mode) {
+  StepIO io{};
+  io.mode = mode;
+  io.obs_kind = e->obs_kind;
+  io.obs_es = e->obs_es ? e->obs_es : e->obs_dim;
+  io.obs_fs = e->obs_es ? e->obs_fs : 1;
+  io.nsteps = 1;
+  return io;
+}
+
+extern "C" int orlg_reset(orlg_engine* e, int full, void* stream) {
+  if (!e) return ORLG_EINVAL;
+  if (int rc = check_source(e)) return rc;
+  cudaSetDevice(e->device);
+  StepIO io = make_io(e, full ? MODE_RESET_FULL : MODE_RESET_EPISODE);
+  io.obs = nullptr;
+  return launch(e, io, stream);
+}
+
+extern "C" int orlg_step(orlg_engine* e, const int32_t* dev_actions, int32_t* dev_reward, uint8_t* dev_done,
+                         void* dev_obs, int32_t* dev_alloc, void* stream) {
+  if (!e || !dev_actions) return ORLG_EINVAL;
+  if (int rc = check_source(e)) return rc;
+  cudaSetDevice(e->device);
+  StepIO io = make_io(e, MODE_STEP);
+  io.actions = dev_actions;
+  io.reward = dev_reward;
+  io.done = dev_done;
+  io.obs = e->obs_kind ? dev_obs : nullptr;
+  io.alloc = dev_alloc;
+  return launch(e, io, stream);
+}
+
+extern "C" int orlg_observation(orlg_engine* e, int obs_kind, void* dev_obs, void* stream) {
+  if (!e || !dev_obs || obs_kind < ORLG_OBS_F64 || obs_kind > ORLG_OBS_MATRIX_U8) return ORLG_EINVAL;
+  if ((obs_kind == ORLG_OBS_F64 || obs_kind == ORLG_OBS_F32) && e->p.kind == ORLG_ENV_RMCSA) return ORLG_EINVAL;
+  cudaSetDevice(e->device);
+  StepIO io = make_io(e, MODE_OBS);
+  io.obs_kind = obs_kind;
+  io.obs = dev_obs;
+  if (!e->obs_es)
+    io.obs_es = obs_kind == ORLG_OBS_MATRIX_U8 ? 2 * e->p.n_nodes + e->p.cores * e->p.E * e->p.S
+                                               : 1 + 2 * e->p.n_nodes + (2 * e->p.j + 3) * e->p.k;
+  return launch(e, io, stream);
+}
+
+extern "C" int orlg_heuristic(orlg_engine* e, int hid, int32_t* dev_actions, void* stream) {
+  if (!e || !dev_actions || hid < ORLG_H_SP_FF || hid > ORLG_H_SAP_BM_FC_FF) return ORLG_EINVAL;
+  cudaSetDevice(e->device);
+  StepIO io = make_io(e, MODE_HEURISTIC);
+  io.heuristic = hid;
+  io.actions_out = dev_actions;
+  io.obs = nullptr;
+  return launch(e, io, stream);
+}
+
+extern "C" int orlg_rollout(orlg_engine* e, int hid, int nsteps, int64_t* dev_reward_sum, void* stream) {
+  if (!e || nsteps < 1 || hid < ORLG_H_SP_FF || hid > ORLG_H_SAP_BM_FC_FF) return ORLG_EINVAL;
+  if (int rc = check_source(e)) return rc;
+  cudaSetDevice(e->device);
+  StepIO io = make_io(e, MODE_ROLLOUT);
+  io.heuristic = hid;
+  io.nsteps = nsteps;
+  io.reward_sum = (long long*)dev_reward_sum;
+  io.obs = nullptr;
+  return launch(e, io, stream);
+}
+
+extern "C" int orlg_get_counters(orlg_engine* e, int64_t* dev_out, void* stream) {
+  if (!e || !dev_out) return ORLG_EINVAL;
+  cudaSetDevice(e->device);
+  counters_kernel<<<(e->p.num_envs + 255) / 256, 256, 0, (cudaStream_t)stream>>>(e->p, (long long*)dev_out);
+  CK(cudaGetLastError());
+  e->launches++;
+  return ORLG_OK;
+}
+
+extern "C" int orlg_export_state(orlg_engine* e, uint8_t* dev_out, void* stream) {
+  if (!e || !dev_out) return ORLG_EINVAL;
+  cudaSetDevice(e->device);
+  export_state_kernel<<<148 * 8, 256, 0, (cudaStream_t)stream>>>(e->p, e->W, e->BD, dev_out);
+  CK(cudaGetLastError());
+  e->launches++;
+  return ORLG_OK;
+}
+
+extern "C" int orlg_get_requests(orlg_engine* e, orlg_request* dev_out, void* stream) {
+  if (!e || !dev_out) return ORLG_EINVAL;
+  cudaSetDevice(e->device);
+  requests_kernel<<<(e->p.num_envs + 255) / 256, 256, 0, (cudaStream_t)stream>>>(e->p, dev_out);
+  CK(cudaGetLastError());
+  e->launches++;
+  return ORLG_OK;
+}
+
+// Host-buffer step: H2D actions, step, D2H outputs, stream sync (bench.py "e2e").
+extern "C" int orlg_step_host(orlg_engine* e, const int32_t* h_actions, int32_t* h_reward, uint8_t* h_done,
+                              void* h_obs, int32_t* h_alloc, void* stream) {
+  if (!e || !h_actions) return ORLG_EINVAL;
+  cudaSetDevice(e->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t n = e->p.num_envs;
+  int rc = 0;
+  if (!e->d_actions) {
+    if ((rc = dev_alloc(e, &e->d_actions, n * e->p.action_dim)) || (rc = dev_alloc(e, &e->d_reward, n)) ||
+        (rc = dev_alloc(e, &e->d_done, n)) || (rc = dev_alloc(e, &e->d_alloc, n * 4)))
+      return rc;
+    if (e->obs_dim) {
+      unsigned char* o = nullptr;
+      if ((rc = dev_alloc(e, &o, n * e->obs_dim * e->obs_elem))) return rc;
+      e->d_obs = o;
+    }
+  }
+  CK(cudaMemcpyAsync(e->d_actions, h_actions, n * e->p.action_dim * sizeof(int), cudaMemcpyHostToDevice, st));
+  if ((rc = orlg_step(e, e->d_actions, e->d_reward, e->d_done, e->d_obs, e->d_alloc, stream))) return rc;
+  if (h_reward) CK(cudaMemcpyAsync(h_reward, e->d_reward, n * sizeof(int), cudaMemcpyDeviceToHost, st));
+  if (h_done) CK(cudaMemcpyAsync(h_done, e->d_done, n, cudaMemcpyDeviceToHost, st));
+  if (h_alloc) CK(cudaMemcpyAsync(h_alloc, e->d_alloc, n * 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
+  if (h_obs && e->d_obs)
+    CK(cudaMemcpyAsync(h_obs, e->d_obs, n * e->obs_dim * e->obs_elem, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return ORLG_OK;
+}
