@@ -1,0 +1,422 @@
+#!/usr/bin/env python
+"""bench.py — env-steps/sec of the batched stepping engine on B200 (driver contract).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA engine
+    python bench.py --impl reference --gpus N --steps K ...   # CPU arm (oracle port)
+
+One "step" = one pass of the hot path over one batch of envs: the device
+heuristic picks an action for every env (orlg_heuristic), then every env takes
+one gym step (orlg_step: validate -> provision -> release queue -> next request
+-> reward/done -> DeepRMSA observation).  The default workload is
+BASELINE.json configs[1]: DeepRMSA-v0 on NSFNET, k=5, 100 slots, 65536 envs per
+GPU (weak scaling: env count per GPU is fixed, envs are sharded with no
+data-path collective; NCCL only all-reduces the episode statistics at the end).
+
+`value`   device-resident throughput (actions, state and outputs stay in HBM).
+`e2e`     the same metric through the host-buffer C-ABI call (orlg_step_host):
+          a numpy policy on the host picks actions from the previous host
+          observation, actions go H2D from pinned memory, obs/reward/done come
+          back D2H every step; copies and host policy are inside the timed region.
+`roofline` the step kernel: algorithmic bytes per env-step x envs /
+          its CUDA-event duration, against MEASURED_PEAKS.json hbm_gbs.
+`cpu_baseline` the C oracle port (oracle/, test infrastructure) stepping a
+          bounded sample of the same workload on all host threads.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+for _p in (REPO, os.path.join(REPO, "oracle"), os.path.join(REPO, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+from optical_rl_gym_qot_aware_b200 import spec as S  # noqa: E402
+from optical_rl_gym_qot_aware_b200.tables import TopologyTables  # noqa: E402
+
+GOLDEN = os.path.join(REPO, "tests", "golden")
+METRIC = "env-steps/sec"
+
+# node probabilities of the reference's DeepRMSA driver (tests/test_deeprmsa.py:30-47)
+DEEPRMSA_NODE_PROBS = [0.01801802, 0.04004004, 0.05305305, 0.01901902, 0.04504505, 0.02402402, 0.06706707,
+                       0.08908909, 0.13813814, 0.12212212, 0.07607608, 0.12012012, 0.01901902, 0.16916917]
+
+# name -> (env id, topology fixture, kwargs, heuristic, obs kind, algorithmic bytes per env-step)
+# bytes/env-step are SURVEY.md section 8(d) / DESIGN.md "Algorithmic bytes".
+WORKLOADS = {
+    "c1_rmsa_nsfnet_100": ("RMSA-v0", "nsfnet", dict(load=50, num_spectrum_resources=100, episode_length=1000),
+                           S.H_SAP_FF, S.OBS_NONE, 609),
+    "c2_deeprmsa_nsfnet_100": ("DeepRMSA-v0", "nsfnet",
+                               dict(j=1, mean_service_holding_time=7.5, mean_service_inter_arrival_time=1 / 12.0,
+                                    num_spectrum_resources=100, episode_length=50,
+                                    node_request_probabilities=DEEPRMSA_NODE_PROBS),
+                               S.H_SAP_FF, S.OBS_F32, 825),
+    "c3_rmcsa_jpn12_320": ("RMCSA-v0", "jpn12_k5",
+                           dict(load=250, mean_service_holding_time=25, num_spectrum_resources=320,
+                                num_spatial_resources=7, worst_xt=-84.7, episode_length=1000),
+                           S.H_SAP_BM_FC_FF, S.OBS_NONE, 6454),
+    "c5_rmsa_spn_100": ("RMSA-v0", "spn", dict(load=100, mean_service_holding_time=25,
+                                               num_spectrum_resources=100, episode_length=1000),
+                        S.H_SAP_FF, S.OBS_NONE, 517),
+    "c5_rmsa_spn_320": ("RMSA-v0", "spn", dict(load=400, mean_service_holding_time=25,
+                                               num_spectrum_resources=320, episode_length=1000),
+                        S.H_SAP_FF, S.OBS_NONE, 1039),
+}
+DEFAULT_WORKLOAD = "c2_deeprmsa_nsfnet_100"
+PREROLL = 600  # steps run before any timing so that the networks are in steady state
+
+
+def make_workload(name, seed=0x5EED):
+    env_id, topo, kw, hid, obs_kind, bytes_per_step = WORKLOADS[name]
+    tables = TopologyTables.load(os.path.join(GOLDEN, f"topology_{topo}.npz"))
+    spec = S.make_spec(env_id, tables, seed=seed, request_source=S.SRC_PHILOX, auto_reset=True,
+                       obs_kind=obs_kind, **kw)
+    return spec, hid, bytes_per_step, env_id
+
+
+def measured_peaks():
+    p = os.path.join(REPO, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.lines = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def host_policy_kspff(obs_fm, n_nodes, k, j):
+    """K-SP-FF (deeprmsa_env.py:146-155) evaluated on the host from the observation:
+    path p has a fitting block iff its first block-length feature is not -1.
+    obs_fm: [obs_dim, n_env] (feature-major host buffer).  Returns int32 [n_env, 1]."""
+    rowlen = 2 * j + 3
+    base = 1 + 2 * n_nodes
+    has = np.stack([obs_fm[base + p * rowlen + 1] != -1.0 for p in range(k)], axis=0)  # [k, n_env]
+    first = np.argmax(has, axis=0)
+    act = np.where(has.any(axis=0), first * j, k * j).astype(np.int32)
+    return act.reshape(-1, 1)
+
+
+def cpu_arm(spec, hid, n_sample, min_seconds, threads, steps=None, warmup=0):
+    """Times the oracle port on host threads.  Returns (steps/s, ms per pass, passes)."""
+    import oracle_binding as OB
+
+    pool = OB.OraclePool(spec, 0, n_sample)
+    pool.rollout(PREROLL, hid, threads)
+    for _ in range(warmup):
+        pool.rollout(1, hid, threads)
+    done_steps, passes = 0, 0
+    t0 = time.perf_counter()
+    if steps is not None:
+        for _ in range(steps):
+            done_steps += pool.rollout(1, hid, threads)
+            passes += 1
+    else:
+        while time.perf_counter() - t0 < min_seconds:
+            done_steps += pool.rollout(50, hid, threads)
+            passes += 50
+    dt = time.perf_counter() - t0
+    cnt = pool.counters()
+    blocking = 1.0 - cnt[:, 1].sum() / max(1, cnt[:, 0].sum())
+    pool.close()
+    return done_steps / dt, dt * 1e3 / max(1, passes), passes, float(blocking)
+
+
+def run_reference(args, spec, hid, env_id, wl):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    n_sample = args.ref_envs
+    v, ms, passes, blocking = cpu_arm(spec, hid, n_sample, 0, threads, steps=args.steps, warmup=args.warmup)
+    sample = (f"{n_sample} envs of the {args.envs}-env batch per pass, oracle C port (oracle/orlg_oracle.c) "
+              f"with its own heuristic, {threads} pthreads, {PREROLL} pre-roll steps")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "env-steps/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u32 bitmask + f64 clock (oracle: u8 cells + f64)",
+        "data": "synthetic (Philox request streams, seed 0x5eed, keyed by global env id)",
+        "config": {"workload": wl, "env": env_id, "envs_per_pass": n_sample, "heuristic": int(hid),
+                   "blocking": blocking},
+        "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
+    import torch
+
+    from optical_rl_gym_qot_aware_b200.engine import Engine
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: the engine has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=dev)
+    n_env = args.envs
+    eng = Engine(spec, n_env, device=local, global_env_offset=rank * n_env)
+    eng.reset(True)
+    eng.rollout(hid, PREROLL)
+    act = torch.zeros((n_env, eng.action_dim), dtype=torch.int32, device=dev)
+    rew = torch.zeros(n_env, dtype=torch.int32, device=dev)
+    done = torch.zeros(n_env, dtype=torch.uint8, device=dev)
+    obs = eng.new_obs() if eng.obs_dim else None
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev) if not args.no_flush else None
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def one_step(evs=None):
+        if flush is not None:
+            flush.fill_(1)  # evict the 126 MB L2 (untimed: outside the event pairs)
+        if evs is not None:
+            evs[0].record()
+        eng.heuristic(hid, act)
+        if evs is not None:
+            evs[1].record()
+        eng.step(act, rew, done, obs, None)
+        if evs is not None:
+            evs[2].record()
+
+    for _ in range(args.warmup):
+        one_step()
+    K = args.steps
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K)]
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    launches0 = eng.launch_count
+    barrier()
+    for t in range(K):
+        one_step(evs[t])
+    barrier()
+    launches = eng.launch_count - launches0
+    step_ms = sum(e[0].elapsed_time(e[2]) for e in evs)
+    kern_ms = sum(e[1].elapsed_time(e[2]) for e in evs)
+
+    # warm-L2 variant (what a training loop sees when the state fits L2): one event pair around K steps
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    saved, flush = flush, None
+    barrier()
+    e0.record()
+    for t in range(K):
+        one_step()
+    e1.record()
+    barrier()
+    warm_ms = e0.elapsed_time(e1)
+    flush = saved
+
+    # fused rollout (heuristic + step in one launch, state on chip between steps), informational
+    e0.record()
+    eng.rollout(hid, K)
+    e1.record()
+    torch.cuda.synchronize()
+    roll_ms = e0.elapsed_time(e1)
+
+    # ---- e2e: host buffers through orlg_step_host, host policy, copies inside the timed region ----
+    t_nodes, t_k = spec.tables.n_nodes, spec.tables.k_paths
+    h_act = torch.zeros((n_env, eng.action_dim), dtype=torch.int32).pin_memory()
+    h_rew = torch.zeros(n_env, dtype=torch.int32).pin_memory()
+    h_done = torch.zeros(n_env, dtype=torch.uint8).pin_memory()
+    use_obs_policy = env_id == "DeepRMSA-v0" and eng.obs_dim > 0
+    h_obs = None
+    if eng.obs_dim:
+        odt = {S.OBS_F64: torch.float64, S.OBS_F32: torch.float32, S.OBS_MATRIX_U8: torch.uint8}[spec.obs_kind]
+        h_obs = torch.zeros((eng.obs_dim, n_env), dtype=odt).pin_memory()  # feature-major, as the device buffer
+        eng.observation(obs)
+        h_obs.copy_(obs.t())
+    torch.cuda.synchronize()
+
+    def e2e_step():
+        if use_obs_policy:
+            h_act.numpy()[:] = host_policy_kspff(h_obs.numpy(), t_nodes, t_k, spec.j)
+        else:  # no observation to decide from: device heuristic, actions round-trip through the host
+            eng.heuristic(hid, act)
+            h_act.copy_(act)
+        eng.step_host(h_act, h_rew, h_done, h_obs, None)
+        return int(h_rew.numpy()[0])
+
+    Ke = max(1, min(K, args.e2e_steps))
+    for _ in range(min(args.warmup, 5)):
+        e2e_step()
+    barrier()
+    e0.record()
+    w0 = time.perf_counter()
+    for t in range(Ke):
+        e2e_step()
+    e1.record()
+    barrier()
+    e2e_wall_ms = (time.perf_counter() - w0) * 1e3
+    e2e_ms = max(e0.elapsed_time(e1), e2e_wall_ms)
+    clocks = sampler.stop() if rank == 0 else None
+    h2d = h_act.numel() * 4
+    d2h = h_rew.numel() * 4 + h_done.numel() + (h_obs.numel() * h_obs.element_size() if h_obs is not None else 0)
+
+    # ---- episode statistics: the only collective on this path (NCCL all-reduce, off the step path) ----
+    cnt = eng.counters()
+    stats = torch.stack([cnt[:, 0].sum(), cnt[:, 1].sum(), cnt[:, 4].sum(), cnt[:, 5].sum(), cnt[:, 11].sum(),
+                         cnt[:, 10].max()]).to(torch.int64)
+    times = torch.tensor([step_ms, kern_ms, warm_ms, roll_ms, e2e_ms], dtype=torch.float64, device=dev)
+    if dist is not None:
+        fault = stats[5:6].clone()
+        dist.all_reduce(stats, op=dist.ReduceOp.SUM)
+        dist.all_reduce(fault, op=dist.ReduceOp.MAX)
+        stats[5] = fault[0]
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    step_ms, kern_ms, warm_ms, roll_ms, e2e_ms = [float(x) for x in times.cpu()]
+    stats = [int(x) for x in stats.cpu()]
+    if stats[5] != 0:
+        raise RuntimeError(f"device fault bits set: {stats[5]}")
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    total_envs = n_env * world
+    value = total_envs * K / (step_ms * 1e-3)
+    peak, peak_src = measured_peaks()
+    kern_avg_s = kern_ms * 1e-3 / K
+    achieved = bytes_per_step * n_env / kern_avg_s / 1e9
+    traffic = None
+    tp = os.path.join(REPO, "profiles", "traffic.json")
+    if os.path.exists(tp):
+        try:
+            traffic = json.load(open(tp)).get(wl, {}).get("dram_bytes_per_launch")
+        except Exception:
+            traffic = None
+    line = {
+        "metric": METRIC, "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": K,
+        "warmup": args.warmup, "ms_per_step": step_ms / K, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u32 bitmask + f64 clock",
+        "data": "synthetic (Philox request streams, seed 0x5eed, keyed by global env id)",
+        "config": {
+            "workload": wl, "env": env_id, "envs_per_gpu": n_env, "heuristic": int(hid),
+            "obs": {0: "none", 1: "f64", 2: "f32", 3: "matrix_u8"}[spec.obs_kind],
+            "step": "orlg_heuristic + orlg_step (2 launches), actions/obs/reward/done resident in HBM",
+            "l2": ("flushed before every step by a 256 MiB fill outside the per-step event pairs"
+                   if not args.no_flush else "not flushed (state may be L2 resident)"),
+            "preroll_steps": PREROLL, "parallelism": f"envs sharded x{world}, no data-path collective",
+            "blocking": 1.0 - stats[1] / max(1, stats[0]), "episodes": stats[4],
+        },
+        "e2e": {"value": total_envs * Ke / (e2e_ms * 1e-3), "unit": "env-steps/s", "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "steps": Ke,
+                "policy": "numpy K-SP-FF from the host observation" if use_obs_policy
+                else "device heuristic, actions D2H then H2D"},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": traffic, "kernel": "env_kernel (MODE_STEP)", "peak_source": peak_src,
+                     "bytes_per_env_step": bytes_per_step, "kernel_ms": kern_avg_s * 1e3},
+        "extra": {"warm_l2_env_steps_per_s": total_envs * K / (warm_ms * 1e-3),
+                  "fused_rollout_env_steps_per_s": total_envs * K / (roll_ms * 1e-3),
+                  "hbm_bytes_per_gpu": eng.hbm_bytes},
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        v, ms, passes, blk = cpu_arm(spec, hid, args.ref_envs, args.cpu_seconds, threads)
+        line["cpu_baseline"] = {
+            "value": v, "unit": "env-steps/s", "cores": threads, "kind": "port",
+            "sample": (f"{args.ref_envs} envs x {passes} steps of the same workload (blocking {blk:.3f}), oracle C port "
+                       f"on {threads} pthreads, {PREROLL} pre-roll steps untimed"),
+        }
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--envs", type=int, default=65536, help="envs per GPU")
+    ap.add_argument("--ref-envs", type=int, default=8192, help="envs in the CPU arm's bounded sample")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--e2e-steps", type=int, default=100)
+    ap.add_argument("--no-flush", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    spec, hid, bytes_per_step, env_id = make_workload(args.workload)
+    if args.impl == "reference":
+        run_reference(args, spec, hid, env_id, args.workload)
+    else:
+        run_b200(args, spec, hid, bytes_per_step, env_id, args.workload)
+
+
+if __name__ == "__main__":
+    main()

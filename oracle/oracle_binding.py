@@ -93,6 +93,15 @@ def lib():
             C.POINTER(OracleConfig), C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int,
             C.c_void_p, C.c_void_p, C.c_void_p,
         ]
+        L.oracle_pool_create.restype = C.c_void_p
+        L.oracle_pool_create.argtypes = [C.POINTER(OracleConfig), C.c_int64, C.c_int64]
+        L.oracle_pool_destroy.argtypes = [C.c_void_p]
+        L.oracle_pool_rollout.restype = C.c_int64
+        L.oracle_pool_rollout.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
+        L.oracle_pool_env.restype = C.c_void_p
+        L.oracle_pool_env.argtypes = [C.c_void_p, C.c_int64]
+        L.oracle_pool_reward_sum.restype = C.c_int64
+        L.oracle_pool_reward_sum.argtypes = [C.c_void_p]
         L.oracle_dlog.restype = C.c_double
         L.oracle_dlog.argtypes = [C.c_double]
         L.oracle_philox4x32.argtypes = [C.c_uint32] * 6 + [C.c_void_p]
@@ -237,3 +246,36 @@ def rollout_many(spec, env0, n_envs, nsteps, heuristic_id, threads, want_state=F
     steps = L.oracle_rollout_many(C.byref(os_.cfg), env0, n_envs, nsteps, heuristic_id, threads,
                                   counters.ctypes.data, _ptr(state), rsum.ctypes.data)
     return steps, counters, state, rsum
+
+
+class OraclePool:
+    """n_envs persistent oracle envs stepped with a heuristic on host threads."""
+
+    def __init__(self, spec, env0: int, n_envs: int):
+        self.L = lib()
+        self.ospec = spec if isinstance(spec, OracleSpec) else OracleSpec(spec)
+        self.n_envs = int(n_envs)
+        self.h = self.L.oracle_pool_create(C.byref(self.ospec.cfg), env0, n_envs)
+
+    def rollout(self, nsteps: int, heuristic_id: int, threads: int) -> int:
+        return int(self.L.oracle_pool_rollout(self.h, nsteps, heuristic_id, threads))
+
+    def counters(self):
+        out = np.zeros((self.n_envs, 12), np.int64)
+        for i in range(self.n_envs):
+            self.L.oracle_counters(self.L.oracle_pool_env(self.h, i), out[i].ctypes.data)
+        return out
+
+    def reward_sum(self) -> int:
+        return int(self.L.oracle_pool_reward_sum(self.h))
+
+    def close(self):
+        if self.h:
+            self.L.oracle_pool_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

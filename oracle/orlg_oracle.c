@@ -640,3 +640,67 @@ int64_t oracle_rollout_many(const oracle_config* cfg, int64_t env0, int64_t n_en
   for (int t = 1; t < threads; t++) pthread_join(th[t], NULL);
   return n_envs * (int64_t)nsteps;
 }
+
+/* ---- persistent pool of envs (bench.py --impl reference / cpu_baseline): the
+ * envs keep their network state between calls, like a VecEnv of reference envs ---- */
+struct oracle_pool {
+  oracle_env** envs;
+  int64_t n;
+  int64_t next;
+  int nsteps, hid;
+  int64_t reward_sum;
+};
+
+oracle_pool* oracle_pool_create(const oracle_config* cfg, int64_t env0, int64_t n_envs) {
+  oracle_pool* p = (oracle_pool*)calloc(1, sizeof(oracle_pool));
+  p->envs = (oracle_env**)calloc((size_t)n_envs, sizeof(oracle_env*));
+  p->n = n_envs;
+  for (int64_t i = 0; i < n_envs; i++) {
+    p->envs[i] = oracle_create(cfg, env0 + i);
+    oracle_reset(p->envs[i], 1);
+  }
+  return p;
+}
+
+void oracle_pool_destroy(oracle_pool* p) {
+  if (!p) return;
+  for (int64_t i = 0; i < p->n; i++) oracle_destroy(p->envs[i]);
+  free(p->envs);
+  free(p);
+}
+
+static void* pool_worker(void* arg) {
+  oracle_pool* p = (oracle_pool*)arg;
+  int64_t rs = 0;
+  double obs[1024];
+  for (;;) {
+    int64_t i = __atomic_fetch_add(&p->next, 1, __ATOMIC_RELAXED);
+    if (i >= p->n) break;
+    oracle_env* e = p->envs[i];
+    int32_t a[4], r;
+    uint8_t d;
+    for (int t = 0; t < p->nsteps; t++) {
+      oracle_heuristic(e, p->hid, a);
+      oracle_step(e, a, &r, &d, e->c.env_kind == 1 ? obs : NULL, NULL);
+      rs += r;
+    }
+  }
+  __atomic_fetch_add(&p->reward_sum, rs, __ATOMIC_RELAXED);
+  return NULL;
+}
+
+int64_t oracle_pool_rollout(oracle_pool* p, int nsteps, int hid, int threads) {
+  p->next = 0;
+  p->nsteps = nsteps;
+  p->hid = hid;
+  if (threads < 1) threads = 1;
+  if (threads > 256) threads = 256;
+  pthread_t th[256];
+  for (int t = 1; t < threads; t++) pthread_create(&th[t], NULL, pool_worker, p);
+  pool_worker(p);
+  for (int t = 1; t < threads; t++) pthread_join(th[t], NULL);
+  return p->n * (int64_t)nsteps;
+}
+
+oracle_env* oracle_pool_env(oracle_pool* p, int64_t i) { return (i >= 0 && i < p->n) ? p->envs[i] : NULL; }
+int64_t oracle_pool_reward_sum(const oracle_pool* p) { return p->reward_sum; }

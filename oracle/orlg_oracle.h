@@ -83,6 +83,15 @@ int64_t oracle_rollout_many(const oracle_config* cfg, int64_t env0, int64_t n_en
                             uint8_t* state_out /* [n_envs][cores*E*S] or NULL */,
                             int64_t* reward_sum_out /* [n_envs] or NULL */);
 
+/* persistent pool of envs stepped with a heuristic on host threads (the envs keep
+ * their state between calls); the timed CPU arm of bench.py */
+typedef struct oracle_pool oracle_pool;
+oracle_pool* oracle_pool_create(const oracle_config* cfg, int64_t env0, int64_t n_envs);
+void oracle_pool_destroy(oracle_pool* p);
+int64_t oracle_pool_rollout(oracle_pool* p, int nsteps, int heuristic_id, int threads);
+oracle_env* oracle_pool_env(oracle_pool* p, int64_t i);
+int64_t oracle_pool_reward_sum(const oracle_pool* p);
+
 /* deterministic RNG pieces, exposed for tests */
 void oracle_philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
                        uint32_t k1, uint32_t out[4]);
