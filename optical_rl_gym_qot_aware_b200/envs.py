@@ -1,0 +1,221 @@
+"""Gym-facing surface of the engine: same ids, kwargs and return shapes as the reference.
+
+The reference exposes its envs through ``gym.make(id, **kwargs)`` and the gym ``Env``
+protocol (optical_rl_gym/__init__.py:3-31; rmsa_env.py:222-341,343-457;
+deeprmsa_env.py:48-124; rmcsa_env.py:209-339).  This module keeps that surface and puts
+the C-ABI engine underneath:
+
+* :class:`BatchedEnv`   ``num_envs`` envs on one GPU; torch CUDA tensors in and out
+  (``reset() -> obs``, ``step(actions) -> (obs, reward, done, info)``).
+* :class:`OrlgVecEnv`   Stable-Baselines3 ``VecEnv`` protocol over host numpy arrays
+  (``reset``, ``step_async``/``step_wait``, auto-reset = the reference's counters-only
+  reset), built on the host-buffer call ``orlg_step_host``.
+* :class:`GymEnv`       ``num_envs == 1`` compatibility wrapper returning the scalar
+  4-tuple of the reference, with the attributes its heuristics read
+  (``current_service``, ``topology.graph["available_slots"]``, ``k_paths``, ``j`` ...).
+* :func:`make`          ``make("RMSA-v0", topology=..., num_envs=..., **kwargs)``.
+
+All stepping happens in the CUDA kernels; nothing here computes an env transition.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from types import SimpleNamespace
+from typing import Any, Dict, Optional
+
+import numpy as np
+
+from . import spec as S
+from .tables import TopologyTables, tables_from_topology
+
+HEURISTICS = {
+    "shortest_path_first_fit": S.H_SP_FF, "sp_ff": S.H_SP_FF,
+    "shortest_available_path_first_fit": S.H_SAP_FF, "sap_ff": S.H_SAP_FF, "ksp_ff": S.H_SAP_FF,
+    "least_loaded_path_first_fit": S.H_LLP_FF, "llp_ff": S.H_LLP_FF,
+    "shortest_available_path_best_modulation_first_core_first_fit": S.H_SAP_BM_FC_FF,
+    "sap_bm_fc_ff": S.H_SAP_BM_FC_FF,
+}
+
+
+def _as_tables(topology) -> TopologyTables:
+    if isinstance(topology, TopologyTables):
+        return topology
+    if isinstance(topology, str):
+        return TopologyTables.load(topology)
+    return tables_from_topology(topology)
+
+
+def _heuristic_id(h) -> int:
+    return HEURISTICS[h] if isinstance(h, str) else int(h)
+
+
+# -- minimal space descriptions (gym itself is API-only for the reference) -----------------
+@dataclass
+class Discrete:
+    n: int
+    shape = ()
+    dtype = np.int64
+
+
+@dataclass
+class MultiDiscrete:
+    nvec: tuple
+
+    @property
+    def shape(self):
+        return (len(self.nvec),)
+
+    dtype = np.int64
+
+
+@dataclass
+class Box:
+    low: float
+    high: float
+    shape: tuple
+    dtype: Any
+
+
+class BatchedEnv:
+    """``num_envs`` independent envs of one kind on one GPU."""
+
+    def __init__(self, env_id: str, topology, num_envs: int = 1, device: int = 0, global_env_offset: int = 0,
+                 request_source: str = "philox", obs_dtype: Optional[str] = None, auto_reset: bool = False,
+                 observation: Optional[str] = None, **kwargs):
+        import torch
+
+        from .engine import Engine
+
+        self.torch = torch
+        self.env_id = env_id
+        tables = _as_tables(topology)
+        kind = S.ENV_IDS[env_id]
+        if kind == S.ENV_PHYRMSA:
+            raise NotImplementedError("PhyRMSA-v0 is not built yet (SURVEY.md section 8, rows a16-a20)")
+        obs_kind = None
+        if observation == "matrix":  # SimpleMatrixObservation rmsa_env.py:940-971
+            obs_kind = S.OBS_MATRIX_U8
+        elif kind == S.ENV_DEEPRMSA:
+            obs_kind = S.OBS_F32 if obs_dtype in ("float32", "f32") else S.OBS_F64
+        src = {"philox": S.SRC_PHILOX, "replay": S.SRC_REPLAY}[request_source]
+        self.spec = S.make_spec(env_id, tables, request_source=src, auto_reset=auto_reset, obs_kind=obs_kind,
+                                **kwargs)
+        self.engine = Engine(self.spec, num_envs, device=device, global_env_offset=global_env_offset)
+        self.num_envs = int(num_envs)
+        self.device = self.engine.device
+        t = tables
+        # attributes the reference's drivers and heuristics read
+        self.k_paths = t.k_paths
+        self.j = self.spec.j
+        self.num_spectrum_resources = self.spec.num_slots
+        self.num_spatial_resources = self.spec.num_cores
+        self.episode_length = self.spec.episode_length
+        self.allow_rejection = self.spec.allow_rejection
+        self.load = self.spec.load
+        self.mean_service_holding_time = self.spec.mean_holding
+        self.mean_service_inter_arrival_time = self.spec.mean_iat
+        rej = 1 if self.spec.allow_rejection else 0
+        if kind == S.ENV_RMSA:  # rmsa_env.py:197-208
+            self.action_space = MultiDiscrete((t.k_paths + rej, self.spec.num_slots + rej))
+        elif kind == S.ENV_DEEPRMSA:  # deeprmsa_env.py:35-43
+            self.action_space = Discrete(t.k_paths * self.j + rej)
+        else:  # rmcsa_env.py:181-194
+            self.action_space = MultiDiscrete((t.k_paths + rej, len(t.mod_names) + rej,
+                                               self.spec.num_cores + rej, self.spec.num_slots + rej))
+        if self.spec.obs_kind in (S.OBS_F64, S.OBS_F32):
+            self.observation_space = Box(0, 1, (self.engine.obs_dim,),
+                                         np.float64 if self.spec.obs_kind == S.OBS_F64 else np.float32)
+        elif self.spec.obs_kind == S.OBS_MATRIX_U8:
+            self.observation_space = Box(0, 1, (self.engine.obs_dim,), np.uint8)
+        else:
+            self.observation_space = None
+        n, dev = self.num_envs, self.device
+        self._reward = torch.zeros(n, dtype=torch.int32, device=dev)
+        self._done = torch.zeros(n, dtype=torch.uint8, device=dev)
+        self._alloc = torch.zeros((n, 4), dtype=torch.int32, device=dev)
+        self._obs = self.engine.new_obs() if self.engine.obs_dim else None
+        self._actions = torch.zeros((n, self.engine.action_dim), dtype=torch.int32, device=dev)
+        self._started = False
+        if src == S.SRC_PHILOX:
+            self.reset(only_episode_counters=False)  # the constructor draws the first request (rmsa_env.py:219-220)
+
+    # -- request sources ---------------------------------------------------------------
+    def load_trace(self, trace) -> None:
+        """Replay source: ``trace[r, i]`` is request r of local env i (engine.REQUEST_DTYPE);
+        performs the constructor-time reset, consuming request 0."""
+        self.engine.load_trace(trace)
+        self.reset(only_episode_counters=False)
+
+    # -- gym protocol --------------------------------------------------------------------
+    def reset(self, only_episode_counters: bool = True):
+        """rmsa_env.py:343-457: by default only the per-episode counters are cleared and the
+        network keeps its state."""
+        self.engine.reset(full=not only_episode_counters or not self._started)
+        self._started = True
+        return self.observation()
+
+    def observation(self):
+        if self._obs is None:
+            return None
+        self.engine.observation(self._obs)
+        return self._obs
+
+    def step(self, actions):
+        """actions: int tensor/array [num_envs, action_dim] (or [num_envs] for DeepRMSA).
+        Returns (obs, reward, done, info); info holds the decision taken per env."""
+        torch = self.torch
+        a = actions
+        if not torch.is_tensor(a):
+            a = torch.as_tensor(np.asarray(a), device=self.device)
+        a = a.to(device=self.device, dtype=torch.int32).reshape(self.num_envs, self.engine.action_dim).contiguous()
+        self.engine.step(a, self._reward, self._done, self._obs, self._alloc)
+        info = {"accepted": self._alloc[:, 0], "path": self._alloc[:, 1] & 0xFFFF, "core": self._alloc[:, 1] >> 16,
+                "initial_slot": self._alloc[:, 2], "number_slots": self._alloc[:, 3]}
+        return self._obs, self._reward, self._done, info
+
+    def reward(self):
+        return self._reward
+
+    def render(self, mode="human"):  # rmsa_env.py:459-460
+        return None
+
+    def close(self):
+        self.engine.close()
+
+    # -- device heuristics and fused rollouts -----------------------------------------------
+    def heuristic(self, name):
+        """Action the named reference heuristic would take, for every env (device tensor)."""
+        self.engine.heuristic(_heuristic_id(name), self._actions)
+        return self._actions
+
+    def rollout(self, name, nsteps: int, reward_sum=None):
+        """``nsteps`` x (heuristic -> step) in one launch (utils.evaluate_heuristic, utils.py:124-162)."""
+        self.engine.rollout(_heuristic_id(name), nsteps, reward_sum)
+
+    # -- views ------------------------------------------------------------------------------------
+    def counters(self):
+        return self.engine.counters()
+
+    def available_slots(self):
+        """topology.graph["available_slots"] of every env: uint8 [num_envs, cores, E, S]."""
+        return self.engine.export_state()
+
+    def current_requests(self):
+        return self.engine.requests()
+
+    def info(self) -> Dict[str, Any]:
+        """Counter-derived entries of the reference's info dict (rmsa_env.py:293-307), per env."""
+        c = self.counters().to(self.torch.float64)
+        safe = lambda x: self.torch.clamp(x, min=1.0)  # noqa: E731
+        return {
+            "service_blocking_rate": (c[:, 0] - c[:, 1]) / safe(c[:, 0]),
+            "episode_service_blocking_rate": (c[:, 2] - c[:, 3]) / safe(c[:, 2]),
+            "bit_rate_blocking_rate": (c[:, 4] - c[:, 5]) / safe(c[:, 4]),
+            "episode_bit_rate_blocking_rate": (c[:, 6] - c[:, 7]) / safe(c[:, 6]),
+        }
+
+    def episode_stats(self, reward_sum=None, group=None):
+        """Statistics summed over every rank's shard (the path's only collective)."""
+        from .sharding import reduce_episode_stats
+
+        return reduce_episode_stats(self.counters(), reward_sum, group)
