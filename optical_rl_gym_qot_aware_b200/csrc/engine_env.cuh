@@ -4,8 +4,9 @@
 
 namespace orlg {
 
-constexpr int HEAP_D = 4;    // 4-ary implicit min-heap keyed by release time
-constexpr int HEAP_PAD = 3;  // logical index i lives in slot i+3 -> child groups are 64B aligned
+constexpr int HEAP_D = 8;    // 8-ary implicit min-heap keyed by release time: one 128 B line per child group
+constexpr int HEAP_PAD = 7;  // logical index i lives in slot i+7 -> the children of i are slots 8i+8..8i+15 (line aligned)
+constexpr int HEAP_TAIL = 8; // slack after the last entry so that a whole child group can be read unconditionally
 
 // payload of a heap entry: what _release_path needs (rmsa_env.py:515-535)
 __device__ __forceinline__ unsigned long long pack_service(int pair, int path, int core, int start, int n) {
@@ -42,6 +43,13 @@ struct Env {
 #pragma unroll
     for (int i = 0; i < CNT_N; i++) cnt[i] = p.counters[(size_t)i * p.NP + e];
   }
+  // only the pending request (enough for the heuristics and the observation)
+  __device__ __forceinline__ void load_request() {
+    uint32_t m = p.meta[e];
+    bit_rate = (int)(m & 0xFFFFu);
+    src = (int)((m >> 16) & 0xFFu);
+    dst = (int)(m >> 24);
+  }
   __device__ __forceinline__ void store_scalars() {
     p.now[e] = now;
     p.holding[e] = holding;
@@ -75,78 +83,102 @@ struct Env {
     heap[i] = make_ulonglong2((unsigned long long)__double_as_longlong(key), payload);
     if (i == 0) next_rel = key;
   }
-  // removes the minimum and returns its payload
+  // removes the minimum and returns its payload.  The HEAP_D children of a node are read with
+  // independent loads (slots past the end are masked by index), so one level = one memory round trip.
   __device__ __forceinline__ unsigned long long heap_pop() {
     ulonglong2 root = heap[0];
     ulonglong2 last = heap[--heap_len];
-    int n = heap_len;
+    const int n = heap_len;
+    const double inf = __longlong_as_double(0x7FF0000000000000ll);
     if (n > 0) {
-      double lk = key_of(last);
+      const double lk = key_of(last);
+      double rk = lk;  // key that ends up at the root
       int i = 0;
       for (;;) {
-        int c = HEAP_D * i + 1;
+        const int c = HEAP_D * i + 1;
         if (c >= n) break;
-        ulonglong2 best = heap[c];
-        int bi = c;
+        ulonglong2 v[HEAP_D];
 #pragma unroll
-        for (int d = 1; d < HEAP_D; d++) {
-          if (c + d < n) {
-            ulonglong2 v = heap[c + d];
-            if (key_of(v) < key_of(best)) {
-              best = v;
-              bi = c + d;
-            }
+        for (int d = 0; d < HEAP_D; d++) v[d] = heap[c + d];
+        double bk = inf;
+        int bd = 0;
+#pragma unroll
+        for (int d = 0; d < HEAP_D; d++) {
+          double k = (c + d < n) ? key_of(v[d]) : inf;
+          if (k < bk) {
+            bk = k;
+            bd = d;
           }
         }
-        if (key_of(best) < lk) {
-          heap[i] = best;
-          i = bi;
+        if (bk < lk) {
+          unsigned long long pay = v[0].y;
+#pragma unroll
+          for (int d = 1; d < HEAP_D; d++) pay = (bd == d) ? v[d].y : pay;
+          heap[i] = make_ulonglong2((unsigned long long)__double_as_longlong(bk), pay);
+          if (i == 0) rk = bk;
+          i = c + bd;
         } else {
           break;
         }
       }
       heap[i] = last;
-      next_rel = (i == 0) ? lk : key_of(heap[0]);
+      next_rel = rk;
     } else {
-      next_rel = __longlong_as_double(0x7FF0000000000000ll);  // +inf
+      next_rel = inf;
     }
     return root.y;
   }
 
   // ---- _next_service rmsa_env.py:643-695 / rmcsa_env.py:690-739 ----
-  __device__ __forceinline__ void next_service() {
-    long long r = cnt[CNT_DRAWN];
+  // The five draws of the next request depend only on the request index and the clock, not on
+  // the decision being taken, so they can be evaluated ahead of it (draw_request) and applied
+  // after it (commit_request); the reference's order of state changes is kept by commit_request.
+  struct Req {
+    double now, holding;
+    int bit_rate, src, dst;
+  };
+  __device__ __forceinline__ Req draw_request() {
+    Req q;
+    const long long r = cnt[CNT_DRAWN];
     if (p.request_source == ORLG_SRC_REPLAY) {
       long long rr = r < p.trace_len ? r : p.trace_len - 1;
       if (r >= p.trace_len) cnt[CNT_FAULT] |= 2;  // trace exhausted
-      const orlg_request* q = p.trace + (size_t)rr * p.num_envs + e;
-      now = q->arrival;
-      holding = q->holding;
-      bit_rate = q->bit_rate;
-      src = q->src;
-      dst = q->dst;
+      const orlg_request* t = p.trace + (size_t)rr * p.num_envs + e;
+      q.now = t->arrival;
+      q.holding = t->holding;
+      q.bit_rate = t->bit_rate;
+      q.src = t->src;
+      q.dst = t->dst;
     } else {
       unsigned long long g = (unsigned long long)(p.genv0 + e);
       uint2 key = make_uint2((uint32_t)p.seed, (uint32_t)(p.seed >> 32));
       uint4 R0 = philox4x32_10(make_uint4((uint32_t)r, (uint32_t)((unsigned long long)r >> 32), (uint32_t)g, 0u), key);
       uint4 R1 = philox4x32_10(make_uint4((uint32_t)r, (uint32_t)((unsigned long long)r >> 32), (uint32_t)g, 1u), key);
       double lam_a = 1.0 / p.mean_iat, lam_h = 1.0 / p.mean_holding;
-      now = now + (-det_log(1.0 - res53(R0.x, R0.y)) / lam_a);
-      holding = -det_log(1.0 - res53(R0.z, R0.w)) / lam_h;
+      q.now = now + (-det_log(1.0 - res53(R0.x, R0.y)) / lam_a);
+      q.holding = -det_log(1.0 - res53(R0.z, R0.w)) / lam_h;
       const double inv32 = 1.0 / 4294967296.0;
       int n = p.n_nodes;
-      src = bisect_right(p.src_cum, ((double)R1.x * inv32) * __ldg(p.src_cum + n - 1), n - 1);
-      const double* dc = p.dst_cum + (size_t)src * n;
-      dst = bisect_right(dc, ((double)R1.y * inv32) * __ldg(dc + n - 1), n - 1);
+      q.src = bisect_right(p.src_cum, ((double)R1.x * inv32) * __ldg(p.src_cum + n - 1), n - 1);
+      const double* dc = p.dst_cum + (size_t)q.src * n;
+      q.dst = bisect_right(dc, ((double)R1.y * inv32) * __ldg(dc + n - 1), n - 1);
       double ub = (double)R1.z * inv32;
       if (p.n_bit_rates > 0) {
         int nb = p.n_bit_rates;
-        bit_rate = __ldg(p.bit_rates + bisect_right(p.br_cum, ub * __ldg(p.br_cum + nb - 1), nb - 1));
+        q.bit_rate = __ldg(p.bit_rates + bisect_right(p.br_cum, ub * __ldg(p.br_cum + nb - 1), nb - 1));
       } else {
-        bit_rate = p.br_lo + (int)floor(ub * (double)(p.br_hi - p.br_lo + 1));
+        q.bit_rate = p.br_lo + (int)floor(ub * (double)(p.br_hi - p.br_lo + 1));
       }
     }
-    cnt[CNT_DRAWN] = r + 1;
+    return q;
+  }
+  __device__ __forceinline__ void commit_request(const Req& q) {
+    now = q.now;
+    holding = q.holding;
+    bit_rate = q.bit_rate;
+    src = q.src;
+    dst = q.dst;
+    cnt[CNT_DRAWN]++;
     if (p.kind != ORLG_ENV_RMCSA) {  // rmsa_env.py:673-674
       cnt[CNT_PROC]++;
       cnt[CNT_EP_PROC]++;
@@ -157,6 +189,20 @@ struct Env {
       unsigned long long s = heap_pop();
       PathRec rec = load_path(p, (int)(s & 0xFFFF), (int)((s >> 16) & 0xFF));
       tile.set_range(rec, (int)((s >> 24) & 0xFF), (int)((s >> 32) & 0xFFFF), (int)(s >> 48));
+    }
+  }
+  __device__ __forceinline__ void next_service() { commit_request(draw_request()); }
+
+  // Pull the heap lines the coming push / pops will touch towards L2 while the tile is in flight.
+  __device__ __forceinline__ void prefetch_queue(double upcoming_now) const {
+    if (heap_len > 0) {
+      const ulonglong2* parent = heap + (heap_len - 1) / HEAP_D;  // parent of the insertion slot
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(parent));
+      if (next_rel <= upcoming_now) {
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(heap));       // root (slot 7, line 0)
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(heap + 1));   // its child group (line 1)
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(heap + heap_len - 1));  // the entry that refills the root
+      }
     }
   }
 

@@ -10,7 +10,8 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
 }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  // single-CTA use: make the init visible to the async proxy (no cluster-scope fence -> no L1 flush)
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
@@ -40,15 +41,18 @@ __device__ __forceinline__ void bulk_s2g(void* gmem_dst, const void* smem_src, u
                "r"(smem_u32(smem_src)), "r"(bytes)
                : "memory");
   asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  // the kernel may exit once the source tile has been read; the global writes complete on their own
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
 __device__ __forceinline__ void fence_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
 // One launch = one pass of the hot path over every env (or nsteps passes in
-// rollout mode).  Grid = NP / BD tiles, one thread per env.
-template <int W, int BD>
+// rollout mode).  Grid = NP / BD tiles, one thread per env.  MT is the mode the
+// instantiation is specialised for (MODE_STEP / MODE_HEURISTIC / MODE_ROLLOUT), or
+// -1 for the rarely used modes (observation, resets), which read io.mode.
+template <int W, int BD, int MT>
 __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t bar;
@@ -56,22 +60,24 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
   const int tid = threadIdx.x;
   const int e = blockIdx.x * BD + tid;
   const bool active = e < p.num_envs;
-  const int mode = io.mode;
+  const int mode = MT >= 0 ? MT : io.mode;
   const uint32_t tile_bytes = (uint32_t)p.planes * BD * 4u;
   uint32_t* tile_g = p.occ + (size_t)blockIdx.x * p.planes * BD;
   const bool need_tile = mode != MODE_RESET_FULL && mode != MODE_RESET_EPISODE;
   const bool dirty_tile = mode == MODE_STEP || mode == MODE_ROLLOUT || mode == MODE_RESET_FULL;
+  const bool stepping = mode == MODE_STEP || mode == MODE_ROLLOUT;
 
   if (need_tile) {
-    if (tid == 0) mbar_init(&bar, 1);
-    __syncthreads();
     if (tid == 0) {
+      mbar_init(&bar, 1);
       mbar_expect_tx(&bar, tile_bytes);
       bulk_g2s(tile_s, tile_g, tile_bytes, &bar);
     }
   }
 
   Env<W, BD> env(p, tile_s, tid, active ? e : 0);
+  typename Env<W, BD>::Req nx{};
+  int a[4] = {0, 0, 0, 0};
   if (mode == MODE_RESET_FULL) {
     // rmsa_env.py:391-457: empty network, clock 0, counters 0, then the first request
     for (int pl = 0; pl < p.planes; pl++) tile_s[pl * BD + tid] = mask_word(pl % W, 0, p.S);
@@ -84,26 +90,56 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
     for (int i = 0; i < CNT_N; i++) env.cnt[i] = 0;
     if (active) env.next_service();
   } else if (active) {
-    env.load_scalars();
+    // everything that does not need the tile happens while the bulk copy is in flight
+    if (mode == MODE_HEURISTIC || mode == MODE_OBS) {
+      env.load_request();
+    } else {
+      env.load_scalars();
+      if (mode == MODE_STEP) {
+        if (p.action_dim == 1) {
+          a[0] = io.actions[e];
+        } else if (p.action_dim == 2) {
+          int2 v = reinterpret_cast<const int2*>(io.actions)[e];
+          a[0] = v.x;
+          a[1] = v.y;
+        } else {
+          int4 v = reinterpret_cast<const int4*>(io.actions)[e];
+          a[0] = v.x;
+          a[1] = v.y;
+          a[2] = v.z;
+          a[3] = v.w;
+        }
+      }
+      if (stepping) {
+        nx = env.draw_request();
+        env.prefetch_queue(nx.now);
+      }
+    }
   }
-  if (need_tile) mbar_wait(&bar, 0);
+  if (need_tile) {
+    __syncthreads();  // the barrier init by thread 0 is visible to every waiter
+    mbar_wait(&bar, 0);
+  }
 
   if (active) {
     if (mode == MODE_RESET_EPISODE) {
       env.reset_episode();
     } else if (mode == MODE_HEURISTIC) {
-      int a[4];
       heuristic_action<W, BD>(env, io.heuristic, a);
-      for (int i = 0; i < p.action_dim; i++) io.actions_out[(size_t)e * p.action_dim + i] = a[i];
-    } else if (mode == MODE_STEP || mode == MODE_ROLLOUT) {
+      if (p.action_dim == 1) {
+        io.actions_out[e] = a[0];
+      } else if (p.action_dim == 2) {
+        reinterpret_cast<int2*>(io.actions_out)[e] = make_int2(a[0], a[1]);
+      } else {
+        reinterpret_cast<int4*>(io.actions_out)[e] = make_int4(a[0], a[1], a[2], a[3]);
+      }
+    } else if (stepping) {
       const int nsteps = (mode == MODE_ROLLOUT) ? io.nsteps : 1;
       long long rsum = 0;
       for (int t = 0; t < nsteps; t++) {
-        int a[4];
         if (mode == MODE_ROLLOUT) {
           heuristic_action<W, BD>(env, io.heuristic, a);
-        } else {
-          for (int i = 0; i < p.action_dim; i++) a[i] = io.actions[(size_t)e * p.action_dim + i];
+          if (t > 0) nx = env.draw_request();
         }
         Decision d;
         if (p.kind == ORLG_ENV_RMSA) d = rmsa_decide<W, BD>(env, a[0], a[1]);
@@ -117,7 +153,7 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
         }
         // reward: optical_network_env.py:213-214 ; deeprmsa_env.py:123-124
         int r = (p.kind == ORLG_ENV_DEEPRMSA) ? (d.accepted ? 1 : -1) : (d.accepted ? 1 : 0);
-        env.next_service();
+        env.commit_request(nx);
         int dn = env.cnt[CNT_EP_PROC] == (long long)p.episode_length;  // rmsa_env.py:339
         if (dn) {
           env.cnt[CNT_EPISODES]++;
@@ -152,53 +188,6 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
     __syncthreads();
     if (tid == 0) bulk_s2g(tile_g, tile_s, tile_bytes);
   }
-}
-
-// ---- small utility kernels ----------------------------------------------------
-// counters [CNT_N][NP] (+ heap_len) -> [num_envs][ORLG_NUM_COUNTERS]
-__global__ void counters_kernel(const Params p, long long* out) {
-  int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= p.num_envs) return;
-  long long* o = out + (size_t)e * ORLG_NUM_COUNTERS;
-  auto c = [&](int i) { return p.counters[(size_t)i * p.NP + e]; };
-  o[ORLG_C_SERVICES_PROCESSED] = c(CNT_PROC);
-  o[ORLG_C_SERVICES_ACCEPTED] = c(CNT_ACC);
-  o[ORLG_C_EP_SERVICES_PROCESSED] = c(CNT_EP_PROC);
-  o[ORLG_C_EP_SERVICES_ACCEPTED] = c(CNT_EP_ACC);
-  o[ORLG_C_BIT_RATE_REQUESTED] = c(CNT_BR_REQ);
-  o[ORLG_C_BIT_RATE_PROVISIONED] = c(CNT_BR_PROV);
-  o[ORLG_C_EP_BIT_RATE_REQUESTED] = c(CNT_EP_BR_REQ);
-  o[ORLG_C_EP_BIT_RATE_PROVISIONED] = c(CNT_EP_BR_PROV);
-  o[ORLG_C_REQUESTS_DRAWN] = c(CNT_DRAWN);
-  o[ORLG_C_QUEUE_LEN] = p.heap_len[e];
-  o[ORLG_C_FAULT] = c(CNT_FAULT);
-  o[ORLG_C_EPISODES] = c(CNT_EPISODES);
-}
-
-// packed tiles -> uint8 [num_envs][cores][E][S]
-__global__ void export_state_kernel(const Params p, int W, int BD, unsigned char* out) {
-  long long cells = (long long)p.cores * p.E * p.S;
-  long long total = cells * p.num_envs;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    long long e = i / cells, c = i % cells;
-    int row = (int)(c / p.S), s = (int)(c % p.S);
-    size_t w = ((size_t)(e / BD) * p.planes + (size_t)row * W + (s >> 5)) * BD + (e % BD);
-    out[i] = (unsigned char)((p.occ[w] >> (s & 31)) & 1u);
-  }
-}
-
-__global__ void requests_kernel(const Params p, orlg_request* out) {
-  int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= p.num_envs) return;
-  uint32_t m = p.meta[e];
-  orlg_request r;
-  r.arrival = p.now[e];
-  r.holding = p.holding[e];
-  r.bit_rate = (int)(m & 0xFFFFu);
-  r.src = (int16_t)((m >> 16) & 0xFFu);
-  r.dst = (int16_t)(m >> 24);
-  out[e] = r;
 }
 
 }  // namespace orlg

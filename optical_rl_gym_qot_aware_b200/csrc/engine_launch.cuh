@@ -1,0 +1,55 @@
+// engine_launch.cuh — host-side launch of env_kernel<W, BD, MT>.  Each word count W is
+// instantiated in its own translation unit (orlg_w2.cu / orlg_w4.cu / orlg_w10.cu) so the
+// three compile in parallel; orlg.cu only sees the declaration of launch_w.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "engine_kernel.cuh"
+
+namespace orlg {
+
+struct LaunchGeom {
+  int BD, NP, device;
+  size_t smem_bytes;
+};
+
+template <int W>
+cudaError_t launch_w(const LaunchGeom& g, const Params& p, const StepIO& io, cudaStream_t st);
+
+#ifdef ORLG_INSTANTIATE_W
+template <int W, int BD, int MT>
+static cudaError_t launch_t(const LaunchGeom& g, const Params& p, const StepIO& io, cudaStream_t st) {
+  static size_t configured[64] = {};  // largest dynamic smem opted into, per device
+  if (g.smem_bytes > 48 * 1024 && configured[g.device & 63] < g.smem_bytes) {
+    cudaError_t rc = cudaFuncSetAttribute(env_kernel<W, BD, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)g.smem_bytes);
+    if (rc != cudaSuccess) return rc;
+    configured[g.device & 63] = g.smem_bytes;
+  }
+  env_kernel<W, BD, MT><<<g.NP / BD, BD, g.smem_bytes, st>>>(p, io);
+  return cudaGetLastError();
+}
+
+template <int W, int BD>
+static cudaError_t launch_m(const LaunchGeom& g, const Params& p, const StepIO& io, cudaStream_t st) {
+  switch (io.mode) {
+    case MODE_STEP: return launch_t<W, BD, MODE_STEP>(g, p, io, st);
+    case MODE_HEURISTIC: return launch_t<W, BD, MODE_HEURISTIC>(g, p, io, st);
+    case MODE_ROLLOUT: return launch_t<W, BD, MODE_ROLLOUT>(g, p, io, st);
+    default: return launch_t<W, BD, -1>(g, p, io, st);
+  }
+}
+
+template <int W>
+cudaError_t launch_w(const LaunchGeom& g, const Params& p, const StepIO& io, cudaStream_t st) {
+  switch (g.BD) {
+    case 32: return launch_m<W, 32>(g, p, io, st);
+    case 64: return launch_m<W, 64>(g, p, io, st);
+    default: return launch_m<W, 128>(g, p, io, st);
+  }
+}
+
+template cudaError_t launch_w<ORLG_INSTANTIATE_W>(const LaunchGeom&, const Params&, const StepIO&, cudaStream_t);
+#endif
+
+}  // namespace orlg

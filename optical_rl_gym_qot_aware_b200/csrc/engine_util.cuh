@@ -1,0 +1,55 @@
+// engine_util.cuh — small non-template kernels behind the read-only ABI calls
+// (orlg_get_counters, orlg_export_state, orlg_get_requests).  Included by orlg.cu only.
+#pragma once
+#include "engine_env.cuh"
+
+namespace orlg {
+
+// ---- small utility kernels ----------------------------------------------------
+// counters [CNT_N][NP] (+ heap_len) -> [num_envs][ORLG_NUM_COUNTERS]
+__global__ void counters_kernel(const Params p, long long* out) {
+  int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= p.num_envs) return;
+  long long* o = out + (size_t)e * ORLG_NUM_COUNTERS;
+  auto c = [&](int i) { return p.counters[(size_t)i * p.NP + e]; };
+  o[ORLG_C_SERVICES_PROCESSED] = c(CNT_PROC);
+  o[ORLG_C_SERVICES_ACCEPTED] = c(CNT_ACC);
+  o[ORLG_C_EP_SERVICES_PROCESSED] = c(CNT_EP_PROC);
+  o[ORLG_C_EP_SERVICES_ACCEPTED] = c(CNT_EP_ACC);
+  o[ORLG_C_BIT_RATE_REQUESTED] = c(CNT_BR_REQ);
+  o[ORLG_C_BIT_RATE_PROVISIONED] = c(CNT_BR_PROV);
+  o[ORLG_C_EP_BIT_RATE_REQUESTED] = c(CNT_EP_BR_REQ);
+  o[ORLG_C_EP_BIT_RATE_PROVISIONED] = c(CNT_EP_BR_PROV);
+  o[ORLG_C_REQUESTS_DRAWN] = c(CNT_DRAWN);
+  o[ORLG_C_QUEUE_LEN] = p.heap_len[e];
+  o[ORLG_C_FAULT] = c(CNT_FAULT);
+  o[ORLG_C_EPISODES] = c(CNT_EPISODES);
+}
+
+// packed tiles -> uint8 [num_envs][cores][E][S]
+__global__ void export_state_kernel(const Params p, int W, int BD, unsigned char* out) {
+  long long cells = (long long)p.cores * p.E * p.S;
+  long long total = cells * p.num_envs;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    long long e = i / cells, c = i % cells;
+    int row = (int)(c / p.S), s = (int)(c % p.S);
+    size_t w = ((size_t)(e / BD) * p.planes + (size_t)row * W + (s >> 5)) * BD + (e % BD);
+    out[i] = (unsigned char)((p.occ[w] >> (s & 31)) & 1u);
+  }
+}
+
+__global__ void requests_kernel(const Params p, orlg_request* out) {
+  int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= p.num_envs) return;
+  uint32_t m = p.meta[e];
+  orlg_request r;
+  r.arrival = p.now[e];
+  r.holding = p.holding[e];
+  r.bit_rate = (int)(m & 0xFFFFu);
+  r.src = (int16_t)((m >> 16) & 0xFFu);
+  r.dst = (int16_t)(m >> 24);
+  out[e] = r;
+}
+
+}  // namespace orlg

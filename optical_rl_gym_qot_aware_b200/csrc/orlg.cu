@@ -9,7 +9,8 @@
 #include <string>
 #include <vector>
 
-#include "engine_kernel.cuh"
+#include "engine_launch.cuh"
+#include "engine_util.cuh"
 
 using namespace orlg;
 
@@ -75,41 +76,20 @@ static int dev_upload(orlg_engine* e, const T** out, const T* host, size_t count
 
 extern "C" int orlg_abi_version(void) { return ORLG_ABI_VERSION; }
 extern "C" const char* orlg_build_info(void) {
-  return "orlg sm_100a engine: TMA-staged tiles, thread-per-env, W in {2,4,10}, BD in {32,64,128}";
+  return "orlg sm_100a engine: TMA-staged tiles, thread-per-env, W in {2,4,10}, BD in {32,64,128}, 8-ary release heap";
 }
 extern "C" const char* orlg_last_error(const orlg_engine* e) {
   return e ? e->err.c_str() : g_create_error.c_str();
 }
 
-template <int W, int BD>
-static cudaError_t launch_t(orlg_engine* e, const StepIO& io, cudaStream_t st) {
-  static size_t configured[64] = {};  // largest dynamic smem opted into, per device
-  if (e->smem_bytes > 48 * 1024 && configured[e->device & 63] < e->smem_bytes) {
-    cudaError_t rc = cudaFuncSetAttribute(env_kernel<W, BD>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          (int)e->smem_bytes);
-    if (rc != cudaSuccess) return rc;
-    configured[e->device & 63] = e->smem_bytes;
-  }
-  env_kernel<W, BD><<<e->p.NP / BD, BD, e->smem_bytes, st>>>(e->p, io);
-  return cudaGetLastError();
-}
-
-template <int W>
-static cudaError_t launch_w(orlg_engine* e, const StepIO& io, cudaStream_t st) {
-  switch (e->BD) {
-    case 32: return launch_t<W, 32>(e, io, st);
-    case 64: return launch_t<W, 64>(e, io, st);
-    default: return launch_t<W, 128>(e, io, st);
-  }
-}
-
 static int launch(orlg_engine* e, const StepIO& io, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
+  LaunchGeom g{e->BD, e->p.NP, e->device, e->smem_bytes};
   cudaError_t rc;
   switch (e->W) {
-    case 2: rc = launch_w<2>(e, io, st); break;
-    case 4: rc = launch_w<4>(e, io, st); break;
-    default: rc = launch_w<10>(e, io, st); break;
+    case 2: rc = launch_w<2>(g, e->p, io, st); break;
+    case 4: rc = launch_w<4>(g, e->p, io, st); break;
+    default: rc = launch_w<10>(g, e->p, io, st); break;
   }
   if (rc != cudaSuccess) {
     e->err = std::string("kernel launch: ") + cudaGetErrorString(rc);
@@ -241,7 +221,7 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   int min_slots = (int)std::ceil((double)min_br / ((double)max_se * c->channel_width)) + 1;
   long long bound = (long long)cores * p.E * (p.S / min_slots);
   p.heap_cap = c->heap_capacity > 0 ? c->heap_capacity : (int)(bound < 16 ? 16 : bound);
-  p.heap_stride = (p.heap_cap + HEAP_PAD + 3) & ~3;
+  p.heap_stride = (p.heap_cap + HEAP_PAD + HEAP_TAIL + 7) & ~7;  // 128 B multiples: child groups stay line aligned
 
   int rc = 0;
   const uint4* drec = nullptr;
@@ -262,7 +242,7 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   if ((rc = dev_alloc(e, &p.occ, (size_t)p.planes * NP)) || (rc = dev_alloc(e, &p.now, NP)) ||
       (rc = dev_alloc(e, &p.holding, NP)) || (rc = dev_alloc(e, &p.meta, NP)) ||
       (rc = dev_alloc(e, &p.next_rel, NP)) || (rc = dev_alloc(e, &p.heap_len, NP)) ||
-      (rc = dev_alloc(e, &p.heap, NP * p.heap_stride, false)) ||
+      (rc = dev_alloc(e, &p.heap, NP * p.heap_stride)) ||
       (rc = dev_alloc(e, &p.counters, (size_t)CNT_N * NP)))
     return fail_create(e, rc, e->err);
 

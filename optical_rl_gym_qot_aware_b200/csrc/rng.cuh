@@ -66,14 +66,14 @@ __device__ __forceinline__ double res53(uint32_t a, uint32_t b) {
   return ((double)(a >> 5) * 67108864.0 + (double)(b >> 6)) / 9007199254740992.0;
 }
 
-// bisect.bisect_right(cum, x, 0, hi) as used by random.choices
+// bisect.bisect_right(cum, x, 0, hi) as used by random.choices.  cum is non-decreasing, so the
+// insertion point equals the number of entries <= x: hi independent loads instead of a
+// dependent binary-search chain.
 __device__ __forceinline__ int bisect_right(const double* __restrict__ cum, double x, int hi) {
-  int lo = 0;
-  while (lo < hi) {
-    int mid = (lo + hi) >> 1;
-    if (x < __ldg(cum + mid)) hi = mid; else lo = mid + 1;
-  }
-  return lo;
+  int c = 0;
+#pragma unroll 8
+  for (int i = 0; i < hi; i++) c += (x >= __ldg(cum + i)) ? 1 : 0;
+  return c;
 }
 
 }  // namespace orlg

@@ -219,3 +219,172 @@ class BatchedEnv:
         from .sharding import reduce_episode_stats
 
         return reduce_episode_stats(self.counters(), reward_sum, group)
+
+
+class OrlgVecEnv:
+    """Stable-Baselines3 ``VecEnv`` protocol (not shipped by the reference) over
+    host numpy arrays.  ``step_wait`` makes one ``orlg_step_host`` call: actions H2D from pinned
+    memory, one step of every env, obs/reward/done D2H, stream synchronised.  Envs whose episode
+    ended are reset in-kernel with the reference's counters-only reset (rmsa_env.py:344-389)."""
+
+    def __init__(self, env_id: str, topology, num_envs: int, **kwargs):
+        import torch
+
+        kwargs.setdefault("auto_reset", True)
+        self.env = BatchedEnv(env_id, topology, num_envs=num_envs, **kwargs)
+        self.num_envs = self.env.num_envs
+        self.action_space = self.env.action_space
+        self.observation_space = self.env.observation_space
+        e = self.env.engine
+        odt = {S.OBS_F64: torch.float64, S.OBS_F32: torch.float32, S.OBS_MATRIX_U8: torch.uint8}.get(
+            self.env.spec.obs_kind)
+        n = self.num_envs
+        self._h_act = torch.zeros((n, e.action_dim), dtype=torch.int32).pin_memory()
+        self._h_rew = torch.zeros(n, dtype=torch.int32).pin_memory()
+        self._h_done = torch.zeros(n, dtype=torch.uint8).pin_memory()
+        self._h_alloc = torch.zeros((n, 4), dtype=torch.int32).pin_memory()
+        # the device buffer is feature-major; the host copy is exposed as its [num_envs, obs_dim] view
+        self._h_obs = torch.zeros((e.obs_dim, n), dtype=odt).pin_memory() if e.obs_dim else None
+        self._pending = False
+
+    def _obs_view(self):
+        return None if self._h_obs is None else self._h_obs.numpy().T
+
+    def reset(self):
+        obs = self.env.reset(only_episode_counters=True)
+        if obs is not None:
+            self._h_obs.copy_(obs.t())
+            self.env.torch.cuda.synchronize(self.env.device)
+        return self._obs_view()
+
+    def step_async(self, actions) -> None:
+        a = np.asarray(actions, dtype=np.int32).reshape(self.num_envs, -1)
+        self._h_act.numpy()[:] = a
+        self._pending = True
+
+    def step_wait(self):
+        assert self._pending, "step_wait without step_async"
+        self._pending = False
+        self.env.engine.step_host(self._h_act, self._h_rew, self._h_done, self._h_obs, self._h_alloc)
+        rew = self._h_rew.numpy().astype(np.float32)
+        done = self._h_done.numpy().astype(bool)
+        al = self._h_alloc.numpy()
+        infos = [{"accepted": bool(al[i, 0])} for i in range(self.num_envs)] if self.num_envs <= 64 else \
+            {"accepted": al[:, 0].astype(bool), "path": al[:, 1] & 0xFFFF, "core": al[:, 1] >> 16,
+             "initial_slot": al[:, 2], "number_slots": al[:, 3]}
+        return self._obs_view(), rew, done, infos
+
+    def step(self, actions):
+        self.step_async(actions)
+        return self.step_wait()
+
+    def seed(self, seed=None):
+        return [None] * self.num_envs
+
+    def get_attr(self, name, indices=None):
+        return [getattr(self.env, name)] * self.num_envs
+
+    def env_is_wrapped(self, wrapper_class, indices=None):
+        return [False] * self.num_envs
+
+    def close(self):
+        self.env.close()
+
+
+class GymEnv:
+    """Scalar gym ``Env`` look-alike over a one-env engine: ``step`` returns the reference's
+    4-tuple ``(observation, reward, done, info)`` (rmsa_env.py:336-341) with Python scalars."""
+
+    metadata = {"metrics": ["service_blocking_rate", "episode_service_blocking_rate", "bit_rate_blocking_rate",
+                            "episode_bit_rate_blocking_rate"]}
+
+    def __init__(self, env_id: str, topology, **kwargs):
+        self._b = BatchedEnv(env_id, topology, num_envs=1, **kwargs)
+        for name in ("k_paths", "j", "num_spectrum_resources", "num_spatial_resources", "episode_length",
+                     "allow_rejection", "load", "mean_service_holding_time", "mean_service_inter_arrival_time",
+                     "action_space", "observation_space", "spec"):
+            setattr(self, name, getattr(self._b, name))
+        self.tables = self._b.spec.tables
+        self.topology = SimpleNamespace(graph=_GraphView(self))
+
+    # -- the attributes reference heuristics read (rmsa_env.py:854-937, deeprmsa_env.py:135-155) --
+    @property
+    def current_service(self):
+        r = self._b.current_requests()[0]
+        c = self._b.counters()[0].cpu().numpy()
+        names = self.tables.node_names
+        return SimpleNamespace(
+            service_id=int(c[2]) - 1 if self._b.spec.env_kind != S.ENV_RMCSA else int(c[2]),  # rmsa_env.py:661-674
+            source=names[int(r["src"])], source_id=int(r["src"]), destination=names[int(r["dst"])],
+            destination_id=int(r["dst"]), arrival_time=float(r["arrival"]), holding_time=float(r["holding"]),
+            bit_rate=int(r["bit_rate"]))
+
+    def _counter(self, i):
+        return int(self._b.counters()[0, i])
+
+    services_processed = property(lambda s: s._counter(0))
+    services_accepted = property(lambda s: s._counter(1))
+    episode_services_processed = property(lambda s: s._counter(2))
+    episode_services_accepted = property(lambda s: s._counter(3))
+    bit_rate_requested = property(lambda s: s._counter(4))
+    bit_rate_provisioned = property(lambda s: s._counter(5))
+    episode_bit_rate_requested = property(lambda s: s._counter(6))
+    episode_bit_rate_provisioned = property(lambda s: s._counter(7))
+
+    def _obs_np(self, obs):
+        return None if obs is None else obs[0].cpu().numpy().copy()
+
+    def reset(self, only_episode_counters: bool = True):
+        return self._obs_np(self._b.reset(only_episode_counters))
+
+    def observation(self):
+        return self._obs_np(self._b.observation())
+
+    def step(self, action):
+        obs, rew, done, info = self._b.step(np.atleast_1d(np.asarray(action, dtype=np.int64))[None])
+        i = {k: (float(v[0]) if v.dtype.is_floating_point else int(v[0])) for k, v in self._b.info().items()}
+        i.update({k: int(v[0]) for k, v in info.items()})
+        return self._obs_np(obs), int(rew[0]), bool(done[0]), i
+
+    def heuristic(self, name):
+        a = self._b.heuristic(name)[0].cpu().numpy()
+        return int(a[0]) if a.size == 1 else tuple(int(x) for x in a)
+
+    def load_trace(self, trace):
+        self._b.load_trace(np.asarray(trace).reshape(-1, 1))
+
+    def render(self, mode="human"):
+        return None
+
+    def close(self):
+        self._b.close()
+
+
+class _GraphView(dict):
+    """``env.topology.graph`` with a lazily fetched ``available_slots`` (rmsa_env.py:396-398)."""
+
+    def __init__(self, env: GymEnv):
+        super().__init__(k_paths=env.k_paths, num_spectrum_resources=env.num_spectrum_resources,
+                         name=env.tables.name, node_indices=list(env.tables.node_names))
+        self._env = env
+
+    def __getitem__(self, key):
+        if key == "available_slots":
+            a = self._env._b.available_slots()[0].cpu().numpy().astype(np.int64)
+            return a if self._env._b.spec.env_kind == S.ENV_RMCSA else a[0]
+        return super().__getitem__(key)
+
+
+def make(env_id: str, topology=None, num_envs: Optional[int] = None, vec_env: bool = False, **kwargs):
+    """Counterpart of ``gym.make(id, **kwargs)`` for the ids in optical_rl_gym/__init__.py:3-31.
+    ``num_envs=None`` -> scalar :class:`GymEnv`; an int -> :class:`BatchedEnv` (device tensors) or,
+    with ``vec_env=True``, :class:`OrlgVecEnv` (host numpy, SB3 protocol)."""
+    if env_id not in S.ENV_IDS:
+        raise KeyError(f"unknown env id {env_id!r}; known: {sorted(S.ENV_IDS)}")
+    if topology is None:
+        raise TypeError("make() needs topology=")
+    if num_envs is None:
+        return GymEnv(env_id, topology, **kwargs)
+    if vec_env:
+        return OrlgVecEnv(env_id, topology, num_envs, **kwargs)
+    return BatchedEnv(env_id, topology, num_envs=num_envs, **kwargs)

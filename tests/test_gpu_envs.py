@@ -1,0 +1,142 @@
+"""GPU tests of the gym-facing surface (make / BatchedEnv / OrlgVecEnv / GymEnv): the wrappers
+must hand back exactly what the engine computes, in the reference's shapes."""
+import numpy as np
+import pytest
+
+import golden_util as G
+from optical_rl_gym_qot_aware_b200 import spec as S
+
+pytestmark = pytest.mark.gpu
+
+HEUR = {"rmsa_nsfnet_sapff": "shortest_available_path_first_fit",
+        "deeprmsa_nsfnet_kspff": "shortest_available_path_first_fit",
+        "rmcsa_jpn12_heur": "shortest_available_path_best_modulation_first_core_first_fit"}
+
+
+def _kwargs(g):
+    kw = {}
+    for k in g["kwargs_keys"]:
+        v = g["kw_" + str(k)]
+        kw[str(k)] = v.item() if v.ndim == 0 else v
+    return kw
+
+
+@pytest.mark.parametrize("case", sorted(HEUR))
+def test_scalar_gym_env_replays_reference_trace(case):
+    """make(id, topology=...) -> scalar env; heuristic + step reproduce the golden trace 4-tuples."""
+    import optical_rl_gym_qot_aware_b200 as pkg
+
+    g, spec = G.load_case(case)
+    env = pkg.make(G.ENV_NAME[int(g["env_kind"])], topology=spec.tables, request_source="replay", **_kwargs(g))
+    env.load_trace(g["requests"])
+    n = min(400, len(g["actions"]))
+    if spec.env_kind == 1:
+        assert np.array_equal(env.observation(), g["obs0"])
+    for t in range(n):
+        cs = env.current_service
+        assert (cs.arrival_time, cs.holding_time, cs.bit_rate, cs.source_id, cs.destination_id) == tuple(
+            g["requests"][t].tolist())
+        a = env.heuristic(HEUR[case])
+        assert np.array_equal(np.atleast_1d(a), g["actions"][t])
+        obs, r, d, info = env.step(a)
+        assert isinstance(r, int) and isinstance(d, bool)
+        assert (r, d, info["accepted"]) == (int(g["reward"][t]), bool(g["done"][t]), int(g["accepted"][t]))
+        if spec.env_kind == 1:
+            assert np.array_equal(obs, g["obs"][t])
+        if d:
+            env.reset()
+        assert env.episode_services_processed == int(g["counters"][t][2])
+    av = env.topology.graph["available_slots"]
+    assert av.shape == ((spec.num_cores,) if spec.env_kind == 2 else ()) + (spec.tables.n_edges, spec.num_slots)
+    env.close()
+
+
+def test_vecenv_matches_device_path_and_oracle():
+    """OrlgVecEnv (host numpy, orlg_step_host) == BatchedEnv (device tensors) == CPU oracle."""
+    import torch
+
+    import optical_rl_gym_qot_aware_b200 as pkg
+    import oracle_binding as OB
+
+    kw = dict(seed=99, mean_service_holding_time=7.5, mean_service_inter_arrival_time=1 / 12.0, episode_length=30,
+              j=2)
+    n_env, n_steps = 300, 90
+    topo = G.topology("nsfnet")
+    vec = pkg.make("DeepRMSA-v0", topology=topo, num_envs=n_env, vec_env=True, **kw)
+    dev = pkg.make("DeepRMSA-v0", topology=topo, num_envs=n_env, auto_reset=True, **kw)
+    obs_h = vec.reset()
+    obs_d = dev.reset()
+    assert obs_h.shape == (n_env, 1 + 28 + 7 * 5) and obs_h.dtype == np.float64
+    assert np.array_equal(obs_h, obs_d.cpu().numpy())
+    rsum = np.zeros(n_env, np.int64)
+    episodes = 0
+    for t in range(n_steps):
+        act = dev.heuristic("sap_ff")
+        a_host = act.cpu().numpy()
+        obs_h, rew_h, done_h, infos = vec.step(a_host)
+        obs_d, rew_d, done_d, info_d = dev.step(act)
+        assert np.array_equal(obs_h, obs_d.cpu().numpy()), t
+        assert np.array_equal(rew_h, rew_d.cpu().numpy().astype(np.float32))
+        assert np.array_equal(done_h, done_d.cpu().numpy().astype(bool))
+        assert np.array_equal(infos["accepted"], info_d["accepted"].cpu().numpy().astype(bool))
+        rsum += rew_d.cpu().numpy()
+        episodes += int(done_h.sum())
+    assert episodes == n_env * (n_steps // 29)
+    spec = S.make_spec("DeepRMSA-v0", topo, auto_reset=True, **kw)
+    _, o_cnt, o_state, o_rsum = OB.rollout_many(spec, 0, n_env, n_steps, S.H_SAP_FF, 4, want_state=True)
+    assert np.array_equal(dev.counters().cpu().numpy()[:, :9], o_cnt[:, :9])
+    assert np.array_equal(rsum, o_rsum)
+    assert np.array_equal(dev.available_slots().cpu().numpy(), o_state)
+    st = dev.episode_stats(torch.from_numpy(rsum).to(dev.device))
+    assert st["envs"] == n_env and st["fault"] == 0 and st["reward_sum"] == int(o_rsum.sum())
+    assert st["services_processed"] == int(o_cnt[:, 0].sum())
+    vec.close()
+    dev.close()
+
+
+def test_sharded_engines_equal_single_engine():
+    """Global env ids: 2 shards (offsets 0 and n/2) == one engine holding all envs."""
+    import torch
+
+    from optical_rl_gym_qot_aware_b200.engine import Engine
+    from optical_rl_gym_qot_aware_b200.sharding import shard_bounds
+
+    spec = S.make_spec("RMSA-v0", G.topology("spn"), seed=5, load=100, mean_service_holding_time=25,
+                       num_spectrum_resources=100, episode_length=60, auto_reset=True)
+    n, steps = 333, 150
+    whole = Engine(spec, n)
+    whole.reset(True)
+    whole.rollout(S.H_SAP_FF, steps)
+    cw, sw = whole.counters().cpu(), whole.export_state().cpu()
+    for r in range(2):
+        lo, hi = shard_bounds(n, 2, r)
+        part = Engine(spec, hi - lo, global_env_offset=lo)
+        part.reset(True)
+        part.rollout(S.H_SAP_FF, steps)
+        assert torch.equal(part.counters().cpu(), cw[lo:hi])
+        assert torch.equal(part.export_state().cpu(), sw[lo:hi])
+        part.close()
+    whole.close()
+
+
+def test_matrix_observation_matches_oracle():
+    import torch
+
+    import oracle_binding as OB
+    from optical_rl_gym_qot_aware_b200.engine import Engine
+
+    spec = S.make_spec("RMCSA-v0", G.topology("nsfnet"), seed=8, load=250, mean_service_holding_time=25,
+                       num_spectrum_resources=64, num_spatial_resources=7, episode_length=100,
+                       obs_kind=S.OBS_MATRIX_U8)
+    eng = Engine(spec, 5, obs_layout="env_major")
+    eng.reset(True)
+    eng.rollout(S.H_SAP_BM_FC_FF, 80)
+    obs = eng.new_obs()
+    eng.observation(obs)
+    for i in (0, 4):
+        o = OB.OracleEnv(spec, i)
+        o.reset(True)
+        for _ in range(80):
+            o.step(o.heuristic(S.H_SAP_BM_FC_FF))
+        assert np.array_equal(obs[i].cpu().numpy(), o.matrix_observation())
+    eng.close()
