@@ -201,6 +201,33 @@ int orlg_export_state(orlg_engine* e, uint8_t* dev_out, void* stream);
 /* Pending request of every env (current_service). */
 int orlg_get_requests(orlg_engine* e, orlg_request* dev_out, void* stream);
 
+/* ---- GN-model GSNR: calculate_osnr, examples/calculate_osnr.py:9-56 --------------------
+ * Physical inputs the reference leaves undefined are explicit here.  Every
+ * link is split into span_count[l] equal spans of span_length_km[l]
+ * (examples/create_topology_gn.py:122-134: int(length // 80) + 1 spans).  A service that
+ * occupies slots [first, first+n) has bandwidth n*slot_hz and centre frequency
+ * f0_hz + (first + n/2)*slot_hz. */
+typedef struct orlg_gsnr_params {
+  double launch_power_w;    /* per-channel launch power (1e-3 = 0 dBm) */
+  double attenuation_per_m; /* field attenuation alpha [1/m]: power falls as exp(-2*alpha*L) */
+  double noise_figure_lin;  /* amplifier noise figure, linear */
+  double f0_hz;             /* lower edge of slot 0 */
+  double slot_hz;           /* slot width in Hz (channel_width * 1e9) */
+  const int32_t* span_count;    /* host, [n_edges] */
+  const double* span_length_km; /* host, [n_edges] */
+} orlg_gsnr_params;
+
+int orlg_gsnr_configure(orlg_engine* e, const orlg_gsnr_params* params);
+
+/* For every env: dev_query int32[num_envs][4] = (path | core << 16, first_slot, n_slots,
+ * spectral efficiency of the candidate's modulation or 0 = the path's best modulation) of a
+ * candidate lightpath for the pending request (not provisioned).  dev_out f64[num_envs][2]:
+ *   [0] GSNR in dB of the candidate given the env's running services;
+ *   [1] the lowest GSNR in dB among its neighbours - running services that share a link (and
+ *       core) with the candidate - re-evaluated with the candidate present; +inf if none.
+ * A query with path < 0 or path >= k_paths yields NaN in both. */
+int orlg_gsnr(orlg_engine* e, const int32_t* dev_query, double* dev_out, void* stream);
+
 /* kernels launched by this engine so far (bench.py "gpu_launches") */
 int64_t orlg_launch_count(const orlg_engine* e);
 

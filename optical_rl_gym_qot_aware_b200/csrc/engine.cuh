@@ -45,6 +45,9 @@ struct Params {
   int planes, rec_u4, episode_length, allow_rejection, auto_reset, request_source;
   int n_bit_rates, br_lo, br_hi, heap_cap, heap_stride, action_dim;
   double cw, mean_iat, mean_holding;
+  int cw_x2;                 // 2*channel_width when that is a small integer (12.5 GHz -> 25), else 0
+  const double* obs_pos;     // [S+1]  2*(x - 0.5*S)/S   (deeprmsa_env.py:85-87,101)
+  const double* obs_slots;   // [S+2]  (n - 5.5)/3.5     (deeprmsa_env.py:97)
   unsigned long long seed;
   long long genv0;
   const uint4* path_rec;  // [N*N*k][rec_u4]: byte0 hops, 1 se, 2 best modulation, 3.. link index per hop
@@ -151,9 +154,15 @@ struct Tile {
   }
 };
 
-// get_number_slots: ceil(bit_rate / (SE * channel_width)) + 1, f64 like Python
-__device__ __forceinline__ int number_slots(int bit_rate, int se, double cw) {
-  return (int)ceil((double)bit_rate / ((double)se * cw)) + 1;
+// get_number_slots: ceil(bit_rate / (SE * channel_width)) + 1.  Python evaluates it in f64; when
+// 2*channel_width is a small integer the quotient's distance to the next integer is >= 1/(2cw*SE),
+// far above an ulp, so the integer form ceil(2*br / (2cw*SE)) is exactly the same number.
+__device__ __forceinline__ int number_slots(int bit_rate, int se, const Params& p) {
+  if (p.cw_x2 > 0) {
+    int d = p.cw_x2 * se;
+    return (2 * bit_rate + d - 1) / d + 1;
+  }
+  return (int)ceil((double)bit_rate / ((double)se * p.cw)) + 1;
 }
 
 // first start in [0, S - n) with n free slots (exclusive bound: SURVEY.md F8), -1 if none

@@ -8,11 +8,18 @@ constexpr int HEAP_D = 8;    // 8-ary implicit min-heap keyed by release time: o
 constexpr int HEAP_PAD = 7;  // logical index i lives in slot i+7 -> the children of i are slots 8i+8..8i+15 (line aligned)
 constexpr int HEAP_TAIL = 8; // slack after the last entry so that a whole child group can be read unconditionally
 
-// payload of a heap entry: what _release_path needs (rmsa_env.py:515-535)
-__device__ __forceinline__ unsigned long long pack_service(int pair, int path, int core, int start, int n) {
+// payload of a heap entry: what _release_path needs (rmsa_env.py:515-535) plus the spectral
+// efficiency of the service's modulation (the GN model's per-interferer correction needs it)
+__device__ __forceinline__ unsigned long long pack_service(int pair, int path, int core, int start, int n, int se) {
   return (unsigned long long)pair | ((unsigned long long)path << 16) | ((unsigned long long)core << 24) |
-         ((unsigned long long)start << 32) | ((unsigned long long)n << 48);
+         ((unsigned long long)start << 32) | ((unsigned long long)n << 48) | ((unsigned long long)(se & 15) << 58);
 }
+__device__ __forceinline__ int svc_pair(unsigned long long s) { return (int)(s & 0xFFFF); }
+__device__ __forceinline__ int svc_path(unsigned long long s) { return (int)((s >> 16) & 0xFF); }
+__device__ __forceinline__ int svc_core(unsigned long long s) { return (int)((s >> 24) & 0xFF); }
+__device__ __forceinline__ int svc_start(unsigned long long s) { return (int)((s >> 32) & 0xFFFF); }
+__device__ __forceinline__ int svc_slots(unsigned long long s) { return (int)((s >> 48) & 0x3FF); }
+__device__ __forceinline__ int svc_se(unsigned long long s) { return (int)((s >> 58) & 15); }
 
 template <int W, int BD>
 struct Env {
@@ -187,8 +194,8 @@ struct Env {
     cnt[CNT_EP_BR_REQ] += bit_rate;
     while (next_rel <= now) {  // rmsa_env.py:689-695
       unsigned long long s = heap_pop();
-      PathRec rec = load_path(p, (int)(s & 0xFFFF), (int)((s >> 16) & 0xFF));
-      tile.set_range(rec, (int)((s >> 24) & 0xFF), (int)((s >> 32) & 0xFFFF), (int)(s >> 48));
+      PathRec rec = load_path(p, svc_pair(s), svc_path(s));
+      tile.set_range(rec, svc_core(s), svc_start(s), svc_slots(s));
     }
   }
   __device__ __forceinline__ void next_service() { commit_request(draw_request()); }
@@ -215,13 +222,13 @@ struct Env {
   }
 
   // _provision_path + _add_release (state and counters only)
-  __device__ __forceinline__ void provision(const PathRec& rec, int path, int core, int start, int n) {
+  __device__ __forceinline__ void provision(const PathRec& rec, int path, int core, int start, int n, int se) {
     tile.clear_range(rec, core, start, n);
     cnt[CNT_ACC]++;
     cnt[CNT_EP_ACC]++;
     cnt[CNT_BR_PROV] += bit_rate;
     cnt[CNT_EP_BR_PROV] += bit_rate;
-    heap_push(now + holding, pack_service(pair(), path, core, start, n));
+    heap_push(now + holding, pack_service(pair(), path, core, start, n, se));
   }
 
   // _crosstalk_is_acceptable rmcsa_env.py:341-384 (modulation-only factors precomputed on host)

@@ -33,11 +33,11 @@ __device__ __forceinline__ Decision rmsa_decide(Env<W, BD>& env, int path, int s
   if (path >= 0 && slot >= 0 && path < p.k && slot < p.S) {
     PathRec rec = load_path(p, env.pair(), path);
     if (rec.hops() > 0) {
-      int n = number_slots(env.bit_rate, rec.se(), p.cw);
+      int n = number_slots(env.bit_rate, rec.se(), p);
       if (slot + n <= p.S) {
         Row<W> a = env.tile.path_avail(rec, 0);
         if (range_is_free<W>(a, slot, n)) {
-          env.provision(rec, path, 0, slot, n);
+          env.provision(rec, path, 0, slot, n, rec.se());
           d = Decision{1, path, 0, slot, n};
         }
       }
@@ -55,12 +55,12 @@ __device__ __forceinline__ Decision deeprmsa_decide(Env<W, BD>& env, int act) {
     int route = act / p.j, block = act % p.j;
     PathRec rec = load_path(p, env.pair(), route);
     if (rec.hops() > 0) {
-      int n = number_slots(env.bit_rate, rec.se(), p.cw);
+      int n = number_slots(env.bit_rate, rec.se(), p);
       Row<W> a = env.tile.path_avail(rec, 0);
       int start = -1;
       for_each_block<W>(a, n, block + 1, [&](int b, int s, int) { if (b == block) start = s; });
       if (start >= 0) {  // a block of >= n free slots: is_path_free holds by construction
-        env.provision(rec, route, 0, start, n);
+        env.provision(rec, route, 0, start, n, rec.se());
         d = Decision{1, route, 0, start, n};
       }
     }
@@ -78,12 +78,12 @@ __device__ __forceinline__ Decision rmcsa_decide(Env<W, BD>& env, int path, int 
     int pr = env.pair();
     PathRec rec = load_path(p, pr, path);
     if (rec.hops() > 0) {
-      int n = number_slots(env.bit_rate, __ldg(p.mod_se + mod), p.cw);
+      int n = number_slots(env.bit_rate, __ldg(p.mod_se + mod), p);
       if (slot + n <= p.S) {
         Row<W> a = env.tile.path_avail(rec, core);
         if (range_is_free<W>(a, slot, n) &&
             env.crosstalk_ok(mod, __ldg(p.path_length + (size_t)pr * p.k + path))) {
-          env.provision(rec, path, core, slot, n);
+          env.provision(rec, path, core, slot, n, __ldg(p.mod_se + mod));
           d = Decision{1, path, core, slot, n};
         }
       }
@@ -105,7 +105,7 @@ __device__ __forceinline__ void heuristic_action(Env<W, BD>& env, int hid, int* 
     for (int path = 0; path < npaths; path++) {
       PathRec rec = load_path(p, pr, path);
       if (rec.hops() <= 0) continue;
-      int n = number_slots(env.bit_rate, rec.se(), p.cw);
+      int n = number_slots(env.bit_rate, rec.se(), p);
       Row<W> av = env.tile.path_avail(rec, 0);
       int s = first_fit<W>(av, n, p.S);
       if (s < 0) continue;
@@ -132,7 +132,7 @@ __device__ __forceinline__ void heuristic_action(Env<W, BD>& env, int hid, int* 
     for (int path = 0; path < npaths; path++) {  // deeprmsa_env.py:138-155
       PathRec rec = load_path(p, pr, path);
       if (rec.hops() <= 0) continue;
-      int n = number_slots(env.bit_rate, rec.se(), p.cw);
+      int n = number_slots(env.bit_rate, rec.se(), p);
       Row<W> av = env.tile.path_avail(rec, 0);
       Row<W> b = window_starts<W>(av, n);
       if (lowest_set<W>(b) >= 0) {
@@ -149,7 +149,7 @@ __device__ __forceinline__ void heuristic_action(Env<W, BD>& env, int hid, int* 
       PathRec rec = load_path(p, pr, path);
       int mod = rec.best_mod();
       if (rec.hops() <= 0 || mod >= p.n_mods) continue;
-      int n = number_slots(env.bit_rate, __ldg(p.mod_se + mod), p.cw);
+      int n = number_slots(env.bit_rate, __ldg(p.mod_se + mod), p);
       for (int core = 0; core < p.cores; core++) {
         Row<W> av = env.tile.path_avail(rec, core);
         int s = first_fit<W>(av, n, p.S);
@@ -179,7 +179,6 @@ __device__ __forceinline__ void write_deeprmsa_obs(Env<W, BD>& env, OUT* o, long
   }
   int pr = env.pair();
   const int rowlen = 2 * j + 3;
-  const double dS = (double)S;
   for (int path = 0; path < p.k; path++) {
     OUT* row = o + (long long)(1 + 2 * N + path * rowlen) * fs;
     PathRec rec = load_path(p, pr, path);
@@ -187,20 +186,20 @@ __device__ __forceinline__ void write_deeprmsa_obs(Env<W, BD>& env, OUT* o, long
       for (int i = 0; i < rowlen; i++) row[i * fs] = (OUT)-1.0;
       continue;
     }
-    int n = number_slots(env.bit_rate, rec.se(), p.cw);
+    int n = number_slots(env.bit_rate, rec.se(), p);
     Row<W> av = env.tile.path_avail(rec, 0);
     int nb = for_each_block<W>(av, n, j, [&](int b, int s, int len) {
-      row[(2 * b) * fs] = (OUT)(2.0 * ((double)s - 0.5 * dS) / dS);
-      row[(2 * b + 1) * fs] = (OUT)(((double)len - 8.0) / 8.0);
+      row[(2 * b) * fs] = (OUT)__ldg(p.obs_pos + s);
+      row[(2 * b + 1) * fs] = (OUT)(((double)len - 8.0) * 0.125);  // == /8 exactly
     });
     for (int b = nb; b < j; b++) {
       row[(2 * b) * fs] = (OUT)-1.0;
       row[(2 * b + 1) * fs] = (OUT)-1.0;
     }
-    row[(2 * j) * fs] = (OUT)(((double)n - 5.5) / 3.5);
+    row[(2 * j) * fs] = (OUT)(n <= S + 1 ? __ldg(p.obs_slots + n) : ((double)n - 5.5) / 3.5);
     int tot = popcount<W>(av), runs = count_runs<W>(av);
-    row[(2 * j + 1) * fs] = (OUT)(2.0 * ((double)tot - 0.5 * dS) / dS);
-    row[(2 * j + 2) * fs] = (OUT)(runs > 0 ? ((double)tot / (double)runs - 4.0) / 4.0 : -1.0);
+    row[(2 * j + 1) * fs] = (OUT)__ldg(p.obs_pos + tot);
+    row[(2 * j + 2) * fs] = (OUT)(runs > 0 ? ((double)tot / (double)runs - 4.0) * 0.25 : -1.0);  // == /4 exactly
   }
 }
 

@@ -11,6 +11,7 @@
 
 #include "engine_launch.cuh"
 #include "engine_util.cuh"
+#include "gsnr.cuh"
 
 using namespace orlg;
 
@@ -32,6 +33,8 @@ struct orlg_engine {
   int* d_alloc = nullptr;
   size_t obs_elem = 0;
   long long obs_es = 0, obs_fs = 1;  // 0 = row-major default
+  GsnrParams gp{};
+  bool gsnr_ready = false;
 };
 
 static thread_local std::string g_create_error;
@@ -159,6 +162,10 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   p.br_hi = c->bit_rate_hi;
   p.action_dim = c->env_kind == ORLG_ENV_RMSA ? 2 : c->env_kind == ORLG_ENV_DEEPRMSA ? 1 : 4;
   p.cw = c->channel_width;
+  {
+    double x2 = 2.0 * c->channel_width;
+    p.cw_x2 = (x2 >= 1.0 && x2 <= 4096.0 && x2 == std::floor(x2)) ? (int)x2 : 0;
+  }
   p.mean_iat = c->mean_iat;
   p.mean_holding = c->mean_holding;
   p.seed = c->seed;
@@ -238,6 +245,14 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   if (c->src_cum && (rc = dev_upload(e, &p.src_cum, c->src_cum, c->n_nodes))) return fail_create(e, rc, e->err);
   if (c->dst_cum && (rc = dev_upload(e, &p.dst_cum, c->dst_cum, npairs))) return fail_create(e, rc, e->err);
 
+  {  // observation normalisation tables, f64 in the reference's operation order
+    std::vector<double> pos(p.S + 1), sl(p.S + 2);
+    const double dS = (double)p.S;
+    for (int x = 0; x <= p.S; x++) pos[x] = 2.0 * ((double)x - 0.5 * dS) / dS;
+    for (int n = 0; n <= p.S + 1; n++) sl[n] = ((double)n - 5.5) / 3.5;
+    if ((rc = dev_upload(e, &p.obs_pos, pos.data(), pos.size()))) return fail_create(e, rc, e->err);
+    if ((rc = dev_upload(e, &p.obs_slots, sl.data(), sl.size()))) return fail_create(e, rc, e->err);
+  }
   const size_t NP = p.NP;
   if ((rc = dev_alloc(e, &p.occ, (size_t)p.planes * NP)) || (rc = dev_alloc(e, &p.now, NP)) ||
       (rc = dev_alloc(e, &p.holding, NP)) || (rc = dev_alloc(e, &p.meta, NP)) ||
@@ -415,5 +430,45 @@ extern "C" int orlg_step_host(orlg_engine* e, const int32_t* h_actions, int32_t*
   if (h_obs && e->d_obs)
     CK(cudaMemcpyAsync(h_obs, e->d_obs, n * e->obs_dim * e->obs_elem, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
+  return ORLG_OK;
+}
+
+extern "C" int orlg_gsnr_configure(orlg_engine* e, const orlg_gsnr_params* g) {
+  if (!e || !g || !g->span_count || !g->span_length_km) return ORLG_EINVAL;
+  if (!(g->launch_power_w > 0) || !(g->attenuation_per_m > 0) || !(g->noise_figure_lin > 0) || !(g->slot_hz > 0) ||
+      !(g->f0_hz > 0)) {
+    e->err = "gsnr parameters must be positive";
+    return ORLG_EINVAL;
+  }
+  for (int l = 0; l < e->p.E; l++)
+    if (g->span_count[l] < 1 || !(g->span_length_km[l] > 0)) {
+      e->err = "span_count >= 1 and span_length_km > 0 required for every link";
+      return ORLG_EINVAL;
+    }
+  cudaSetDevice(e->device);
+  int rc;
+  if ((rc = dev_upload(e, &e->gp.span_count, g->span_count, (size_t)e->p.E))) return rc;
+  if ((rc = dev_upload(e, &e->gp.span_km, g->span_length_km, (size_t)e->p.E))) return rc;
+  e->gp.P = g->launch_power_w;
+  e->gp.alpha = g->attenuation_per_m;
+  e->gp.nf = g->noise_figure_lin;
+  e->gp.f0 = g->f0_hz;
+  e->gp.slot_hz = g->slot_hz;
+  e->gsnr_ready = true;
+  return ORLG_OK;
+}
+
+extern "C" int orlg_gsnr(orlg_engine* e, const int32_t* dev_query, double* dev_out, void* stream) {
+  if (!e || !dev_query || !dev_out) return ORLG_EINVAL;
+  if (!e->gsnr_ready) {
+    e->err = "orlg_gsnr before orlg_gsnr_configure";
+    return ORLG_ESTATE;
+  }
+  cudaSetDevice(e->device);
+  const int warps_per_cta = 4;
+  gsnr_kernel<<<(e->p.num_envs + warps_per_cta - 1) / warps_per_cta, warps_per_cta * 32, 0, (cudaStream_t)stream>>>(
+      e->p, e->gp, dev_query, dev_out);
+  CK(cudaGetLastError());
+  e->launches++;
   return ORLG_OK;
 }

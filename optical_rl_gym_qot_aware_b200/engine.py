@@ -32,7 +32,7 @@ EXPORTS = (
     "orlg_action_dim", "orlg_obs_dim", "orlg_state_words", "orlg_hbm_bytes", "orlg_load_trace",
     "orlg_reset", "orlg_step", "orlg_step_host", "orlg_set_obs_layout", "orlg_observation",
     "orlg_heuristic", "orlg_rollout", "orlg_get_counters", "orlg_export_state", "orlg_get_requests",
-    "orlg_launch_count",
+    "orlg_launch_count", "orlg_gsnr_configure", "orlg_gsnr",
 )
 
 
@@ -55,6 +55,12 @@ class OrlgConfig(C.Structure):
         ("src_cum", C.c_void_p), ("dst_cum", C.c_void_p),
         ("heap_capacity", C.c_int32), ("obs_kind", C.c_int32), ("reserved", C.c_int32 * 6),
     ]
+
+
+class OrlgGsnrParams(C.Structure):
+    _fields_ = [("launch_power_w", C.c_double), ("attenuation_per_m", C.c_double), ("noise_figure_lin", C.c_double),
+                ("f0_hz", C.c_double), ("slot_hz", C.c_double), ("span_count", C.c_void_p),
+                ("span_length_km", C.c_void_p)]
 
 
 _lib = None
@@ -92,6 +98,8 @@ def load_library():
         L.orlg_get_counters.argtypes = [vp, vp, vp]
         L.orlg_export_state.argtypes = [vp, vp, vp]
         L.orlg_get_requests.argtypes = [vp, vp, vp]
+        L.orlg_gsnr_configure.argtypes = [vp, C.POINTER(OrlgGsnrParams)]
+        L.orlg_gsnr.argtypes = [vp, vp, vp, vp]
         _lib = L
     return _lib
 
@@ -244,6 +252,27 @@ class Engine:
         out = self.torch.empty((self.num_envs, REQUEST_DTYPE.itemsize), dtype=self.torch.uint8, device=self.device)
         self._ck(self.L.orlg_get_requests(self.h, self._p(out), self._stream()))
         return out.cpu().numpy().view(REQUEST_DTYPE).reshape(self.num_envs)
+
+    def gsnr_configure(self, gp=None):
+        """gp: spec.GsnrParams (default: spec.gsnr_params(tables, channel_width))."""
+        if gp is None:
+            gp = S.gsnr_params(self.spec.tables, self.spec.channel_width)
+        cnt = np.ascontiguousarray(gp.span_count, np.int32)
+        ln = np.ascontiguousarray(gp.span_length_km, np.float64)
+        c = OrlgGsnrParams(gp.launch_power_w, gp.attenuation_per_m, gp.noise_figure_lin, gp.f0_hz, gp.slot_hz,
+                           cnt.ctypes.data, ln.ctypes.data)
+        self._ck(self.L.orlg_gsnr_configure(self.h, C.byref(c)))
+        self.gsnr_params = gp
+
+    def gsnr(self, query, out=None):
+        """query: int32 [num_envs, 4] device tensor (path | core << 16, first_slot, n_slots, se or 0).
+        Returns f64 [num_envs, 2]: candidate GSNR dB, lowest neighbour GSNR dB."""
+        torch = self.torch
+        assert query.dtype == torch.int32 and query.is_cuda and query.is_contiguous()
+        if out is None:
+            out = torch.empty((self.num_envs, 2), dtype=torch.float64, device=self.device)
+        self._ck(self.L.orlg_gsnr(self.h, self._p(query), self._p(out), self._stream()))
+        return out
 
     @property
     def launch_count(self):

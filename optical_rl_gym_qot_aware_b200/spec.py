@@ -208,3 +208,43 @@ def make_spec(
     spec.obs_kind = obs_kind
     assert spec.num_slots <= 1024 and tables.n_edges <= 128
     return spec
+
+
+@dataclass
+class GsnrParams:
+    """Physical inputs of the GN-model GSNR (examples/calculate_osnr.py:9-56).  The reference
+    leaves them undefined; they are fixed here once:
+
+    * spans: ``int(length // max_span_km) + 1`` equal spans per link, 0.2 dB/km, NF 4.5 dB
+      (examples/create_topology_gn.py:26-29,122-134);
+    * ``attenuation_normalized`` alpha [1/m] = a_dB/km / (20 log10 e) / 1e3, consistent with the
+      power loss ``exp(-2 alpha L)`` of calculate_osnr.py:25,51;
+    * ``noise_figure_normalized`` = 10**(NF_dB/10);  launch power 0 dBm per channel;
+    * bandwidth = slots x 12.5 GHz, centre frequency = f0 + (first_slot + slots/2) x 12.5 GHz with
+      f0 = 191.35 THz (lower edge of a 4 THz C band).
+    """
+    launch_power_w: float
+    attenuation_per_m: float
+    noise_figure_lin: float
+    f0_hz: float
+    slot_hz: float
+    span_count: np.ndarray  # [E] int32
+    span_length_km: np.ndarray  # [E] f64
+
+
+def gsnr_params(tables: TopologyTables, channel_width: float = 12.5, launch_power_dbm: float = 0.0,
+                attenuation_db_km: float = 0.2, noise_figure_db: float = 4.5, max_span_km: float = 80.0,
+                f0_hz: float = 191.35e12) -> GsnrParams:
+    import math
+
+    count = np.array([int(float(x) // max_span_km) + 1 for x in tables.edge_length], np.int32)
+    length = np.array([float(x) / int(c) for x, c in zip(tables.edge_length, count)], np.float64)
+    return GsnrParams(
+        launch_power_w=1e-3 * 10 ** (launch_power_dbm / 10.0),
+        attenuation_per_m=attenuation_db_km / (20.0 * math.log10(math.e)) / 1e3,
+        noise_figure_lin=10 ** (noise_figure_db / 10.0),
+        f0_hz=float(f0_hz),
+        slot_hz=float(channel_width) * 1e9,
+        span_count=count,
+        span_length_km=length,
+    )

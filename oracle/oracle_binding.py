@@ -66,6 +66,12 @@ class OracleConfig(C.Structure):
     ]
 
 
+class OracleGsnrParams(C.Structure):
+    _fields_ = [("launch_power_w", C.c_double), ("attenuation_per_m", C.c_double), ("noise_figure_lin", C.c_double),
+                ("f0_hz", C.c_double), ("slot_hz", C.c_double), ("span_count", C.c_void_p),
+                ("span_length_km", C.c_void_p)]
+
+
 _lib = None
 
 
@@ -102,6 +108,9 @@ def lib():
         L.oracle_pool_env.argtypes = [C.c_void_p, C.c_int64]
         L.oracle_pool_reward_sum.restype = C.c_int64
         L.oracle_pool_reward_sum.argtypes = [C.c_void_p]
+        L.oracle_gsnr.argtypes = [C.c_void_p, C.POINTER(OracleGsnrParams), C.c_void_p, C.c_void_p]
+        L.oracle_services.restype = C.c_int64
+        L.oracle_services.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
         L.oracle_dlog.restype = C.c_double
         L.oracle_dlog.argtypes = [C.c_double]
         L.oracle_philox4x32.argtypes = [C.c_uint32] * 6 + [C.c_void_p]
@@ -222,6 +231,24 @@ class OracleEnv:
         o = np.zeros(1, REQUEST_DTYPE)
         self.L.oracle_request_now(self.h, o.ctypes.data)
         return o[0]
+
+    def gsnr(self, gp, query):
+        """gp: spec.GsnrParams; query: 4 ints.  Returns (candidate dB, min neighbour dB)."""
+        cnt = np.ascontiguousarray(gp.span_count, np.int32)
+        ln = np.ascontiguousarray(gp.span_length_km, np.float64)
+        c = OracleGsnrParams(gp.launch_power_w, gp.attenuation_per_m, gp.noise_figure_lin, gp.f0_hz, gp.slot_hz,
+                             cnt.ctypes.data, ln.ctypes.data)
+        q = np.ascontiguousarray(query, np.int32)
+        out = np.zeros(2, np.float64)
+        self.L.oracle_gsnr(self.h, C.byref(c), q.ctypes.data, out.ctypes.data)
+        return out
+
+    def services(self):
+        """Live services: rows (pair, path, core, initial_slot, number_slots, se)."""
+        n = int(self.L.oracle_services(self.h, None, 0))
+        out = np.zeros((max(n, 1), 6), np.int32)
+        self.L.oracle_services(self.h, out.ctypes.data, n)
+        return out[:n]
 
     def close(self):
         if self.h:

@@ -116,6 +116,7 @@ void oracle_philox_request(const oracle_config* c, int64_t genv, int64_t r, doub
 typedef struct svc { /* a provisioned Service (utils.py:56-80), what release needs */
   double release_time;
   int32_t pair, path, core, initial_slot, number_slots;
+  int32_t se; /* current_modulation.spectral_efficiency */
 } svc;
 
 struct oracle_env {
@@ -386,7 +387,8 @@ static int rmsa_decide(oracle_env* e, int path, int slot, int32_t* alloc) {
     if (is_path_free(e, pair, path, 0, slot, n)) {
       provision_path(e, pair, path, 0, slot, n);
       accepted = 1;
-      svc s = {e->cur.arrival + e->cur.holding, pair, path, 0, slot, n};
+      svc s = {e->cur.arrival + e->cur.holding, pair, path, 0, slot, n,
+               e->c.path_se[(size_t)pair * e->c.k_paths + path]};
       heap_push(e, s); /* _add_release */
     }
   }
@@ -428,7 +430,7 @@ void oracle_step(oracle_env* e, const int32_t* a, int32_t* reward, uint8_t* done
           crosstalk_ok(e, mod, e->c.path_length[(size_t)pair * k + path])) {
         provision_path(e, pair, path, core, slot, n);
         accepted = 1;
-        svc s = {e->cur.arrival + e->cur.holding, pair, path, core, slot, n};
+        svc s = {e->cur.arrival + e->cur.holding, pair, path, core, slot, n, e->c.mod_se[mod]};
         heap_push(e, s);
       }
     }
@@ -704,3 +706,136 @@ int64_t oracle_pool_rollout(oracle_pool* p, int nsteps, int hid, int threads) {
 
 oracle_env* oracle_pool_env(oracle_pool* p, int64_t i) { return (i >= 0 && i < p->n) ? p->envs[i] : NULL; }
 int64_t oracle_pool_reward_sum(const oracle_pool* p) { return p->reward_sum; }
+
+
+/* ---- GN-model GSNR: calculate_osnr, examples/calculate_osnr.py:9-56 ------------------
+ * Literal restatement: explicit Span objects per link (the commented-out sketch at
+ * optical_rl_gym/utils.py:38-54, built as in examples/create_topology_gn.py:122-134), a
+ * running_services list per link, one loop iteration per span.  Parity: the reference
+ * function is not importable as shipped; tests/golden/gsnr_*.npz were made by
+ * calling the UNMODIFIED function body through oracle/refharness/gen_gsnr_golden.py, which
+ * injects the missing Span/Link classes into optical_rl_gym.utils before the import. */
+typedef struct gn_span { double length, attenuation_normalized, noise_figure_normalized; } gn_span;
+typedef struct gn_service { int id; double bandwidth, center_frequency, launch_power; int se; } gn_service;
+
+static double gn_calculate_osnr(const gn_service* cur, int n_links, const gn_span* const* spans,
+                                const int* n_spans, const gn_service* const* running, const int* n_running) {
+  const double pi = 3.141592653589793;
+  double beta_2 = -21.3e-27, gamma = 1.3e-3, h_plank = 6.626e-34; /* :10-12 */
+  double acc_gsnr = 0, l_eff_a, l_eff, phi, sum_phi, power_ase, power_nli_span;
+  const double phi_modulation_format[6] = {1, 1, 2.0 / 3, 17.0 / 25, 69.0 / 100, 13.0 / 21}; /* :20 */
+  for (int li = 0; li < n_links; li++) {           /* for link in current_service.path.links */
+    for (int si = 0; si < n_spans[li]; si++) {     /* for span in ...["link"].spans */
+      const gn_span* span = &spans[li][si];
+      l_eff_a = 1 / (2 * span->attenuation_normalized);
+      l_eff = (1 - exp(-2 * span->attenuation_normalized * span->length * 1e3)) / (2 * span->attenuation_normalized);
+      sum_phi = asinh(pi * pi * fabs(beta_2) * (cur->bandwidth * cur->bandwidth) / (4 * span->attenuation_normalized));
+      for (int ri = 0; ri < n_running[li]; ri++) { /* for service in ...["running_services"] */
+        const gn_service* sv = &running[li][ri];
+        if (sv->id != cur->id) {
+          phi = (asinh(pi * pi * fabs(beta_2) * l_eff_a * sv->bandwidth *
+                       (sv->center_frequency - cur->center_frequency + (sv->bandwidth / 2))) -
+                 asinh(pi * pi * fabs(beta_2) * l_eff_a * sv->bandwidth *
+                       (sv->center_frequency - cur->center_frequency - (sv->bandwidth / 2)))) -
+                (phi_modulation_format[sv->se - 1] *
+                 (sv->bandwidth / fabs(sv->center_frequency - cur->center_frequency)) * 5 / 3 *
+                 (l_eff / (span->length * 1e3)));
+          sum_phi += phi; /* applied to other services only, see the header of csrc/gsnr.cuh */
+        }
+      }
+      power_nli_span = pow(cur->launch_power / cur->bandwidth, 3) * (8 / (27 * pi * fabs(beta_2))) *
+                       (gamma * gamma) * l_eff * sum_phi * cur->bandwidth;
+      power_ase = cur->bandwidth * h_plank * cur->center_frequency *
+                  (exp(2 * span->attenuation_normalized * span->length * 1e3) - 1) * span->noise_figure_normalized;
+      acc_gsnr += 1 / (cur->launch_power / (power_ase + power_nli_span));
+    }
+  }
+  return 10 * log10(1 / acc_gsnr);
+}
+
+static gn_service gn_service_of(const oracle_gsnr_params* g, int id, int start, int n, int se) {
+  gn_service s;
+  s.id = id;
+  s.bandwidth = (double)n * g->slot_hz;
+  s.center_frequency = g->f0_hz + ((double)start + 0.5 * (double)n) * g->slot_hz;
+  s.launch_power = g->launch_power_w;
+  s.se = se;
+  return s;
+}
+
+static int path_uses(const oracle_env* e, int pair, int path, int link) {
+  const int16_t* L = links_of(e, pair, path, 0);
+  for (int h = 0; h < hops_of(e, pair, path); h++) if (L[h] == link) return 1;
+  return 0;
+}
+
+/* GSNR of `target` (id tid; tid = -1: the candidate) on its path, with running_services per
+ * link = the env's live services on that link and core (+ the candidate when add_cand). */
+static double gsnr_of(const oracle_env* e, const oracle_gsnr_params* g, int tpair, int tpath, int tcore,
+                      const gn_service* target, int add_cand, int cpair, int cpath, int ccore,
+                      const gn_service* cand) {
+  int hops = hops_of(e, tpair, tpath);
+  const int16_t* L = links_of(e, tpair, tpath, 0);
+  gn_span** spans = (gn_span**)calloc(hops, sizeof(gn_span*));
+  gn_service** running = (gn_service**)calloc(hops, sizeof(gn_service*));
+  int* n_spans = (int*)calloc(hops, sizeof(int));
+  int* n_running = (int*)calloc(hops, sizeof(int));
+  for (int h = 0; h < hops; h++) {
+    int l = L[h];
+    n_spans[h] = g->span_count[l];
+    spans[h] = (gn_span*)malloc(sizeof(gn_span) * n_spans[h]);
+    for (int s = 0; s < n_spans[h]; s++) {
+      spans[h][s].length = g->span_length_km[l];
+      spans[h][s].attenuation_normalized = g->attenuation_per_m;
+      spans[h][s].noise_figure_normalized = g->noise_figure_lin;
+    }
+    running[h] = (gn_service*)malloc(sizeof(gn_service) * (e->heap_len + 1));
+    for (int64_t i = 0; i < e->heap_len; i++) {
+      const svc* s = &e->heap[i];
+      if (s->core == tcore && path_uses(e, s->pair, s->path, l))
+        running[h][n_running[h]++] = gn_service_of(g, (int)i, s->initial_slot, s->number_slots, s->se);
+    }
+    if (add_cand && ccore == tcore && path_uses(e, cpair, cpath, l)) running[h][n_running[h]++] = *cand;
+  }
+  double v = gn_calculate_osnr(target, hops, (const gn_span* const*)spans, n_spans,
+                               (const gn_service* const*)running, n_running);
+  for (int h = 0; h < hops; h++) { free(spans[h]); free(running[h]); }
+  free(spans); free(running); free(n_spans); free(n_running);
+  return v;
+}
+
+void oracle_gsnr(const oracle_env* e, const oracle_gsnr_params* g, const int32_t* query, double* out2) {
+  int path = query[0] & 0xFFFF, core = query[0] >> 16, start = query[1], n = query[2];
+  int pair = cur_pair(e);
+  out2[0] = out2[1] = NAN;
+  if (query[0] < 0 || path >= e->c.k_paths || core >= e->c.num_cores || start < 0 || n < 1 ||
+      start + n > e->c.num_slots || hops_of(e, pair, path) <= 0)
+    return;
+  int se = query[3] > 0 ? query[3] : e->c.path_se[(size_t)pair * e->c.k_paths + path];
+  gn_service cand = gn_service_of(g, -1, start, n, se);
+  out2[0] = gsnr_of(e, g, pair, path, core, &cand, 0, pair, path, core, &cand);
+  double mn = INFINITY;
+  const int16_t* CL = links_of(e, pair, path, 0);
+  for (int64_t i = 0; i < e->heap_len; i++) {
+    const svc* s = &e->heap[i];
+    if (s->core != core) continue;
+    int shares = 0;
+    for (int h = 0; h < hops_of(e, pair, path); h++) shares |= path_uses(e, s->pair, s->path, CL[h]);
+    if (!shares) continue;
+    gn_service t = gn_service_of(g, (int)i, s->initial_slot, s->number_slots, s->se);
+    double v = gsnr_of(e, g, s->pair, s->path, s->core, &t, 1, pair, path, core, &cand);
+    if (v < mn) mn = v;
+  }
+  out2[1] = mn;
+}
+
+/* live services of the env: rows of (pair, path, core, initial_slot, number_slots, se) */
+int64_t oracle_services(const oracle_env* e, int32_t* out6, int64_t max_rows) {
+  int64_t n = e->heap_len < max_rows ? e->heap_len : max_rows;
+  for (int64_t i = 0; i < n; i++) {
+    const svc* s = &e->heap[i];
+    int32_t* o = out6 + 6 * i;
+    o[0] = s->pair; o[1] = s->path; o[2] = s->core; o[3] = s->initial_slot; o[4] = s->number_slots; o[5] = s->se;
+  }
+  return e->heap_len;
+}

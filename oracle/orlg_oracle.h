@@ -83,6 +83,16 @@ int64_t oracle_rollout_many(const oracle_config* cfg, int64_t env0, int64_t n_en
                             uint8_t* state_out /* [n_envs][cores*E*S] or NULL */,
                             int64_t* reward_sum_out /* [n_envs] or NULL */);
 
+/* GN-model GSNR (examples/calculate_osnr.py:9-56); same parameter block as orlg_gsnr_params */
+typedef struct oracle_gsnr_params {
+  double launch_power_w, attenuation_per_m, noise_figure_lin, f0_hz, slot_hz;
+  const int32_t* span_count;
+  const double* span_length_km;
+} oracle_gsnr_params;
+/* query[4] = (path | core << 16, first_slot, n_slots, se or 0); out2 = (candidate dB, min neighbour dB) */
+void oracle_gsnr(const oracle_env* e, const oracle_gsnr_params* g, const int32_t* query, double* out2);
+int64_t oracle_services(const oracle_env* e, int32_t* out6, int64_t max_rows);
+
 /* persistent pool of envs stepped with a heuristic on host threads (the envs keep
  * their state between calls); the timed CPU arm of bench.py */
 typedef struct oracle_pool oracle_pool;

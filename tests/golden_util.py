@@ -17,7 +17,9 @@ TOPO_SHORT = {
     "germany50_5-paths_6-modulations.h5": "germany50",
 }
 
-CASES = sorted(f[:-4] for f in os.listdir(GOLDEN) if f.endswith(".npz") and not f.startswith("topology_"))
+CASES = sorted(f[:-4] for f in os.listdir(GOLDEN)
+               if f.endswith(".npz") and not f.startswith(("topology_", "gsnr_", "phy_")))
+GSNR_CASES = sorted(f[:-4] for f in os.listdir(GOLDEN) if f.startswith("gsnr_") and f.endswith(".npz"))
 ENV_NAME = {0: "RMSA-v0", 1: "DeepRMSA-v0", 2: "RMCSA-v0"}
 
 
