@@ -27,7 +27,6 @@ from __future__ import annotations
 import argparse
 import json
 import os
-import subprocess
 import sys
 import threading
 import time
@@ -93,68 +92,78 @@ def measured_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
-
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
-         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons sampled every 5 ms during the timed region (NVML; the
+    nvidia-smi -lms loop of the recipe starts too slowly for a sub-second region)."""
 
     def __init__(self, index):
-        self.index = index
-        self.lines = []
-        self.proc = None
+        self.index, self.sm, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop = threading.Event()
+        self.thread = None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._pump, daemon=True)
-            self.thread.start()
-        except Exception:
-            self.proc = None
+            import pynvml as N
 
-    def _pump(self):
-        for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            N.nvmlInit()
+            # NVML enumerates all GPUs of the box; honour CUDA_VISIBLE_DEVICES if it is a plain list
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            idx = self.index
+            if vis and all(x.strip().isdigit() for x in vis.split(",")):
+                idx = int(vis.split(",")[self.index])
+            h = N.nvmlDeviceGetHandleByIndex(idx)
+            self.max_mhz = float(N.nvmlDeviceGetMaxClockInfo(h, N.NVML_CLOCK_SM))
+            bits = {"hw_slowdown": N.nvmlClocksThrottleReasonHwSlowdown,
+                    "hw_thermal_slowdown": N.nvmlClocksThrottleReasonHwThermalSlowdown,
+                    "sw_thermal_slowdown": N.nvmlClocksThrottleReasonSwThermalSlowdown,
+                    "sw_power_cap": N.nvmlClocksThrottleReasonSwPowerCap}
+
+            def pump():
+                while not self._stop.is_set():
+                    try:
+                        self.sm.append(float(N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM)))
+                        r = N.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                        for nm, bit in bits.items():
+                            if r & bit:
+                                self.reasons.add(nm)
+                    except Exception:
+                        pass
+                    time.sleep(0.005)
+
+            self.thread = threading.Thread(target=pump, daemon=True)
+            self.thread.start()
+        except Exception as ex:  # no NVML: report it instead of inventing clocks
+            self.reasons.add(f"nvml unavailable: {type(ex).__name__}")
 
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
-            f = [x.strip() for x in ln.split(",")]
-            if len(f) < 9:
-                continue
-            try:
-                sm.append(float(f[1]))
-                mx.append(float(f[2]))
-            except ValueError:
-                continue
-            for nm, v in zip(names, f[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        self._stop.set()
+        if self.thread is not None:
+            self.thread.join(timeout=2)
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.sm)}
 
 
-def host_policy_kspff(obs_fm, n_nodes, k, j):
+_KSPFF_LUT = {}
+
+
+def host_policy_kspff(obs_fm, n_nodes, k, j, out=None):
     """K-SP-FF (deeprmsa_env.py:146-155) evaluated on the host from the observation:
     path p has a fitting block iff its first block-length feature is not -1.
-    obs_fm: [obs_dim, n_env] (feature-major host buffer).  Returns int32 [n_env, 1]."""
+    obs_fm: [obs_dim, n_env] (feature-major host buffer).  Returns int32 [n_env, 1].
+    The k availability bits of an env are packed into one byte and mapped through a table."""
+    assert k <= 8
     rowlen = 2 * j + 3
     base = 1 + 2 * n_nodes
-    has = np.stack([obs_fm[base + p * rowlen + 1] != -1.0 for p in range(k)], axis=0)  # [k, n_env]
-    first = np.argmax(has, axis=0)
-    act = np.where(has.any(axis=0), first * j, k * j).astype(np.int32)
-    return act.reshape(-1, 1)
+    lut = _KSPFF_LUT.get((k, j))
+    if lut is None:
+        lut = np.array([next((p * j for p in range(k) if c >> p & 1), k * j) for c in range(1 << k)], np.int32)
+        _KSPFF_LUT[(k, j)] = lut
+    code = (obs_fm[base + 1] != -1.0).view(np.uint8).copy()
+    for p in range(1, k):
+        code |= (obs_fm[base + p * rowlen + 1] != -1.0).view(np.uint8) << p
+    if out is None:
+        return lut[code].reshape(-1, 1)
+    np.take(lut, code, out=out.reshape(-1))
+    return out
 
 
 def cpu_arm(spec, hid, n_sample, min_seconds, threads, steps=None, warmup=0):
@@ -299,9 +308,13 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
         h_obs.copy_(obs.t())
     torch.cuda.synchronize()
 
+    policy_s = [0.0]
+
     def e2e_step():
         if use_obs_policy:
-            h_act.numpy()[:] = host_policy_kspff(h_obs.numpy(), t_nodes, t_k, spec.j)
+            p0 = time.perf_counter()
+            host_policy_kspff(h_obs.numpy(), t_nodes, t_k, spec.j, out=h_act.numpy())
+            policy_s[0] += time.perf_counter() - p0
         else:  # no observation to decide from: device heuristic, actions round-trip through the host
             eng.heuristic(hid, act)
             h_act.copy_(act)
@@ -312,6 +325,7 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
     for _ in range(min(args.warmup, 5)):
         e2e_step()
     barrier()
+    policy_s[0] = 0.0
     e0.record()
     w0 = time.perf_counter()
     for t in range(Ke):
@@ -371,7 +385,8 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
             "blocking": 1.0 - stats[1] / max(1, stats[0]), "episodes": stats[4],
         },
         "e2e": {"value": total_envs * Ke / (e2e_ms * 1e-3), "unit": "env-steps/s", "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": d2h, "steps": Ke,
+                "d2h_bytes_per_step": d2h, "steps": Ke, "ms_per_step": e2e_ms / Ke,
+                "host_policy_ms_per_step": policy_s[0] * 1e3 / Ke,
                 "policy": "numpy K-SP-FF from the host observation" if use_obs_policy
                 else "device heuristic, actions D2H then H2D"},
         "gpu_launches": int(launches),
