@@ -24,6 +24,7 @@ ENV_RMSA, ENV_DEEPRMSA, ENV_RMCSA, ENV_PHYRMSA = 0, 1, 2, 3
 SRC_REPLAY, SRC_PHILOX = 0, 1
 OBS_NONE, OBS_F64, OBS_F32, OBS_MATRIX_U8 = 0, 1, 2, 3
 H_SP_FF, H_SAP_FF, H_LLP_FF, H_SAP_BM_FC_FF, H_RANDOM = 0, 1, 2, 3, 4
+H_PHY_SAP_FF, H_PHY_SAP_BM, H_PHY_BM_FF, H_PHY_BM_FA_CUT = 5, 6, 7, 8  # phy_rmsa_env.py:1676,1254,1317,1375
 
 ENV_IDS = {
     "RMSA-v0": ENV_RMSA,
@@ -69,10 +70,11 @@ class EnvSpec:
     seed: int = 41
     request_source: int = SRC_PHILOX
     obs_kind: int = OBS_NONE
+    phy: Optional[object] = None  # phy.PhyTables for PhyRMSA-v0
 
     @property
     def action_dim(self) -> int:
-        return {ENV_RMSA: 2, ENV_DEEPRMSA: 1, ENV_RMCSA: 4}.get(self.env_kind, 2)
+        return {ENV_RMSA: 2, ENV_DEEPRMSA: 1, ENV_RMCSA: 4, ENV_PHYRMSA: 9}.get(self.env_kind, 2)
 
     @property
     def obs_dim(self) -> int:
@@ -136,6 +138,17 @@ def make_spec(
     auto_reset: bool = False,
     request_source: int = SRC_PHILOX,
     obs_kind: Optional[int] = None,
+    modulation_level=None,
+    connections_detail=None,
+    gsnr=None,
+    number_spectrum_channels: int = 80,
+    number_spectrum_channels_s_band: int = 108,
+    l_band: bool = True,
+    s_band: bool = True,
+    grooming: bool = False,
+    defrag_period=None,
+    number_moves=None,
+    metric: str = "cut",
 ) -> EnvSpec:
     kind = ENV_IDS[env_id] if isinstance(env_id, str) else int(env_id)
     n = tables.n_nodes
@@ -148,6 +161,20 @@ def make_spec(
         holding = 10800.0 if mean_service_holding_time is None else mean_service_holding_time
     mean_iat = 1 / float(load / float(holding))  # optical_network_env.py:127-129
 
+    phy_tables = None
+    if kind == ENV_PHYRMSA:
+        from . import phy as P
+
+        if grooming or defrag_period:
+            raise NotImplementedError("PhyRMSA grooming / periodic defragmentation are not built yet "
+                                      "(SURVEY.md 8f N2); pass grooming=False, defrag_period=None")
+        if modulation_level is None or connections_detail is None or gsnr is None:
+            raise ValueError("PhyRMSA-v0 needs modulation_level, connections_detail and gsnr")
+        channels = P.num_channels(number_spectrum_channels, number_spectrum_channels_s_band, l_band, s_band)
+        phy_tables = P.build_phy_tables(tables, modulation_level, connections_detail, gsnr, channels)
+        num_spectrum_resources = channels  # channels take the place of slots in the engine
+        if bit_rates is None:
+            bit_rates = P.BIT_RATES
     if bit_rate_selection is None:
         bit_rate_selection = "continuous" if kind == ENV_RMCSA else "discrete"
     assert bit_rate_selection in ("continuous", "discrete")
@@ -206,6 +233,7 @@ def make_spec(
     if obs_kind is None:
         obs_kind = OBS_F64 if kind == ENV_DEEPRMSA else OBS_NONE
     spec.obs_kind = obs_kind
+    spec.phy = phy_tables
     assert spec.num_slots <= 1024 and tables.n_edges <= 128
     return spec
 

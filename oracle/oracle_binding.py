@@ -63,6 +63,13 @@ class OracleConfig(C.Structure):
         ("bit_rate_hi", C.c_int32),
         ("src_cum", C.c_void_p),
         ("dst_cum", C.c_void_p),
+        ("phy_n_tables", C.c_int32),
+        ("phy_pad", C.c_int32),
+        ("phy_table_id", C.c_void_p),
+        ("phy_mod_level", C.c_void_p),
+        ("phy_gsnr", C.c_void_p),
+        ("path_nodes", C.c_void_p),
+        ("edge_nodes", C.c_void_p),
     ]
 
 
@@ -108,6 +115,7 @@ def lib():
         L.oracle_pool_env.argtypes = [C.c_void_p, C.c_int64]
         L.oracle_pool_reward_sum.restype = C.c_int64
         L.oracle_pool_reward_sum.argtypes = [C.c_void_p]
+        L.oracle_phy_stats.argtypes = [C.c_void_p, C.c_void_p]
         L.oracle_gsnr.argtypes = [C.c_void_p, C.POINTER(OracleGsnrParams), C.c_void_p, C.c_void_p]
         L.oracle_services.restype = C.c_int64
         L.oracle_services.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
@@ -148,14 +156,22 @@ class OracleSpec:
         )
         k["src_cum"] = np.ascontiguousarray(spec.src_cum, np.float64)
         k["dst_cum"] = np.ascontiguousarray(spec.dst_cum, np.float64)
+        k["path_nodes"] = np.ascontiguousarray(t.path_nodes, np.int16)
+        k["edge_nodes"] = np.ascontiguousarray(t.edge_nodes, np.int32)
+        ph = getattr(spec, "phy", None)
+        k["phy_table_id"] = None if ph is None else np.ascontiguousarray(ph.table_id, np.int32)
+        k["phy_mod_level"] = None if ph is None else np.ascontiguousarray(ph.mod_level, np.uint8)
+        k["phy_gsnr"] = None if ph is None else np.ascontiguousarray(ph.gsnr, np.float64)
         c = self.cfg = OracleConfig()
         c.env_kind = spec.env_kind
         c.n_nodes, c.n_edges, c.k_paths, c.max_hops = t.n_nodes, t.n_edges, t.k_paths, t.max_hops
         for name in ("path_links", "path_links_by_id", "path_hops", "path_length", "path_se", "mod_se",
                      "mod_max_length", "mod_reach", "mod_snr_coeff", "bit_rates", "bit_rate_cum",
-                     "src_cum", "dst_cum"):
+                     "src_cum", "dst_cum", "path_nodes", "edge_nodes", "phy_table_id", "phy_mod_level",
+                     "phy_gsnr"):
             setattr(c, name, _ptr(k[name]))
         c.n_mods = len(t.mod_names)
+        c.phy_n_tables = 0 if ph is None else ph.n_tables
         c.num_slots, c.num_cores, c.j = spec.num_slots, spec.num_cores, spec.j
         c.episode_length = spec.episode_length
         c.allow_rejection = int(spec.allow_rejection)
@@ -211,8 +227,13 @@ class OracleEnv:
         self.L.oracle_matrix_observation(self.h, obs.ctypes.data)
         return obs
 
+    def phy_stats(self):
+        o = np.zeros(8, np.float64)
+        self.L.oracle_phy_stats(self.h, o.ctypes.data)
+        return o
+
     def heuristic(self, hid):
-        a = np.zeros(4, np.int32)
+        a = np.zeros(16, np.int32)
         self.L.oracle_heuristic(self.h, hid, a.ctypes.data)
         return a[: self.action_dim].copy()
 

@@ -117,6 +117,8 @@ typedef struct svc { /* a provisioned Service (utils.py:56-80), what release nee
   double release_time;
   int32_t pair, path, core, initial_slot, number_slots;
   int32_t se; /* current_modulation.spectral_efficiency */
+  int32_t nch;      /* PhyRMSA: service.channels */
+  int16_t ch[8];
 } svc;
 
 struct oracle_env {
@@ -131,6 +133,11 @@ struct oracle_env {
   int64_t services_processed, services_accepted, ep_processed, ep_accepted;
   int64_t br_requested, br_provisioned, ep_br_requested, ep_br_provisioned;
   int64_t requests_drawn, episodes;
+  /* PhyRMSA episode sums (phy_rmsa_env.py:431-439) */
+  double total_path_length_ep, total_gsnr_ep;
+  int64_t total_path_index_ep, total_mod_level_ep, channels_accepted_ep, physical_accepted_ep;
+  double info_cuts, info_rss; /* number_cuts_total / rss_total_metric of the last step's info (:313-314) */
+  int16_t* link_of; /* [N][N] edge index or -1 (topology[a][b]["index"]) */
   const oracle_request* trace;
   int64_t trace_len, trace_stride;
 };
@@ -146,6 +153,15 @@ oracle_env* oracle_create(const oracle_config* cfg, int64_t genv) {
   e->avail = (uint8_t*)malloc((size_t)e->c.num_cores * e->c.n_edges * e->c.num_slots);
   e->heap_cap = 64;
   e->heap = (svc*)malloc(sizeof(svc) * e->heap_cap);
+  if (e->c.env_kind == 3 && e->c.edge_nodes) {
+    int N = e->c.n_nodes;
+    e->link_of = (int16_t*)malloc(sizeof(int16_t) * N * N);
+    for (int i = 0; i < N * N; i++) e->link_of[i] = -1;
+    for (int l = 0; l < e->c.n_edges; l++) {
+      int a = e->c.edge_nodes[2 * l], b = e->c.edge_nodes[2 * l + 1];
+      e->link_of[a * N + b] = e->link_of[b * N + a] = (int16_t)l;
+    }
+  }
   return e;
 }
 
@@ -153,6 +169,7 @@ void oracle_destroy(oracle_env* e) {
   if (!e) return;
   free(e->avail);
   free(e->heap);
+  free(e->link_of);
   free(e);
 }
 
@@ -163,7 +180,7 @@ void oracle_set_trace(oracle_env* e, const oracle_request* t, int64_t n, int64_t
 }
 
 int oracle_action_dim(const oracle_env* e) {
-  return e->c.env_kind == 0 ? 2 : e->c.env_kind == 1 ? 1 : 4;
+  return e->c.env_kind == 0 ? 2 : e->c.env_kind == 1 ? 1 : e->c.env_kind == 2 ? 4 : ORACLE_PHY_ADIM;
 }
 int oracle_obs_dim(const oracle_env* e) { /* deeprmsa_env.py:35-37 */
   return 1 + 2 * e->c.n_nodes + (2 * e->c.j + 3) * e->c.k_paths;
@@ -256,6 +273,11 @@ static void provision_path(oracle_env* e, int pair, int path, int core, int star
 static void release_path(oracle_env* e, const svc* s) {
   const int16_t* L = links_of(e, s->pair, s->path, 0);
   int h = hops_of(e, s->pair, s->path);
+  if (e->c.env_kind == 3) { /* phy_rmsa_env.py:781-861 without grooming: every channel of the service is freed */
+    for (int i = 0; i < h; i++)
+      for (int c = 0; c < s->nch; c++) AV(e, 0, L[i])[s->ch[c]] = 1;
+    return;
+  }
   for (int i = 0; i < h; i++) memset(AV(e, s->core, L[i]) + s->initial_slot, 1, (size_t)s->number_slots);
 }
 
@@ -327,6 +349,8 @@ static void next_service(oracle_env* e) {
 void oracle_reset(oracle_env* e, int full) {
   e->ep_br_requested = e->ep_br_provisioned = 0;
   e->ep_processed = e->ep_accepted = 0;
+  e->total_path_length_ep = e->total_gsnr_ep = 0.0; /* phy_rmsa_env.py:431-439 */
+  e->total_path_index_ep = e->total_mod_level_ep = e->channels_accepted_ep = e->physical_accepted_ep = 0;
   if (!full) {
     if (e->new_service) { /* pending service is re-counted, rmsa_env.py:370-374 */
       e->ep_processed++;
@@ -378,6 +402,195 @@ static void finish_step(oracle_env* e, int accepted, int32_t* reward, uint8_t* d
   if (done) *done = (uint8_t)d;
 }
 
+/* ------------------------------------------------------- PhyRMSA-v0 -- */
+/* phy_rmsa_env.py, physical layer only: grooming=False, defrag_period=None
+ * (SURVEY.md 8f N2 is a later row).  Channels take the place of slots:
+ * available_channels[E][C] lives in e->avail with one core. */
+static int phy_level(const oracle_env* e, int table, int ch, int idp) {
+  return e->c.phy_mod_level[((size_t)table * e->c.num_slots + ch) * e->c.k_paths + idp];
+}
+static const int16_t* nodes_of(const oracle_env* e, int pair, int path) {
+  return e->c.path_nodes + ((size_t)pair * e->c.k_paths + path) * (e->c.max_hops + 1);
+}
+
+/* is_channel_free phy_rmsa_env.py:1029-1035 */
+static int is_channel_free(const oracle_env* e, int pair, int path, int ch) {
+  const int16_t* L = links_of(e, pair, path, 0);
+  for (int i = 0; i < hops_of(e, pair, path); i++)
+    if (AV(e, 0, L[i])[ch] == 0) return 0;
+  return 1;
+}
+
+/* calculate_r_cut(channel, links, defrag_flag=False, path, modified=True) phy_rmsa_env.py:1140-1193 */
+static int calculate_r_cut(const oracle_env* e, int pair, int path, int ch) {
+  int N = e->c.n_nodes, E = e->c.n_edges, h = hops_of(e, pair, path);
+  const int16_t* nl = nodes_of(e, pair, path);
+  const int16_t* L = links_of(e, pair, path, 0);
+  int nn = h + 1;
+  uint8_t tmp[256];
+  int result[2];
+  for (int pass = 0; pass < 2; pass++) {
+    for (int l = 0; l < E; l++) tmp[l] = AV(e, 0, l)[ch];
+    if (pass == 1) for (int i = 0; i < h; i++) tmp[L[i]] = 0; /* temporary_channels2[i] = 0 */
+    int cut = 0;
+    for (int i = 0; i < nn; i++) {
+      for (int key = 0; key < N; key++) { /* for node_key in self.topology[path.node_list[i]] */
+        int lk = e->link_of[nl[i] * N + key];
+        if (lk < 0) continue;
+        int on_path = 0;
+        for (int q = 0; q < nn; q++) on_path |= (nl[q] == key);
+        if (on_path) continue;
+        if (i == nn - 1) cut += abs(tmp[e->link_of[nl[i - 1] * N + nl[i]]] - tmp[lk]);
+        else if (i == 0) cut += abs(tmp[e->link_of[nl[i] * N + nl[i + 1]]] - tmp[lk]);
+        else cut += abs(tmp[e->link_of[nl[i] * N + nl[i + 1]]] - tmp[lk]) +
+                    abs(tmp[e->link_of[nl[i - 1] * N + nl[i]]] - tmp[lk]);
+      }
+    }
+    result[pass] = cut;
+  }
+  return result[0] - result[1];
+}
+
+typedef struct phy_cand { int mod, frag, ch, idp; } phy_cand;
+
+/* sorted(row, key=...) is stable: insertion sort by the heuristic's key */
+static int cand_before(const phy_cand* a, const phy_cand* b, int hid) {
+  if (hid == 5) return a->ch < b->ch;                                  /* sapff_rmsa :1704 key x[1] */
+  if (hid == 6 || hid == 7) return a->mod != b->mod ? a->mod > b->mod : a->ch < b->ch; /* (-mod, ch) :1282,1343 */
+  return a->mod != b->mod ? a->mod > b->mod : a->frag > b->frag;      /* (-mod, -frag) :1405 */
+}
+
+/* phy_aware_bmfa_rmsa :1375-1438 (grooming False), phy_aware_bmff_rmsa :1317-1372,
+ * phy_aware_sapbm_rmsa :1254-1314, sapff_rmsa :1676-1737 with use_existing_channels -> (-3, []) */
+static void phy_heuristic(oracle_env* e, int hid, int32_t* a) {
+  int k = e->c.k_paths, C = e->c.num_slots, pair = cur_pair(e);
+  for (int i = 0; i < ORACLE_PHY_ADIM; i++) a[i] = -1;
+  a[0] = -2; /* (-2, []) : blocked */
+  int table = e->c.phy_table_id[pair];
+  if (table < 0) return;
+  phy_cand* rows = (phy_cand*)malloc(sizeof(phy_cand) * (size_t)k * C);
+  int* len = (int*)calloc(k, sizeof(int));
+  int* alive = (int*)calloc(k, sizeof(int));
+  for (int idp = 0; idp < k; idp++) {
+    phy_cand* row = rows + (size_t)idp * C;
+    if (hops_of(e, pair, idp) <= 0) continue;
+    for (int ch = 0; ch < C; ch++) {
+      if (!is_channel_free(e, pair, idp, ch)) continue;
+      phy_cand c = {phy_level(e, table, ch, idp), hid == 8 ? calculate_r_cut(e, pair, idp, ch) : 0, ch, idp};
+      int pos = len[idp]++;
+      while (pos > 0 && cand_before(&c, &row[pos - 1], hid)) { row[pos] = row[pos - 1]; pos--; }
+      row[pos] = c;
+    }
+    alive[idp] = 1;
+  }
+  for (;;) {
+    int best = -1;
+    for (int i = 0; i < k; i++) {
+      if (!alive[i] || len[i] == 0) continue;
+      const phy_cand* hd = rows + (size_t)i * C;
+      if (hid == 5 || hid == 6) { best = i; break; }          /* first non-empty row :1289-1297 */
+      if (best < 0) { best = i; continue; }
+      const phy_cand* bh = rows + (size_t)best * C;
+      if (hid == 7) { if (hd->mod > bh->mod) best = i; }      /* :1350-1355 */
+      else if (hd->mod > bh->mod || (hd->mod == bh->mod && hd->frag > bh->frag)) best = i; /* :1414-1421 */
+    }
+    if (best < 0) break;
+    int unassigned = e->cur.bit_rate, n = 0;
+    const phy_cand* row = rows + (size_t)best * C;
+    for (int i = 0; i < len[best]; i++) {
+      unassigned -= row[i].mod * 100;
+      if (n < ORACLE_PHY_ADIM - 1) a[1 + n] = row[i].ch;
+      n++;
+      if (unassigned <= 0) {
+        a[0] = n <= ORACLE_PHY_ADIM - 1 ? row[i].idp : -2;
+        if (a[0] == -2) for (int q = 1; q < ORACLE_PHY_ADIM; q++) a[q] = -1;
+        free(rows); free(len); free(alive);
+        return;
+      }
+    }
+    for (int q = 1; q < ORACLE_PHY_ADIM; q++) a[q] = -1;
+    alive[best] = 0; /* sorted_free_channels.pop(row) */
+  }
+  free(rows); free(len); free(alive);
+}
+
+/* PhyRMSAEnv.step phy_rmsa_env.py:272-309 (physical path branch) */
+static int phy_decide(oracle_env* e, const int32_t* a, int32_t* alloc) {
+  int k = e->c.k_paths, C = e->c.num_slots, pair = cur_pair(e);
+  int path = a[0], nch = 0, accepted = 0;
+  while (nch < ORACLE_PHY_ADIM - 1 && a[1 + nch] >= 0) nch++;
+  int ok = path >= 0 && path < k && nch > 0 && hops_of(e, pair, path) > 0 && e->c.phy_table_id[pair] >= 0;
+  for (int i = 0; ok && i < nch; i++) {
+    ok = a[1 + i] < C;
+    for (int q = 0; ok && q < i; q++) ok = a[1 + q] != a[1 + i];
+  }
+  for (int i = 0; ok && i < nch; i++) ok = is_channel_free(e, pair, path, a[1 + i]); /* is_path_free_on_channels */
+  if (ok) {
+    int table = e->c.phy_table_id[pair];
+    const int16_t* L = links_of(e, pair, path, 0);
+    svc s = {e->cur.arrival + e->cur.holding, pair, path, 0, a[1], nch, 0, nch, {0}};
+    for (int i = 0; i < hops_of(e, pair, path); i++)
+      for (int c = 0; c < nch; c++) AV(e, 0, L[i])[a[1 + c]] = 0; /* _provision_path :576-590 */
+    for (int c = 0; c < nch; c++) { /* :592-598 */
+      s.ch[c] = (int16_t)a[1 + c];
+      e->total_gsnr_ep += e->c.phy_gsnr[((size_t)table * C + a[1 + c]) * k + path];
+      e->total_mod_level_ep += phy_level(e, table, a[1 + c], path);
+      e->channels_accepted_ep++;
+    }
+    e->services_accepted++; /* _service_acceptance(False) :767-778 */
+    e->ep_accepted++;
+    e->total_path_length_ep += e->c.path_length[(size_t)pair * k + path];
+    e->total_path_index_ep += path + 1;
+    e->physical_accepted_ep++;
+    e->br_provisioned += e->cur.bit_rate;
+    e->ep_br_provisioned += e->cur.bit_rate;
+    heap_push(e, s);
+    accepted = 1;
+  }
+  if (alloc) {
+    alloc[0] = accepted;
+    alloc[1] = accepted ? path : -1;
+    alloc[2] = accepted ? a[1] : -1;
+    alloc[3] = accepted ? nch : 0;
+  }
+  return accepted;
+}
+
+/* _calculate_total_cuts :1195-1203, calculate_total_r_spatial :1110-1121 */
+static void phy_fragmentation(const oracle_env* e, double* cuts, double* rss) {
+  int E = e->c.n_edges, C = e->c.num_slots;
+  int64_t number_cut = 0;
+  double r_spatial = 0;
+  uint8_t col[256];
+  int pos[256], len[256];
+  uint8_t val[256];
+  for (int ch = 0; ch < C; ch++) {
+    for (int l = 0; l < E; l++) col[l] = AV(e, 0, l)[ch];
+    int nr = rle(col, E, pos, val, len);
+    int64_t sum_sq = 0, sum = 0;
+    for (int r = 0; r < nr; r++) {
+      number_cut += val[r]; /* np.sum(values) */
+      if (val[r] == 1) { sum_sq += (int64_t)len[r] * len[r]; sum += len[r]; }
+    }
+    r_spatial += sqrt((double)sum_sq) / (double)(sum + 1);
+  }
+  *cuts = (double)number_cut / (double)C;
+  *rss = r_spatial / (double)C;
+}
+
+/* out[6], out[7]: as computed by the last step() for its info dict, i.e. after the provisioning
+ * and BEFORE the releases of _next_service (phy_rmsa_env.py:313-314 precede :351) */
+void oracle_phy_stats(const oracle_env* e, double* out) {
+  out[0] = e->total_path_length_ep;
+  out[1] = e->total_gsnr_ep;
+  out[2] = (double)e->total_path_index_ep;
+  out[3] = (double)e->total_mod_level_ep;
+  out[4] = (double)e->channels_accepted_ep;
+  out[5] = (double)e->physical_accepted_ep;
+  out[6] = e->info_cuts;
+  out[7] = e->info_rss;
+}
+
 /* RMSAEnv.step rmsa_env.py:222-341 (decision part) */
 static int rmsa_decide(oracle_env* e, int path, int slot, int32_t* alloc) {
   int pair = cur_pair(e), accepted = 0, n = 0;
@@ -420,6 +633,9 @@ void oracle_step(oracle_env* e, const int32_t* a, int32_t* reward, uint8_t* done
       }
     }
     accepted = rmsa_decide(e, path, slot, alloc);
+  } else if (e->c.env_kind == 3) {
+    accepted = phy_decide(e, a, alloc);
+    phy_fragmentation(e, &e->info_cuts, &e->info_rss);
   } else { /* RMCSAEnv.step rmcsa_env.py:209-339 */
     int path = a[0], mod = a[1], core = a[2], slot = a[3], n = 0;
     int pair = cur_pair(e);
@@ -501,6 +717,7 @@ static int first_fit(const oracle_env* e, int pair, int path, int core, int n) {
 }
 
 void oracle_heuristic(oracle_env* e, int hid, int32_t* a) {
+  if (e->c.env_kind == 3) { phy_heuristic(e, hid, a); return; }
   int k = e->c.k_paths, S = e->c.num_slots, pair = cur_pair(e);
   if (e->c.env_kind == 0) {
     a[0] = k; a[1] = S;
@@ -613,7 +830,7 @@ static void* rollout_worker(void* arg) {
     if (i >= jb->n_envs) break;
     oracle_env* e = oracle_create(cfg, jb->env0 + i);
     oracle_reset(e, 1);
-    int32_t a[4], r;
+    int32_t a[16], r;
     uint8_t d;
     int64_t rs = 0;
     double obs[1024];
@@ -679,7 +896,7 @@ static void* pool_worker(void* arg) {
     int64_t i = __atomic_fetch_add(&p->next, 1, __ATOMIC_RELAXED);
     if (i >= p->n) break;
     oracle_env* e = p->envs[i];
-    int32_t a[4], r;
+    int32_t a[16], r;
     uint8_t d;
     for (int t = 0; t < p->nsteps; t++) {
       oracle_heuristic(e, p->hid, a);

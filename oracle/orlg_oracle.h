@@ -32,7 +32,7 @@ typedef struct oracle_request { /* same layout as orlg_request */
 } oracle_request;
 
 typedef struct oracle_config {
-  int32_t env_kind; /* 0 RMSA, 1 DeepRMSA, 2 RMCSA */
+  int32_t env_kind; /* 0 RMSA, 1 DeepRMSA, 2 RMCSA, 3 PhyRMSA */
   int32_t n_nodes, n_edges, k_paths, max_hops;
   const int16_t* path_links;
   const int16_t* path_links_by_id; /* may be NULL */
@@ -54,6 +54,13 @@ typedef struct oracle_config {
   int32_t bit_rate_lo, bit_rate_hi;
   const double* src_cum;
   const double* dst_cum;
+  /* PhyRMSA-v0 (env_kind 3, phy_rmsa_env.py): channels take the place of slots */
+  int32_t phy_n_tables, phy_pad;
+  const int32_t* phy_table_id;   /* [n_nodes*n_nodes] first connections_detail row of the unordered pair */
+  const uint8_t* phy_mod_level;  /* [n_tables][num_slots][k_paths]  modulation_level[table][channel][idp] */
+  const double* phy_gsnr;        /* [n_tables][num_slots][k_paths]  gsnr[table][channel][idp] */
+  const int16_t* path_nodes;     /* [n_nodes*n_nodes][k_paths][max_hops+1] node ids, -1 padded */
+  const int32_t* edge_nodes;     /* [n_edges][2] */
 } oracle_config;
 
 typedef struct oracle_env oracle_env;
@@ -82,6 +89,14 @@ int64_t oracle_rollout_many(const oracle_config* cfg, int64_t env0, int64_t n_en
                             int64_t* counters_out /* [n_envs][12] or NULL */,
                             uint8_t* state_out /* [n_envs][cores*E*S] or NULL */,
                             int64_t* reward_sum_out /* [n_envs] or NULL */);
+
+/* PhyRMSA: actions are int32[ORACLE_PHY_ADIM] = (path, channel_0 .. channel_7), -1 terminated;
+ * heuristic ids 5 SAP-FF, 6 SAP-BM, 7 BM-FF, 8 BM-FA-Cut (physical layer, no grooming).
+ * stats out8 = total_path_length_episode, total_gsnr_episode, total_path_index_episode,
+ * total_modulation_level_episode, channels_accepted_episode, physical_services_accepted_episode,
+ * number_cuts_total, rss_total_metric (phy_rmsa_env.py:313-348). */
+#define ORACLE_PHY_ADIM 9
+void oracle_phy_stats(const oracle_env* e, double* out8);
 
 /* GN-model GSNR (examples/calculate_osnr.py:9-56); same parameter block as orlg_gsnr_params */
 typedef struct oracle_gsnr_params {

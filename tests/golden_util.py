@@ -18,9 +18,10 @@ TOPO_SHORT = {
 }
 
 CASES = sorted(f[:-4] for f in os.listdir(GOLDEN)
-               if f.endswith(".npz") and not f.startswith(("topology_", "gsnr_", "phy_")))
+               if f.endswith(".npz") and not f.startswith(("topology_", "gsnr_", "phy_", "phytab_")))
+PHY_CASES = sorted(f[:-4] for f in os.listdir(GOLDEN) if f.startswith("phy_") and f.endswith(".npz"))
 GSNR_CASES = sorted(f[:-4] for f in os.listdir(GOLDEN) if f.startswith("gsnr_") and f.endswith(".npz"))
-ENV_NAME = {0: "RMSA-v0", 1: "DeepRMSA-v0", 2: "RMCSA-v0"}
+ENV_NAME = {0: "RMSA-v0", 1: "DeepRMSA-v0", 2: "RMCSA-v0", 3: "PhyRMSA-v0"}
 
 
 def topology(short: str) -> TopologyTables:
@@ -40,5 +41,11 @@ def load_case(name: str):
         else:
             kw[str(k)] = v
     tables = topology(TOPO_SHORT[str(g["topo_file"])])
+    if "tables_key" in g:  # PhyRMSA: the QoT tables the reference run used
+        z = np.load(os.path.join(GOLDEN, f"phytab_{str(g['tables_key'])}.npz"), allow_pickle=False)
+        kw.update(modulation_level=z["phy_mod"].astype(np.int64), connections_detail=z["phy_conn"],
+                  gsnr=z["phy_gsnr"])
+        kw.pop("num_spectrum_resources", None)  # irrelevant to PhyRMSA's allocation
+        kw.pop("bit_rate_selection", None)
     spec = S.make_spec(ENV_NAME[int(g["env_kind"])], tables, request_source=S.SRC_REPLAY, **kw)
     return g, spec
