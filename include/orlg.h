@@ -21,6 +21,9 @@
  *   orlg_get_counters<- the counters behind the info dict rmsa_env.py:293-307
  *   orlg_export_state<- topology.graph["available_slots"] rmsa_env.py:396-398
  *   orlg_gsnr        <- calculate_osnr examples/calculate_osnr.py:9-56
+ *   PhyRMSA-v0 (env_kind 3): orlg_step <- PhyRMSAEnv.step phy_rmsa_env.py:272-351,
+ *                       orlg_heuristic <- phy_rmsa_env.py:1254-1438,1676-1737,
+ *                       orlg_phy_get_stats <- the info dict phy_rmsa_env.py:319-348
  *
  * All pointers named dev_* are CUDA device pointers owned by the caller; the
  * engine owns its internal state.  Functions return 0 or a negative ORLG_E*.
@@ -58,10 +61,23 @@ enum {
   ORLG_H_SAP_FF = 1,   /* rmsa_env.py:901-913 ; DeepRMSA: deeprmsa_env.py:146-155 */
   ORLG_H_LLP_FF = 2,   /* rmsa_env.py:916-937 */
   ORLG_H_SAP_BM_FC_FF = 3, /* rmcsa_env.py:882-911 */
-  ORLG_H_RANDOM = 4    /* uniform action from the env's Philox stream */
+  ORLG_H_RANDOM = 4,   /* uniform action from the env's Philox stream */
+  /* PhyRMSA-v0, physical layer (grooming off): */
+  ORLG_H_PHY_SAP_FF = 5,     /* sapff_rmsa           phy_rmsa_env.py:1676-1737 */
+  ORLG_H_PHY_SAP_BM = 6,     /* phy_aware_sapbm_rmsa phy_rmsa_env.py:1254-1314 */
+  ORLG_H_PHY_BM_FF = 7,      /* phy_aware_bmff_rmsa  phy_rmsa_env.py:1317-1372 */
+  ORLG_H_PHY_BM_FA_CUT = 8   /* phy_aware_bmfa_rmsa  phy_rmsa_env.py:1375-1438 */
 };
 
-enum { ORLG_OBS_NONE = 0, ORLG_OBS_F64 = 1, ORLG_OBS_F32 = 2, ORLG_OBS_MATRIX_U8 = 3 };
+enum {
+  ORLG_OBS_NONE = 0, ORLG_OBS_F64 = 1, ORLG_OBS_F32 = 2, ORLG_OBS_MATRIX_U8 = 3,
+  /* PhyRMSA-v0: f64 (number_cuts_total, rss_total_metric) of the step's info dict
+   * (phy_rmsa_env.py:313-314,337-338; what UseInfoReward wrappers.py:4-16 feeds back) */
+  ORLG_OBS_PHY_INFO = 4,
+  ORLG_OBS_PHY_CUTS = 5 /* number_cuts_total only (the RSS pass is ~5x the cost of a step) */
+};
+
+#define ORLG_PHY_ACTION_DIM 9 /* PhyRMSA action: (path, 8 channel numbers), -1 terminated; path -2 = block */
 
 /* One request as drawn by _next_service (rmsa_env.py:646-659).  `arrival` is the
  * absolute clock value after the draw (current_time + expovariate), `holding`
@@ -118,6 +134,15 @@ typedef struct orlg_config {
   int32_t heap_capacity;  /* release-queue entries per env; 0 = provable bound */
   int32_t obs_kind;       /* ORLG_OBS_* written by orlg_step */
   int32_t reserved[6];
+
+  /* PhyRMSA-v0 (phy_rmsa_env.py:51-53,93-95): num_slots = number of channels, num_cores = 1 */
+  int32_t phy_n_tables;   /* rows of connections_detail */
+  int32_t phy_max_terms;  /* row length of phy_cut_links (<= 63 used per path) */
+  const int32_t* phy_table_id;   /* [n_nodes*n_nodes] first row matching the unordered pair, -1 = none */
+  const uint8_t* phy_mod_level;  /* [phy_n_tables][num_slots][k_paths], levels 1..8 */
+  const double* phy_gsnr;        /* [phy_n_tables][num_slots][k_paths] dB */
+  const uint8_t* phy_cut_links;  /* [n_nodes*n_nodes*k_paths][phy_max_terms] neighbour link per r_cut term */
+  const int32_t* phy_cut_count;  /* [n_nodes*n_nodes*k_paths] */
 } orlg_config;
 
 typedef struct orlg_engine orlg_engine;
@@ -193,6 +218,12 @@ int orlg_rollout(orlg_engine* e, int heuristic_id, int nsteps, int64_t* dev_rewa
 
 int orlg_get_counters(orlg_engine* e, int64_t* dev_out /* [num_envs][ORLG_NUM_COUNTERS] */,
                       void* stream);
+
+/* PhyRMSA-v0 per-env statistics, f64 [num_envs][8]: total_path_length_episode, total_gsnr_episode,
+ * total_path_index_episode, total_modulation_level_episode, channels_accepted_episode,
+ * physical_services_accepted_episode (phy_rmsa_env.py:431-439), then number_cuts_total and
+ * rss_total_metric (:1195-1203, :1110-1121) of the CURRENT channel map. */
+int orlg_phy_get_stats(orlg_engine* e, double* dev_out, void* stream);
 
 /* Unpacked occupancy: uint8 [num_envs][num_cores][n_edges][num_slots], 1 = free,
  * i.e. topology.graph["available_slots"] of every env. */

@@ -69,7 +69,19 @@ struct Params {
   long long* counters;
   const orlg_request* trace;
   long long trace_len;
+  // PhyRMSA-v0 (phy_rmsa_env.py): channels take the place of slots, one core
+  const int* phy_table_id;              // [N*N] row of the QoT tables for the unordered pair
+  const unsigned char* phy_mod;         // [T][S][k] modulation_level
+  const double* phy_gsnr;               // [T][S][k] gsnr
+  const uint32_t* phy_level_mask;       // [T][k][PHY_LEVELS][W] channels whose level == m
+  const unsigned char* phy_cut_links;   // [N*N*k][phy_max_terms] neighbour link of every r_cut term
+  const int* phy_cut_count;             // [N*N*k]
+  int phy_max_terms, phy_mask_w;
+  double* phy_f;                        // [2][NP] episode sums: path length, gsnr
+  long long* phy_i;                     // [4][NP] episode sums: path index, modulation level, channels, physical services
 };
+constexpr int PHY_LEVELS = 8;   // modulation levels 1..8 (100 Gb/s per level per channel, phy_rmsa_env.py:1424)
+constexpr int PHY_ADIM = 9;     // action = (path, 8 channel numbers, -1 terminated)
 
 struct StepIO {
   int mode, heuristic, nsteps, obs_kind;

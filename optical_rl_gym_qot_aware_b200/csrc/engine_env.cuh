@@ -21,7 +21,7 @@ __device__ __forceinline__ int svc_start(unsigned long long s) { return (int)((s
 __device__ __forceinline__ int svc_slots(unsigned long long s) { return (int)((s >> 48) & 0x3FF); }
 __device__ __forceinline__ int svc_se(unsigned long long s) { return (int)((s >> 58) & 15); }
 
-template <int W, int BD>
+template <int W, int BD, bool PHY = false>
 struct Env {
   const Params& p;
   Tile<W, BD> tile;
@@ -30,6 +30,8 @@ struct Env {
   double now, holding, next_rel;
   int bit_rate, src, dst, heap_len;
   long long cnt[CNT_N];
+  double fsum[2];      // PhyRMSA episode sums (phy_rmsa_env.py:431-439)
+  long long isum[4];
 
   __device__ __forceinline__ Env(const Params& p_, uint32_t* smem, int tid, int e_)
       : p(p_), tile{smem, tid, p_.E}, e(e_) {
@@ -49,6 +51,12 @@ struct Env {
     heap_len = p.heap_len[e];
 #pragma unroll
     for (int i = 0; i < CNT_N; i++) cnt[i] = p.counters[(size_t)i * p.NP + e];
+    if constexpr (PHY) {
+      fsum[0] = p.phy_f[e];
+      fsum[1] = p.phy_f[(size_t)p.NP + e];
+#pragma unroll
+      for (int i = 0; i < 4; i++) isum[i] = p.phy_i[(size_t)i * p.NP + e];
+    }
   }
   // only the pending request (enough for the heuristics and the observation)
   __device__ __forceinline__ void load_request() {
@@ -65,6 +73,12 @@ struct Env {
     p.heap_len[e] = heap_len;
 #pragma unroll
     for (int i = 0; i < CNT_N; i++) p.counters[(size_t)i * p.NP + e] = cnt[i];
+    if constexpr (PHY) {
+      p.phy_f[e] = fsum[0];
+      p.phy_f[(size_t)p.NP + e] = fsum[1];
+#pragma unroll
+      for (int i = 0; i < 4; i++) p.phy_i[(size_t)i * p.NP + e] = isum[i];
+    }
   }
 
   // ---- release queue: heapq of (arrival+holding, service), optical_network_env.py:178-189 ----
@@ -219,6 +233,10 @@ struct Env {
     cnt[CNT_EP_BR_PROV] = 0;
     cnt[CNT_EP_PROC] = 1;
     cnt[CNT_EP_BR_REQ] = bit_rate;
+    if constexpr (PHY) {
+      fsum[0] = fsum[1] = 0.0;
+      isum[0] = isum[1] = isum[2] = isum[3] = 0;
+    }
   }
 
   // _provision_path + _add_release (state and counters only)

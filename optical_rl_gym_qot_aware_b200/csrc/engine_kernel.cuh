@@ -1,6 +1,6 @@
 // engine_kernel.cuh — the stepping kernel: TMA-staged tile in, step(s), tile out.
 #pragma once
-#include "engine_step.cuh"
+#include "engine_phy.cuh"
 
 namespace orlg {
 
@@ -52,7 +52,7 @@ __device__ __forceinline__ void fence_async_smem() {
 // rollout mode).  Grid = NP / BD tiles, one thread per env.  MT is the mode the
 // instantiation is specialised for (MODE_STEP / MODE_HEURISTIC / MODE_ROLLOUT), or
 // -1 for the rarely used modes (observation, resets), which read io.mode.
-template <int W, int BD, int MT>
+template <int W, int BD, int MT, bool PHY>
 __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t bar;
@@ -75,9 +75,12 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
     }
   }
 
-  Env<W, BD> env(p, tile_s, tid, active ? e : 0);
-  typename Env<W, BD>::Req nx{};
-  int a[4] = {0, 0, 0, 0};
+  Env<W, BD, PHY> env(p, tile_s, tid, active ? e : 0);
+  typename Env<W, BD, PHY>::Req nx{};
+  constexpr int ADIM = PHY ? PHY_ADIM : 4;
+  int a[ADIM];
+#pragma unroll
+  for (int i = 0; i < ADIM; i++) a[i] = 0;
   if (mode == MODE_RESET_FULL) {
     // rmsa_env.py:391-457: empty network, clock 0, counters 0, then the first request
     for (int pl = 0; pl < p.planes; pl++) tile_s[pl * BD + tid] = mask_word(pl % W, 0, p.S);
@@ -88,6 +91,8 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
     env.next_rel = __longlong_as_double(0x7FF0000000000000ll);
 #pragma unroll
     for (int i = 0; i < CNT_N; i++) env.cnt[i] = 0;
+    env.fsum[0] = env.fsum[1] = 0.0;
+    env.isum[0] = env.isum[1] = env.isum[2] = env.isum[3] = 0;
     if (active) env.next_service();
   } else if (active) {
     // everything that does not need the tile happens while the bulk copy is in flight
@@ -95,7 +100,10 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
       env.load_request();
     } else {
       env.load_scalars();
-      if (mode == MODE_STEP) {
+      if (mode == MODE_STEP && PHY) {
+#pragma unroll
+        for (int i = 0; i < ADIM; i++) a[i] = io.actions[(size_t)e * ADIM + i];
+      } else if (mode == MODE_STEP) {
         if (p.action_dim == 1) {
           a[0] = io.actions[e];
         } else if (p.action_dim == 2) {
@@ -124,8 +132,12 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
   if (active) {
     if (mode == MODE_RESET_EPISODE) {
       env.reset_episode();
+    } else if (mode == MODE_HEURISTIC && PHY) {
+      if constexpr (PHY) phy_heuristic<W, BD>(env, io.heuristic, a);
+#pragma unroll
+      for (int i = 0; i < ADIM; i++) io.actions_out[(size_t)e * ADIM + i] = a[i];
     } else if (mode == MODE_HEURISTIC) {
-      heuristic_action<W, BD>(env, io.heuristic, a);
+      if constexpr (!PHY) heuristic_action<W, BD>(env, io.heuristic, a);
       if (p.action_dim == 1) {
         io.actions_out[e] = a[0];
       } else if (p.action_dim == 2) {
@@ -138,13 +150,23 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
       long long rsum = 0;
       for (int t = 0; t < nsteps; t++) {
         if (mode == MODE_ROLLOUT) {
-          heuristic_action<W, BD>(env, io.heuristic, a);
+          if constexpr (PHY) phy_heuristic<W, BD>(env, io.heuristic, a);
+          else heuristic_action<W, BD>(env, io.heuristic, a);
           if (t > 0) nx = env.draw_request();
         }
         Decision d;
-        if (p.kind == ORLG_ENV_RMSA) d = rmsa_decide<W, BD>(env, a[0], a[1]);
-        else if (p.kind == ORLG_ENV_DEEPRMSA) d = deeprmsa_decide<W, BD>(env, a[0]);
-        else d = rmcsa_decide<W, BD>(env, a[0], a[1], a[2], a[3]);
+        if constexpr (PHY) {
+          d = phy_decide<W, BD>(env, a);
+          // the info metrics are taken after the provisioning and before the releases (:313-314 vs :351)
+          if (mode == MODE_STEP && io.obs != nullptr &&
+              (io.obs_kind == ORLG_OBS_PHY_INFO || io.obs_kind == ORLG_OBS_PHY_CUTS))
+            phy_info<W, BD>(env, reinterpret_cast<double*>(io.obs) + (long long)e * io.obs_es, io.obs_fs,
+                            io.obs_kind == ORLG_OBS_PHY_INFO);
+        } else {
+          if (p.kind == ORLG_ENV_RMSA) d = rmsa_decide<W, BD>(env, a[0], a[1]);
+          else if (p.kind == ORLG_ENV_DEEPRMSA) d = deeprmsa_decide<W, BD>(env, a[0]);
+          else d = rmcsa_decide<W, BD>(env, a[0], a[1], a[2], a[3]);
+        }
         if (p.kind == ORLG_ENV_RMCSA) {  // rmcsa_env.py:292-295
           env.cnt[CNT_PROC]++;
           env.cnt[CNT_EP_PROC]++;
@@ -173,11 +195,16 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
       if (io.reward_sum) io.reward_sum[e] += rsum;
     }
     if ((mode == MODE_STEP || mode == MODE_OBS || mode == MODE_RESET_FULL) && io.obs != nullptr) {
-      if (io.obs_kind == ORLG_OBS_F64)
-        write_deeprmsa_obs<W, BD, double>(env, reinterpret_cast<double*>(io.obs) + (long long)e * io.obs_es, io.obs_fs);
-      else if (io.obs_kind == ORLG_OBS_F32)
-        write_deeprmsa_obs<W, BD, float>(env, reinterpret_cast<float*>(io.obs) + (long long)e * io.obs_es, io.obs_fs);
-      else if (io.obs_kind == ORLG_OBS_MATRIX_U8)
+      if constexpr (!PHY) {
+        if (io.obs_kind == ORLG_OBS_F64)
+          write_deeprmsa_obs<W, BD, double>(env, reinterpret_cast<double*>(io.obs) + (long long)e * io.obs_es, io.obs_fs);
+        else if (io.obs_kind == ORLG_OBS_F32)
+          write_deeprmsa_obs<W, BD, float>(env, reinterpret_cast<float*>(io.obs) + (long long)e * io.obs_es, io.obs_fs);
+      } else if (mode != MODE_STEP && (io.obs_kind == ORLG_OBS_PHY_INFO || io.obs_kind == ORLG_OBS_PHY_CUTS)) {
+        phy_info<W, BD>(env, reinterpret_cast<double*>(io.obs) + (long long)e * io.obs_es, io.obs_fs,
+                        io.obs_kind == ORLG_OBS_PHY_INFO);
+      }
+      if (io.obs_kind == ORLG_OBS_MATRIX_U8)
         write_matrix_obs<W, BD>(env, reinterpret_cast<unsigned char*>(io.obs) + (long long)e * io.obs_es, io.obs_fs);
     }
     if (mode != MODE_HEURISTIC && mode != MODE_OBS) env.store_scalars();

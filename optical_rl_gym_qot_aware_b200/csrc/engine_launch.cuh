@@ -1,4 +1,4 @@
-// engine_launch.cuh — host-side launch of env_kernel<W, BD, MT>.  Each word count W is
+// engine_launch.cuh — host-side launch of env_kernel<W, BD, MT, PHY>.  Each word count W is
 // instantiated in its own translation unit (orlg_w2.cu / orlg_w4.cu / orlg_w10.cu) so the
 // three compile in parallel; orlg.cu only sees the declaration of launch_w.
 #pragma once
@@ -15,41 +15,52 @@ struct LaunchGeom {
 
 template <int W>
 cudaError_t launch_w(const LaunchGeom& g, const Params& p, const StepIO& io, cudaStream_t st);
+// PhyRMSA-v0 instantiations (tile of 32 envs), compiled in orlg_phy.cu
+template <int W>
+cudaError_t launch_phy(const LaunchGeom& g, const Params& p, const StepIO& io, cudaStream_t st);
 
-#ifdef ORLG_INSTANTIATE_W
-template <int W, int BD, int MT>
+#if defined(ORLG_INSTANTIATE_W) || defined(ORLG_INSTANTIATE_PHY)
+template <int W, int BD, int MT, bool PHY>
 static cudaError_t launch_t(const LaunchGeom& g, const Params& p, const StepIO& io, cudaStream_t st) {
   static size_t configured[64] = {};  // largest dynamic smem opted into, per device
   if (g.smem_bytes > 48 * 1024 && configured[g.device & 63] < g.smem_bytes) {
-    cudaError_t rc = cudaFuncSetAttribute(env_kernel<W, BD, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t rc = cudaFuncSetAttribute(env_kernel<W, BD, MT, PHY>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)g.smem_bytes);
     if (rc != cudaSuccess) return rc;
     configured[g.device & 63] = g.smem_bytes;
   }
-  env_kernel<W, BD, MT><<<g.NP / BD, BD, g.smem_bytes, st>>>(p, io);
+  env_kernel<W, BD, MT, PHY><<<g.NP / BD, BD, g.smem_bytes, st>>>(p, io);
   return cudaGetLastError();
 }
 
-template <int W, int BD>
+template <int W, int BD, bool PHY>
 static cudaError_t launch_m(const LaunchGeom& g, const Params& p, const StepIO& io, cudaStream_t st) {
   switch (io.mode) {
-    case MODE_STEP: return launch_t<W, BD, MODE_STEP>(g, p, io, st);
-    case MODE_HEURISTIC: return launch_t<W, BD, MODE_HEURISTIC>(g, p, io, st);
-    case MODE_ROLLOUT: return launch_t<W, BD, MODE_ROLLOUT>(g, p, io, st);
-    default: return launch_t<W, BD, -1>(g, p, io, st);
+    case MODE_STEP: return launch_t<W, BD, MODE_STEP, PHY>(g, p, io, st);
+    case MODE_HEURISTIC: return launch_t<W, BD, MODE_HEURISTIC, PHY>(g, p, io, st);
+    case MODE_ROLLOUT: return launch_t<W, BD, MODE_ROLLOUT, PHY>(g, p, io, st);
+    default: return launch_t<W, BD, -1, PHY>(g, p, io, st);
   }
 }
 
+#endif
+#ifdef ORLG_INSTANTIATE_W
 template <int W>
 cudaError_t launch_w(const LaunchGeom& g, const Params& p, const StepIO& io, cudaStream_t st) {
   switch (g.BD) {
-    case 32: return launch_m<W, 32>(g, p, io, st);
-    case 64: return launch_m<W, 64>(g, p, io, st);
-    default: return launch_m<W, 128>(g, p, io, st);
+    case 32: return launch_m<W, 32, false>(g, p, io, st);
+    case 64: return launch_m<W, 64, false>(g, p, io, st);
+    default: return launch_m<W, 128, false>(g, p, io, st);
   }
 }
-
 template cudaError_t launch_w<ORLG_INSTANTIATE_W>(const LaunchGeom&, const Params&, const StepIO&, cudaStream_t);
+#endif
+#ifdef ORLG_INSTANTIATE_PHY
+template <int W>
+cudaError_t launch_phy(const LaunchGeom& g, const Params& p, const StepIO& io, cudaStream_t st) {
+  return launch_m<W, 32, true>(g, p, io, st);
+}
+template cudaError_t launch_phy<ORLG_INSTANTIATE_PHY>(const LaunchGeom&, const Params&, const StepIO&, cudaStream_t);
 #endif
 
 }  // namespace orlg

@@ -1,0 +1,283 @@
+// engine_phy.cuh — PhyRMSA-v0 on the stepping engine (optical_rl_gym/envs/phy_rmsa_env.py,
+// physical layer: grooming=False, no periodic defragmentation).
+//
+// Channels take the place of slots: the tile holds available_channels[E][C] as packed rows
+// (bit = 1 = free, phy_rmsa_env.py:185-189).  A service owns a *set* of whole channels on its
+// path; it enters the release heap as one entry per channel (same key), so release is the
+// generic "set one bit on every link of the path".
+//
+//   step (physical path)      phy_rmsa_env.py:272-309, _provision_path :544-623,
+//                             _service_acceptance :767-778, _release_path :781-861
+//   is_channel_free           :1029-1035  -> AND of the path's link rows
+//   calculate_r_cut(modified) :1140-1193  -> T - 2 * (number of term links whose bit is set), per
+//                             channel, counted for all channels at once with bit-sliced adders
+//   _calculate_total_cuts     :1195-1203, calculate_total_r_spatial :1110-1121 (info metrics)
+//   heuristics                sapff_rmsa :1676-1737, phy_aware_sapbm_rmsa :1254-1314,
+//                             phy_aware_bmff_rmsa :1317-1372, phy_aware_bmfa_rmsa :1375-1438
+//
+// Python's `sorted(row, key=(-mod, -frag))` + "take channels until the bit rate is covered" is
+// evaluated without sorting: modulation levels are visited from high to low through per-level
+// channel masks, inside a level the channels with the lowest neighbour count (highest r_cut) come
+// first, ties in ascending channel order (stability of sorted()).
+#pragma once
+#include "engine_step.cuh"
+
+namespace orlg {
+
+constexpr int PHY_PLANES = 6;  // bit-sliced neighbour counters: up to 63 r_cut terms per path
+
+template <int W>
+__device__ __forceinline__ bool row_any(const Row<W>& r) {
+  uint32_t o = 0;
+#pragma unroll
+  for (int i = 0; i < W; i++) o |= r.w[i];
+  return o != 0;
+}
+template <int W>
+__device__ __forceinline__ bool row_bit(const Row<W>& r, int pos) {
+  uint32_t v = 0;
+#pragma unroll
+  for (int i = 0; i < W; i++) v = (pos >> 5) == i ? r.w[i] : v;
+  return (v >> (pos & 31)) & 1u;
+}
+template <int W>
+__device__ __forceinline__ void row_clear_bit(Row<W>& r, int pos) {
+#pragma unroll
+  for (int i = 0; i < W; i++)
+    if ((pos >> 5) == i) r.w[i] &= ~(1u << (pos & 31));
+}
+
+template <int W>
+__device__ __forceinline__ Row<W> level_mask(const Params& p, int table, int idp, int m) {
+  const uint32_t* a = p.phy_level_mask + (((size_t)table * p.k + idp) * PHY_LEVELS + (m - 1)) * W;
+  Row<W> r;
+#pragma unroll
+  for (int i = 0; i < W; i++) r.w[i] = __ldg(a + i);
+  return r;
+}
+
+template <int W>
+struct CutPlanes {
+  Row<W> b[PHY_PLANES];
+};
+
+// per-channel number of r_cut terms whose neighbour link has the channel free
+template <int W, int BD, typename ENV>
+__device__ __forceinline__ void count_terms(ENV& env, int pathg, CutPlanes<W>& c) {
+  const Params& p = env.p;
+#pragma unroll
+  for (int q = 0; q < PHY_PLANES; q++)
+#pragma unroll
+    for (int i = 0; i < W; i++) c.b[q].w[i] = 0u;
+  const int T = __ldg(p.phy_cut_count + pathg);
+  const unsigned char* links = p.phy_cut_links + (size_t)pathg * p.phy_max_terms;
+  for (int t = 0; t < T; t++) {
+    const int l = __ldg(links + t);
+#pragma unroll
+    for (int i = 0; i < W; i++) {
+      uint32_t carry = env.tile.word(0, l, i);
+#pragma unroll
+      for (int q = 0; q < PHY_PLANES; q++) {
+        uint32_t t2 = c.b[q].w[i] & carry;
+        c.b[q].w[i] ^= carry;
+        carry = t2;
+      }
+    }
+  }
+}
+
+// subset of `cand` with the smallest counter value
+template <int W>
+__device__ __forceinline__ Row<W> min_count_subset(const Row<W>& cand, const CutPlanes<W>& c) {
+  Row<W> s = cand;
+#pragma unroll
+  for (int q = PHY_PLANES - 1; q >= 0; q--) {
+    Row<W> t;
+#pragma unroll
+    for (int i = 0; i < W; i++) t.w[i] = s.w[i] & ~c.b[q].w[i];
+    if (row_any<W>(t)) s = t;
+  }
+  return s;
+}
+template <int W>
+__device__ __forceinline__ int count_at(const CutPlanes<W>& c, int ch) {
+  int v = 0;
+#pragma unroll
+  for (int q = 0; q < PHY_PLANES; q++) v |= (int)row_bit<W>(c.b[q], ch) << q;
+  return v;
+}
+
+// The reference heuristic's action for the pending request: a[0] = path or -2, a[1..8] channels.
+template <int W, int BD, typename ENV>
+__device__ void phy_heuristic(ENV& env, int hid, int* a) {
+  const Params& p = env.p;
+#pragma unroll
+  for (int i = 0; i < PHY_ADIM; i++) a[i] = -1;
+  a[0] = -2;
+  const int pr = env.pair();
+  const int table = __ldg(p.phy_table_id + pr);
+  if (table < 0) return;
+  int best = -1, best_mod = -1, best_frag = -(1 << 30);
+  for (int idp = 0; idp < p.k; idp++) {
+    PathRec rec = load_path(p, pr, idp);
+    if (rec.hops() <= 0) continue;
+    Row<W> A = env.tile.path_avail(rec, 0);
+    if (!row_any<W>(A)) continue;
+    int cap = 0, head = 0;
+#pragma unroll 1
+    for (int m = PHY_LEVELS; m >= 1; m--) {
+      Row<W> L = level_mask<W>(p, table, idp, m);
+      and_into(L, A);
+      int c = popcount<W>(L);
+      cap += m * c;
+      if (head == 0 && c > 0) head = m;
+    }
+    if (cap * 100 < env.bit_rate) continue;  // the row would be tried, found short and popped
+    if (hid == ORLG_H_PHY_SAP_FF || hid == ORLG_H_PHY_SAP_BM) {  // first row that can carry the request
+      best = idp;
+      break;
+    }
+    if (hid == ORLG_H_PHY_BM_FF) {  // :1350-1355, strict '>' keeps the earliest row
+      if (head > best_mod) {
+        best = idp;
+        best_mod = head;
+      }
+      continue;
+    }
+    // BM-FA-Cut :1414-1421: head of the row = (highest level, highest r_cut inside it)
+    CutPlanes<W> cp;
+    const int pathg = pr * p.k + idp;
+    count_terms<W, BD>(env, pathg, cp);
+    Row<W> cand = level_mask<W>(p, table, idp, head);
+    and_into(cand, A);
+    Row<W> s = min_count_subset<W>(cand, cp);
+    int frag = __ldg(p.phy_cut_count + pathg) - 2 * count_at<W>(cp, lowest_set<W>(s));
+    if (head > best_mod || (head == best_mod && frag > best_frag)) {
+      best = idp;
+      best_mod = head;
+      best_frag = frag;
+    }
+  }
+  if (best < 0) return;
+  // channels of the chosen row in the heuristic's order until the bit rate is covered
+  PathRec rec = load_path(p, pr, best);
+  Row<W> A = env.tile.path_avail(rec, 0);
+  int need = env.bit_rate, n = 0;
+  if (hid == ORLG_H_PHY_SAP_FF) {  // ascending channel number, whatever the level (:1704)
+    while (need > 0 && n < PHY_ADIM - 1) {
+      int ch = lowest_set<W>(A);
+      if (ch < 0) break;
+      row_clear_bit<W>(A, ch);
+      a[1 + n++] = ch;
+      need -= (int)__ldg(p.phy_mod + ((size_t)table * p.S + ch) * p.k + best) * 100;
+    }
+  } else {
+    CutPlanes<W> cp;
+    if (hid == ORLG_H_PHY_BM_FA_CUT) count_terms<W, BD>(env, pr * p.k + best, cp);
+#pragma unroll 1
+    for (int m = PHY_LEVELS; m >= 1 && need > 0; m--) {
+      Row<W> cand = level_mask<W>(p, table, best, m);
+      and_into(cand, A);
+      while (need > 0 && n < PHY_ADIM - 1 && row_any<W>(cand)) {
+        Row<W> s = cand;
+        if (hid == ORLG_H_PHY_BM_FA_CUT) s = min_count_subset<W>(cand, cp);
+        int ch = lowest_set<W>(s);
+        row_clear_bit<W>(cand, ch);
+        a[1 + n++] = ch;
+        need -= m * 100;
+      }
+    }
+  }
+  if (need <= 0) {
+    a[0] = best;
+  } else {  // more than 8 channels would be needed: treated as blocked (documented cap)
+#pragma unroll
+    for (int i = 1; i < PHY_ADIM; i++) a[i] = -1;
+  }
+}
+
+// PhyRMSAEnv.step, physical path branch (phy_rmsa_env.py:290-309)
+template <int W, int BD, typename ENV>
+__device__ Decision phy_decide(ENV& env, const int* a) {
+  const Params& p = env.p;
+  Decision d{0, -1, 0, -1, 0};
+  const int path = a[0], pr = env.pair();
+  int nch = 0;
+  while (nch < PHY_ADIM - 1 && a[1 + nch] >= 0) nch++;
+  if (path < 0 || path >= p.k || nch == 0) return d;
+  const int table = __ldg(p.phy_table_id + pr);
+  PathRec rec = load_path(p, pr, path);
+  if (table < 0 || rec.hops() <= 0) return d;
+  Row<W> A = env.tile.path_avail(rec, 0);
+  bool ok = true;
+  for (int i = 0; i < nch; i++) {  // is_path_free_on_channels :1019-1027 (+ range / duplicate checks)
+    int ch = a[1 + i];
+    ok = ok && ch < p.S && row_bit<W>(A, ch < p.S ? ch : 0);
+    if (ok) row_clear_bit<W>(A, ch);
+  }
+  if (!ok) return d;
+  const double key = env.now + env.holding;
+  for (int i = 0; i < nch; i++) {  // _provision_path :576-598
+    const int ch = a[1 + i];
+    env.tile.clear_range(rec, 0, ch, 1);
+    const size_t tix = ((size_t)table * p.S + ch) * p.k + path;
+    const int level = __ldg(p.phy_mod + tix);
+    env.fsum[1] += __ldg(p.phy_gsnr + tix);
+    env.isum[1] += level;
+    env.isum[2]++;
+    env.heap_push(key, pack_service(pr, path, 0, ch, 1, level));
+  }
+  env.cnt[CNT_ACC]++;  // _service_acceptance(False) :767-778
+  env.cnt[CNT_EP_ACC]++;
+  env.fsum[0] += __ldg(p.path_length + (size_t)pr * p.k + path);
+  env.isum[0] += path + 1;
+  env.isum[3]++;
+  env.cnt[CNT_BR_PROV] += env.bit_rate;
+  env.cnt[CNT_EP_BR_PROV] += env.bit_rate;
+  d = Decision{1, path, 0, a[1], nch};
+  return d;
+}
+
+// number_cuts_total and rss_total_metric of the step's info dict (phy_rmsa_env.py:313-314),
+// evaluated where the reference evaluates them: after the provisioning, before the releases.
+template <int W, int BD, typename ENV>
+__device__ void phy_info(ENV& env, double* o, long long fs, bool want_rss) {
+  const Params& p = env.p;
+  // _calculate_total_cuts :1195-1203: runs of free links (in link-index order) per channel
+  long long cuts = 0;
+  for (int l = 0; l < p.E; l++) {
+#pragma unroll
+    for (int i = 0; i < W; i++) {
+      uint32_t cur = env.tile.word(0, l, i);
+      uint32_t prev = l > 0 ? env.tile.word(0, l - 1, i) : 0u;
+      cuts += __popc(cur & ~prev);
+    }
+  }
+  o[0] = (double)cuts / (double)p.S;
+  if (!want_rss) return;
+  // calculate_total_r_spatial :1110-1121: sqrt(sum len^2) / (sum len + 1) over the free runs
+  double r_spatial = 0.0;
+  for (int i = 0; i < W; i++) {
+    for (int b = 0; b < 32; b++) {
+      const int ch = 32 * i + b;
+      if (ch >= p.S) break;
+      long long sum_sq = 0;
+      int sum = 0, run = 0;
+      for (int l = 0; l < p.E; l++) {
+        if ((env.tile.word(0, l, i) >> b) & 1u) {
+          run++;
+        } else {
+          sum_sq += (long long)run * run;
+          sum += run;
+          run = 0;
+        }
+      }
+      sum_sq += (long long)run * run;
+      sum += run;
+      r_spatial += sqrt((double)sum_sq) / (double)(sum + 1);
+    }
+  }
+  o[fs] = r_spatial / (double)p.S;
+}
+
+}  // namespace orlg

@@ -204,8 +204,8 @@ __device__ __forceinline__ void write_deeprmsa_obs(Env<W, BD>& env, OUT* o, long
 }
 
 // SimpleMatrixObservation (rmsa_env.py:940-971, rmcsa_env.py:914-947): one-hot pair + unpacked slots
-template <int W, int BD>
-__device__ __forceinline__ void write_matrix_obs(Env<W, BD>& env, unsigned char* o, long long fs) {
+template <int W, int BD, typename ENV>
+__device__ __forceinline__ void write_matrix_obs(ENV& env, unsigned char* o, long long fs) {
   const Params& p = env.p;
   int mn = min(env.src, env.dst), mx = max(env.src, env.dst);
   for (int i = 0; i < p.n_nodes; i++) {

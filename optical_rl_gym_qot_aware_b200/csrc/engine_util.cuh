@@ -52,4 +52,51 @@ __global__ void requests_kernel(const Params p, orlg_request* out) {
   out[e] = r;
 }
 
+
+// PhyRMSA-v0 statistics, one warp per env: episode sums + fragmentation metrics of the current
+// channel map (phy_rmsa_env.py:1195-1203, 1110-1121).  Lanes take channels round-robin; the
+// per-channel terms are reduced with warp shuffles.  (The sums over channels are therefore
+// reassociated: number_cuts_total is an exact integer ratio, rss_total_metric agrees with the
+// reference's sequential f64 sum to ~1e-15 relative.)
+__global__ void __launch_bounds__(128) phy_stats_kernel(const Params p, int W, int BD, double* out) {
+  const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (e >= p.num_envs) return;
+  const uint32_t* tile = p.occ + (size_t)(e / BD) * p.planes * BD + (e % BD);
+  long long cuts = 0;
+  double rss = 0.0;
+  for (int ch = lane; ch < p.S; ch += 32) {
+    const int wi = ch >> 5, b = ch & 31;
+    long long sum_sq = 0;
+    int sum = 0, run = 0, prev = 0;
+    for (int l = 0; l < p.E; l++) {
+      int bit = (tile[(size_t)(l * W + wi) * BD] >> b) & 1u;
+      cuts += bit & ~prev;
+      prev = bit;
+      if (bit) {
+        run++;
+      } else {
+        sum_sq += (long long)run * run;
+        sum += run;
+        run = 0;
+      }
+    }
+    sum_sq += (long long)run * run;
+    sum += run;
+    rss += sqrt((double)sum_sq) / (double)(sum + 1);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    cuts += __shfl_xor_sync(0xFFFFFFFFu, cuts, o);
+    rss += __shfl_xor_sync(0xFFFFFFFFu, rss, o);
+  }
+  if (lane == 0) {
+    double* o = out + (size_t)e * 8;
+    o[0] = p.phy_f[e];
+    o[1] = p.phy_f[(size_t)p.NP + e];
+    for (int i = 0; i < 4; i++) o[2 + i] = (double)p.phy_i[(size_t)i * p.NP + e];
+    o[6] = (double)cuts / (double)p.S;
+    o[7] = rss / (double)p.S;
+  }
+}
+
 }  // namespace orlg

@@ -89,10 +89,18 @@ static int launch(orlg_engine* e, const StepIO& io, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   LaunchGeom g{e->BD, e->p.NP, e->device, e->smem_bytes};
   cudaError_t rc;
-  switch (e->W) {
-    case 2: rc = launch_w<2>(g, e->p, io, st); break;
-    case 4: rc = launch_w<4>(g, e->p, io, st); break;
-    default: rc = launch_w<10>(g, e->p, io, st); break;
+  if (e->p.kind == ORLG_ENV_PHYRMSA) {
+    switch (e->W) {
+      case 2: rc = launch_phy<2>(g, e->p, io, st); break;
+      case 4: rc = launch_phy<4>(g, e->p, io, st); break;
+      default: rc = launch_phy<10>(g, e->p, io, st); break;
+    }
+  } else {
+    switch (e->W) {
+      case 2: rc = launch_w<2>(g, e->p, io, st); break;
+      case 4: rc = launch_w<4>(g, e->p, io, st); break;
+      default: rc = launch_w<10>(g, e->p, io, st); break;
+    }
   }
   if (rc != cudaSuccess) {
     e->err = std::string("kernel launch: ") + cudaGetErrorString(rc);
@@ -115,8 +123,12 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   if (!c || !out) return fail_create(nullptr, ORLG_EINVAL, "null argument");
   *out = nullptr;
   if (c->abi_version != ORLG_ABI_VERSION) return fail_create(nullptr, ORLG_EINVAL, "abi_version mismatch");
-  if (c->env_kind < ORLG_ENV_RMSA || c->env_kind > ORLG_ENV_RMCSA)
+  if (c->env_kind < ORLG_ENV_RMSA || c->env_kind > ORLG_ENV_PHYRMSA)
     return fail_create(nullptr, ORLG_EINVAL, "env_kind not supported by this build");
+  const bool phy = c->env_kind == ORLG_ENV_PHYRMSA;
+  if (phy && (!c->phy_table_id || !c->phy_mod_level || !c->phy_gsnr || !c->phy_cut_links || !c->phy_cut_count ||
+              c->phy_n_tables < 1 || c->phy_max_terms < 1))
+    return fail_create(nullptr, ORLG_EINVAL, "PhyRMSA needs the QoT tables (table_id, mod_level, gsnr, cut terms)");
   if (c->num_envs < 1 || c->n_nodes < 2 || c->n_nodes > 255 || c->n_edges < 1 || c->n_edges > 255 ||
       c->k_paths < 1 || c->k_paths > 15 || c->max_hops < 1 || c->max_hops > 29 || c->num_slots < 2 ||
       c->num_slots > 320 || c->episode_length < 1)
@@ -160,7 +172,7 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   p.n_bit_rates = c->n_bit_rates;
   p.br_lo = c->bit_rate_lo;
   p.br_hi = c->bit_rate_hi;
-  p.action_dim = c->env_kind == ORLG_ENV_RMSA ? 2 : c->env_kind == ORLG_ENV_DEEPRMSA ? 1 : 4;
+  p.action_dim = c->env_kind == ORLG_ENV_RMSA ? 2 : c->env_kind == ORLG_ENV_DEEPRMSA ? 1 : phy ? PHY_ADIM : 4;
   p.cw = c->channel_width;
   {
     double x2 = 2.0 * c->channel_width;
@@ -175,7 +187,8 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   const size_t bytes_per_env = (size_t)p.planes * 4;
   int bd = 128;
   while (bd > 32 && bytes_per_env * bd > 72 * 1024) bd >>= 1;
-  if (const char* s = getenv("ORLG_BD")) {
+  if (phy) bd = 32;  // PhyRMSA kernels are instantiated for 32-env tiles only
+  if (const char* s = getenv("ORLG_BD"); s && !phy) {
     int v = atoi(s);
     if (v == 32 || v == 64 || v == 128) bd = v;
   }
@@ -226,6 +239,7 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   }
   if (c->request_source == ORLG_SRC_REPLAY || min_br < 1) min_br = 1;
   int min_slots = (int)std::ceil((double)min_br / ((double)max_se * c->channel_width)) + 1;
+  if (phy) min_slots = 1;  // one queue entry per occupied channel
   long long bound = (long long)cores * p.E * (p.S / min_slots);
   p.heap_cap = c->heap_capacity > 0 ? c->heap_capacity : (int)(bound < 16 ? 16 : bound);
   p.heap_stride = (p.heap_cap + HEAP_PAD + HEAP_TAIL + 7) & ~7;  // 128 B multiples: child groups stay line aligned
@@ -253,7 +267,34 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
     if ((rc = dev_upload(e, &p.obs_pos, pos.data(), pos.size()))) return fail_create(e, rc, e->err);
     if ((rc = dev_upload(e, &p.obs_slots, sl.data(), sl.size()))) return fail_create(e, rc, e->err);
   }
+  if (phy) {  // QoT tables, per-level channel masks, r_cut term lists
+    const size_t T = c->phy_n_tables, S = p.S, K = p.k, Wd = e->W;
+    for (size_t i = 0; i < npaths; i++)
+      if (c->phy_cut_count[i] < 0 || c->phy_cut_count[i] > 63 || c->phy_cut_count[i] > c->phy_max_terms)
+        return fail_create(e, ORLG_EINVAL, "more than 63 r_cut terms on a path");
+    std::vector<uint32_t> masks(T * K * PHY_LEVELS * Wd, 0u);
+    for (size_t t = 0; t < T; t++)
+      for (size_t ch = 0; ch < S; ch++)
+        for (size_t ip = 0; ip < K; ip++) {
+          int m = c->phy_mod_level[(t * S + ch) * K + ip];
+          if (m < 1 || m > PHY_LEVELS) return fail_create(e, ORLG_EINVAL, "modulation levels must be in 1..8");
+          masks[((t * K + ip) * PHY_LEVELS + (m - 1)) * Wd + (ch >> 5)] |= 1u << (ch & 31);
+        }
+    for (size_t i = 0; i < npairs; i++)
+      if (c->phy_table_id[i] >= c->phy_n_tables) return fail_create(e, ORLG_EINVAL, "phy_table_id out of range");
+    if ((rc = dev_upload(e, &p.phy_table_id, c->phy_table_id, npairs)) ||
+        (rc = dev_upload(e, &p.phy_mod, c->phy_mod_level, T * S * K)) ||
+        (rc = dev_upload(e, &p.phy_gsnr, c->phy_gsnr, T * S * K)) ||
+        (rc = dev_upload(e, &p.phy_level_mask, masks.data(), masks.size())) ||
+        (rc = dev_upload(e, &p.phy_cut_links, c->phy_cut_links, npaths * (size_t)c->phy_max_terms)) ||
+        (rc = dev_upload(e, &p.phy_cut_count, c->phy_cut_count, npaths)))
+      return fail_create(e, rc, e->err);
+    p.phy_max_terms = c->phy_max_terms;
+    p.phy_mask_w = e->W;
+  }
   const size_t NP = p.NP;
+  if (phy && ((rc = dev_alloc(e, &p.phy_f, 2 * NP)) || (rc = dev_alloc(e, &p.phy_i, 4 * NP))))
+    return fail_create(e, rc, e->err);
   if ((rc = dev_alloc(e, &p.occ, (size_t)p.planes * NP)) || (rc = dev_alloc(e, &p.now, NP)) ||
       (rc = dev_alloc(e, &p.holding, NP)) || (rc = dev_alloc(e, &p.meta, NP)) ||
       (rc = dev_alloc(e, &p.next_rel, NP)) || (rc = dev_alloc(e, &p.heap_len, NP)) ||
@@ -268,7 +309,13 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   } else if (c->obs_kind == ORLG_OBS_MATRIX_U8) {
     e->obs_dim = 2 * p.n_nodes + cores * p.E * p.S;
     e->obs_elem = 1;
+  } else if (c->obs_kind == ORLG_OBS_PHY_INFO || c->obs_kind == ORLG_OBS_PHY_CUTS) {
+    if (!phy) return fail_create(e, ORLG_EINVAL, "ORLG_OBS_PHY_* needs env_kind PhyRMSA");
+    e->obs_dim = c->obs_kind == ORLG_OBS_PHY_INFO ? 2 : 1;
+    e->obs_elem = 8;
   }
+  if (phy && (c->obs_kind == ORLG_OBS_F64 || c->obs_kind == ORLG_OBS_F32))
+    return fail_create(e, ORLG_EINVAL, "the DeepRMSA observation is not defined for PhyRMSA");
   *out = e;
   return ORLG_OK;
 }
@@ -309,6 +356,12 @@ static int check_source(orlg_engine* e) {
   return ORLG_OK;
 }
 
+static bool heuristic_ok(const orlg_engine* e, int hid) {
+  if (!e) return false;
+  if (e->p.kind == ORLG_ENV_PHYRMSA) return hid >= ORLG_H_PHY_SAP_FF && hid <= ORLG_H_PHY_BM_FA_CUT;
+  return hid >= ORLG_H_SP_FF && hid <= ORLG_H_SAP_BM_FC_FF;
+}
+
 static StepIO make_io(orlg_engine* e, int mode) {
   StepIO io{};
   io.mode = mode;
@@ -343,20 +396,24 @@ extern "C" int orlg_step(orlg_engine* e, const int32_t* dev_actions, int32_t* de
 }
 
 extern "C" int orlg_observation(orlg_engine* e, int obs_kind, void* dev_obs, void* stream) {
-  if (!e || !dev_obs || obs_kind < ORLG_OBS_F64 || obs_kind > ORLG_OBS_MATRIX_U8) return ORLG_EINVAL;
-  if ((obs_kind == ORLG_OBS_F64 || obs_kind == ORLG_OBS_F32) && e->p.kind == ORLG_ENV_RMCSA) return ORLG_EINVAL;
+  if (!e || !dev_obs || obs_kind < ORLG_OBS_F64 || obs_kind > ORLG_OBS_PHY_CUTS) return ORLG_EINVAL;
+  const bool deep = obs_kind == ORLG_OBS_F64 || obs_kind == ORLG_OBS_F32;
+  const bool phyobs = obs_kind == ORLG_OBS_PHY_INFO || obs_kind == ORLG_OBS_PHY_CUTS;
+  if (deep && (e->p.kind == ORLG_ENV_RMCSA || e->p.kind == ORLG_ENV_PHYRMSA)) return ORLG_EINVAL;
+  if (phyobs && e->p.kind != ORLG_ENV_PHYRMSA) return ORLG_EINVAL;
   cudaSetDevice(e->device);
   StepIO io = make_io(e, MODE_OBS);
   io.obs_kind = obs_kind;
   io.obs = dev_obs;
   if (!e->obs_es)
     io.obs_es = obs_kind == ORLG_OBS_MATRIX_U8 ? 2 * e->p.n_nodes + e->p.cores * e->p.E * e->p.S
-                                               : 1 + 2 * e->p.n_nodes + (2 * e->p.j + 3) * e->p.k;
+                : obs_kind == ORLG_OBS_PHY_INFO ? 2 : obs_kind == ORLG_OBS_PHY_CUTS ? 1
+                : 1 + 2 * e->p.n_nodes + (2 * e->p.j + 3) * e->p.k;
   return launch(e, io, stream);
 }
 
 extern "C" int orlg_heuristic(orlg_engine* e, int hid, int32_t* dev_actions, void* stream) {
-  if (!e || !dev_actions || hid < ORLG_H_SP_FF || hid > ORLG_H_SAP_BM_FC_FF) return ORLG_EINVAL;
+  if (!e || !dev_actions || !heuristic_ok(e, hid)) return ORLG_EINVAL;
   cudaSetDevice(e->device);
   StepIO io = make_io(e, MODE_HEURISTIC);
   io.heuristic = hid;
@@ -366,7 +423,7 @@ extern "C" int orlg_heuristic(orlg_engine* e, int hid, int32_t* dev_actions, voi
 }
 
 extern "C" int orlg_rollout(orlg_engine* e, int hid, int nsteps, int64_t* dev_reward_sum, void* stream) {
-  if (!e || nsteps < 1 || hid < ORLG_H_SP_FF || hid > ORLG_H_SAP_BM_FC_FF) return ORLG_EINVAL;
+  if (!e || nsteps < 1 || !heuristic_ok(e, hid)) return ORLG_EINVAL;
   if (int rc = check_source(e)) return rc;
   cudaSetDevice(e->device);
   StepIO io = make_io(e, MODE_ROLLOUT);
@@ -468,6 +525,21 @@ extern "C" int orlg_gsnr(orlg_engine* e, const int32_t* dev_query, double* dev_o
   const int warps_per_cta = 4;
   gsnr_kernel<<<(e->p.num_envs + warps_per_cta - 1) / warps_per_cta, warps_per_cta * 32, 0, (cudaStream_t)stream>>>(
       e->p, e->gp, dev_query, dev_out);
+  CK(cudaGetLastError());
+  e->launches++;
+  return ORLG_OK;
+}
+
+extern "C" int orlg_phy_get_stats(orlg_engine* e, double* dev_out, void* stream) {
+  if (!e || !dev_out) return ORLG_EINVAL;
+  if (e->p.kind != ORLG_ENV_PHYRMSA) {
+    e->err = "orlg_phy_get_stats needs env_kind PhyRMSA";
+    return ORLG_ESTATE;
+  }
+  cudaSetDevice(e->device);
+  const int warps_per_cta = 4;
+  phy_stats_kernel<<<(e->p.num_envs + warps_per_cta - 1) / warps_per_cta, warps_per_cta * 32, 0, (cudaStream_t)stream>>>(
+      e->p, e->W, e->BD, dev_out);
   CK(cudaGetLastError());
   e->launches++;
   return ORLG_OK;

@@ -1,0 +1,3 @@
+// PhyRMSA-v0 env_kernel instantiations for W = 2 words per link row (see engine_launch.cuh)
+#define ORLG_INSTANTIATE_PHY 2
+#include "engine_launch.cuh"

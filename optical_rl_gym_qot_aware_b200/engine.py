@@ -32,7 +32,7 @@ EXPORTS = (
     "orlg_action_dim", "orlg_obs_dim", "orlg_state_words", "orlg_hbm_bytes", "orlg_load_trace",
     "orlg_reset", "orlg_step", "orlg_step_host", "orlg_set_obs_layout", "orlg_observation",
     "orlg_heuristic", "orlg_rollout", "orlg_get_counters", "orlg_export_state", "orlg_get_requests",
-    "orlg_launch_count", "orlg_gsnr_configure", "orlg_gsnr",
+    "orlg_launch_count", "orlg_gsnr_configure", "orlg_gsnr", "orlg_phy_get_stats",
 )
 
 
@@ -54,6 +54,9 @@ class OrlgConfig(C.Structure):
         ("bit_rate_lo", C.c_int32), ("bit_rate_hi", C.c_int32),
         ("src_cum", C.c_void_p), ("dst_cum", C.c_void_p),
         ("heap_capacity", C.c_int32), ("obs_kind", C.c_int32), ("reserved", C.c_int32 * 6),
+        ("phy_n_tables", C.c_int32), ("phy_max_terms", C.c_int32),
+        ("phy_table_id", C.c_void_p), ("phy_mod_level", C.c_void_p), ("phy_gsnr", C.c_void_p),
+        ("phy_cut_links", C.c_void_p), ("phy_cut_count", C.c_void_p),
     ]
 
 
@@ -100,6 +103,7 @@ def load_library():
         L.orlg_get_requests.argtypes = [vp, vp, vp]
         L.orlg_gsnr_configure.argtypes = [vp, C.POINTER(OrlgGsnrParams)]
         L.orlg_gsnr.argtypes = [vp, vp, vp, vp]
+        L.orlg_phy_get_stats.argtypes = [vp, vp, vp]
         _lib = L
     return _lib
 
@@ -139,7 +143,16 @@ class Engine:
         k["bit_rate_cum"] = None if spec.bit_rate_cum is None else np.ascontiguousarray(spec.bit_rate_cum, np.float64)
         k["src_cum"] = np.ascontiguousarray(spec.src_cum, np.float64)
         k["dst_cum"] = np.ascontiguousarray(spec.dst_cum, np.float64)
+        ph = getattr(spec, "phy", None)
+        if ph is not None:
+            k["phy_table_id"] = np.ascontiguousarray(ph.table_id, np.int32)
+            k["phy_mod_level"] = np.ascontiguousarray(ph.mod_level, np.uint8)
+            k["phy_gsnr"] = np.ascontiguousarray(ph.gsnr, np.float64)
+            k["phy_cut_links"] = np.ascontiguousarray(ph.cut_links, np.uint8)
+            k["phy_cut_count"] = np.ascontiguousarray(ph.cut_count, np.int32)
         c = OrlgConfig()
+        if ph is not None:
+            c.phy_n_tables, c.phy_max_terms = ph.n_tables, ph.max_terms
         c.abi_version = self.L.orlg_abi_version()
         c.env_kind, c.device, c.num_envs = spec.env_kind, device, self.num_envs
         c.global_env_offset = global_env_offset
@@ -168,9 +181,8 @@ class Engine:
         if obs_layout == "feature_major":
             self._ck(self.L.orlg_set_obs_layout(h, 1, self.num_envs))
         self._trace = None
-        self._obs_dtype = {S.OBS_F64: torch.float64, S.OBS_F32: torch.float32, S.OBS_MATRIX_U8: torch.uint8}.get(
-            spec.obs_kind
-        )
+        self._obs_dtype = {S.OBS_F64: torch.float64, S.OBS_F32: torch.float32, S.OBS_MATRIX_U8: torch.uint8,
+                           S.OBS_PHY_INFO: torch.float64, S.OBS_PHY_CUTS: torch.float64}.get(spec.obs_kind)
 
     # -- helpers -----------------------------------------------------------
     def _ck(self, rc):
@@ -188,7 +200,8 @@ class Engine:
         """Device buffer for observations, returned as an [num_envs, obs_dim] view."""
         torch = self.torch
         dt = self._obs_dtype if kind is None else {S.OBS_F64: torch.float64, S.OBS_F32: torch.float32,
-                                                   S.OBS_MATRIX_U8: torch.uint8}[kind]
+                                                   S.OBS_MATRIX_U8: torch.uint8, S.OBS_PHY_INFO: torch.float64,
+                                                   S.OBS_PHY_CUTS: torch.float64}[kind]
         dim = self.obs_dim if kind is None else self._dim_of(kind)
         if self.obs_layout == "feature_major":
             return torch.empty((dim, self.num_envs), dtype=dt, device=self.device).t()
@@ -198,6 +211,8 @@ class Engine:
         s, t = self.spec, self.spec.tables
         if kind == S.OBS_MATRIX_U8:
             return 2 * t.n_nodes + s.num_cores * t.n_edges * s.num_slots
+        if kind in (S.OBS_PHY_INFO, S.OBS_PHY_CUTS):
+            return 2 if kind == S.OBS_PHY_INFO else 1
         return 1 + 2 * t.n_nodes + (2 * s.j + 3) * t.k_paths
 
     def _obs_base(self, obs):
@@ -252,6 +267,12 @@ class Engine:
         out = self.torch.empty((self.num_envs, REQUEST_DTYPE.itemsize), dtype=self.torch.uint8, device=self.device)
         self._ck(self.L.orlg_get_requests(self.h, self._p(out), self._stream()))
         return out.cpu().numpy().view(REQUEST_DTYPE).reshape(self.num_envs)
+
+    def phy_stats(self):
+        """PhyRMSA-v0: f64 [num_envs, 8] (see orlg_phy_get_stats in include/orlg.h)."""
+        out = self.torch.empty((self.num_envs, 8), dtype=self.torch.float64, device=self.device)
+        self._ck(self.L.orlg_phy_get_stats(self.h, self._p(out), self._stream()))
+        return out
 
     def gsnr_configure(self, gp=None):
         """gp: spec.GsnrParams (default: spec.gsnr_params(tables, channel_width))."""

@@ -22,7 +22,7 @@ from .tables import TopologyTables
 
 ENV_RMSA, ENV_DEEPRMSA, ENV_RMCSA, ENV_PHYRMSA = 0, 1, 2, 3
 SRC_REPLAY, SRC_PHILOX = 0, 1
-OBS_NONE, OBS_F64, OBS_F32, OBS_MATRIX_U8 = 0, 1, 2, 3
+OBS_NONE, OBS_F64, OBS_F32, OBS_MATRIX_U8, OBS_PHY_INFO, OBS_PHY_CUTS = 0, 1, 2, 3, 4, 5
 H_SP_FF, H_SAP_FF, H_LLP_FF, H_SAP_BM_FC_FF, H_RANDOM = 0, 1, 2, 3, 4
 H_PHY_SAP_FF, H_PHY_SAP_BM, H_PHY_BM_FF, H_PHY_BM_FA_CUT = 5, 6, 7, 8  # phy_rmsa_env.py:1676,1254,1317,1375
 
@@ -83,6 +83,8 @@ class EnvSpec:
             return 1 + 2 * t.n_nodes + (2 * self.j + 3) * t.k_paths  # deeprmsa_env.py:35-37
         if self.obs_kind == OBS_MATRIX_U8:
             return 2 * t.n_nodes + self.num_cores * t.n_edges * self.num_slots  # rmsa_env.py:943-946
+        if self.obs_kind in (OBS_PHY_INFO, OBS_PHY_CUTS):
+            return 2 if self.obs_kind == OBS_PHY_INFO else 1
         return 0
 
     @property
@@ -92,6 +94,8 @@ class EnvSpec:
             return (t.k_paths, self.num_slots)
         if self.env_kind == ENV_DEEPRMSA:
             return (t.k_paths * self.j,)
+        if self.env_kind == ENV_PHYRMSA:
+            return (-2,) + (-1,) * 8  # (-2, []) phy_rmsa_env.py:1423
         return (t.k_paths, len(t.mod_names), self.num_cores, self.num_slots)
 
 

@@ -1,0 +1,126 @@
+"""GPU parity for PhyRMSA-v0 through the C-ABI: golden traces of the unmodified reference
+(heuristic actions, accept/block, reward, done, counters, f64 episode sums, fragmentation
+metrics, final channel map) and the CPU oracle on Philox-driven envs."""
+import numpy as np
+import pytest
+
+import golden_util as G
+from optical_rl_gym_qot_aware_b200 import spec as S
+
+pytestmark = pytest.mark.gpu
+
+HEUR = {"bmfa_cut": S.H_PHY_BM_FA_CUT, "sapff": S.H_PHY_SAP_FF, "bmff": S.H_PHY_BM_FF, "sapbm": S.H_PHY_SAP_BM}
+
+
+def heuristic_of(case):
+    return next(v for k, v in HEUR.items() if k in case)
+
+
+@pytest.mark.parametrize("case", G.PHY_CASES)
+def test_engine_replays_phy_golden(case):
+    import torch
+
+    from optical_rl_gym_qot_aware_b200.engine import Engine
+
+    g, spec = G.load_case(case)
+    spec.obs_kind = S.OBS_PHY_INFO
+    hid = heuristic_of(case)
+    n_env = 3
+    eng = Engine(spec, n_env)
+    assert eng.action_dim == 9 and eng.obs_dim == 2
+    eng.load_trace(np.repeat(g["requests"][:, None], n_env, axis=1))
+    eng.reset(True)
+    dev = eng.device
+    reward = torch.zeros(n_env, dtype=torch.int32, device=dev)
+    done = torch.zeros(n_env, dtype=torch.uint8, device=dev)
+    alloc = torch.zeros((n_env, 4), dtype=torch.int32, device=dev)
+    obs = eng.new_obs()
+    hact = torch.zeros((n_env, 9), dtype=torch.int32, device=dev)
+    n = len(g["actions"])
+    for t in range(n):
+        eng.heuristic(hid, hact)
+        ha = hact.cpu().numpy()
+        assert np.array_equal(ha[0], g["actions"][t]) and np.array_equal(ha[2], g["actions"][t]), (case, t, ha[0])
+        eng.step(hact, reward, done, obs, alloc)
+        a = alloc.cpu().numpy()
+        assert a[1, 0] == g["accepted"][t] and reward.cpu().numpy()[2] == g["reward"][t], (case, t)
+        d = bool(done.cpu().numpy()[0])
+        assert d == bool(g["done"][t]), (case, t)
+        st = eng.phy_stats().cpu().numpy()
+        assert np.array_equal(st[0, :6], g["stats"][t][:6]) and np.array_equal(st[2, :6], g["stats"][t][:6]), (case, t)
+        info = obs.cpu().numpy()
+        assert info[1, 0] == g["stats"][t][6], (case, t, info[1], g["stats"][t][6:])
+        assert abs(info[1, 1] - g["stats"][t][7]) <= 1e-12 * abs(g["stats"][t][7]), (case, t)
+        if d:
+            eng.reset(False)
+        assert np.array_equal(eng.counters().cpu().numpy()[1, :8], g["counters"][t]), (case, t)
+        assert eng.requests()[0] == g["requests"][t + 1]
+    stt = eng.export_state().cpu().numpy()
+    assert np.array_equal(stt[0], g["final_avail"]) and np.array_equal(stt[2], g["final_avail"])
+    assert int(eng.counters()[:, 10].max()) == 0
+    eng.close()
+
+
+@pytest.mark.parametrize("hid,channels,load", [(S.H_PHY_BM_FA_CUT, (80, 108), 1400), (S.H_PHY_SAP_FF, (30, 40), 1500),
+                                               (S.H_PHY_BM_FF, (20, 24), 1300), (S.H_PHY_SAP_BM, (30, 40), 1600)])
+def test_phy_rollout_matches_oracle_on_philox(hid, channels, load):
+    import torch
+
+    import oracle_binding as OB
+    from optical_rl_gym_qot_aware_b200.engine import Engine
+
+    g, spec0 = G.load_case("phy_us14_bmfa_cut")
+    ph = np.load(G.os.path.join(G.GOLDEN, f"phytab_{str(g['tables_key'])}.npz"))
+    spec = S.make_spec("PhyRMSA-v0", spec0.tables, seed=77, load=load, mean_service_holding_time=25, episode_length=120,
+                       auto_reset=True, modulation_level=ph["phy_mod"], connections_detail=ph["phy_conn"],
+                       gsnr=ph["phy_gsnr"], number_spectrum_channels=channels[0],
+                       number_spectrum_channels_s_band=channels[1])
+    big = channels[0] == 80
+    n_env, n_steps = (40, 400) if big else (150, 1500)
+    o_steps, o_cnt, o_state, o_rsum = OB.rollout_many(spec, 3, n_env, n_steps, hid, 8, want_state=True)
+    eng = Engine(spec, n_env, global_env_offset=3)
+    eng.reset(True)
+    rsum = torch.zeros(n_env, dtype=torch.int64, device=eng.device)
+    eng.rollout(hid, n_steps // 3, rsum)
+    eng.rollout(hid, n_steps - n_steps // 3, rsum)
+    cnt = eng.counters().cpu().numpy()
+    assert int(cnt[:, 10].max()) == 0
+    assert np.array_equal(cnt[:, :9], o_cnt[:, :9])
+    assert np.array_equal(cnt[:, 11], o_cnt[:, 11])
+    assert np.array_equal(rsum.cpu().numpy(), o_rsum)
+    assert np.array_equal(eng.export_state().cpu().numpy(), o_state)
+    if not big:
+        assert (cnt[:, 1] < cnt[:, 0]).any(), "the case should see blocking"
+    # episode sums and current-map metrics against single oracle envs
+    st = eng.phy_stats().cpu().numpy()
+    for i in (0, n_env - 1):
+        o = OB.OracleEnv(spec, 3 + i)
+        o.reset(True)
+        for _ in range(n_steps):
+            o.step(o.heuristic(hid))
+        ost = o.phy_stats()
+        assert np.array_equal(st[i, :6], ost[:6]), (i, st[i], ost)
+    eng.close()
+
+
+def test_phy_invalid_actions_are_rejections():
+    import torch
+
+    from optical_rl_gym_qot_aware_b200.engine import Engine
+
+    g, spec = G.load_case("phy_jpn12_bmfa_cut_64ch")
+    spec.request_source = S.SRC_PHILOX
+    n = 6
+    eng = Engine(spec, n)
+    eng.reset(True)
+    C = spec.num_slots
+    acts = torch.tensor([[-2] + [-1] * 8, [0, C, -1, -1, -1, -1, -1, -1, -1], [0, 3, 3, -1, -1, -1, -1, -1, -1],
+                         [spec.tables.k_paths, 1, -1, -1, -1, -1, -1, -1, -1], [0] + [-1] * 8,
+                         [0, 5, 6, -1, -1, -1, -1, -1, -1]], dtype=torch.int32, device=eng.device)
+    alloc = torch.zeros((n, 4), dtype=torch.int32, device=eng.device)
+    eng.step(acts, None, None, None, alloc)
+    a = alloc.cpu().numpy()
+    assert a[:5, 0].tolist() == [0, 0, 0, 0, 0] and a[5].tolist() == [1, 0, 5, 2]
+    st = eng.export_state().cpu().numpy()
+    assert st[:5].min() == 1 and st[5].sum() < st[0].sum()
+    eng.close()
