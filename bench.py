@@ -69,13 +69,25 @@ WORKLOADS = {
                                                num_spectrum_resources=320, episode_length=1000),
                         S.H_SAP_FF, S.OBS_NONE, 1039),
 }
+# C4: PhyRMSA-v0 (phy-frag) on US14 with 320 channels.  The shipped QoT tables have 268 channels
+# (SURVEY.md F4); the synthetic 320-channel tables keep them and replicate the S-band tail.
+WORKLOADS["c4_phyrmsa_us14_320"] = ("PhyRMSA-v0", "us14", dict(load=1400, mean_service_holding_time=25,
+                                                               episode_length=200, number_spectrum_channels=160,
+                                                               s_band=False),
+                                    S.H_PHY_BM_FA_CUT, S.OBS_PHY_CUTS, 1426)
 DEFAULT_WORKLOAD = "c2_deeprmsa_nsfnet_100"
 PREROLL = 600  # steps run before any timing so that the networks are in steady state
+PREROLL_OF = {"c4_phyrmsa_us14_320": 6000, "c3_rmcsa_jpn12_320": 1500}  # loads of 1400 / 250 Erlang fill up slowly
 
 
 def make_workload(name, seed=0x5EED):
     env_id, topo, kw, hid, obs_kind, bytes_per_step = WORKLOADS[name]
     tables = TopologyTables.load(os.path.join(GOLDEN, f"topology_{topo}.npz"))
+    if env_id == "PhyRMSA-v0":
+        z = np.load(os.path.join(GOLDEN, "phytab_Results_K3SP_FRP_SLC_CBG_USB14.npz"))
+        cols = np.concatenate([np.arange(268), np.arange(268 - 52, 268)])  # 320 channels
+        kw = dict(kw, modulation_level=z["phy_mod"][:, cols], gsnr=z["phy_gsnr"][:, cols],
+                  connections_detail=z["phy_conn"])
     spec = S.make_spec(env_id, tables, seed=seed, request_source=S.SRC_PHILOX, auto_reset=True,
                        obs_kind=obs_kind, **kw)
     return spec, hid, bytes_per_step, env_id
@@ -166,12 +178,12 @@ def host_policy_kspff(obs_fm, n_nodes, k, j, out=None):
     return out
 
 
-def cpu_arm(spec, hid, n_sample, min_seconds, threads, steps=None, warmup=0):
+def cpu_arm(spec, hid, n_sample, min_seconds, threads, steps=None, warmup=0, preroll=PREROLL):
     """Times the oracle port on host threads.  Returns (steps/s, ms per pass, passes)."""
     import oracle_binding as OB
 
     pool = OB.OraclePool(spec, 0, n_sample)
-    pool.rollout(PREROLL, hid, threads)
+    pool.rollout(preroll, hid, threads)
     for _ in range(warmup):
         pool.rollout(1, hid, threads)
     done_steps, passes = 0, 0
@@ -197,7 +209,9 @@ def run_reference(args, spec, hid, env_id, wl):
         return
     threads = os.cpu_count() or 1
     n_sample = args.ref_envs
-    v, ms, passes, blocking = cpu_arm(spec, hid, n_sample, 0, threads, steps=args.steps, warmup=args.warmup)
+    PREROLL = PREROLL_OF.get(wl, 600)
+    v, ms, passes, blocking = cpu_arm(spec, hid, n_sample, 0, threads, steps=args.steps, warmup=args.warmup,
+                                      preroll=PREROLL)
     sample = (f"{n_sample} envs of the {args.envs}-env batch per pass, oracle C port (oracle/orlg_oracle.c) "
               f"with its own heuristic, {threads} pthreads, {PREROLL} pre-roll steps")
     line = {
@@ -231,6 +245,7 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
         import torch.distributed as dist
 
         dist.init_process_group("nccl", device_id=dev)
+    PREROLL = PREROLL_OF.get(wl, 600)
     n_env = args.envs
     eng = Engine(spec, n_env, device=local, global_env_offset=rank * n_env)
     eng.reset(True)
@@ -302,7 +317,8 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
     use_obs_policy = env_id == "DeepRMSA-v0" and eng.obs_dim > 0
     h_obs = None
     if eng.obs_dim:
-        odt = {S.OBS_F64: torch.float64, S.OBS_F32: torch.float32, S.OBS_MATRIX_U8: torch.uint8}[spec.obs_kind]
+        odt = {S.OBS_F64: torch.float64, S.OBS_F32: torch.float32, S.OBS_MATRIX_U8: torch.uint8,
+               S.OBS_PHY_INFO: torch.float64, S.OBS_PHY_CUTS: torch.float64}[spec.obs_kind]
         h_obs = torch.zeros((eng.obs_dim, n_env), dtype=odt).pin_memory()  # feature-major, as the device buffer
         eng.observation(obs)
         h_obs.copy_(obs.t())
@@ -377,7 +393,8 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
         "data": "synthetic (Philox request streams, seed 0x5eed, keyed by global env id)",
         "config": {
             "workload": wl, "env": env_id, "envs_per_gpu": n_env, "heuristic": int(hid),
-            "obs": {0: "none", 1: "f64", 2: "f32", 3: "matrix_u8"}[spec.obs_kind],
+            "obs": {0: "none", 1: "f64", 2: "f32", 3: "matrix_u8", 4: "phy cuts+rss f64", 5: "phy cuts f64"}[
+                spec.obs_kind],
             "step": "orlg_heuristic + orlg_step (2 launches), actions/obs/reward/done resident in HBM",
             "l2": ("flushed before every step by a 256 MiB fill outside the per-step event pairs"
                    if not args.no_flush else "not flushed (state may be L2 resident)"),
@@ -400,7 +417,7 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
     }
     if world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
-        v, ms, passes, blk = cpu_arm(spec, hid, args.ref_envs, args.cpu_seconds, threads)
+        v, ms, passes, blk = cpu_arm(spec, hid, args.ref_envs, args.cpu_seconds, threads, preroll=PREROLL)
         line["cpu_baseline"] = {
             "value": v, "unit": "env-steps/s", "cores": threads, "kind": "port",
             "sample": (f"{args.ref_envs} envs x {passes} steps of the same workload (blocking {blk:.3f}), oracle C port "

@@ -34,6 +34,9 @@ HEURISTICS = {
     "least_loaded_path_first_fit": S.H_LLP_FF, "llp_ff": S.H_LLP_FF,
     "shortest_available_path_best_modulation_first_core_first_fit": S.H_SAP_BM_FC_FF,
     "sap_bm_fc_ff": S.H_SAP_BM_FC_FF,
+    # PhyRMSA-v0 (phy_rmsa_env.py), physical layer
+    "sapff_rmsa": S.H_PHY_SAP_FF, "phy_aware_sapbm_rmsa": S.H_PHY_SAP_BM, "phy_aware_bmff_rmsa": S.H_PHY_BM_FF,
+    "phy_aware_bmfa_rmsa": S.H_PHY_BM_FA_CUT, "bm_fa_cut": S.H_PHY_BM_FA_CUT,
 }
 
 
@@ -90,10 +93,11 @@ class BatchedEnv:
         self.env_id = env_id
         tables = _as_tables(topology)
         kind = S.ENV_IDS[env_id]
-        if kind == S.ENV_PHYRMSA:
-            raise NotImplementedError("PhyRMSA-v0 is not built yet (SURVEY.md section 8, rows a16-a20)")
         obs_kind = None
-        if observation == "matrix":  # SimpleMatrixObservation rmsa_env.py:940-971
+        if kind == S.ENV_PHYRMSA and observation in ("info", "cuts"):
+            # the step's number_cuts_total (and rss_total_metric): what UseInfoReward feeds back
+            obs_kind = S.OBS_PHY_INFO if observation == "info" else S.OBS_PHY_CUTS
+        elif observation == "matrix":  # SimpleMatrixObservation rmsa_env.py:940-971
             obs_kind = S.OBS_MATRIX_U8
         elif kind == S.ENV_DEEPRMSA:
             obs_kind = S.OBS_F32 if obs_dtype in ("float32", "f32") else S.OBS_F64
@@ -119,6 +123,8 @@ class BatchedEnv:
             self.action_space = MultiDiscrete((t.k_paths + rej, self.spec.num_slots + rej))
         elif kind == S.ENV_DEEPRMSA:  # deeprmsa_env.py:35-43
             self.action_space = Discrete(t.k_paths * self.j + rej)
+        elif kind == S.ENV_PHYRMSA:  # the reference declares (k, S) (phy_rmsa_env.py:251-256) but takes (path, channels)
+            self.action_space = MultiDiscrete((t.k_paths + rej,) + (self.spec.num_slots,) * 8)
         else:  # rmcsa_env.py:181-194
             self.action_space = MultiDiscrete((t.k_paths + rej, len(t.mod_names) + rej,
                                                self.spec.num_cores + rej, self.spec.num_slots + rej))
@@ -127,6 +133,8 @@ class BatchedEnv:
                                          np.float64 if self.spec.obs_kind == S.OBS_F64 else np.float32)
         elif self.spec.obs_kind == S.OBS_MATRIX_U8:
             self.observation_space = Box(0, 1, (self.engine.obs_dim,), np.uint8)
+        elif self.spec.obs_kind in (S.OBS_PHY_INFO, S.OBS_PHY_CUTS):
+            self.observation_space = Box(0, np.inf, (self.engine.obs_dim,), np.float64)
         else:
             self.observation_space = None
         n, dev = self.num_envs, self.device
@@ -195,6 +203,21 @@ class BatchedEnv:
     # -- views ------------------------------------------------------------------------------------
     def counters(self):
         return self.engine.counters()
+
+    def phy_info(self) -> Dict[str, Any]:
+        """PhyRMSA-v0: the remaining entries of the reference's info dict (phy_rmsa_env.py:319-348),
+        per env, with the fragmentation metrics of the current channel map."""
+        st = self.engine.phy_stats()
+        return {
+            "number_cuts_total": st[:, 6], "rss_total_metric": st[:, 7],
+            "total_path_length": st[:, 0] / (st[:, 5] + 1), "avrage_gsnr": st[:, 1] / (st[:, 4] + 1),
+            "average_mod_level": st[:, 3] / (st[:, 4] + 1), "average_path_index": st[:, 2] / (st[:, 5] + 1),
+            "path_index": st[:, 2], "physical_paths": st[:, 5],
+        }
+
+    def available_channels(self):
+        """PhyRMSA-v0: topology.graph["available_channels"] of every env, uint8 [num_envs, E, C]."""
+        return self.engine.export_state()[:, 0]
 
     def available_slots(self):
         """topology.graph["available_slots"] of every env: uint8 [num_envs, cores, E, S]."""
@@ -299,6 +322,9 @@ class GymEnv:
                             "episode_bit_rate_blocking_rate"]}
 
     def __init__(self, env_id: str, topology, **kwargs):
+        self._phy = S.ENV_IDS[env_id] == S.ENV_PHYRMSA
+        if self._phy:
+            kwargs.setdefault("observation", "info")  # number_cuts_total / rss_total_metric at the reference's point
         self._b = BatchedEnv(env_id, topology, num_envs=1, **kwargs)
         for name in ("k_paths", "j", "num_spectrum_resources", "num_spatial_resources", "episode_length",
                      "allow_rejection", "load", "mean_service_holding_time", "mean_service_inter_arrival_time",
@@ -332,7 +358,22 @@ class GymEnv:
     episode_bit_rate_provisioned = property(lambda s: s._counter(7))
 
     def _obs_np(self, obs):
-        return None if obs is None else obs[0].cpu().numpy().copy()
+        if obs is None or self._phy:  # rmsa_env.py:697-701 / phy_rmsa_env.py: {"topology", "current_service"}
+            return {"topology": self.topology, "current_service": self.current_service}
+        return obs[0].cpu().numpy().copy()
+
+    def _phy_action(self, action):
+        """(path, [(channel, used, free, capacity, virtual), ...]) of the reference heuristics
+        (phy_rmsa_env.py:1429-1432) or a flat (path, ch0, ch1, ...) -> the engine's 9 ints."""
+        a = np.full(9, -1, np.int64)
+        if len(action) == 2 and isinstance(action[1], (list, tuple)):
+            a[0] = action[0]
+            for i, c in enumerate(action[1][:8]):
+                a[1 + i] = c[0] if isinstance(c, (list, tuple)) else c
+        else:
+            flat = np.asarray(action, dtype=np.int64).reshape(-1)
+            a[: len(flat)] = flat
+        return a
 
     def reset(self, only_episode_counters: bool = True):
         return self._obs_np(self._b.reset(only_episode_counters))
@@ -341,13 +382,36 @@ class GymEnv:
         return self._obs_np(self._b.observation())
 
     def step(self, action):
+        """4-tuple like rmsa_env.py:336-341; PhyRMSA-v0 returns the reference's 5-tuple
+        (obs, reward, done, False, info) of phy_rmsa_env.py:418-424."""
+        if self._phy:
+            action = self._phy_action(action)
         obs, rew, done, info = self._b.step(np.atleast_1d(np.asarray(action, dtype=np.int64))[None])
         i = {k: (float(v[0]) if v.dtype.is_floating_point else int(v[0])) for k, v in self._b.info().items()}
         i.update({k: int(v[0]) for k, v in info.items()})
+        if self._phy:
+            i.update({k: float(v[0]) for k, v in self._b.phy_info().items()})
+            if obs is not None:  # the step's own metrics, taken before the releases (phy_rmsa_env.py:313-314)
+                m = obs[0].cpu().numpy()
+                i["number_cuts_total"] = float(m[0])
+                if m.size > 1:
+                    i["rss_total_metric"] = float(m[1])
+            return self._obs_np(obs), int(rew[0]), bool(done[0]), False, i
         return self._obs_np(obs), int(rew[0]), bool(done[0]), i
 
     def heuristic(self, name):
         a = self._b.heuristic(name)[0].cpu().numpy()
+        if self._phy:  # rebuild the reference's channel tuples (channel, used, free, capacity, False)
+            if a[0] < 0:
+                return (-2, [])
+            ph, t, cs = self.spec.phy, self.tables, self._b.current_requests()[0]
+            table = ph.table_id[int(cs["src"]) * t.n_nodes + int(cs["dst"])]
+            un, out = int(cs["bit_rate"]), []
+            for ch in [int(c) for c in a[1:] if c >= 0]:
+                lvl = int(ph.mod_level[table, ch, int(a[0])])
+                un -= lvl * 100
+                out.append((ch, lvl + un / 100, un / -100, lvl, False) if un <= 0 else (ch, lvl, 0, lvl, False))
+            return (int(a[0]), out)
         return int(a[0]) if a.size == 1 else tuple(int(x) for x in a)
 
     def load_trace(self, trace):
@@ -369,9 +433,11 @@ class _GraphView(dict):
         self._env = env
 
     def __getitem__(self, key):
-        if key == "available_slots":
+        if key in ("available_slots", "available_channels"):
             a = self._env._b.available_slots()[0].cpu().numpy().astype(np.int64)
             return a if self._env._b.spec.env_kind == S.ENV_RMCSA else a[0]
+        if key == "num_channel_resources":
+            return self._env.num_spectrum_resources
         return super().__getitem__(key)
 
 
@@ -388,3 +454,20 @@ def make(env_id: str, topology=None, num_envs: Optional[int] = None, vec_env: bo
     if vec_env:
         return OrlgVecEnv(env_id, topology, num_envs, **kwargs)
     return BatchedEnv(env_id, topology, num_envs=num_envs, **kwargs)
+
+
+class UseInfoReward:
+    """wrappers.py:4-16: replace the reward by ``info[key]``.  With PhyRMSA-v0 and
+    ``key in ("number_cuts_total", "rss_total_metric")`` this is the physical-layer
+    fragmentation-aware reward of the phy-frag configuration."""
+
+    def __init__(self, env, key: str):
+        self.env, self.key = env, key
+
+    def __getattr__(self, name):
+        return getattr(self.env, name)
+
+    def step(self, action):
+        out = self.env.step(action)
+        info = out[-1]
+        return (out[0], info[self.key]) + tuple(out[2:])

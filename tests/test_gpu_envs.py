@@ -140,3 +140,38 @@ def test_matrix_observation_matches_oracle():
             o.step(o.heuristic(S.H_SAP_BM_FC_FF))
         assert np.array_equal(obs[i].cpu().numpy(), o.matrix_observation())
     eng.close()
+
+
+def test_phy_scalar_env_five_tuple_and_info_reward():
+    """make("PhyRMSA-v0") -> 5-tuple step, reference-format heuristic actions, info
+    metrics at the reference's point in the step, UseInfoReward."""
+    import optical_rl_gym_qot_aware_b200 as pkg
+    from optical_rl_gym_qot_aware_b200.envs import UseInfoReward
+
+    g, spec = G.load_case("phy_us14_bmfa_cut_100ch")
+    z = np.load(G.os.path.join(G.GOLDEN, f"phytab_{str(g['tables_key'])}.npz"))
+    kw = _kwargs(g)
+    kw.pop("num_spectrum_resources")
+    kw.pop("bit_rate_selection")
+    env = pkg.make("PhyRMSA-v0", topology=spec.tables, request_source="replay", modulation_level=z["phy_mod"],
+                   connections_detail=z["phy_conn"], gsnr=z["phy_gsnr"], **kw)
+    env.load_trace(g["requests"])
+    wrapped = UseInfoReward(env, "number_cuts_total")
+    for t in range(300):
+        path, chans = env.heuristic("phy_aware_bmfa_rmsa")
+        want = g["actions"][t]
+        assert path == want[0] and [c[0] for c in chans] == [c for c in want[1:] if c >= 0], t
+        if chans:  # the last channel may be partially used (phy_rmsa_env.py:1429)
+            assert all(c[1] == c[3] and c[2] == 0 for c in chans[:-1]) and chans[-1][1] + chans[-1][2] == chans[-1][3]
+        out = wrapped.step((path, chans)) if t % 2 else env.step((path, chans))
+        assert len(out) == 5 and out[3] is False
+        obs, r, d, _, info = out
+        assert info["accepted"] == int(g["accepted"][t]) and d == bool(g["done"][t])
+        assert info["number_cuts_total"] == g["stats"][t][6]
+        assert abs(info["rss_total_metric"] - g["stats"][t][7]) < 1e-12
+        assert r == (info["number_cuts_total"] if t % 2 else int(g["reward"][t]))
+        assert set(obs) == {"topology", "current_service"}
+        if d:
+            env.reset()
+    assert env.topology.graph["available_channels"].shape == (spec.tables.n_edges, spec.num_slots)
+    env.close()
