@@ -66,7 +66,9 @@ enum {
   ORLG_H_PHY_SAP_FF = 5,     /* sapff_rmsa           phy_rmsa_env.py:1676-1737 */
   ORLG_H_PHY_SAP_BM = 6,     /* phy_aware_sapbm_rmsa phy_rmsa_env.py:1254-1314 */
   ORLG_H_PHY_BM_FF = 7,      /* phy_aware_bmff_rmsa  phy_rmsa_env.py:1317-1372 */
-  ORLG_H_PHY_BM_FA_CUT = 8   /* phy_aware_bmfa_rmsa  phy_rmsa_env.py:1375-1438 */
+  ORLG_H_PHY_BM_FA_CUT = 8,  /* phy_aware_bmfa_rmsa  phy_rmsa_env.py:1375-1438 */
+  ORLG_H_PATH_FF = 9,        /* PathOnlyFirstFitAction rmsa_env.py:974-1008 (orlg_path_first_fit only) */
+  ORLG_H_PHY_FA_FF = 10      /* phy_aware_faff_rmsa  phy_rmsa_env.py:1508-1569 */
 };
 
 enum {
@@ -210,6 +212,11 @@ int orlg_observation(orlg_engine* e, int obs_kind, void* dev_obs, void* stream);
 
 /* Device-side heuristic: writes the action the reference heuristic would return. */
 int orlg_heuristic(orlg_engine* e, int heuristic_id, int32_t* dev_actions, void* stream);
+
+/* PathOnlyFirstFitAction.action (rmsa_env.py:982-1005), RMSA-v0 only: dev_paths int32[num_envs]
+ * (path index or k_paths = reject) -> dev_actions int32[num_envs][2] = (path, first-fit slot) or
+ * (k_paths, num_slots). */
+int orlg_path_first_fit(orlg_engine* e, const int32_t* dev_paths, int32_t* dev_actions, void* stream);
 
 /* nsteps x (heuristic -> step) in one launch, state staged on chip between steps.
  * dev_reward_sum (optional) int64[num_envs] accumulates rewards. */

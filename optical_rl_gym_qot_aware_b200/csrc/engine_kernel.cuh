@@ -137,7 +137,9 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
 #pragma unroll
       for (int i = 0; i < ADIM; i++) io.actions_out[(size_t)e * ADIM + i] = a[i];
     } else if (mode == MODE_HEURISTIC) {
-      if constexpr (!PHY) heuristic_action<W, BD>(env, io.heuristic, a);
+      if constexpr (!PHY)
+        heuristic_action<W, BD>(env, io.heuristic, a,
+                                (io.heuristic == ORLG_H_PATH_FF && io.actions) ? io.actions[e] : 0);
       if (p.action_dim == 1) {
         io.actions_out[e] = a[0];
       } else if (p.action_dim == 2) {

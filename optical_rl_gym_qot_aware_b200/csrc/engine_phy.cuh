@@ -144,12 +144,18 @@ __device__ void phy_heuristic(ENV& env, int hid, int* a) {
       }
       continue;
     }
-    // BM-FA-Cut :1414-1421: head of the row = (highest level, highest r_cut inside it)
+    // BM-FA-Cut :1414-1421: head of the row = (highest level, highest r_cut inside it);
+    // FA-FF :1546-1550: head = highest r_cut over the whole row, levels ignored
     CutPlanes<W> cp;
     const int pathg = pr * p.k + idp;
     count_terms<W, BD>(env, pathg, cp);
-    Row<W> cand = level_mask<W>(p, table, idp, head);
-    and_into(cand, A);
+    Row<W> cand = A;
+    if (hid == ORLG_H_PHY_FA_FF) {
+      head = 0;
+    } else {
+      cand = level_mask<W>(p, table, idp, head);
+      and_into(cand, A);
+    }
     Row<W> s = min_count_subset<W>(cand, cp);
     int frag = __ldg(p.phy_cut_count + pathg) - 2 * count_at<W>(cp, lowest_set<W>(s));
     if (head > best_mod || (head == best_mod && frag > best_frag)) {
@@ -163,9 +169,13 @@ __device__ void phy_heuristic(ENV& env, int hid, int* a) {
   PathRec rec = load_path(p, pr, best);
   Row<W> A = env.tile.path_avail(rec, 0);
   int need = env.bit_rate, n = 0;
-  if (hid == ORLG_H_PHY_SAP_FF) {  // ascending channel number, whatever the level (:1704)
+  if (hid == ORLG_H_PHY_SAP_FF || hid == ORLG_H_PHY_FA_FF) {
+    // SAP-FF: ascending channel number, whatever the level (:1704); FA-FF: descending r_cut, then
+    // ascending channel (:1537); each channel counts with its own level
+    CutPlanes<W> cp;
+    if (hid == ORLG_H_PHY_FA_FF) count_terms<W, BD>(env, pr * p.k + best, cp);
     while (need > 0 && n < PHY_ADIM - 1) {
-      int ch = lowest_set<W>(A);
+      int ch = lowest_set<W>(hid == ORLG_H_PHY_FA_FF ? min_count_subset<W>(A, cp) : A);
       if (ch < 0) break;
       row_clear_bit<W>(A, ch);
       a[1 + n++] = ch;

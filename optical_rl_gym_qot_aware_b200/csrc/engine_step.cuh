@@ -94,10 +94,23 @@ __device__ __forceinline__ Decision rmcsa_decide(Env<W, BD>& env, int path, int 
 
 // Reference heuristics; `a` receives action_dim ints.
 template <int W, int BD>
-__device__ __forceinline__ void heuristic_action(Env<W, BD>& env, int hid, int* a) {
+__device__ __forceinline__ void heuristic_action(Env<W, BD>& env, int hid, int* a, int in_path = 0) {
   const Params& p = env.p;
   int pr = env.pair();
-  if (p.kind == ORLG_ENV_RMSA) {
+  if (p.kind == ORLG_ENV_RMSA && hid == ORLG_H_PATH_FF) {  // PathOnlyFirstFitAction rmsa_env.py:982-1005
+    a[0] = p.k;
+    a[1] = p.S;
+    if (in_path >= 0 && in_path < p.k) {
+      PathRec rec = load_path(p, pr, in_path);
+      if (rec.hops() > 0) {
+        int s = first_fit<W>(env.tile.path_avail(rec, 0), number_slots(env.bit_rate, rec.se(), p), p.S);
+        if (s >= 0) {
+          a[0] = in_path;
+          a[1] = s;
+        }
+      }
+    }
+  } else if (p.kind == ORLG_ENV_RMSA) {
     a[0] = p.k;
     a[1] = p.S;
     long long best_free = 0;

@@ -358,7 +358,8 @@ static int check_source(orlg_engine* e) {
 
 static bool heuristic_ok(const orlg_engine* e, int hid) {
   if (!e) return false;
-  if (e->p.kind == ORLG_ENV_PHYRMSA) return hid >= ORLG_H_PHY_SAP_FF && hid <= ORLG_H_PHY_BM_FA_CUT;
+  if (e->p.kind == ORLG_ENV_PHYRMSA)
+    return (hid >= ORLG_H_PHY_SAP_FF && hid <= ORLG_H_PHY_BM_FA_CUT) || hid == ORLG_H_PHY_FA_FF;
   return hid >= ORLG_H_SP_FF && hid <= ORLG_H_SAP_BM_FC_FF;
 }
 
@@ -417,6 +418,21 @@ extern "C" int orlg_heuristic(orlg_engine* e, int hid, int32_t* dev_actions, voi
   cudaSetDevice(e->device);
   StepIO io = make_io(e, MODE_HEURISTIC);
   io.heuristic = hid;
+  io.actions_out = dev_actions;
+  io.obs = nullptr;
+  return launch(e, io, stream);
+}
+
+extern "C" int orlg_path_first_fit(orlg_engine* e, const int32_t* dev_paths, int32_t* dev_actions, void* stream) {
+  if (!e || !dev_paths || !dev_actions) return ORLG_EINVAL;
+  if (e->p.kind != ORLG_ENV_RMSA) {
+    e->err = "orlg_path_first_fit is defined for RMSA-v0 (rmsa_env.py:974-1008)";
+    return ORLG_ESTATE;
+  }
+  cudaSetDevice(e->device);
+  StepIO io = make_io(e, MODE_HEURISTIC);
+  io.heuristic = ORLG_H_PATH_FF;
+  io.actions = dev_paths;
   io.actions_out = dev_actions;
   io.obs = nullptr;
   return launch(e, io, stream);

@@ -32,7 +32,7 @@ EXPORTS = (
     "orlg_action_dim", "orlg_obs_dim", "orlg_state_words", "orlg_hbm_bytes", "orlg_load_trace",
     "orlg_reset", "orlg_step", "orlg_step_host", "orlg_set_obs_layout", "orlg_observation",
     "orlg_heuristic", "orlg_rollout", "orlg_get_counters", "orlg_export_state", "orlg_get_requests",
-    "orlg_launch_count", "orlg_gsnr_configure", "orlg_gsnr", "orlg_phy_get_stats",
+    "orlg_launch_count", "orlg_gsnr_configure", "orlg_gsnr", "orlg_phy_get_stats", "orlg_path_first_fit",
 )
 
 
@@ -104,6 +104,7 @@ def load_library():
         L.orlg_gsnr_configure.argtypes = [vp, C.POINTER(OrlgGsnrParams)]
         L.orlg_gsnr.argtypes = [vp, vp, vp, vp]
         L.orlg_phy_get_stats.argtypes = [vp, vp, vp]
+        L.orlg_path_first_fit.argtypes = [vp, vp, vp, vp]
         _lib = L
     return _lib
 
@@ -247,6 +248,11 @@ class Engine:
 
     def heuristic(self, heuristic_id, actions):
         self._ck(self.L.orlg_heuristic(self.h, heuristic_id, self._p(actions), self._stream()))
+
+    def path_first_fit(self, paths, actions):
+        """PathOnlyFirstFitAction (rmsa_env.py:974-1008): int32 [num_envs] paths -> [num_envs, 2] actions."""
+        assert paths.dtype == self.torch.int32 and paths.is_cuda and paths.is_contiguous()
+        self._ck(self.L.orlg_path_first_fit(self.h, self._p(paths), self._p(actions), self._stream()))
 
     def rollout(self, heuristic_id, nsteps, reward_sum=None):
         self._ck(self.L.orlg_rollout(self.h, heuristic_id, int(nsteps), self._p(reward_sum), self._stream()))

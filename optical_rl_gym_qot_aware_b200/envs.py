@@ -37,6 +37,7 @@ HEURISTICS = {
     # PhyRMSA-v0 (phy_rmsa_env.py), physical layer
     "sapff_rmsa": S.H_PHY_SAP_FF, "phy_aware_sapbm_rmsa": S.H_PHY_SAP_BM, "phy_aware_bmff_rmsa": S.H_PHY_BM_FF,
     "phy_aware_bmfa_rmsa": S.H_PHY_BM_FA_CUT, "bm_fa_cut": S.H_PHY_BM_FA_CUT,
+    "phy_aware_faff_rmsa": S.H_PHY_FA_FF, "fa_ff": S.H_PHY_FA_FF,
 }
 
 
@@ -454,6 +455,29 @@ def make(env_id: str, topology=None, num_envs: Optional[int] = None, vec_env: bo
     if vec_env:
         return OrlgVecEnv(env_id, topology, num_envs, **kwargs)
     return BatchedEnv(env_id, topology, num_envs=num_envs, **kwargs)
+
+
+class PathOnlyFirstFitAction:
+    """rmsa_env.py:974-1008: the agent picks only the path; the first fitting slot is found on
+    the device (``orlg_path_first_fit``).  Wraps a :class:`BatchedEnv` of RMSA-v0."""
+
+    def __init__(self, env: BatchedEnv):
+        assert env.spec.env_kind == S.ENV_RMSA
+        self.env = env
+        self.action_space = Discrete(env.k_paths + (1 if env.allow_rejection else 0))
+        self.observation_space = env.observation_space
+
+    def __getattr__(self, name):
+        return getattr(self.env, name)
+
+    def action(self, paths):
+        torch = self.env.torch
+        p = torch.as_tensor(paths, device=self.env.device).to(torch.int32).reshape(self.env.num_envs).contiguous()
+        self.env.engine.path_first_fit(p, self.env._actions)
+        return self.env._actions
+
+    def step(self, paths):
+        return self.env.step(self.action(paths))
 
 
 class UseInfoReward:

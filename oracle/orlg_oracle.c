@@ -457,6 +457,7 @@ typedef struct phy_cand { int mod, frag, ch, idp; } phy_cand;
 static int cand_before(const phy_cand* a, const phy_cand* b, int hid) {
   if (hid == 5) return a->ch < b->ch;                                  /* sapff_rmsa :1704 key x[1] */
   if (hid == 6 || hid == 7) return a->mod != b->mod ? a->mod > b->mod : a->ch < b->ch; /* (-mod, ch) :1282,1343 */
+  if (hid == 10) return a->frag > b->frag;                            /* phy_aware_faff_rmsa key (-frag) :1537 */
   return a->mod != b->mod ? a->mod > b->mod : a->frag > b->frag;      /* (-mod, -frag) :1405 */
 }
 
@@ -476,7 +477,7 @@ static void phy_heuristic(oracle_env* e, int hid, int32_t* a) {
     if (hops_of(e, pair, idp) <= 0) continue;
     for (int ch = 0; ch < C; ch++) {
       if (!is_channel_free(e, pair, idp, ch)) continue;
-      phy_cand c = {phy_level(e, table, ch, idp), hid == 8 ? calculate_r_cut(e, pair, idp, ch) : 0, ch, idp};
+      phy_cand c = {phy_level(e, table, ch, idp), (hid == 8 || hid == 10) ? calculate_r_cut(e, pair, idp, ch) : 0, ch, idp};
       int pos = len[idp]++;
       while (pos > 0 && cand_before(&c, &row[pos - 1], hid)) { row[pos] = row[pos - 1]; pos--; }
       row[pos] = c;
@@ -492,6 +493,7 @@ static void phy_heuristic(oracle_env* e, int hid, int32_t* a) {
       if (best < 0) { best = i; continue; }
       const phy_cand* bh = rows + (size_t)best * C;
       if (hid == 7) { if (hd->mod > bh->mod) best = i; }      /* :1350-1355 */
+      else if (hid == 10) { if (hd->frag > bh->frag) best = i; } /* :1546-1550 */
       else if (hd->mod > bh->mod || (hd->mod == bh->mod && hd->frag > bh->frag)) best = i; /* :1414-1421 */
     }
     if (best < 0) break;

@@ -91,7 +91,7 @@ int64_t oracle_rollout_many(const oracle_config* cfg, int64_t env0, int64_t n_en
                             int64_t* reward_sum_out /* [n_envs] or NULL */);
 
 /* PhyRMSA: actions are int32[ORACLE_PHY_ADIM] = (path, channel_0 .. channel_7), -1 terminated;
- * heuristic ids 5 SAP-FF, 6 SAP-BM, 7 BM-FF, 8 BM-FA-Cut (physical layer, no grooming).
+ * heuristic ids 5 SAP-FF, 6 SAP-BM, 7 BM-FF, 8 BM-FA-Cut, 10 FA-FF (physical layer, no grooming).
  * stats out8 = total_path_length_episode, total_gsnr_episode, total_path_index_episode,
  * total_modulation_level_episode, channels_accepted_episode, physical_services_accepted_episode,
  * number_cuts_total, rss_total_metric (phy_rmsa_env.py:313-348). */

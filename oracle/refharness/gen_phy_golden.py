@@ -54,7 +54,12 @@ def counters_of(env):
                      env.episode_bit_rate_requested, env.episode_bit_rate_provisioned], np.int64)
 
 
+ONLY = set(sys.argv[1:])  # optional: names of the cases to (re)generate
+
+
 def run(name, topo_file, mat_key, heuristic, no_groom_stub, n_steps, **kw):
+    if ONLY and name not in ONLY:
+        return
     topo = refenv.load_topology(topo_file)
     conn, mod, gs = load_tables(mat_key)
     kwargs = dict(num_spectrum_resources=64, bit_rate_selection="discrete", grooming=False,
@@ -124,6 +129,8 @@ def main():
         episode_length=205, **tiny)
     run("phy_us14_sapff_100ch", us, US, ref.sapff_rmsa, True, 1500, seed=12, load=1500, episode_length=150, **small)
     run("phy_us14_bmff_100ch", us, US, ref.phy_aware_bmff_rmsa, True, 1500, seed=13, load=1600, episode_length=300,
+        **small)
+    run("phy_us14_faff_100ch", us, US, ref.phy_aware_faff_rmsa, True, 1500, seed=16, load=1500, episode_length=250,
         **small)
     run("phy_jpn12_sapbm_64ch", jpn, JPN, ref.phy_aware_sapbm_rmsa, True, 1500, seed=14, load=1300,
         episode_length=100, **tiny)

@@ -175,3 +175,25 @@ def test_phy_scalar_env_five_tuple_and_info_reward():
             env.reset()
     assert env.topology.graph["available_channels"].shape == (spec.tables.n_edges, spec.num_slots)
     env.close()
+
+
+def test_path_only_first_fit_action_wrapper():
+    """PathOnlyFirstFitAction (rmsa_env.py:974-1008): path 0 + device first fit == the SP-FF golden trace."""
+    import torch
+
+    import optical_rl_gym_qot_aware_b200 as pkg
+    from optical_rl_gym_qot_aware_b200.envs import PathOnlyFirstFitAction
+
+    g, spec = G.load_case("rmsa_nsfnet_spff")
+    n_env = 2
+    env = pkg.make("RMSA-v0", topology=spec.tables, num_envs=n_env, request_source="replay", **_kwargs(g))
+    env.load_trace(np.repeat(g["requests"][:, None], n_env, axis=1))
+    w = PathOnlyFirstFitAction(env)
+    for t in range(400):
+        act = w.action(torch.zeros(n_env, dtype=torch.int32)).cpu().numpy()
+        assert np.array_equal(act[0], g["actions"][t]), (t, act, g["actions"][t])
+        obs, r, d, info = w.step([0, spec.tables.k_paths])  # env 1 always rejects through the wrapper
+        assert int(info["accepted"][0]) == int(g["accepted"][t]) and int(info["accepted"][1]) == 0
+        if bool(d[0]):
+            env.reset()
+    env.close()

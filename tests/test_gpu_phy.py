@@ -9,7 +9,8 @@ from optical_rl_gym_qot_aware_b200 import spec as S
 
 pytestmark = pytest.mark.gpu
 
-HEUR = {"bmfa_cut": S.H_PHY_BM_FA_CUT, "sapff": S.H_PHY_SAP_FF, "bmff": S.H_PHY_BM_FF, "sapbm": S.H_PHY_SAP_BM}
+HEUR = {"bmfa_cut": S.H_PHY_BM_FA_CUT, "sapff": S.H_PHY_SAP_FF, "bmff": S.H_PHY_BM_FF, "sapbm": S.H_PHY_SAP_BM,
+        "faff": S.H_PHY_FA_FF}
 
 
 def heuristic_of(case):
@@ -62,7 +63,8 @@ def test_engine_replays_phy_golden(case):
 
 
 @pytest.mark.parametrize("hid,channels,load", [(S.H_PHY_BM_FA_CUT, (80, 108), 1400), (S.H_PHY_SAP_FF, (30, 40), 1500),
-                                               (S.H_PHY_BM_FF, (20, 24), 1300), (S.H_PHY_SAP_BM, (30, 40), 1600)])
+                                               (S.H_PHY_BM_FF, (20, 24), 1300), (S.H_PHY_SAP_BM, (30, 40), 1600),
+                                               (S.H_PHY_FA_FF, (30, 40), 1500)])
 def test_phy_rollout_matches_oracle_on_philox(hid, channels, load):
     import torch
 
