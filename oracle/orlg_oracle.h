@@ -8,8 +8,10 @@
  * traces exported from the unmodified reference run in the build container
  * (oracle/refharness/gen_golden.py -> tests/golden/ (npz files), checked by
  * tests/test_oracle_golden.py).  The reference itself holds no golden vectors
- * (SURVEY.md F13).  GN-model GSNR (examples/calculate_osnr.py) is "parity
- * unpinned": the reference function is not importable.
+ * (SURVEY.md F13).  PhyRMSA-v0: PINNED the same way (gen_phy_golden.py, tests/test_phy_oracle.py).
+ * GN-model GSNR (examples/calculate_osnr.py): the formula is PINNED against numbers produced by the
+ * reference's own function body (gen_gsnr_golden.py injects the missing Span/Link classes, SURVEY.md
+ * F2); the physical inputs the reference never defines are ours (spec.gsnr_params).
  *
  * Deliberately literal: one byte per (core, link, slot) like the reference's
  * numpy int arrays, run-length encoding by scanning, heap as in heapq.  It
