@@ -261,12 +261,18 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
             dist.barrier()
         torch.cuda.synchronize()
 
+    fused = not args.two_launch
+    eng.heuristic(hid, act)  # action for the first pending request
+    if fused:  # every step also writes the heuristic's action for the next request into `act`
+        eng.set_next_action_hint(hid, act)
+
     def one_step(evs=None):
         if flush is not None:
             flush.fill_(1)  # evict the 126 MB L2 (untimed: outside the event pairs)
         if evs is not None:
             evs[0].record()
-        eng.heuristic(hid, act)
+        if not fused:
+            eng.heuristic(hid, act)
         if evs is not None:
             evs[1].record()
         eng.step(act, rew, done, obs, None)
@@ -302,6 +308,23 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
     warm_ms = e0.elapsed_time(e1)
     flush = saved
 
+    # the same step as two launches (orlg_heuristic, then orlg_step without the hint), informational
+    two_ms = None
+    if fused:
+        eng.set_next_action_hint(hid, None)
+        fused = False
+        for _ in range(3):
+            one_step()
+        barrier()
+        ev2 = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K)]
+        for t in range(K):
+            one_step(ev2[t])
+        barrier()
+        two_ms = sum(e[0].elapsed_time(e[2]) for e in ev2)
+        fused = True
+        eng.heuristic(hid, act)
+        eng.set_next_action_hint(hid, act)
+
     # fused rollout (heuristic + step in one launch, state on chip between steps), informational
     e0.record()
     eng.rollout(hid, K)
@@ -331,12 +354,14 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
             p0 = time.perf_counter()
             host_policy_kspff(h_obs.numpy(), t_nodes, t_k, spec.j, out=h_act.numpy())
             policy_s[0] += time.perf_counter() - p0
-        else:  # no observation to decide from: device heuristic, actions round-trip through the host
-            eng.heuristic(hid, act)
+        else:  # no observation to decide from: device heuristic (or its fused hint), actions D2H then H2D
+            if not fused:
+                eng.heuristic(hid, act)
             h_act.copy_(act)
         eng.step_host(h_act, h_rew, h_done, h_obs, None)
         return int(h_rew.numpy()[0])
 
+    eng.heuristic(hid, act)  # the rollout above moved the envs on: refresh the pending actions
     Ke = max(1, min(K, args.e2e_steps))
     for _ in range(min(args.warmup, 5)):
         e2e_step()
@@ -350,6 +375,56 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
     barrier()
     e2e_wall_ms = (time.perf_counter() - w0) * 1e3
     e2e_ms = max(e0.elapsed_time(e1), e2e_wall_ms)
+    e2e_serial_ms, e2e_mode = e2e_ms, "one orlg_step_host call per step (serial: policy, H2D, step, D2H)"
+
+    # ---- e2e, pipelined: the batch as two VecEnv halves on two streams (step_async / step_wait);
+    # the host policy of one half overlaps the copies and the kernel of the other ----
+    if use_obs_policy and n_env % 2 == 0 and not args.e2e_serial:
+        nh = n_env // 2
+        halves = []
+        for hi in range(2):
+            he = Engine(spec, nh, device=local, global_env_offset=rank * n_env + hi * nh)
+            he.reset(True)
+            he.rollout(hid, PREROLL)
+            dobs = he.new_obs()
+            he.observation(dobs)
+            ho = torch.zeros((he.obs_dim, nh), dtype=h_obs.dtype).pin_memory()
+            ho.copy_(dobs.t())
+            halves.append(dict(e=he, st=torch.cuda.Stream(device=dev), act=torch.zeros((nh, 1), dtype=torch.int32).pin_memory(),
+                               rew=torch.zeros(nh, dtype=torch.int32).pin_memory(),
+                               done=torch.zeros(nh, dtype=torch.uint8).pin_memory(), obs=ho))
+        torch.cuda.synchronize()
+
+        def submit(h):
+            p0 = time.perf_counter()
+            host_policy_kspff(h["obs"].numpy(), t_nodes, t_k, spec.j, out=h["act"].numpy())
+            policy_s[0] += time.perf_counter() - p0
+            h["e"].step_host_async(h["act"], h["rew"], h["done"], h["obs"], None, stream=h["st"])
+
+        def pipelined(nsteps):
+            for h in halves:
+                submit(h)
+            for _ in range(nsteps - 1):
+                for h in halves:
+                    h["e"].step_host_wait(stream=h["st"])
+                    submit(h)
+            for h in halves:
+                h["e"].step_host_wait(stream=h["st"])
+
+        pipelined(5)
+        barrier()
+        policy_s[0] = 0.0
+        e0.record()
+        w0 = time.perf_counter()
+        pipelined(Ke)
+        e1.record()
+        barrier()
+        e2e_ms = max(e0.elapsed_time(e1), (time.perf_counter() - w0) * 1e3)
+        e2e_mode = "two VecEnv halves on two streams, orlg_step_host_async / _wait (policy overlaps copies)"
+        for h in halves:
+            if int(h["e"].counters()[:, 10].max()) != 0:
+                raise RuntimeError("device fault bits set in the pipelined e2e run")
+            h["e"].close()
     clocks = sampler.stop() if rank == 0 else None
     h2d = h_act.numel() * 4
     d2h = h_rew.numel() * 4 + h_done.numel() + (h_obs.numel() * h_obs.element_size() if h_obs is not None else 0)
@@ -358,14 +433,14 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
     cnt = eng.counters()
     stats = torch.stack([cnt[:, 0].sum(), cnt[:, 1].sum(), cnt[:, 4].sum(), cnt[:, 5].sum(), cnt[:, 11].sum(),
                          cnt[:, 10].max()]).to(torch.int64)
-    times = torch.tensor([step_ms, kern_ms, warm_ms, roll_ms, e2e_ms], dtype=torch.float64, device=dev)
+    times = torch.tensor([step_ms, kern_ms, warm_ms, roll_ms, e2e_ms, e2e_serial_ms], dtype=torch.float64, device=dev)
     if dist is not None:
         fault = stats[5:6].clone()
         dist.all_reduce(stats, op=dist.ReduceOp.SUM)
         dist.all_reduce(fault, op=dist.ReduceOp.MAX)
         stats[5] = fault[0]
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    step_ms, kern_ms, warm_ms, roll_ms, e2e_ms = [float(x) for x in times.cpu()]
+    step_ms, kern_ms, warm_ms, roll_ms, e2e_ms, e2e_serial_ms = [float(x) for x in times.cpu()]
     stats = [int(x) for x in stats.cpu()]
     if stats[5] != 0:
         raise RuntimeError(f"device fault bits set: {stats[5]}")
@@ -395,14 +470,16 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
             "workload": wl, "env": env_id, "envs_per_gpu": n_env, "heuristic": int(hid),
             "obs": {0: "none", 1: "f64", 2: "f32", 3: "matrix_u8", 4: "phy cuts+rss f64", 5: "phy cuts f64"}[
                 spec.obs_kind],
-            "step": "orlg_heuristic + orlg_step (2 launches), actions/obs/reward/done resident in HBM",
+            "step": ("orlg_step with the fused next-action hint of the device heuristic (1 launch)" if fused
+                     else "orlg_heuristic + orlg_step (2 launches)") + ", actions/obs/reward/done resident in HBM",
             "l2": ("flushed before every step by a 256 MiB fill outside the per-step event pairs"
                    if not args.no_flush else "not flushed (state may be L2 resident)"),
             "preroll_steps": PREROLL, "parallelism": f"envs sharded x{world}, no data-path collective",
             "blocking": 1.0 - stats[1] / max(1, stats[0]), "episodes": stats[4],
         },
         "e2e": {"value": total_envs * Ke / (e2e_ms * 1e-3), "unit": "env-steps/s", "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": d2h, "steps": Ke, "ms_per_step": e2e_ms / Ke,
+                "d2h_bytes_per_step": d2h, "steps": Ke, "ms_per_step": e2e_ms / Ke, "mode": e2e_mode,
+                "serial_value": total_envs * Ke / (e2e_serial_ms * 1e-3),
                 "host_policy_ms_per_step": policy_s[0] * 1e3 / Ke,
                 "policy": "numpy K-SP-FF from the host observation" if use_obs_policy
                 else "device heuristic, actions D2H then H2D"},
@@ -411,7 +488,8 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "kernel": "env_kernel (MODE_STEP)", "peak_source": peak_src,
                      "bytes_per_env_step": bytes_per_step, "kernel_ms": kern_avg_s * 1e3},
-        "extra": {"warm_l2_env_steps_per_s": total_envs * K / (warm_ms * 1e-3),
+        "extra": {"two_launch_env_steps_per_s": (total_envs * K / (two_ms * 1e-3)) if two_ms else None,
+                  "warm_l2_env_steps_per_s": total_envs * K / (warm_ms * 1e-3),
                   "fused_rollout_env_steps_per_s": total_envs * K / (roll_ms * 1e-3),
                   "hbm_bytes_per_gpu": eng.hbm_bytes},
     }
@@ -440,6 +518,8 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--e2e-steps", type=int, default=100)
     ap.add_argument("--no-flush", action="store_true")
+    ap.add_argument("--e2e-serial", action="store_true", help="no two-half pipelining of the e2e loop")
+    ap.add_argument("--two-launch", action="store_true", help="orlg_heuristic + orlg_step instead of the fused hint")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)

@@ -201,6 +201,14 @@ int orlg_step(orlg_engine* e, const int32_t* dev_actions, int32_t* dev_reward,
 int orlg_step_host(orlg_engine* e, const int32_t* host_actions, int32_t* host_reward,
                    uint8_t* host_done, void* host_obs, int32_t* host_alloc, void* stream);
 
+/* The two halves of orlg_step_host, the VecEnv step_async / step_wait pair: _async enqueues the H2D
+ * copy, the step and the D2H copies on `stream` and returns; the host buffers (pinned memory for real
+ * overlap) are valid after orlg_step_host_wait(stream).  Engines driven on different streams
+ * overlap their copies, kernels and the caller's host work. */
+int orlg_step_host_async(orlg_engine* e, const int32_t* host_actions, int32_t* host_reward,
+                         uint8_t* host_done, void* host_obs, int32_t* host_alloc, void* stream);
+int orlg_step_host_wait(orlg_engine* e, void* stream);
+
 /* Layout of dev_obs for orlg_step / orlg_observation, in elements: feature f of
  * env i is written at dev_obs[i*env_stride + f*feat_stride].  Default (obs_dim, 1)
  * = row-major [num_envs][obs_dim]; (1, num_envs) = feature-major, which makes the
@@ -212,6 +220,14 @@ int orlg_observation(orlg_engine* e, int obs_kind, void* dev_obs, void* stream);
 
 /* Device-side heuristic: writes the action the reference heuristic would return. */
 int orlg_heuristic(orlg_engine* e, int heuristic_id, int32_t* dev_actions, void* stream);
+
+/* Fused next-action hint.  With a non-NULL dev_next_actions (int32 [num_envs][action_dim], kept by
+ * the engine until replaced or cleared with NULL) every following orlg_step / orlg_step_host also
+ * writes, for the NEW pending request of every env, the action the reference heuristic
+ * `heuristic_id` takes on the updated network: exactly what an orlg_heuristic launch after the step
+ * would write, without a second launch and a second read of the occupancy.  The buffer may be the
+ * dev_actions buffer of the same orlg_step call (an env reads its action before it writes its hint). */
+int orlg_set_next_action_hint(orlg_engine* e, int heuristic_id, int32_t* dev_next_actions);
 
 /* PathOnlyFirstFitAction.action (rmsa_env.py:982-1005), RMSA-v0 only: dev_paths int32[num_envs]
  * (path index or k_paths = reject) -> dev_actions int32[num_envs][2] = (path, first-fit slot) or

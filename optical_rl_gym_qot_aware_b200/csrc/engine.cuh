@@ -93,6 +93,8 @@ struct StepIO {
   long long obs_es, obs_fs;  // element strides: env, feature
   int* alloc;
   long long* reward_sum;
+  int* hint_actions;   // optional: the heuristic's action for the NEW pending request (fused next-action hint)
+  int hint_heuristic;
 };
 
 // ---- path records ----------------------------------------------------------

@@ -209,6 +209,23 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
       if (io.obs_kind == ORLG_OBS_MATRIX_U8)
         write_matrix_obs<W, BD>(env, reinterpret_cast<unsigned char*>(io.obs) + (long long)e * io.obs_es, io.obs_fs);
     }
+    if (mode == MODE_STEP && io.hint_actions != nullptr) {
+      // fused next-action hint: what orlg_heuristic would write if it were launched now
+      if constexpr (PHY) {
+        phy_heuristic<W, BD>(env, io.hint_heuristic, a);
+#pragma unroll
+        for (int i = 0; i < ADIM; i++) io.hint_actions[(size_t)e * ADIM + i] = a[i];
+      } else {
+        heuristic_action<W, BD>(env, io.hint_heuristic, a);
+        if (p.action_dim == 1) {
+          io.hint_actions[e] = a[0];
+        } else if (p.action_dim == 2) {
+          reinterpret_cast<int2*>(io.hint_actions)[e] = make_int2(a[0], a[1]);
+        } else {
+          reinterpret_cast<int4*>(io.hint_actions)[e] = make_int4(a[0], a[1], a[2], a[3]);
+        }
+      }
+    }
     if (mode != MODE_HEURISTIC && mode != MODE_OBS) env.store_scalars();
   }
 

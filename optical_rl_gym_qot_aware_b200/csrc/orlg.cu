@@ -35,6 +35,8 @@ struct orlg_engine {
   long long obs_es = 0, obs_fs = 1;  // 0 = row-major default
   GsnrParams gp{};
   bool gsnr_ready = false;
+  int* hint_actions = nullptr;
+  int hint_heuristic = 0;
 };
 
 static thread_local std::string g_create_error;
@@ -393,6 +395,8 @@ extern "C" int orlg_step(orlg_engine* e, const int32_t* dev_actions, int32_t* de
   io.done = dev_done;
   io.obs = e->obs_kind ? dev_obs : nullptr;
   io.alloc = dev_alloc;
+  io.hint_actions = e->hint_actions;
+  io.hint_heuristic = e->hint_heuristic;
   return launch(e, io, stream);
 }
 
@@ -438,6 +442,14 @@ extern "C" int orlg_path_first_fit(orlg_engine* e, const int32_t* dev_paths, int
   return launch(e, io, stream);
 }
 
+extern "C" int orlg_set_next_action_hint(orlg_engine* e, int hid, int32_t* dev_next_actions) {
+  if (!e) return ORLG_EINVAL;
+  if (dev_next_actions && (!heuristic_ok(e, hid) || hid == ORLG_H_PATH_FF)) return ORLG_EINVAL;
+  e->hint_actions = dev_next_actions;
+  e->hint_heuristic = hid;
+  return ORLG_OK;
+}
+
 extern "C" int orlg_rollout(orlg_engine* e, int hid, int nsteps, int64_t* dev_reward_sum, void* stream) {
   if (!e || nsteps < 1 || !heuristic_ok(e, hid)) return ORLG_EINVAL;
   if (int rc = check_source(e)) return rc;
@@ -478,8 +490,8 @@ extern "C" int orlg_get_requests(orlg_engine* e, orlg_request* dev_out, void* st
 }
 
 // Host-buffer step: H2D actions, step, D2H outputs, stream sync (bench.py "e2e").
-extern "C" int orlg_step_host(orlg_engine* e, const int32_t* h_actions, int32_t* h_reward, uint8_t* h_done,
-                              void* h_obs, int32_t* h_alloc, void* stream) {
+extern "C" int orlg_step_host_async(orlg_engine* e, const int32_t* h_actions, int32_t* h_reward, uint8_t* h_done,
+                                    void* h_obs, int32_t* h_alloc, void* stream) {
   if (!e || !h_actions) return ORLG_EINVAL;
   cudaSetDevice(e->device);
   cudaStream_t st = (cudaStream_t)stream;
@@ -502,8 +514,20 @@ extern "C" int orlg_step_host(orlg_engine* e, const int32_t* h_actions, int32_t*
   if (h_alloc) CK(cudaMemcpyAsync(h_alloc, e->d_alloc, n * 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
   if (h_obs && e->d_obs)
     CK(cudaMemcpyAsync(h_obs, e->d_obs, n * e->obs_dim * e->obs_elem, cudaMemcpyDeviceToHost, st));
-  CK(cudaStreamSynchronize(st));
   return ORLG_OK;
+}
+
+extern "C" int orlg_step_host_wait(orlg_engine* e, void* stream) {
+  if (!e) return ORLG_EINVAL;
+  cudaSetDevice(e->device);
+  CK(cudaStreamSynchronize((cudaStream_t)stream));
+  return ORLG_OK;
+}
+
+extern "C" int orlg_step_host(orlg_engine* e, const int32_t* h_actions, int32_t* h_reward, uint8_t* h_done,
+                              void* h_obs, int32_t* h_alloc, void* stream) {
+  if (int rc = orlg_step_host_async(e, h_actions, h_reward, h_done, h_obs, h_alloc, stream)) return rc;
+  return orlg_step_host_wait(e, stream);
 }
 
 extern "C" int orlg_gsnr_configure(orlg_engine* e, const orlg_gsnr_params* g) {

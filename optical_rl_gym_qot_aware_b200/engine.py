@@ -32,7 +32,7 @@ EXPORTS = (
     "orlg_action_dim", "orlg_obs_dim", "orlg_state_words", "orlg_hbm_bytes", "orlg_load_trace",
     "orlg_reset", "orlg_step", "orlg_step_host", "orlg_set_obs_layout", "orlg_observation",
     "orlg_heuristic", "orlg_rollout", "orlg_get_counters", "orlg_export_state", "orlg_get_requests",
-    "orlg_launch_count", "orlg_gsnr_configure", "orlg_gsnr", "orlg_phy_get_stats", "orlg_path_first_fit",
+    "orlg_launch_count", "orlg_gsnr_configure", "orlg_gsnr", "orlg_phy_get_stats", "orlg_path_first_fit", "orlg_set_next_action_hint", "orlg_step_host_async", "orlg_step_host_wait",
 )
 
 
@@ -94,6 +94,8 @@ def load_library():
         L.orlg_reset.argtypes = [vp, i32, vp]
         L.orlg_step.argtypes = [vp, vp, vp, vp, vp, vp, vp]
         L.orlg_step_host.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+        L.orlg_step_host_async.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+        L.orlg_step_host_wait.argtypes = [vp, vp]
         L.orlg_set_obs_layout.argtypes = [vp, i64, i64]
         L.orlg_observation.argtypes = [vp, i32, vp, vp]
         L.orlg_heuristic.argtypes = [vp, i32, vp, vp]
@@ -105,6 +107,7 @@ def load_library():
         L.orlg_gsnr.argtypes = [vp, vp, vp, vp]
         L.orlg_phy_get_stats.argtypes = [vp, vp, vp]
         L.orlg_path_first_fit.argtypes = [vp, vp, vp, vp]
+        L.orlg_set_next_action_hint.argtypes = [vp, i32, vp]
         _lib = L
     return _lib
 
@@ -242,12 +245,29 @@ class Engine:
         self._ck(self.L.orlg_step_host(self.h, self._p(actions), self._p(reward), self._p(done),
                                        self._p(obs), self._p(alloc), self._stream()))
 
+    def step_host_async(self, actions, reward=None, done=None, obs=None, alloc=None, stream=None):
+        """Enqueue H2D actions, one step, D2H outputs on ``stream`` (a torch.cuda.Stream; default: the
+        current stream) without waiting; pair with :meth:`step_host_wait`."""
+        st = self._stream() if stream is None else C.c_void_p(stream.cuda_stream)
+        self._ck(self.L.orlg_step_host_async(self.h, self._p(actions), self._p(reward), self._p(done),
+                                             self._p(obs), self._p(alloc), st))
+
+    def step_host_wait(self, stream=None):
+        st = self._stream() if stream is None else C.c_void_p(stream.cuda_stream)
+        self._ck(self.L.orlg_step_host_wait(self.h, st))
+
     def observation(self, obs, kind=None):
         kind = self.spec.obs_kind if kind is None else kind
         self._ck(self.L.orlg_observation(self.h, kind, self._obs_base(obs), self._stream()))
 
     def heuristic(self, heuristic_id, actions):
         self._ck(self.L.orlg_heuristic(self.h, heuristic_id, self._p(actions), self._stream()))
+
+    def set_next_action_hint(self, heuristic_id, actions):
+        """Every later step() also writes the heuristic's action for the new pending request into
+        ``actions`` (int32 [num_envs, action_dim] device tensor, kept alive here); None turns it off."""
+        self._hint = actions
+        self._ck(self.L.orlg_set_next_action_hint(self.h, int(heuristic_id), self._p(actions)))
 
     def path_first_fit(self, paths, actions):
         """PathOnlyFirstFitAction (rmsa_env.py:974-1008): int32 [num_envs] paths -> [num_envs, 2] actions."""

@@ -270,6 +270,7 @@ class OrlgVecEnv:
         # the device buffer is feature-major; the host copy is exposed as its [num_envs, obs_dim] view
         self._h_obs = torch.zeros((e.obs_dim, n), dtype=odt).pin_memory() if e.obs_dim else None
         self._pending = False
+        self._stream = torch.cuda.Stream(device=self.env.device)  # own stream: several VecEnvs overlap
 
     def _obs_view(self):
         return None if self._h_obs is None else self._h_obs.numpy().T
@@ -285,11 +286,14 @@ class OrlgVecEnv:
         a = np.asarray(actions, dtype=np.int32).reshape(self.num_envs, -1)
         self._h_act.numpy()[:] = a
         self._pending = True
+        self._stream.wait_stream(self.env.torch.cuda.current_stream(self.env.device))
+        self.env.engine.step_host_async(self._h_act, self._h_rew, self._h_done, self._h_obs, self._h_alloc,
+                                        stream=self._stream)
 
     def step_wait(self):
         assert self._pending, "step_wait without step_async"
         self._pending = False
-        self.env.engine.step_host(self._h_act, self._h_rew, self._h_done, self._h_obs, self._h_alloc)
+        self.env.engine.step_host_wait(stream=self._stream)
         rew = self._h_rew.numpy().astype(np.float32)
         done = self._h_done.numpy().astype(bool)
         al = self._h_alloc.numpy()

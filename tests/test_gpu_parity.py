@@ -133,3 +133,36 @@ def test_step_mode_equals_rollout_mode():
     obs_b = b.new_obs()
     b.observation(obs_b)
     assert torch.equal(obs, obs_b)
+
+
+@pytest.mark.parametrize("env_id,topo,kw,hid", [
+    ("DeepRMSA-v0", "nsfnet", dict(mean_service_holding_time=7.5, mean_service_inter_arrival_time=1 / 12.0,
+                                   episode_length=50, j=2), 1),
+    ("RMSA-v0", "spn", dict(load=100, mean_service_holding_time=25, num_spectrum_resources=100, episode_length=80), 2),
+    ("RMCSA-v0", "nsfnet", dict(load=250, mean_service_holding_time=25, num_spectrum_resources=64,
+                                num_spatial_resources=7, episode_length=90), 3),
+])
+def test_fused_next_action_hint_equals_heuristic_launch(env_id, topo, kw, hid):
+    """orlg_set_next_action_hint: the action written by the step kernel for the new pending request
+    is what a separate orlg_heuristic launch writes, also when it aliases the action buffer."""
+    import torch
+
+    spec = S.make_spec(env_id, G.topology(topo), seed=21, auto_reset=True, **kw)
+    n_env, n_steps = 400, 150
+    a, b = _engine(spec, n_env), _engine(spec, n_env)
+    a.reset(True)
+    b.reset(True)
+    act_a = torch.zeros((n_env, a.action_dim), dtype=torch.int32, device=a.device)
+    act_b = torch.zeros_like(act_a)
+    a.heuristic(hid, act_a)
+    a.set_next_action_hint(hid, act_a)  # aliased: read as action, overwritten with the next one
+    for t in range(n_steps):
+        b.heuristic(hid, act_b)
+        assert torch.equal(act_a, act_b), t
+        a.step(act_a)
+        b.step(act_b)
+    assert torch.equal(a.counters(), b.counters()) and torch.equal(a.export_state(), b.export_state())
+    a.set_next_action_hint(hid, None)
+    before = act_a.clone()
+    a.step(act_a)
+    assert torch.equal(act_a, before)
