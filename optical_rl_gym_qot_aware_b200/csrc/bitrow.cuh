@@ -56,17 +56,28 @@ __device__ __forceinline__ void and_into(Row<W>& a, const Row<W>& b) {
   for (int i = 0; i < W; i++) a.w[i] &= b.w[i];
 }
 
+// number of shift-amount bits that matter for a W-word row: amounts < 32*W
+template <int W>
+struct ShiftBits {
+  static constexpr int value = W <= 1 ? 5 : W <= 2 ? 6 : W <= 4 ? 7 : W <= 8 ? 8 : W <= 16 ? 9 : 10;
+};
+
 template <int W, int B>
-__device__ __forceinline__ void shr_step(Row<W>& x, int amount) {
+__device__ __forceinline__ void shr_words(Row<W>& x, int amount) {
   if ((amount >> B) & 1) x = shr_pow2<W, B>(x);
-  if constexpr (B + 1 < 10) shr_step<W, B + 1>(x, amount);
+  if constexpr (B + 1 < ShiftBits<W>::value) shr_words<W, B + 1>(x, amount);
 }
 
-// right shift by an arbitrary amount in [0, 1024)
+// right shift by an arbitrary amount in [0, 32*W): one funnel shift per word for the sub-word part,
+// then conditional whole-word moves
 template <int W>
 __device__ __forceinline__ Row<W> shr_var(Row<W> x, int amount) {
-  shr_step<W, 0>(x, amount);
-  return x;
+  Row<W> r;
+  const int s = amount & 31;
+#pragma unroll
+  for (int i = 0; i < W; i++) r.w[i] = __funnelshift_r(x.w[i], (i + 1 < W) ? x.w[i + 1] : 0u, s);
+  shr_words<W, 5>(r, amount);
+  return r;
 }
 
 template <int W, int B>
@@ -76,13 +87,18 @@ __device__ __forceinline__ void window_step(Row<W>& b, int& len, int n) {
     and_into(b, s);
     len *= 2;
   }
-  if constexpr (B + 1 < 10) window_step<W, B + 1>(b, len, n);
+  if constexpr (B + 1 < ShiftBits<W>::value) window_step<W, B + 1>(b, len, n);
 }
 
 // bit p of the result is 1 iff bits p .. p+n-1 of `a` are all 1 (n >= 1)
 template <int W>
 __device__ __forceinline__ Row<W> window_starts(const Row<W>& a, int n) {
   Row<W> b = a;
+  if (n > 32 * W) {  // longer than the row: no window (also keeps every shift amount below 32*W)
+#pragma unroll
+    for (int i = 0; i < W; i++) b.w[i] = 0u;
+    return b;
+  }
   int len = 1;
   window_step<W, 0>(b, len, n);
   int r = n - len;  // 0 <= r < len

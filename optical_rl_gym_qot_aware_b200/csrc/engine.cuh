@@ -46,6 +46,7 @@ struct Params {
   int n_bit_rates, br_lo, br_hi, heap_cap, heap_stride, action_dim;
   double cw, mean_iat, mean_holding;
   int cw_x2;                 // 2*channel_width when that is a small integer (12.5 GHz -> 25), else 0
+  unsigned slot_magic[16];   // floor(2^32 / (cw_x2*se)) + 1: exact division by multiplication for se < 16
   const double* obs_pos;     // [S+1]  2*(x - 0.5*S)/S   (deeprmsa_env.py:85-87,101)
   const double* obs_slots;   // [S+2]  (n - 5.5)/3.5     (deeprmsa_env.py:97)
   unsigned long long seed;
@@ -98,29 +99,70 @@ struct StepIO {
 };
 
 // ---- path records ----------------------------------------------------------
+// 16 B (hops <= 12) or 32 B records: word 0 = hops | se << 8 | best modulation << 16, then one
+// byte per hop (edge "index"), four hops per word.
+#ifndef ORLG_LINK_UNROLL
+#define ORLG_LINK_UNROLL 1
+#endif
+
 struct PathRec {
-  unsigned long long q[4];
-  __device__ __forceinline__ int byte_at(int i) const {
-    unsigned long long v = (i < 8) ? q[0] : (i < 16) ? q[1] : (i < 24) ? q[2] : q[3];
-    return (int)((v >> ((i & 7) * 8)) & 0xFFull);
+  uint32_t w[8];
+  __device__ __forceinline__ int hops() const { return (int)(w[0] & 0xFF); }
+  __device__ __forceinline__ int se() const { return (int)((w[0] >> 8) & 0xFF); }
+  __device__ __forceinline__ int best_mod() const { return (int)((w[0] >> 16) & 0xFF); }
+  __device__ __forceinline__ int link(int h) const {  // random access (cold paths only)
+    const int g = (h >> 2) + 1;
+    uint32_t v = w[1];
+#pragma unroll
+    for (int i = 2; i < 8; i++) v = (g == i) ? w[i] : v;
+    return (int)((v >> ((h & 3) * 8)) & 0xFFu);
   }
-  __device__ __forceinline__ int hops() const { return (int)(q[0] & 0xFF); }
-  __device__ __forceinline__ int se() const { return (int)((q[0] >> 8) & 0xFF); }
-  __device__ __forceinline__ int best_mod() const { return (int)((q[0] >> 16) & 0xFF); }
-  __device__ __forceinline__ int link(int h) const { return byte_at(h + 3); }
 };
+
+// f(link) for every hop in order; hops are unrolled with static byte positions
+template <typename F>
+__device__ __forceinline__ void for_each_link(const PathRec& r, F f) {
+  const int h = r.hops();
+#if ORLG_LINK_UNROLL
+#pragma unroll
+  for (int g = 0; g < 3; g++) {
+    if (4 * g < h) {
+      const uint32_t wd = r.w[g + 1];
+#pragma unroll
+      for (int u = 0; u < 4; u++)
+        if (4 * g + u < h) f((int)((wd >> (8 * u)) & 0xFFu));
+    }
+  }
+  for (int i = 12; i < h; i++) f(r.link(i));  // long paths (32-byte records)
+#else
+  // one copy of the four-hop body; the group's word is picked by selects (no indexed registers)
+#pragma unroll 1
+  for (int g = 0; 4 * g < h; g++) {
+    uint32_t wd = r.w[1];
+#pragma unroll
+    for (int i = 2; i < 8; i++) wd = (g + 1 == i) ? r.w[i] : wd;
+#pragma unroll
+    for (int u = 0; u < 4; u++)
+      if (4 * g + u < h) f((int)((wd >> (8 * u)) & 0xFFu));
+  }
+#endif
+}
 
 __device__ __forceinline__ PathRec load_path(const Params& p, int pair, int path) {
   const uint4* a = p.path_rec + ((size_t)pair * p.k + path) * p.rec_u4;
   PathRec r;
   uint4 v = __ldg(a);
-  r.q[0] = ((unsigned long long)v.y << 32) | v.x;
-  r.q[1] = ((unsigned long long)v.w << 32) | v.z;
-  r.q[2] = r.q[3] = 0ull;
+  r.w[0] = v.x;
+  r.w[1] = v.y;
+  r.w[2] = v.z;
+  r.w[3] = v.w;
+  r.w[4] = r.w[5] = r.w[6] = r.w[7] = 0u;
   if (p.rec_u4 > 1) {
     uint4 u = __ldg(a + 1);
-    r.q[2] = ((unsigned long long)u.y << 32) | u.x;
-    r.q[3] = ((unsigned long long)u.w << 32) | u.z;
+    r.w[4] = u.x;
+    r.w[5] = u.y;
+    r.w[6] = u.z;
+    r.w[7] = u.w;
   }
   return r;
 }
@@ -133,38 +175,36 @@ struct Tile {
   __device__ __forceinline__ uint32_t& word(int core, int link, int wi) {
     return s[(((core * E) + link) * W + wi) * BD + tid];
   }
-  // AND of the rows of every link of the path (core plane `core`)
+  // AND of the rows of every link of the path (core plane `core`).  Not inlined: one copy of the
+  // unrolled hop loop serves every call site.
   __device__ __forceinline__ Row<W> path_avail(const PathRec& r, int core) {
     Row<W> a = row_ones<W>();
-    int h = r.hops();
-    for (int i = 0; i < h; i++) {
-      int l = r.link(i);
+    const uint32_t* base = s + (size_t)core * E * W * BD + tid;
+    for_each_link(r, [&](int l) {
+      const uint32_t* q = base + l * (W * BD);
 #pragma unroll
-      for (int wi = 0; wi < W; wi++) a.w[wi] &= word(core, l, wi);
-    }
+      for (int wi = 0; wi < W; wi++) a.w[wi] &= q[wi * BD];
+    });
     return a;
   }
-  __device__ __forceinline__ void clear_range(const PathRec& r, int core, int start, int n) {
-    int h = r.hops();
-    for (int i = 0; i < h; i++) {
-      int l = r.link(i);
+  // clear (provision) or set (release) slots [start, start+n) on every link of the path
+  __device__ __forceinline__ void apply_range(const PathRec& r, int core, int start, int n, bool set) {
+    uint32_t m[W];
 #pragma unroll
-      for (int wi = 0; wi < W; wi++) {
-        uint32_t m = mask_word(wi, start, start + n);
-        if (m) word(core, l, wi) &= ~m;
-      }
-    }
+    for (int wi = 0; wi < W; wi++) m[wi] = mask_word(wi, start, start + n);
+    uint32_t* base = s + (size_t)core * E * W * BD + tid;
+    for_each_link(r, [&](int l) {
+      uint32_t* q = base + l * (W * BD);
+#pragma unroll
+      for (int wi = 0; wi < W; wi++)
+        if (m[wi]) q[wi * BD] = set ? (q[wi * BD] | m[wi]) : (q[wi * BD] & ~m[wi]);
+    });
+  }
+  __device__ __forceinline__ void clear_range(const PathRec& r, int core, int start, int n) {
+    apply_range(r, core, start, n, false);
   }
   __device__ __forceinline__ void set_range(const PathRec& r, int core, int start, int n) {
-    int h = r.hops();
-    for (int i = 0; i < h; i++) {
-      int l = r.link(i);
-#pragma unroll
-      for (int wi = 0; wi < W; wi++) {
-        uint32_t m = mask_word(wi, start, start + n);
-        if (m) word(core, l, wi) |= m;
-      }
-    }
+    apply_range(r, core, start, n, true);
   }
 };
 
@@ -172,9 +212,10 @@ struct Tile {
 // 2*channel_width is a small integer the quotient's distance to the next integer is >= 1/(2cw*SE),
 // far above an ulp, so the integer form ceil(2*br / (2cw*SE)) is exactly the same number.
 __device__ __forceinline__ int number_slots(int bit_rate, int se, const Params& p) {
-  if (p.cw_x2 > 0) {
-    int d = p.cw_x2 * se;
-    return (2 * bit_rate + d - 1) / d + 1;
+  if (p.cw_x2 > 0 && se < 16) {
+    // floor(x / d) == umulhi(x, floor(2^32/d) + 1) for x * d < 2^32 (x <= 2*65535 + d, d <= 2*cw*15)
+    const unsigned d = (unsigned)(p.cw_x2 * se);
+    return (int)__umulhi(2u * (unsigned)bit_rate + d - 1u, p.slot_magic[se]) + 1;
   }
   return (int)ceil((double)bit_rate / ((double)se * p.cw)) + 1;
 }

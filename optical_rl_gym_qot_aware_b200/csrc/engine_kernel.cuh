@@ -196,12 +196,17 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
       }
       if (io.reward_sum) io.reward_sum[e] += rsum;
     }
+    unsigned fit_mask = 0u;
+    bool have_fit_mask = false;
     if ((mode == MODE_STEP || mode == MODE_OBS || mode == MODE_RESET_FULL) && io.obs != nullptr) {
       if constexpr (!PHY) {
-        if (io.obs_kind == ORLG_OBS_F64)
-          write_deeprmsa_obs<W, BD, double>(env, reinterpret_cast<double*>(io.obs) + (long long)e * io.obs_es, io.obs_fs);
-        else if (io.obs_kind == ORLG_OBS_F32)
-          write_deeprmsa_obs<W, BD, float>(env, reinterpret_cast<float*>(io.obs) + (long long)e * io.obs_es, io.obs_fs);
+        if (io.obs_kind == ORLG_OBS_F64) {
+          fit_mask = write_deeprmsa_obs<W, BD, double>(env, reinterpret_cast<double*>(io.obs) + (long long)e * io.obs_es, io.obs_fs);
+          have_fit_mask = true;
+        } else if (io.obs_kind == ORLG_OBS_F32) {
+          fit_mask = write_deeprmsa_obs<W, BD, float>(env, reinterpret_cast<float*>(io.obs) + (long long)e * io.obs_es, io.obs_fs);
+          have_fit_mask = true;
+        }
       } else if (mode != MODE_STEP && (io.obs_kind == ORLG_OBS_PHY_INFO || io.obs_kind == ORLG_OBS_PHY_CUTS)) {
         phy_info<W, BD>(env, reinterpret_cast<double*>(io.obs) + (long long)e * io.obs_es, io.obs_fs,
                         io.obs_kind == ORLG_OBS_PHY_INFO);
@@ -216,7 +221,16 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
 #pragma unroll
         for (int i = 0; i < ADIM; i++) io.hint_actions[(size_t)e * ADIM + i] = a[i];
       } else {
-        heuristic_action<W, BD>(env, io.hint_heuristic, a);
+        if (p.kind == ORLG_ENV_DEEPRMSA && have_fit_mask &&
+            (io.hint_heuristic == ORLG_H_SAP_FF || io.hint_heuristic == ORLG_H_SP_FF)) {
+          // deeprmsa_env.py:135-155 decided from the blocks the observation just enumerated
+          if (io.hint_heuristic == ORLG_H_SP_FF)
+            a[0] = (!p.allow_rejection || (fit_mask & 1u)) ? 0 : p.k * p.j;
+          else
+            a[0] = fit_mask ? (__ffs((int)fit_mask) - 1) * p.j : p.k * p.j;
+        } else {
+          heuristic_action<W, BD>(env, io.hint_heuristic, a);
+        }
         if (p.action_dim == 1) {
           io.hint_actions[e] = a[0];
         } else if (p.action_dim == 2) {

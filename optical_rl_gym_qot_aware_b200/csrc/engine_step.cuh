@@ -180,8 +180,11 @@ __device__ __forceinline__ void heuristic_action(Env<W, BD>& env, int hid, int* 
 
 // DeepRMSAEnv.observation (deeprmsa_env.py:60-121), f64 arithmetic in the reference's
 // operation order; OUT is double or float (one rounding at the store).
+// Returns the bitmask of paths that have at least one fitting block (what the K-SP-FF / SP-FF
+// heuristics of deeprmsa_env.py:135-155 decide on), so a fused next-action hint costs nothing extra.
 template <int W, int BD, typename OUT>
-__device__ __forceinline__ void write_deeprmsa_obs(Env<W, BD>& env, OUT* o, long long fs) {
+__device__ __forceinline__ unsigned write_deeprmsa_obs(Env<W, BD>& env, OUT* o, long long fs) {
+  unsigned fit_mask = 0u;
   const Params& p = env.p;
   const int N = p.n_nodes, S = p.S, j = p.j;
   o[0] = (OUT)((double)env.bit_rate / 100.0);
@@ -205,6 +208,7 @@ __device__ __forceinline__ void write_deeprmsa_obs(Env<W, BD>& env, OUT* o, long
       row[(2 * b) * fs] = (OUT)__ldg(p.obs_pos + s);
       row[(2 * b + 1) * fs] = (OUT)(((double)len - 8.0) * 0.125);  // == /8 exactly
     });
+    if (nb > 0) fit_mask |= 1u << path;
     for (int b = nb; b < j; b++) {
       row[(2 * b) * fs] = (OUT)-1.0;
       row[(2 * b + 1) * fs] = (OUT)-1.0;
@@ -214,6 +218,7 @@ __device__ __forceinline__ void write_deeprmsa_obs(Env<W, BD>& env, OUT* o, long
     row[(2 * j + 1) * fs] = (OUT)__ldg(p.obs_pos + tot);
     row[(2 * j + 2) * fs] = (OUT)(runs > 0 ? ((double)tot / (double)runs - 4.0) * 0.25 : -1.0);  // == /4 exactly
   }
+  return fit_mask;
 }
 
 // SimpleMatrixObservation (rmsa_env.py:940-971, rmcsa_env.py:914-947): one-hot pair + unpacked slots

@@ -132,9 +132,9 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
               c->phy_n_tables < 1 || c->phy_max_terms < 1))
     return fail_create(nullptr, ORLG_EINVAL, "PhyRMSA needs the QoT tables (table_id, mod_level, gsnr, cut terms)");
   if (c->num_envs < 1 || c->n_nodes < 2 || c->n_nodes > 255 || c->n_edges < 1 || c->n_edges > 255 ||
-      c->k_paths < 1 || c->k_paths > 15 || c->max_hops < 1 || c->max_hops > 29 || c->num_slots < 2 ||
+      c->k_paths < 1 || c->k_paths > 15 || c->max_hops < 1 || c->max_hops > 28 || c->num_slots < 2 ||
       c->num_slots > 320 || c->episode_length < 1)
-    return fail_create(nullptr, ORLG_EINVAL, "config out of range (nodes/edges<=255, k<=15, hops<=29, slots<=320)");
+    return fail_create(nullptr, ORLG_EINVAL, "config out of range (nodes/edges<=255, k<=15, hops<=28, slots<=320)");
   if (!c->path_links || !c->path_hops || !c->path_se || !c->path_length)
     return fail_create(nullptr, ORLG_EINVAL, "missing topology tables");
   if (!(c->mean_iat > 0) || !(c->mean_holding > 0) || !(c->channel_width > 0))
@@ -178,7 +178,9 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   p.cw = c->channel_width;
   {
     double x2 = 2.0 * c->channel_width;
-    p.cw_x2 = (x2 >= 1.0 && x2 <= 4096.0 && x2 == std::floor(x2)) ? (int)x2 : 0;
+    p.cw_x2 = (x2 >= 1.0 && x2 <= 1024.0 && x2 == std::floor(x2)) ? (int)x2 : 0;
+    for (int se = 0; se < 16; se++)
+      p.slot_magic[se] = (p.cw_x2 > 0 && se > 0) ? (unsigned)(4294967296ull / (unsigned long long)(p.cw_x2 * se)) + 1u : 0u;
   }
   p.mean_iat = c->mean_iat;
   p.mean_holding = c->mean_holding;
@@ -201,7 +203,7 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   p.NP = (c->num_envs + bd - 1) / bd * bd;
 
   // path records
-  p.rec_u4 = c->max_hops <= 13 ? 1 : 2;
+  p.rec_u4 = c->max_hops <= 12 ? 1 : 2;
   std::vector<unsigned char> rec(npaths * 16 * p.rec_u4, 0);
   int max_se = 1;
   for (size_t i = 0; i < npaths; i++) {
@@ -227,7 +229,7 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
     for (int k = 0; k < h; k++) {
       int l = c->path_links[i * c->max_hops + k];
       if (l < 0 || l >= c->n_edges) return fail_create(e, ORLG_EINVAL, "path_links out of range");
-      r[3 + k] = (unsigned char)l;
+      r[4 + k] = (unsigned char)l;
     }
   }
   if (c->mod_se)

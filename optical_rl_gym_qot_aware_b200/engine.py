@@ -15,7 +15,8 @@ import numpy as np
 from . import spec as S
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "liborlg.so")
+# ORLG_LIB selects another build of the same library (A/B runs of kernel variants)
+LIB_PATH = os.environ.get("ORLG_LIB") or os.path.join(_HERE, "liborlg.so")
 
 REQUEST_DTYPE = np.dtype(
     [("arrival", "<f8"), ("holding", "<f8"), ("bit_rate", "<i4"), ("src", "<i2"), ("dst", "<i2")]
