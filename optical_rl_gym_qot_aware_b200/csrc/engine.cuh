@@ -170,7 +170,7 @@ __device__ __forceinline__ PathRec load_path(const Params& p, int pair, int path
 // ---- occupancy tile in shared memory ----------------------------------------
 template <int W, int BD>
 struct Tile {
-  uint32_t* s;  // [planes][BD]
+  uint32_t* s;  // [planes][BD]: shared-memory tile, or (BD == 1) this env's rows in HBM
   int tid, E;
   __device__ __forceinline__ uint32_t& word(int core, int link, int wi) {
     return s[(((core * E) + link) * W + wi) * BD + tid];
@@ -182,8 +182,26 @@ struct Tile {
     const uint32_t* base = s + (size_t)core * E * W * BD + tid;
     for_each_link(r, [&](int l) {
       const uint32_t* q = base + l * (W * BD);
+      if constexpr (BD == 1 && W % 4 == 0) {  // env-major rows in HBM: 16-byte aligned
 #pragma unroll
-      for (int wi = 0; wi < W; wi++) a.w[wi] &= q[wi * BD];
+        for (int wi = 0; wi < W; wi += 4) {
+          uint4 v = *reinterpret_cast<const uint4*>(q + wi);
+          a.w[wi] &= v.x;
+          a.w[wi + 1] &= v.y;
+          a.w[wi + 2] &= v.z;
+          a.w[wi + 3] &= v.w;
+        }
+      } else if constexpr (BD == 1 && W % 2 == 0) {  // 8-byte aligned (W = 2, 10)
+#pragma unroll
+        for (int wi = 0; wi < W; wi += 2) {
+          uint2 v = *reinterpret_cast<const uint2*>(q + wi);
+          a.w[wi] &= v.x;
+          a.w[wi + 1] &= v.y;
+        }
+      } else {
+#pragma unroll
+        for (int wi = 0; wi < W; wi++) a.w[wi] &= q[wi * BD];
+      }
     });
     return a;
   }

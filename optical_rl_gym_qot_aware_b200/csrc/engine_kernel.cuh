@@ -52,19 +52,26 @@ __device__ __forceinline__ void fence_async_smem() {
 // rollout mode).  Grid = NP / BD tiles, one thread per env.  MT is the mode the
 // instantiation is specialised for (MODE_STEP / MODE_HEURISTIC / MODE_ROLLOUT), or
 // -1 for the rarely used modes (observation, resets), which read io.mode.
-template <int W, int BD, int MT, bool PHY>
+//
+// DIRECT = false: the tile of BD envs is staged through shared memory (occ[tile][plane][BD]).
+// DIRECT = true : nothing is staged; the occupancy is env-major in HBM (occ[env][plane], i.e. the
+// same layout with a tile of one env) and every thread reads and writes its own rows in place
+// with vector loads.  This is the variant for envs whose occupancy is so large (multi-core, wide
+// spectra, many links) that only a warp or two of staged tiles would fit on an SM.
+template <int W, int BD, int MT, bool PHY, bool DIRECT = false>
 __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t bar;
-  uint32_t* tile_s = reinterpret_cast<uint32_t*>(smem_raw);
+  constexpr int PS = DIRECT ? 1 : BD;  // plane stride of the occupancy this thread sees
   const int tid = threadIdx.x;
   const int e = blockIdx.x * BD + tid;
   const bool active = e < p.num_envs;
+  uint32_t* tile_s = DIRECT ? p.occ + (size_t)(active ? e : 0) * p.planes : reinterpret_cast<uint32_t*>(smem_raw);
   const int mode = MT >= 0 ? MT : io.mode;
   const uint32_t tile_bytes = (uint32_t)p.planes * BD * 4u;
   uint32_t* tile_g = p.occ + (size_t)blockIdx.x * p.planes * BD;
-  const bool need_tile = mode != MODE_RESET_FULL && mode != MODE_RESET_EPISODE;
-  const bool dirty_tile = mode == MODE_STEP || mode == MODE_ROLLOUT || mode == MODE_RESET_FULL;
+  const bool need_tile = !DIRECT && mode != MODE_RESET_FULL && mode != MODE_RESET_EPISODE;
+  const bool dirty_tile = !DIRECT && (mode == MODE_STEP || mode == MODE_ROLLOUT || mode == MODE_RESET_FULL);
   const bool stepping = mode == MODE_STEP || mode == MODE_ROLLOUT;
 
   if (need_tile) {
@@ -75,15 +82,16 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
     }
   }
 
-  Env<W, BD, PHY> env(p, tile_s, tid, active ? e : 0);
-  typename Env<W, BD, PHY>::Req nx{};
+  Env<W, PS, PHY> env(p, tile_s, DIRECT ? 0 : tid, active ? e : 0);
+  typename Env<W, PS, PHY>::Req nx{};
   constexpr int ADIM = PHY ? PHY_ADIM : 4;
   int a[ADIM];
 #pragma unroll
   for (int i = 0; i < ADIM; i++) a[i] = 0;
   if (mode == MODE_RESET_FULL) {
     // rmsa_env.py:391-457: empty network, clock 0, counters 0, then the first request
-    for (int pl = 0; pl < p.planes; pl++) tile_s[pl * BD + tid] = mask_word(pl % W, 0, p.S);
+    if (!DIRECT || active)
+      for (int pl = 0; pl < p.planes; pl++) tile_s[pl * PS + (DIRECT ? 0 : tid)] = mask_word(pl % W, 0, p.S);
     env.now = 0.0;
     env.holding = 0.0;
     env.bit_rate = env.src = env.dst = 0;
@@ -133,12 +141,12 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
     if (mode == MODE_RESET_EPISODE) {
       env.reset_episode();
     } else if (mode == MODE_HEURISTIC && PHY) {
-      if constexpr (PHY) phy_heuristic<W, BD>(env, io.heuristic, a);
+      if constexpr (PHY) phy_heuristic<W, PS>(env, io.heuristic, a);
 #pragma unroll
       for (int i = 0; i < ADIM; i++) io.actions_out[(size_t)e * ADIM + i] = a[i];
     } else if (mode == MODE_HEURISTIC) {
       if constexpr (!PHY)
-        heuristic_action<W, BD>(env, io.heuristic, a,
+        heuristic_action<W, PS>(env, io.heuristic, a,
                                 (io.heuristic == ORLG_H_PATH_FF && io.actions) ? io.actions[e] : 0);
       if (p.action_dim == 1) {
         io.actions_out[e] = a[0];
@@ -152,22 +160,22 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
       long long rsum = 0;
       for (int t = 0; t < nsteps; t++) {
         if (mode == MODE_ROLLOUT) {
-          if constexpr (PHY) phy_heuristic<W, BD>(env, io.heuristic, a);
-          else heuristic_action<W, BD>(env, io.heuristic, a);
+          if constexpr (PHY) phy_heuristic<W, PS>(env, io.heuristic, a);
+          else heuristic_action<W, PS>(env, io.heuristic, a);
           if (t > 0) nx = env.draw_request();
         }
         Decision d;
         if constexpr (PHY) {
-          d = phy_decide<W, BD>(env, a);
+          d = phy_decide<W, PS>(env, a);
           // the info metrics are taken after the provisioning and before the releases (:313-314 vs :351)
           if (mode == MODE_STEP && io.obs != nullptr &&
               (io.obs_kind == ORLG_OBS_PHY_INFO || io.obs_kind == ORLG_OBS_PHY_CUTS))
-            phy_info<W, BD>(env, reinterpret_cast<double*>(io.obs) + (long long)e * io.obs_es, io.obs_fs,
+            phy_info<W, PS>(env, reinterpret_cast<double*>(io.obs) + (long long)e * io.obs_es, io.obs_fs,
                             io.obs_kind == ORLG_OBS_PHY_INFO);
         } else {
-          if (p.kind == ORLG_ENV_RMSA) d = rmsa_decide<W, BD>(env, a[0], a[1]);
-          else if (p.kind == ORLG_ENV_DEEPRMSA) d = deeprmsa_decide<W, BD>(env, a[0]);
-          else d = rmcsa_decide<W, BD>(env, a[0], a[1], a[2], a[3]);
+          if (p.kind == ORLG_ENV_RMSA) d = rmsa_decide<W, PS>(env, a[0], a[1]);
+          else if (p.kind == ORLG_ENV_DEEPRMSA) d = deeprmsa_decide<W, PS>(env, a[0]);
+          else d = rmcsa_decide<W, PS>(env, a[0], a[1], a[2], a[3]);
         }
         if (p.kind == ORLG_ENV_RMCSA) {  // rmcsa_env.py:292-295
           env.cnt[CNT_PROC]++;
@@ -201,23 +209,23 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
     if ((mode == MODE_STEP || mode == MODE_OBS || mode == MODE_RESET_FULL) && io.obs != nullptr) {
       if constexpr (!PHY) {
         if (io.obs_kind == ORLG_OBS_F64) {
-          fit_mask = write_deeprmsa_obs<W, BD, double>(env, reinterpret_cast<double*>(io.obs) + (long long)e * io.obs_es, io.obs_fs);
+          fit_mask = write_deeprmsa_obs<W, PS, double>(env, reinterpret_cast<double*>(io.obs) + (long long)e * io.obs_es, io.obs_fs);
           have_fit_mask = true;
         } else if (io.obs_kind == ORLG_OBS_F32) {
-          fit_mask = write_deeprmsa_obs<W, BD, float>(env, reinterpret_cast<float*>(io.obs) + (long long)e * io.obs_es, io.obs_fs);
+          fit_mask = write_deeprmsa_obs<W, PS, float>(env, reinterpret_cast<float*>(io.obs) + (long long)e * io.obs_es, io.obs_fs);
           have_fit_mask = true;
         }
       } else if (mode != MODE_STEP && (io.obs_kind == ORLG_OBS_PHY_INFO || io.obs_kind == ORLG_OBS_PHY_CUTS)) {
-        phy_info<W, BD>(env, reinterpret_cast<double*>(io.obs) + (long long)e * io.obs_es, io.obs_fs,
+        phy_info<W, PS>(env, reinterpret_cast<double*>(io.obs) + (long long)e * io.obs_es, io.obs_fs,
                         io.obs_kind == ORLG_OBS_PHY_INFO);
       }
       if (io.obs_kind == ORLG_OBS_MATRIX_U8)
-        write_matrix_obs<W, BD>(env, reinterpret_cast<unsigned char*>(io.obs) + (long long)e * io.obs_es, io.obs_fs);
+        write_matrix_obs<W, PS>(env, reinterpret_cast<unsigned char*>(io.obs) + (long long)e * io.obs_es, io.obs_fs);
     }
     if (mode == MODE_STEP && io.hint_actions != nullptr) {
       // fused next-action hint: what orlg_heuristic would write if it were launched now
       if constexpr (PHY) {
-        phy_heuristic<W, BD>(env, io.hint_heuristic, a);
+        phy_heuristic<W, PS>(env, io.hint_heuristic, a);
 #pragma unroll
         for (int i = 0; i < ADIM; i++) io.hint_actions[(size_t)e * ADIM + i] = a[i];
       } else {
@@ -229,7 +237,7 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
           else
             a[0] = fit_mask ? (__ffs((int)fit_mask) - 1) * p.j : p.k * p.j;
         } else {
-          heuristic_action<W, BD>(env, io.hint_heuristic, a);
+          heuristic_action<W, PS>(env, io.hint_heuristic, a);
         }
         if (p.action_dim == 1) {
           io.hint_actions[e] = a[0];

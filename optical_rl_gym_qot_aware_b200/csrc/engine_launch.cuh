@@ -9,9 +9,11 @@
 namespace orlg {
 
 struct LaunchGeom {
-  int BD, NP, device;
+  int BD, NP, device;  // BD = threads per CTA (= envs per staged tile)
   size_t smem_bytes;
+  bool direct;  // env-major occupancy, no staging (DIRECT instantiations, CTAs of DIRECT_CTA threads)
 };
+constexpr int DIRECT_CTA = 64;
 
 template <int W>
 cudaError_t launch_w(const LaunchGeom& g, const Params& p, const StepIO& io, cudaStream_t st);
@@ -20,26 +22,26 @@ template <int W>
 cudaError_t launch_phy(const LaunchGeom& g, const Params& p, const StepIO& io, cudaStream_t st);
 
 #if defined(ORLG_INSTANTIATE_W) || defined(ORLG_INSTANTIATE_PHY)
-template <int W, int BD, int MT, bool PHY>
+template <int W, int BD, int MT, bool PHY, bool DIRECT>
 static cudaError_t launch_t(const LaunchGeom& g, const Params& p, const StepIO& io, cudaStream_t st) {
   static size_t configured[64] = {};  // largest dynamic smem opted into, per device
   if (g.smem_bytes > 48 * 1024 && configured[g.device & 63] < g.smem_bytes) {
-    cudaError_t rc = cudaFuncSetAttribute(env_kernel<W, BD, MT, PHY>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t rc = cudaFuncSetAttribute(env_kernel<W, BD, MT, PHY, DIRECT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)g.smem_bytes);
     if (rc != cudaSuccess) return rc;
     configured[g.device & 63] = g.smem_bytes;
   }
-  env_kernel<W, BD, MT, PHY><<<g.NP / BD, BD, g.smem_bytes, st>>>(p, io);
+  env_kernel<W, BD, MT, PHY, DIRECT><<<(g.NP + BD - 1) / BD, BD, g.smem_bytes, st>>>(p, io);
   return cudaGetLastError();
 }
 
-template <int W, int BD, bool PHY>
+template <int W, int BD, bool PHY, bool DIRECT = false>
 static cudaError_t launch_m(const LaunchGeom& g, const Params& p, const StepIO& io, cudaStream_t st) {
   switch (io.mode) {
-    case MODE_STEP: return launch_t<W, BD, MODE_STEP, PHY>(g, p, io, st);
-    case MODE_HEURISTIC: return launch_t<W, BD, MODE_HEURISTIC, PHY>(g, p, io, st);
-    case MODE_ROLLOUT: return launch_t<W, BD, MODE_ROLLOUT, PHY>(g, p, io, st);
-    default: return launch_t<W, BD, -1, PHY>(g, p, io, st);
+    case MODE_STEP: return launch_t<W, BD, MODE_STEP, PHY, DIRECT>(g, p, io, st);
+    case MODE_HEURISTIC: return launch_t<W, BD, MODE_HEURISTIC, PHY, DIRECT>(g, p, io, st);
+    case MODE_ROLLOUT: return launch_t<W, BD, MODE_ROLLOUT, PHY, DIRECT>(g, p, io, st);
+    default: return launch_t<W, BD, -1, PHY, DIRECT>(g, p, io, st);
   }
 }
 
@@ -47,6 +49,7 @@ static cudaError_t launch_m(const LaunchGeom& g, const Params& p, const StepIO& 
 #ifdef ORLG_INSTANTIATE_W
 template <int W>
 cudaError_t launch_w(const LaunchGeom& g, const Params& p, const StepIO& io, cudaStream_t st) {
+  if (g.direct) return launch_m<W, DIRECT_CTA, false, true>(g, p, io, st);
   switch (g.BD) {
     case 32: return launch_m<W, 32, false>(g, p, io, st);
     case 64: return launch_m<W, 64, false>(g, p, io, st);
@@ -58,6 +61,7 @@ template cudaError_t launch_w<ORLG_INSTANTIATE_W>(const LaunchGeom&, const Param
 #ifdef ORLG_INSTANTIATE_PHY
 template <int W>
 cudaError_t launch_phy(const LaunchGeom& g, const Params& p, const StepIO& io, cudaStream_t st) {
+  if (g.direct) return launch_m<W, DIRECT_CTA, true, true>(g, p, io, st);
   return launch_m<W, 32, true>(g, p, io, st);
 }
 template cudaError_t launch_phy<ORLG_INSTANTIATE_PHY>(const LaunchGeom&, const Params&, const StepIO&, cudaStream_t);

@@ -18,7 +18,9 @@ using namespace orlg;
 struct orlg_engine {
   Params p{};
   orlg_config cfg{};
-  int W = 0, BD = 0, device = 0;
+  int W = 0, BD = 0, device = 0;  // BD = threads per CTA
+  int layout_bd = 0;              // envs per occupancy tile in HBM (1 = env-major, direct kernels)
+  bool direct = false;
   size_t smem_bytes = 0;
   int obs_kind = 0, obs_dim = 0;
   std::vector<void*> allocs;
@@ -81,7 +83,7 @@ static int dev_upload(orlg_engine* e, const T** out, const T* host, size_t count
 
 extern "C" int orlg_abi_version(void) { return ORLG_ABI_VERSION; }
 extern "C" const char* orlg_build_info(void) {
-  return "orlg sm_100a engine: TMA-staged tiles, thread-per-env, W in {2,4,10}, BD in {32,64,128}, 8-ary release heap";
+  return "orlg sm_100a engine: thread-per-env, TMA-staged tiles (BD in {32,64,128}) or env-major direct rows, W in {2,4,10}, 8-ary release heap";
 }
 extern "C" const char* orlg_last_error(const orlg_engine* e) {
   return e ? e->err.c_str() : g_create_error.c_str();
@@ -89,7 +91,7 @@ extern "C" const char* orlg_last_error(const orlg_engine* e) {
 
 static int launch(orlg_engine* e, const StepIO& io, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
-  LaunchGeom g{e->BD, e->p.NP, e->device, e->smem_bytes};
+  LaunchGeom g{e->BD, e->p.NP, e->device, e->smem_bytes, e->direct};
   cudaError_t rc;
   if (e->p.kind == ORLG_ENV_PHYRMSA) {
     switch (e->W) {
@@ -187,7 +189,9 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   p.seed = c->seed;
   p.genv0 = c->global_env_offset;
 
-  // tile geometry: as many envs per CTA as keep >= 3 CTAs resident per SM
+  // tile geometry: as many envs per CTA as keep >= 3 CTAs resident per SM.  Envs whose occupancy
+  // is too large for that (fewer than ~8 warps of tiles per SM) are not staged at all: env-major
+  // occupancy, rows read in place (DIRECT kernels).  ORLG_DIRECT=0/1 overrides the choice.
   const size_t bytes_per_env = (size_t)p.planes * 4;
   int bd = 128;
   while (bd > 32 && bytes_per_env * bd > 72 * 1024) bd >>= 1;
@@ -196,11 +200,16 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
     int v = atoi(s);
     if (v == 32 || v == 64 || v == 128) bd = v;
   }
-  if (bytes_per_env * bd > 220 * 1024)
-    return fail_create(e, ORLG_EINVAL, "occupancy of one tile exceeds shared memory (cores*edges*slots too large)");
-  e->BD = bd;
-  e->smem_bytes = bytes_per_env * bd;
-  p.NP = (c->num_envs + bd - 1) / bd * bd;
+  // measured on B200 (65 536 envs): staged wins at 352 B/env (C1/C2) and for PhyRMSA, whose metrics read
+  // every row anyway; direct wins from 896 B/env (C5 +28 %/+64 %) to 4 760 B/env (C3, 4.2x)
+  bool direct = !phy && bytes_per_env * 256 > 200 * 1024;
+  if (const char* s = getenv("ORLG_DIRECT"); s && *s) direct = atoi(s) != 0;
+  if (!direct && bytes_per_env * bd > 220 * 1024) direct = true;
+  e->direct = direct;
+  e->BD = direct ? DIRECT_CTA : bd;
+  e->layout_bd = direct ? 1 : bd;
+  e->smem_bytes = direct ? 0 : bytes_per_env * bd;
+  p.NP = (c->num_envs + e->BD - 1) / e->BD * e->BD;
 
   // path records
   p.rec_u4 = c->max_hops <= 12 ? 1 : 2;
@@ -476,7 +485,7 @@ extern "C" int orlg_get_counters(orlg_engine* e, int64_t* dev_out, void* stream)
 extern "C" int orlg_export_state(orlg_engine* e, uint8_t* dev_out, void* stream) {
   if (!e || !dev_out) return ORLG_EINVAL;
   cudaSetDevice(e->device);
-  export_state_kernel<<<148 * 8, 256, 0, (cudaStream_t)stream>>>(e->p, e->W, e->BD, dev_out);
+  export_state_kernel<<<148 * 8, 256, 0, (cudaStream_t)stream>>>(e->p, e->W, e->layout_bd, dev_out);
   CK(cudaGetLastError());
   e->launches++;
   return ORLG_OK;
@@ -581,7 +590,7 @@ extern "C" int orlg_phy_get_stats(orlg_engine* e, double* dev_out, void* stream)
   cudaSetDevice(e->device);
   const int warps_per_cta = 4;
   phy_stats_kernel<<<(e->p.num_envs + warps_per_cta - 1) / warps_per_cta, warps_per_cta * 32, 0, (cudaStream_t)stream>>>(
-      e->p, e->W, e->BD, dev_out);
+      e->p, e->W, e->layout_bd, dev_out);
   CK(cudaGetLastError());
   e->launches++;
   return ORLG_OK;
