@@ -51,6 +51,8 @@ struct Params {
   const double* obs_slots;   // [S+2]  (n - 5.5)/3.5     (deeprmsa_env.py:97)
   unsigned long long seed;
   long long genv0;
+  const unsigned char* hot_tab;  // path records + request distributions in one allocation of hot_tab_lines * 128 B
+  int hot_tab_lines;
   const uint4* path_rec;  // [N*N*k][rec_u4]: byte0 hops, 1 se, 2 best modulation, 3.. link index per hop
   const double* path_length;
   const int* mod_se;

@@ -2,6 +2,7 @@
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo --fmad=false -shared -Xcompiler -fPIC
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -258,19 +259,36 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   p.heap_stride = (p.heap_cap + HEAP_PAD + HEAP_TAIL + 7) & ~7;  // 128 B multiples: child groups stay line aligned
 
   int rc = 0;
-  const uint4* drec = nullptr;
-  if ((rc = dev_upload(e, &drec, (const uint4*)rec.data(), npaths * p.rec_u4))) return fail_create(e, rc, e->err);
-  p.path_rec = drec;
+  {  // the tables every step reads (path records, request distributions) share one contiguous
+     // allocation (a few L2 lines instead of five scattered ones).  Warming L1 with them at kernel
+     // start was measured and changed nothing: the early stalls are the cold per-env scalar loads.
+    auto pad = [](size_t b) { return (b + 127) & ~(size_t)127; };
+    const size_t o_rec = 0, b_rec = npaths * 16 * p.rec_u4;
+    const bool have_br = c->bit_rates && c->n_bit_rates > 0;
+    const size_t o_src = pad(o_rec + b_rec), b_src = c->src_cum ? (size_t)c->n_nodes * 8 : 0;
+    const size_t o_brc = o_src + b_src, b_brc = have_br ? (size_t)c->n_bit_rates * 8 : 0;
+    const size_t o_brv = o_brc + b_brc, b_brv = have_br ? (size_t)c->n_bit_rates * 4 : 0;
+    const size_t o_dst = pad(o_brv + b_brv), b_dst = c->dst_cum ? npairs * 8 : 0;
+    std::vector<unsigned char> blob(pad(o_dst + b_dst), 0);
+    memcpy(blob.data() + o_rec, rec.data(), b_rec);
+    if (b_src) memcpy(blob.data() + o_src, c->src_cum, b_src);
+    if (b_brc) memcpy(blob.data() + o_brc, c->bit_rate_cum, b_brc);
+    if (b_brv) memcpy(blob.data() + o_brv, c->bit_rates, b_brv);
+    if (b_dst) memcpy(blob.data() + o_dst, c->dst_cum, b_dst);
+    const unsigned char* d = nullptr;
+    if ((rc = dev_upload(e, &d, blob.data(), blob.size()))) return fail_create(e, rc, e->err);
+    p.hot_tab = d;
+    p.hot_tab_lines = (int)(blob.size() / 128);
+    p.path_rec = reinterpret_cast<const uint4*>(d + o_rec);
+    if (b_src) p.src_cum = reinterpret_cast<const double*>(d + o_src);
+    if (b_brc) p.br_cum = reinterpret_cast<const double*>(d + o_brc);
+    if (b_brv) p.bit_rates = reinterpret_cast<const int*>(d + o_brv);
+    if (b_dst) p.dst_cum = reinterpret_cast<const double*>(d + o_dst);
+  }
   if ((rc = dev_upload(e, &p.path_length, c->path_length, npaths))) return fail_create(e, rc, e->err);
   if (c->mod_se && (rc = dev_upload(e, &p.mod_se, c->mod_se, c->n_mods))) return fail_create(e, rc, e->err);
   if (c->mod_reach && (rc = dev_upload(e, &p.mod_reach, c->mod_reach, c->n_mods))) return fail_create(e, rc, e->err);
   if (c->mod_snr_coeff && (rc = dev_upload(e, &p.mod_coeff, c->mod_snr_coeff, c->n_mods))) return fail_create(e, rc, e->err);
-  if (c->bit_rates && c->n_bit_rates > 0) {
-    if ((rc = dev_upload(e, &p.bit_rates, c->bit_rates, c->n_bit_rates))) return fail_create(e, rc, e->err);
-    if ((rc = dev_upload(e, &p.br_cum, c->bit_rate_cum, c->n_bit_rates))) return fail_create(e, rc, e->err);
-  }
-  if (c->src_cum && (rc = dev_upload(e, &p.src_cum, c->src_cum, c->n_nodes))) return fail_create(e, rc, e->err);
-  if (c->dst_cum && (rc = dev_upload(e, &p.dst_cum, c->dst_cum, npairs))) return fail_create(e, rc, e->err);
 
   {  // observation normalisation tables, f64 in the reference's operation order
     std::vector<double> pos(p.S + 1), sl(p.S + 2);
