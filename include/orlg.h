@@ -68,7 +68,9 @@ enum {
   ORLG_H_PHY_BM_FF = 7,      /* phy_aware_bmff_rmsa  phy_rmsa_env.py:1317-1372 */
   ORLG_H_PHY_BM_FA_CUT = 8,  /* phy_aware_bmfa_rmsa  phy_rmsa_env.py:1375-1438 */
   ORLG_H_PATH_FF = 9,        /* PathOnlyFirstFitAction rmsa_env.py:974-1008 (orlg_path_first_fit only) */
-  ORLG_H_PHY_FA_FF = 10      /* phy_aware_faff_rmsa  phy_rmsa_env.py:1508-1569 */
+  ORLG_H_PHY_FA_FF = 10,     /* phy_aware_faff_rmsa  phy_rmsa_env.py:1508-1569 */
+  ORLG_H_PHY_BM_FA_RSS = 11, /* phy_aware_bmfa_rss_rmsa phy_rmsa_env.py:1441-1505 (calculate_r_spatial :1085-1108; <= 64 links) */
+  ORLG_H_PHY_FA_FF_RSS = 12  /* phy_aware_faff_rss_rmsa phy_rmsa_env.py:1572-1633 */
 };
 
 enum {

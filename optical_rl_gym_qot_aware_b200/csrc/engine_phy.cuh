@@ -13,7 +13,9 @@
 //                             channel, counted for all channels at once with bit-sliced adders
 //   _calculate_total_cuts     :1195-1203, calculate_total_r_spatial :1110-1121 (info metrics)
 //   heuristics                sapff_rmsa :1676-1737, phy_aware_sapbm_rmsa :1254-1314,
-//                             phy_aware_bmff_rmsa :1317-1372, phy_aware_bmfa_rmsa :1375-1438
+//                             phy_aware_bmff_rmsa :1317-1372, phy_aware_bmfa_rmsa :1375-1438,
+//                             phy_aware_faff_rmsa :1508-1569, and the RSS-ranked pair
+//                             phy_aware_bmfa_rss_rmsa :1441-1505, phy_aware_faff_rss_rmsa :1572-1633
 //
 // Python's `sorted(row, key=(-mod, -frag))` + "take channels until the bit rate is covered" is
 // evaluated without sorting: modulation levels are visited from high to low through per-level
@@ -107,6 +109,136 @@ __device__ __forceinline__ int count_at(const CutPlanes<W>& c, int ch) {
   return v;
 }
 
+// ---- RSS-ranked heuristics (phy_aware_bmfa_rss_rmsa :1441-1505, phy_aware_faff_rss_rmsa :1572-1633) ----
+// The fragmentation key is calculate_r_spatial (:1085-1108), an f64: rss(column with the path's links
+// taken) - rss(column), rss = sqrt(sum len^2) / (sum len + 1) over the runs of free links of the
+// channel's column in link-index order.  A column is gathered into one CT word (E <= 8*sizeof(CT)
+// links), its runs are peeled with x & (x + lowbit); sqrt and the division are IEEE, as in numpy.
+template <typename CT>
+__device__ __forceinline__ double column_rss(CT x) {
+  int sum = 0, sum_sq = 0;
+  while (x) {
+    const CT y = x + (x & (CT)(0 - x));  // the carry runs through the lowest run of ones
+    const CT run = x & ~y;
+    const int len = sizeof(CT) == 8 ? __popcll((unsigned long long)run) : __popc((unsigned)run);
+    sum += len;
+    sum_sq += len * len;
+    x &= y;
+  }
+  return sqrt((double)sum_sq) / (double)(sum + 1);
+}
+
+template <int W, int BD, typename CT, typename ENV>
+__device__ __forceinline__ double r_spatial(ENV& env, int ch, CT path_links) {
+  CT col = 0;
+  const int wi = ch >> 5, b = ch & 31;
+  for (int l = 0; l < env.p.E; l++) col |= (CT)((env.tile.word(0, l, wi) >> b) & 1u) << l;
+  return column_rss<CT>(col & ~path_links) - column_rss<CT>(col);
+}
+
+template <int W, int BD, typename CT, typename ENV>
+__device__ void phy_heuristic_rss(ENV& env, int hid, int* a) {
+  const Params& p = env.p;
+  const int pr = env.pair();
+  const int table = __ldg(p.phy_table_id + pr);
+  if (table < 0) return;
+  const bool by_mod = hid == ORLG_H_PHY_BM_FA_RSS;  // key (-mod, -frag) :1469, else (-frag) :1601
+  const double ninf = __longlong_as_double(0xFFF0000000000000ll);
+  int best = -1, best_mod = -1;
+  double best_frag = ninf;
+  for (int idp = 0; idp < p.k; idp++) {
+    PathRec rec = load_path(p, pr, idp);
+    if (rec.hops() <= 0) continue;
+    Row<W> A = env.tile.path_avail(rec, 0);
+    if (!row_any<W>(A)) continue;
+    CT links = 0;
+    for_each_link(rec, [&](int l) { links |= (CT)1 << l; });
+    // head of the sorted row (strict '>' in ascending channel order = stability of sorted()) and
+    // what the whole row can carry
+    int cap = 0, hmod = -1;
+    double hfrag = ninf;
+#pragma unroll
+    for (int i = 0; i < W; i++) {
+      uint32_t m = A.w[i];
+      while (m) {
+        const int ch = 32 * i + (__ffs((int)m) - 1);
+        m &= m - 1;
+        const int mod = __ldg(p.phy_mod + ((size_t)table * p.S + ch) * p.k + idp);
+        cap += mod;
+        if (by_mod && mod < hmod) continue;
+        const double f = r_spatial<W, BD, CT>(env, ch, links);
+        if (by_mod ? (mod > hmod || f > hfrag) : (f > hfrag)) {
+          hmod = mod;
+          hfrag = f;
+        }
+      }
+    }
+    if (cap * 100 < env.bit_rate) continue;  // the row would be tried, found short and popped
+    if (by_mod ? (hmod > best_mod || (hmod == best_mod && hfrag > best_frag)) : (hfrag > best_frag)) {
+      best = idp;
+      best_mod = hmod;
+      best_frag = hfrag;
+    }
+  }
+  if (best < 0) return;
+  // the first channels of the chosen row in sorted order: insertion into a sorted list of 8 held in
+  // registers (strict '>' keeps the earlier channel in front of an equal key)
+  PathRec rec = load_path(p, pr, best);
+  Row<W> A = env.tile.path_avail(rec, 0);
+  CT links = 0;
+  for_each_link(rec, [&](int l) { links |= (CT)1 << l; });
+  double fk[PHY_ADIM - 1];
+  int fm[PHY_ADIM - 1], fc[PHY_ADIM - 1];
+#pragma unroll
+  for (int q = 0; q < PHY_ADIM - 1; q++) {
+    fk[q] = ninf;
+    fm[q] = -1;
+    fc[q] = -1;
+  }
+#pragma unroll
+  for (int i = 0; i < W; i++) {
+    uint32_t m = A.w[i];
+    while (m) {
+      int ch = 32 * i + (__ffs((int)m) - 1);
+      m &= m - 1;
+      int mod = __ldg(p.phy_mod + ((size_t)table * p.S + ch) * p.k + best);
+      if (by_mod && mod < fm[PHY_ADIM - 2]) continue;
+      double f = r_spatial<W, BD, CT>(env, ch, links);
+      bool shifting = false;  // once placed, the displaced entries move down unconditionally
+#pragma unroll
+      for (int q = 0; q < PHY_ADIM - 1; q++) {
+        const bool before = shifting || fc[q] < 0 ||
+                            (by_mod ? (mod > fm[q] || (mod == fm[q] && f > fk[q])) : (f > fk[q]));
+        if (before) {
+          shifting = true;
+          const double tk = fk[q];
+          const int tm = fm[q], tc = fc[q];
+          fk[q] = f;
+          fm[q] = mod;
+          fc[q] = ch;
+          f = tk;
+          mod = tm;
+          ch = tc;
+          if (ch < 0) break;
+        }
+      }
+    }
+  }
+  int need = env.bit_rate, n = 0;
+#pragma unroll
+  for (int q = 0; q < PHY_ADIM - 1; q++)
+    if (need > 0 && fc[q] >= 0) {
+      a[1 + n++] = fc[q];
+      need -= fm[q] * 100;
+    }
+  if (need <= 0) {
+    a[0] = best;
+  } else {  // more than 8 channels would be needed: treated as blocked (documented cap)
+#pragma unroll
+    for (int i = 1; i < PHY_ADIM; i++) a[i] = -1;
+  }
+}
+
 // The reference heuristic's action for the pending request: a[0] = path or -2, a[1..8] channels.
 template <int W, int BD, typename ENV>
 __device__ void phy_heuristic(ENV& env, int hid, int* a) {
@@ -114,6 +246,11 @@ __device__ void phy_heuristic(ENV& env, int hid, int* a) {
 #pragma unroll
   for (int i = 0; i < PHY_ADIM; i++) a[i] = -1;
   a[0] = -2;
+  if (hid == ORLG_H_PHY_BM_FA_RSS || hid == ORLG_H_PHY_FA_FF_RSS) {
+    if (p.E <= 32) phy_heuristic_rss<W, BD, uint32_t>(env, hid, a);
+    else phy_heuristic_rss<W, BD, unsigned long long>(env, hid, a);  // E <= 64, checked by the host
+    return;
+  }
   const int pr = env.pair();
   const int table = __ldg(p.phy_table_id + pr);
   if (table < 0) return;

@@ -390,7 +390,8 @@ static int check_source(orlg_engine* e) {
 static bool heuristic_ok(const orlg_engine* e, int hid) {
   if (!e) return false;
   if (e->p.kind == ORLG_ENV_PHYRMSA)
-    return (hid >= ORLG_H_PHY_SAP_FF && hid <= ORLG_H_PHY_BM_FA_CUT) || hid == ORLG_H_PHY_FA_FF;
+    return (hid >= ORLG_H_PHY_SAP_FF && hid <= ORLG_H_PHY_BM_FA_CUT) || hid == ORLG_H_PHY_FA_FF ||
+           ((hid == ORLG_H_PHY_BM_FA_RSS || hid == ORLG_H_PHY_FA_FF_RSS) && e->p.E <= 64);  // columns are gathered into 64 bits
   return hid >= ORLG_H_SP_FF && hid <= ORLG_H_SAP_BM_FC_FF;
 }
 

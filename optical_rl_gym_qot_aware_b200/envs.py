@@ -38,6 +38,8 @@ HEURISTICS = {
     "sapff_rmsa": S.H_PHY_SAP_FF, "phy_aware_sapbm_rmsa": S.H_PHY_SAP_BM, "phy_aware_bmff_rmsa": S.H_PHY_BM_FF,
     "phy_aware_bmfa_rmsa": S.H_PHY_BM_FA_CUT, "bm_fa_cut": S.H_PHY_BM_FA_CUT,
     "phy_aware_faff_rmsa": S.H_PHY_FA_FF, "fa_ff": S.H_PHY_FA_FF,
+    "phy_aware_bmfa_rss_rmsa": S.H_PHY_BM_FA_RSS, "bm_fa_rss": S.H_PHY_BM_FA_RSS,
+    "phy_aware_faff_rss_rmsa": S.H_PHY_FA_FF_RSS, "fa_ff_rss": S.H_PHY_FA_FF_RSS,
 }
 
 

@@ -26,6 +26,7 @@ OBS_NONE, OBS_F64, OBS_F32, OBS_MATRIX_U8, OBS_PHY_INFO, OBS_PHY_CUTS = 0, 1, 2,
 H_SP_FF, H_SAP_FF, H_LLP_FF, H_SAP_BM_FC_FF, H_RANDOM = 0, 1, 2, 3, 4
 H_PHY_SAP_FF, H_PHY_SAP_BM, H_PHY_BM_FF, H_PHY_BM_FA_CUT = 5, 6, 7, 8  # phy_rmsa_env.py:1676,1254,1317,1375
 H_PATH_FF, H_PHY_FA_FF = 9, 10  # rmsa_env.py:974-1008, phy_rmsa_env.py:1508-1569
+H_PHY_BM_FA_RSS, H_PHY_FA_FF_RSS = 11, 12  # phy_rmsa_env.py:1441-1505, :1572-1633
 
 ENV_IDS = {
     "RMSA-v0": ENV_RMSA,

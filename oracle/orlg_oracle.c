@@ -451,13 +451,37 @@ static int calculate_r_cut(const oracle_env* e, int pair, int path, int ch) {
   return result[0] - result[1];
 }
 
-typedef struct phy_cand { int mod, frag, ch, idp; } phy_cand;
+/* sqrt(sum len^2) / (sum len + 1) over the runs of free links of a channel column, link-index order
+ * (the summand of calculate_r_spatial / calculate_total_r_spatial phy_rmsa_env.py:1085-1121) */
+static double column_rss(const uint8_t* col, int E) {
+  long long sum_sq = 0, sum = 0, run = 0;
+  for (int l = 0; l < E; l++) {
+    if (col[l]) run++;
+    else { sum_sq += run * run; sum += run; run = 0; }
+  }
+  sum_sq += run * run; sum += run;
+  return sqrt((double)sum_sq) / (double)(sum + 1);
+}
+
+/* calculate_r_spatial(channel, links, defrag_flag=False) phy_rmsa_env.py:1085-1108 */
+static double calculate_r_spatial(const oracle_env* e, int pair, int path, int ch) {
+  int E = e->c.n_edges, h = hops_of(e, pair, path);
+  const int16_t* L = links_of(e, pair, path, 0);
+  uint8_t tmp[256];
+  for (int l = 0; l < E; l++) tmp[l] = AV(e, 0, l)[ch];
+  double before = column_rss(tmp, E);
+  for (int i = 0; i < h; i++) tmp[L[i]] = 0;
+  double after = column_rss(tmp, E);
+  return after - before;
+}
+
+typedef struct phy_cand { int mod; double frag; int ch, idp; } phy_cand;
 
 /* sorted(row, key=...) is stable: insertion sort by the heuristic's key */
 static int cand_before(const phy_cand* a, const phy_cand* b, int hid) {
   if (hid == 5) return a->ch < b->ch;                                  /* sapff_rmsa :1704 key x[1] */
   if (hid == 6 || hid == 7) return a->mod != b->mod ? a->mod > b->mod : a->ch < b->ch; /* (-mod, ch) :1282,1343 */
-  if (hid == 10) return a->frag > b->frag;                            /* phy_aware_faff_rmsa key (-frag) :1537 */
+  if (hid == 10 || hid == 12) return a->frag > b->frag;               /* phy_aware_faff(_rss)_rmsa key (-frag) :1537,1601 */
   return a->mod != b->mod ? a->mod > b->mod : a->frag > b->frag;      /* (-mod, -frag) :1405 */
 }
 
@@ -477,7 +501,10 @@ static void phy_heuristic(oracle_env* e, int hid, int32_t* a) {
     if (hops_of(e, pair, idp) <= 0) continue;
     for (int ch = 0; ch < C; ch++) {
       if (!is_channel_free(e, pair, idp, ch)) continue;
-      phy_cand c = {phy_level(e, table, ch, idp), (hid == 8 || hid == 10) ? calculate_r_cut(e, pair, idp, ch) : 0, ch, idp};
+      double frag = 0.0;
+      if (hid == 8 || hid == 10) frag = (double)calculate_r_cut(e, pair, idp, ch);
+      else if (hid == 11 || hid == 12) frag = calculate_r_spatial(e, pair, idp, ch); /* _bmfa_rss_ :1467, _faff_rss_ :1597 */
+      phy_cand c = {phy_level(e, table, ch, idp), frag, ch, idp};
       int pos = len[idp]++;
       while (pos > 0 && cand_before(&c, &row[pos - 1], hid)) { row[pos] = row[pos - 1]; pos--; }
       row[pos] = c;
@@ -493,7 +520,7 @@ static void phy_heuristic(oracle_env* e, int hid, int32_t* a) {
       if (best < 0) { best = i; continue; }
       const phy_cand* bh = rows + (size_t)best * C;
       if (hid == 7) { if (hd->mod > bh->mod) best = i; }      /* :1350-1355 */
-      else if (hid == 10) { if (hd->frag > bh->frag) best = i; } /* :1546-1550 */
+      else if (hid == 10 || hid == 12) { if (hd->frag > bh->frag) best = i; } /* :1546-1550, :1610-1614 */
       else if (hd->mod > bh->mod || (hd->mod == bh->mod && hd->frag > bh->frag)) best = i; /* :1414-1421 */
     }
     if (best < 0) break;

@@ -132,6 +132,10 @@ def main():
         **small)
     run("phy_us14_faff_100ch", us, US, ref.phy_aware_faff_rmsa, True, 1500, seed=16, load=1500, episode_length=250,
         **small)
+    run("phy_us14_bmfarss_100ch", us, US, ref.phy_aware_bmfa_rss_rmsa, False, 1200, seed=17, load=1450,
+        episode_length=220, **small)
+    run("phy_jpn12_faffrss_64ch", jpn, JPN, ref.phy_aware_faff_rss_rmsa, True, 1200, seed=18, load=1150,
+        episode_length=180, **tiny)
     run("phy_jpn12_sapbm_64ch", jpn, JPN, ref.phy_aware_sapbm_rmsa, True, 1500, seed=14, load=1300,
         episode_length=100, **tiny)
 

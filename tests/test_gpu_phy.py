@@ -10,11 +10,11 @@ from optical_rl_gym_qot_aware_b200 import spec as S
 pytestmark = pytest.mark.gpu
 
 HEUR = {"bmfa_cut": S.H_PHY_BM_FA_CUT, "sapff": S.H_PHY_SAP_FF, "bmff": S.H_PHY_BM_FF, "sapbm": S.H_PHY_SAP_BM,
-        "faff": S.H_PHY_FA_FF}
+        "faff": S.H_PHY_FA_FF, "bmfarss": S.H_PHY_BM_FA_RSS, "faffrss": S.H_PHY_FA_FF_RSS}
 
 
 def heuristic_of(case):
-    return next(v for k, v in HEUR.items() if k in case)
+    return next(v for k, v in sorted(HEUR.items(), key=lambda kv: -len(kv[0])) if k in case)
 
 
 @pytest.mark.parametrize("case", G.PHY_CASES)
@@ -64,7 +64,8 @@ def test_engine_replays_phy_golden(case):
 
 @pytest.mark.parametrize("hid,channels,load", [(S.H_PHY_BM_FA_CUT, (80, 108), 1400), (S.H_PHY_SAP_FF, (30, 40), 1500),
                                                (S.H_PHY_BM_FF, (20, 24), 1300), (S.H_PHY_SAP_BM, (30, 40), 1600),
-                                               (S.H_PHY_FA_FF, (30, 40), 1500)])
+                                               (S.H_PHY_FA_FF, (30, 40), 1500), (S.H_PHY_BM_FA_RSS, (20, 24), 1300),
+                                               (S.H_PHY_FA_FF_RSS, (30, 40), 1500)])
 def test_phy_rollout_matches_oracle_on_philox(hid, channels, load):
     import torch
 

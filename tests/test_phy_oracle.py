@@ -7,11 +7,11 @@ import pytest
 import golden_util as G
 import oracle_binding as OB
 
-HEUR = {"bmfa_cut": 8, "sapff": 5, "bmff": 7, "sapbm": 6, "faff": 10}
+HEUR = {"bmfa_cut": 8, "sapff": 5, "bmff": 7, "sapbm": 6, "faff": 10, "bmfarss": 11, "faffrss": 12}
 
 
 def heuristic_of(case):
-    return next(v for k, v in HEUR.items() if k in case)
+    return next(v for k, v in sorted(HEUR.items(), key=lambda kv: -len(kv[0])) if k in case)
 
 
 @pytest.mark.parametrize("case", G.PHY_CASES)
