@@ -137,7 +137,13 @@ typedef struct orlg_config {
 
   int32_t heap_capacity;  /* release-queue entries per env; 0 = provable bound */
   int32_t obs_kind;       /* ORLG_OBS_* written by orlg_step */
-  int32_t reserved[6];
+  /* PhyRMSA virtual layer (grooming, phy_rmsa_env.py:625-659,1650-1673): 0 = channel_state not kept, physical
+   * layer only; 1 = env.grooming True; 2 = env.grooming False with channel_state kept, which is the reference's
+   * behaviour: sapff/sapbm/bmff/faff/faff_rss call use_existing_channels unconditionally, bmfa/bmfa_rss only
+   * under env.grooming.  A virtual action is (idp + 20, channels); shares are taken as the reference's
+   * use_existing_channels takes them (all the free capacity of each channel, the last one the remainder). */
+  int32_t phy_grooming;
+  int32_t reserved[5];
 
   /* PhyRMSA-v0 (phy_rmsa_env.py:51-53,93-95): num_slots = number of channels, num_cores = 1 */
   int32_t phy_n_tables;   /* rows of connections_detail */
@@ -249,6 +255,13 @@ int orlg_get_counters(orlg_engine* e, int64_t* dev_out /* [num_envs][ORLG_NUM_CO
  * physical_services_accepted_episode (phy_rmsa_env.py:431-439), then number_cuts_total and
  * rss_total_metric (:1195-1203, :1110-1121) of the CURRENT channel map. */
 int orlg_phy_get_stats(orlg_engine* e, double* dev_out, void* stream);
+
+/* PhyRMSA-v0 channel_state (phy_rmsa_env.py:158-166,599-601): the partially used channels of every env in
+ * append order, int32 [num_envs][max_entries][6] = (src_id * n_nodes + dst_id, idp, channel, used, free,
+ * capacity) in units of 100 Gb/s, and their number per env in dev_count [num_envs] (entries past
+ * max_entries are counted, not written).  Needs phy_grooming != 0. */
+int orlg_phy_get_channel_state(orlg_engine* e, int32_t* dev_out, int32_t max_entries, int32_t* dev_count,
+                               void* stream);
 
 /* Unpacked occupancy: uint8 [num_envs][num_cores][n_edges][num_slots], 1 = free,
  * i.e. topology.graph["available_slots"] of every env. */

@@ -80,6 +80,12 @@ struct Params {
   const unsigned char* phy_cut_links;   // [N*N*k][phy_max_terms] neighbour link of every r_cut term
   const int* phy_cut_count;             // [N*N*k]
   int phy_max_terms, phy_mask_w;
+  // virtual layer (phy_rmsa_env.py:625-659, 1650-1673): channel_state of every env as one list in append order,
+  // entry i of env e at phy_cs[i * NP + e] = {pair | idp << 16 | channel << 20, used | free << 8 | capacity << 16}
+  int phy_grooming;                     // 0 off, 1 env.grooming, 2 channel_state kept with env.grooming False
+  int phy_cs_cap;
+  uint2* phy_cs;
+  uint32_t* phy_cs_len;                 // [NP] entries in use | tombstones << 16
   double* phy_f;                        // [2][NP] episode sums: path length, gsnr
   long long* phy_i;                     // [4][NP] episode sums: path index, modulation level, channels, physical services
 };

@@ -32,6 +32,7 @@ struct Env {
   long long cnt[CNT_N];
   double fsum[2];      // PhyRMSA episode sums (phy_rmsa_env.py:431-439)
   long long isum[4];
+  int cs_len, cs_dead; // PhyRMSA channel_state list: slots in use (tombstones included), tombstones
 
   __device__ __forceinline__ Env(const Params& p_, uint32_t* smem, int tid, int e_)
       : p(p_), tile{smem, tid, p_.E}, e(e_) {
@@ -56,6 +57,15 @@ struct Env {
       fsum[1] = p.phy_f[(size_t)p.NP + e];
 #pragma unroll
       for (int i = 0; i < 4; i++) isum[i] = p.phy_i[(size_t)i * p.NP + e];
+      load_cs_len();
+    }
+  }
+  __device__ __forceinline__ void load_cs_len() {
+    cs_len = cs_dead = 0;
+    if (PHY && p.phy_grooming) {
+      uint32_t v = p.phy_cs_len[e];
+      cs_len = (int)(v & 0xFFFFu);
+      cs_dead = (int)(v >> 16);
     }
   }
   // only the pending request (enough for the heuristics and the observation)
@@ -64,6 +74,7 @@ struct Env {
     bit_rate = (int)(m & 0xFFFFu);
     src = (int)((m >> 16) & 0xFFu);
     dst = (int)(m >> 24);
+    if constexpr (PHY) load_cs_len();
   }
   __device__ __forceinline__ void store_scalars() {
     p.now[e] = now;
@@ -78,6 +89,68 @@ struct Env {
       p.phy_f[(size_t)p.NP + e] = fsum[1];
 #pragma unroll
       for (int i = 0; i < 4; i++) p.phy_i[(size_t)i * p.NP + e] = isum[i];
+      if (p.phy_grooming) p.phy_cs_len[e] = (uint32_t)cs_len | ((uint32_t)cs_dead << 16);
+    }
+  }
+
+  // ---- PhyRMSA channel_state (phy_rmsa_env.py:599-601, 625-659, 801-846) ----
+  // The reference keeps one Python list of (channel, used, free, capacity) per (src_id, dst_id, idp) and
+  // updates a tuple by remove + append.  Here every env has one list for all keys in append order; a removed
+  // entry becomes a tombstone and the list is squeezed when tombstones pile up, which keeps the order.
+  static constexpr uint32_t CS_DEAD = 0xFFFFFFFFu;
+  __device__ __forceinline__ static uint32_t cs_key(int pr, int idp, int ch) {
+    return (uint32_t)pr | ((uint32_t)idp << 16) | ((uint32_t)ch << 20);
+  }
+  __device__ __forceinline__ uint2& cs_at(int i) const { return p.phy_cs[(size_t)i * p.NP + e]; }
+  __device__ int cs_find(uint32_t key) const {
+    for (int i = 0; i < cs_len; i++)
+      if (cs_at(i).x == key) return i;
+    return -1;
+  }
+  __device__ __forceinline__ void cs_remove(int i) {
+    cs_at(i).x = CS_DEAD;
+    cs_dead++;
+  }
+  __device__ void cs_squeeze() {
+    int j = 0;
+    for (int i = 0; i < cs_len; i++) {
+      uint2 v = cs_at(i);
+      if (v.x != CS_DEAD) {
+        if (j != i) cs_at(j) = v;
+        j++;
+      }
+    }
+    cs_len = j;
+    cs_dead = 0;
+  }
+  __device__ void cs_append(uint32_t key, int used, int free_, int cap) {
+    if (cs_len == p.phy_cs_cap || cs_dead >= 32 + ((cs_len - cs_dead) >> 1)) cs_squeeze();
+    if (cs_len == p.phy_cs_cap) {
+      cnt[CNT_FAULT] |= 4;  // more partially used channels than live lightpaths can have: capacity misconfigured
+      return;
+    }
+    cs_at(cs_len++) = make_uint2(key, (uint32_t)used | ((uint32_t)free_ << 8) | ((uint32_t)cap << 16));
+  }
+  // _release_path :781-861 for one channel tuple (ch, share, ., cap) of a service on (pair, path)
+  __device__ void phy_release(unsigned long long s) {
+    const int share = svc_core(s), cap = svc_se(s), ch = svc_start(s);
+    bool free_it = !p.phy_grooming || share == cap;  // :784 channel[1] == channel[3]
+    if (!free_it) {
+      const uint32_t key = cs_key(svc_pair(s), svc_path(s), ch);
+      const int at = cs_find(key);
+      if (at < 0) {  // unreachable from step (the reference would raise)
+        cnt[CNT_FAULT] |= 8;
+        return;
+      }
+      const uint32_t y = cs_at(at).y;
+      const int used = (int)(y & 0xFFu), fr = (int)((y >> 8) & 0xFFu);
+      cs_remove(at);
+      if (used == share) free_it = true;                              // :821 nobody else is on the channel
+      else cs_append(key, used - share, fr + share, (int)(y >> 16));  // :841-844
+    }
+    if (free_it) {
+      PathRec rec = load_path(p, svc_pair(s), svc_path(s));
+      tile.set_range(rec, 0, ch, 1);
     }
   }
 
@@ -207,9 +280,38 @@ struct Env {
     cnt[CNT_BR_REQ] += bit_rate;  // rmsa_env.py:677-678, rmcsa_env.py:730-731
     cnt[CNT_EP_BR_REQ] += bit_rate;
     while (next_rel <= now) {  // rmsa_env.py:689-695
+      const double rel_key = next_rel;
       unsigned long long s = heap_pop();
-      PathRec rec = load_path(p, svc_pair(s), svc_path(s));
-      tile.set_range(rec, svc_core(s), svc_start(s), svc_slots(s));
+      if constexpr (PHY) {
+        if (!p.phy_grooming) {
+          phy_release(s);
+        } else {
+          // the queue entries of one service (one per channel, same key) come out of the heap in any order;
+          // _release_path walks service.channels in order, and that order decides where the updated
+          // channel_state tuples are appended: regroup by the channel's position in the action
+          unsigned long long grp[8];
+          unsigned have = 0u;
+          const double key = rel_key;
+          for (;;) {
+            const int idx = svc_slots(s) & 7;
+            if (have & (1u << idx)) phy_release(s);  // two services released at the same instant
+            else {
+#pragma unroll
+              for (int q = 0; q < 8; q++)
+                if (idx == q) grp[q] = s;
+              have |= 1u << idx;
+            }
+            if (heap_len == 0 || next_rel != key) break;
+            s = heap_pop();
+          }
+#pragma unroll
+          for (int q = 0; q < 8; q++)
+            if (have & (1u << q)) phy_release(grp[q]);
+        }
+      } else {
+        PathRec rec = load_path(p, svc_pair(s), svc_path(s));
+        tile.set_range(rec, svc_core(s), svc_start(s), svc_slots(s));
+      }
     }
   }
   __device__ __forceinline__ void next_service() { commit_request(draw_request()); }

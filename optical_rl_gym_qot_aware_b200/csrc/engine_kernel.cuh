@@ -96,6 +96,7 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
     env.holding = 0.0;
     env.bit_rate = env.src = env.dst = 0;
     env.heap_len = 0;
+    env.cs_len = env.cs_dead = 0;  // channel_state phy_rmsa_env.py:455-461
     env.next_rel = __longlong_as_double(0x7FF0000000000000ll);
 #pragma unroll
     for (int i = 0; i < CNT_N; i++) env.cnt[i] = 0;

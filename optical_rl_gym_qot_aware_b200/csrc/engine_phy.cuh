@@ -239,6 +239,45 @@ __device__ void phy_heuristic_rss(ENV& env, int hid, int* a) {
   }
 }
 
+// use_existing_channels (phy_rmsa_env.py:1650-1673): the first path whose partially used channels can carry
+// the request; their channels in list order, each giving all its free capacity.  a[0] = idp + 20 (:1380).
+template <typename ENV>
+__device__ bool phy_use_existing_channels(ENV& env, int* a) {
+  const Params& p = env.p;
+  const uint32_t pr = (uint32_t)env.pair();
+  int sum[8];
+#pragma unroll
+  for (int q = 0; q < 8; q++) sum[q] = 0;
+  for (int i = 0; i < env.cs_len; i++) {
+    const uint2 v = env.cs_at(i);
+    if ((v.x & 0xFFFFu) != pr || v.x == ENV::CS_DEAD) continue;
+    const int idp = (int)((v.x >> 16) & 15u), fr = (int)((v.y >> 8) & 0xFFu);
+#pragma unroll
+    for (int q = 0; q < 8; q++) sum[q] += (idp == q) ? fr : 0;
+  }
+  int idp = -1;
+#pragma unroll
+  for (int q = 7; q >= 0; q--)
+    if (q < p.k && sum[q] * 100 >= env.bit_rate) idp = q;
+  if (idp < 0) return false;
+  int need = env.bit_rate, n = 0;
+  const uint32_t want = pr | ((uint32_t)idp << 16);
+  for (int i = 0; i < env.cs_len && need > 0; i++) {
+    const uint2 v = env.cs_at(i);
+    const int fr = (int)((v.y >> 8) & 0xFFu);
+    if ((v.x & 0xFFFFFu) != want || v.x == ENV::CS_DEAD || fr <= 0) continue;
+    if (n == PHY_ADIM - 1) {  // documented cap of 8 channels per action: fall back to the physical layer
+#pragma unroll
+      for (int q = 1; q < PHY_ADIM; q++) a[q] = -1;
+      return false;
+    }
+    a[1 + n++] = (int)(v.x >> 20);
+    need -= fr * 100;
+  }
+  a[0] = idp + 20;
+  return true;
+}
+
 // The reference heuristic's action for the pending request: a[0] = path or -2, a[1..8] channels.
 template <int W, int BD, typename ENV>
 __device__ void phy_heuristic(ENV& env, int hid, int* a) {
@@ -246,6 +285,11 @@ __device__ void phy_heuristic(ENV& env, int hid, int* a) {
 #pragma unroll
   for (int i = 0; i < PHY_ADIM; i++) a[i] = -1;
   a[0] = -2;
+  // the virtual layer first: unconditionally in sapff/sapbm/bmff/faff/faff_rss (:1256,1321,1510,1574,1678),
+  // under env.grooming in bmfa/bmfa_rss (:1377,1443)
+  if (p.phy_grooming == 1 ||
+      (p.phy_grooming == 2 && hid != ORLG_H_PHY_BM_FA_CUT && hid != ORLG_H_PHY_BM_FA_RSS))
+    if (phy_use_existing_channels(env, a)) return;
   if (hid == ORLG_H_PHY_BM_FA_RSS || hid == ORLG_H_PHY_FA_FF_RSS) {
     if (p.E <= 32) phy_heuristic_rss<W, BD, uint32_t>(env, hid, a);
     else phy_heuristic_rss<W, BD, unsigned long long>(env, hid, a);  // E <= 64, checked by the host
@@ -343,7 +387,9 @@ __device__ void phy_heuristic(ENV& env, int hid, int* a) {
   }
 }
 
-// PhyRMSAEnv.step, physical path branch (phy_rmsa_env.py:290-309)
+// PhyRMSAEnv.step (phy_rmsa_env.py:272-309).  The action carries channel numbers; the (used, free) fields of
+// the reference's channel tuples are what its heuristics put there: every channel is used up to its capacity
+// (physical layer) or its free part (virtual layer) until the bit rate is covered, the last one takes the rest.
 template <int W, int BD, typename ENV>
 __device__ Decision phy_decide(ENV& env, const int* a) {
   const Params& p = env.p;
@@ -351,20 +397,73 @@ __device__ Decision phy_decide(ENV& env, const int* a) {
   const int path = a[0], pr = env.pair();
   int nch = 0;
   while (nch < PHY_ADIM - 1 && a[1 + nch] >= 0) nch++;
+  const double key = env.now + env.holding;
+  if (p.phy_grooming && path >= 20 && path < 20 + p.k && nch > 0) {
+    // virtual layer :280-288, _provision_virtual_path :625-659
+    const int idp = path - 20;
+    int at[PHY_ADIM - 1], share[PHY_ADIM - 1];
+    uint32_t yv[PHY_ADIM - 1];
+#pragma unroll
+    for (int i = 0; i < PHY_ADIM - 1; i++) at[i] = -1;
+    for (int j = 0; j < env.cs_len; j++) {  // one pass finds every listed channel
+      const uint2 v = env.cs_at(j);
+      if ((v.x & 0xFFFFFu) != ((uint32_t)pr | ((uint32_t)idp << 16)) || v.x == ENV::CS_DEAD) continue;
+      const int ch = (int)(v.x >> 20);
+#pragma unroll
+      for (int i = 0; i < PHY_ADIM - 1; i++)
+        if (i < nch && a[1 + i] == ch && at[i] < 0) {
+          at[i] = j;
+          yv[i] = v.y;
+        }
+    }
+    bool ok = true;
+    int need = env.bit_rate / 100;
+#pragma unroll
+    for (int i = 0; i < PHY_ADIM - 1; i++)
+      if (i < nch) {
+#pragma unroll
+        for (int q = 0; q < i; q++) ok = ok && a[1 + q] != a[1 + i];
+        const int fr = at[i] >= 0 ? (int)((yv[i] >> 8) & 0xFFu) : 0;
+        ok = ok && fr > 0 && need > 0;
+        share[i] = fr < need ? fr : need;
+        need -= share[i];
+      }
+    if (!ok) return d;
+#pragma unroll
+    for (int i = 0; i < PHY_ADIM - 1; i++)
+      if (i < nch) env.cs_remove(at[i]);
+#pragma unroll
+    for (int i = 0; i < PHY_ADIM - 1; i++)
+      if (i < nch) {  // :643-645 the updated tuple goes to the end of the list
+        const int used = (int)(yv[i] & 0xFFu), fr = (int)((yv[i] >> 8) & 0xFFu), cap = (int)(yv[i] >> 16);
+        env.cs_append(ENV::cs_key(pr, idp, a[1 + i]), used + share[i], fr - share[i], cap);
+        env.heap_push(key, pack_service(pr, idp, share[i], a[1 + i], i, cap));
+      }
+    env.cnt[CNT_ACC]++;  // _service_acceptance(True) :767-778
+    env.cnt[CNT_EP_ACC]++;
+    env.cnt[CNT_BR_PROV] += env.bit_rate;
+    env.cnt[CNT_EP_BR_PROV] += env.bit_rate;
+    return Decision{1, path, 0, a[1], nch};
+  }
   if (path < 0 || path >= p.k || nch == 0) return d;
   const int table = __ldg(p.phy_table_id + pr);
   PathRec rec = load_path(p, pr, path);
   if (table < 0 || rec.hops() <= 0) return d;
   Row<W> A = env.tile.path_avail(rec, 0);
   bool ok = true;
+  int need = env.bit_rate / 100;
   for (int i = 0; i < nch; i++) {  // is_path_free_on_channels :1019-1027 (+ range / duplicate checks)
     int ch = a[1 + i];
     ok = ok && ch < p.S && row_bit<W>(A, ch < p.S ? ch : 0);
     if (ok) row_clear_bit<W>(A, ch);
+    if (ok && p.phy_grooming) {  // with channel_state kept, every listed channel must carry part of the request
+      ok = need > 0;
+      need -= (int)__ldg(p.phy_mod + ((size_t)table * p.S + ch) * p.k + path);
+    }
   }
   if (!ok) return d;
-  const double key = env.now + env.holding;
-  for (int i = 0; i < nch; i++) {  // _provision_path :576-598
+  need = env.bit_rate / 100;
+  for (int i = 0; i < nch; i++) {  // _provision_path :576-601
     const int ch = a[1 + i];
     env.tile.clear_range(rec, 0, ch, 1);
     const size_t tix = ((size_t)table * p.S + ch) * p.k + path;
@@ -372,7 +471,13 @@ __device__ Decision phy_decide(ENV& env, const int* a) {
     env.fsum[1] += __ldg(p.phy_gsnr + tix);
     env.isum[1] += level;
     env.isum[2]++;
-    env.heap_push(key, pack_service(pr, path, 0, ch, 1, level));
+    int share = 0;
+    if (p.phy_grooming) {
+      share = level < need ? level : need;
+      need -= share;
+      if (share != level) env.cs_append(ENV::cs_key(pr, path, ch), share, level - share, level);  // :599-601
+    }
+    env.heap_push(key, pack_service(pr, path, share, ch, i, level));  // "n" = position in service.channels
   }
   env.cnt[CNT_ACC]++;  // _service_acceptance(False) :767-778
   env.cnt[CNT_EP_ACC]++;

@@ -53,6 +53,29 @@ __global__ void requests_kernel(const Params p, orlg_request* out) {
 }
 
 
+// PhyRMSA-v0 channel_state without the tombstones, thread per env
+__global__ void phy_channel_state_kernel(const Params p, int* out, int max_entries, int* count) {
+  int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= p.num_envs) return;
+  const int len = (int)(p.phy_cs_len[e] & 0xFFFFu);
+  int n = 0;
+  for (int i = 0; i < len; i++) {
+    const uint2 v = p.phy_cs[(size_t)i * p.NP + e];
+    if (v.x == 0xFFFFFFFFu) continue;
+    if (n < max_entries) {
+      int* o = out + ((size_t)e * max_entries + n) * 6;
+      o[0] = (int)(v.x & 0xFFFFu);
+      o[1] = (int)((v.x >> 16) & 15u);
+      o[2] = (int)(v.x >> 20);
+      o[3] = (int)(v.y & 0xFFu);
+      o[4] = (int)((v.y >> 8) & 0xFFu);
+      o[5] = (int)(v.y >> 16);
+    }
+    n++;
+  }
+  count[e] = n;
+}
+
 // PhyRMSA-v0 statistics, one warp per env: episode sums + fragmentation metrics of the current
 // channel map (phy_rmsa_env.py:1195-1203, 1110-1121).  Lanes take channels round-robin; the
 // per-channel terms are reduced with warp shuffles.  (The sums over channels are therefore

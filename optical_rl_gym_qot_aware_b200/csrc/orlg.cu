@@ -255,6 +255,8 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   int min_slots = (int)std::ceil((double)min_br / ((double)max_se * c->channel_width)) + 1;
   if (phy) min_slots = 1;  // one queue entry per occupied channel
   long long bound = (long long)cores * p.E * (p.S / min_slots);
+  const long long lightpaths = bound;  // PhyRMSA: occupied (link, channel) cells
+  if (phy && c->phy_grooming) bound *= 2;  // groomed services queue entries without holding spectrum of their own
   p.heap_cap = c->heap_capacity > 0 ? c->heap_capacity : (int)(bound < 16 ? 16 : bound);
   p.heap_stride = (p.heap_cap + HEAP_PAD + HEAP_TAIL + 7) & ~7;  // 128 B multiples: child groups stay line aligned
 
@@ -326,6 +328,16 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   const size_t NP = p.NP;
   if (phy && ((rc = dev_alloc(e, &p.phy_f, 2 * NP)) || (rc = dev_alloc(e, &p.phy_i, 4 * NP))))
     return fail_create(e, rc, e->err);
+  if (phy && c->phy_grooming) {
+    if (c->phy_grooming < 0 || c->phy_grooming > 2) return fail_create(e, ORLG_EINVAL, "phy_grooming must be 0, 1 or 2");
+    if (npairs > 65536 || p.k > 8 || p.S > 4096) return fail_create(e, ORLG_EINVAL, "channel_state keys: pairs <= 65536, k <= 8, channels <= 4096");
+    p.phy_grooming = c->phy_grooming;
+    // a partially used channel belongs to one live lightpath; + slack for tombstones between squeezes
+    long long cap = lightpaths + 64 + lightpaths / 2;
+    p.phy_cs_cap = (int)(cap > 65535 ? 65535 : cap);
+    if ((rc = dev_alloc(e, &p.phy_cs, (size_t)p.phy_cs_cap * NP)) || (rc = dev_alloc(e, &p.phy_cs_len, NP)))
+      return fail_create(e, rc, e->err);
+  }
   if ((rc = dev_alloc(e, &p.occ, (size_t)p.planes * NP)) || (rc = dev_alloc(e, &p.now, NP)) ||
       (rc = dev_alloc(e, &p.holding, NP)) || (rc = dev_alloc(e, &p.meta, NP)) ||
       (rc = dev_alloc(e, &p.next_rel, NP)) || (rc = dev_alloc(e, &p.heap_len, NP)) ||
@@ -595,6 +607,21 @@ extern "C" int orlg_gsnr(orlg_engine* e, const int32_t* dev_query, double* dev_o
   const int warps_per_cta = 4;
   gsnr_kernel<<<(e->p.num_envs + warps_per_cta - 1) / warps_per_cta, warps_per_cta * 32, 0, (cudaStream_t)stream>>>(
       e->p, e->gp, dev_query, dev_out);
+  CK(cudaGetLastError());
+  e->launches++;
+  return ORLG_OK;
+}
+
+extern "C" int orlg_phy_get_channel_state(orlg_engine* e, int32_t* dev_out, int32_t max_entries, int32_t* dev_count,
+                                          void* stream) {
+  if (!e || !dev_count || max_entries < 0 || (max_entries > 0 && !dev_out)) return ORLG_EINVAL;
+  if (e->p.kind != ORLG_ENV_PHYRMSA || !e->p.phy_grooming) {
+    e->err = "orlg_phy_get_channel_state needs a PhyRMSA engine with phy_grooming != 0";
+    return ORLG_ESTATE;
+  }
+  cudaSetDevice(e->device);
+  phy_channel_state_kernel<<<(e->p.num_envs + 127) / 128, 128, 0, (cudaStream_t)stream>>>(e->p, dev_out, max_entries,
+                                                                                          dev_count);
   CK(cudaGetLastError());
   e->launches++;
   return ORLG_OK;

@@ -34,6 +34,7 @@ EXPORTS = (
     "orlg_reset", "orlg_step", "orlg_step_host", "orlg_set_obs_layout", "orlg_observation",
     "orlg_heuristic", "orlg_rollout", "orlg_get_counters", "orlg_export_state", "orlg_get_requests",
     "orlg_launch_count", "orlg_gsnr_configure", "orlg_gsnr", "orlg_phy_get_stats", "orlg_path_first_fit", "orlg_set_next_action_hint", "orlg_step_host_async", "orlg_step_host_wait",
+    "orlg_phy_get_channel_state",
 )
 
 
@@ -54,7 +55,7 @@ class OrlgConfig(C.Structure):
         ("bit_rates", C.c_void_p), ("bit_rate_cum", C.c_void_p),
         ("bit_rate_lo", C.c_int32), ("bit_rate_hi", C.c_int32),
         ("src_cum", C.c_void_p), ("dst_cum", C.c_void_p),
-        ("heap_capacity", C.c_int32), ("obs_kind", C.c_int32), ("reserved", C.c_int32 * 6),
+        ("heap_capacity", C.c_int32), ("obs_kind", C.c_int32), ("phy_grooming", C.c_int32), ("reserved", C.c_int32 * 5),
         ("phy_n_tables", C.c_int32), ("phy_max_terms", C.c_int32),
         ("phy_table_id", C.c_void_p), ("phy_mod_level", C.c_void_p), ("phy_gsnr", C.c_void_p),
         ("phy_cut_links", C.c_void_p), ("phy_cut_count", C.c_void_p),
@@ -107,6 +108,7 @@ def load_library():
         L.orlg_gsnr_configure.argtypes = [vp, C.POINTER(OrlgGsnrParams)]
         L.orlg_gsnr.argtypes = [vp, vp, vp, vp]
         L.orlg_phy_get_stats.argtypes = [vp, vp, vp]
+        L.orlg_phy_get_channel_state.argtypes = [vp, vp, i32, vp, vp]
         L.orlg_path_first_fit.argtypes = [vp, vp, vp, vp]
         L.orlg_set_next_action_hint.argtypes = [vp, i32, vp]
         _lib = L
@@ -158,6 +160,7 @@ class Engine:
         c = OrlgConfig()
         if ph is not None:
             c.phy_n_tables, c.phy_max_terms = ph.n_tables, ph.max_terms
+            c.phy_grooming = int(getattr(spec, "phy_grooming", 0))
         c.abi_version = self.L.orlg_abi_version()
         c.env_kind, c.device, c.num_envs = spec.env_kind, device, self.num_envs
         c.global_env_offset = global_env_offset
@@ -294,6 +297,15 @@ class Engine:
         out = self.torch.empty((self.num_envs, REQUEST_DTYPE.itemsize), dtype=self.torch.uint8, device=self.device)
         self._ck(self.L.orlg_get_requests(self.h, self._p(out), self._stream()))
         return out.cpu().numpy().view(REQUEST_DTYPE).reshape(self.num_envs)
+
+    def phy_channel_state(self, max_entries: int = 256):
+        """PhyRMSA-v0 channel_state: (int32 [num_envs, max_entries, 6], int32 [num_envs] counts); rows are
+        (src_id * n_nodes + dst_id, idp, channel, used, free, capacity) in append order."""
+        torch = self.torch
+        out = torch.zeros((self.num_envs, max_entries, 6), dtype=torch.int32, device=self.device)
+        cnt = torch.zeros(self.num_envs, dtype=torch.int32, device=self.device)
+        self._ck(self.L.orlg_phy_get_channel_state(self.h, self._p(out), max_entries, self._p(cnt), self._stream()))
+        return out, cnt
 
     def phy_stats(self):
         """PhyRMSA-v0: f64 [num_envs, 8] (see orlg_phy_get_stats in include/orlg.h)."""

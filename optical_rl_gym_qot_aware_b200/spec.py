@@ -73,6 +73,10 @@ class EnvSpec:
     request_source: int = SRC_PHILOX
     obs_kind: int = OBS_NONE
     phy: Optional[object] = None  # phy.PhyTables for PhyRMSA-v0
+    # PhyRMSA virtual layer: 0 = channel_state not kept (physical layer only), 1 = grooming=True,
+    # 2 = grooming=False but channel_state kept, i.e. what the reference does: sapff/sapbm/bmff/faff/faff_rss
+    # try use_existing_channels whatever env.grooming says (phy_rmsa_env.py:1256,1321,1510,1574,1678)
+    phy_grooming: int = 0
 
     @property
     def action_dim(self) -> int:
@@ -152,6 +156,7 @@ def make_spec(
     l_band: bool = True,
     s_band: bool = True,
     grooming: bool = False,
+    keep_channel_state: bool = False,
     defrag_period=None,
     number_moves=None,
     metric: str = "cut",
@@ -171,9 +176,9 @@ def make_spec(
     if kind == ENV_PHYRMSA:
         from . import phy as P
 
-        if grooming or defrag_period:
-            raise NotImplementedError("PhyRMSA grooming / periodic defragmentation are not built yet "
-                                      "(SURVEY.md 8f N2); pass grooming=False, defrag_period=None")
+        if defrag_period:
+            raise NotImplementedError("PhyRMSA periodic defragmentation is not built yet (SURVEY.md 8f N2); "
+                                      "pass defrag_period=None")
         if modulation_level is None or connections_detail is None or gsnr is None:
             raise ValueError("PhyRMSA-v0 needs modulation_level, connections_detail and gsnr")
         channels = P.num_channels(number_spectrum_channels, number_spectrum_channels_s_band, l_band, s_band)
@@ -240,6 +245,8 @@ def make_spec(
         obs_kind = OBS_F64 if kind == ENV_DEEPRMSA else OBS_NONE
     spec.obs_kind = obs_kind
     spec.phy = phy_tables
+    if kind == ENV_PHYRMSA:
+        spec.phy_grooming = 1 if grooming else (2 if keep_channel_state else 0)
     assert spec.num_slots <= 1024 and tables.n_edges <= 128
     return spec
 

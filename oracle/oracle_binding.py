@@ -64,7 +64,7 @@ class OracleConfig(C.Structure):
         ("src_cum", C.c_void_p),
         ("dst_cum", C.c_void_p),
         ("phy_n_tables", C.c_int32),
-        ("phy_pad", C.c_int32),
+        ("phy_grooming", C.c_int32),
         ("phy_table_id", C.c_void_p),
         ("phy_mod_level", C.c_void_p),
         ("phy_gsnr", C.c_void_p),
@@ -116,6 +116,8 @@ def lib():
         L.oracle_pool_reward_sum.restype = C.c_int64
         L.oracle_pool_reward_sum.argtypes = [C.c_void_p]
         L.oracle_phy_stats.argtypes = [C.c_void_p, C.c_void_p]
+        L.oracle_phy_channel_state.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
+        L.oracle_phy_channel_state.restype = C.c_int64
         L.oracle_gsnr.argtypes = [C.c_void_p, C.POINTER(OracleGsnrParams), C.c_void_p, C.c_void_p]
         L.oracle_services.restype = C.c_int64
         L.oracle_services.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
@@ -172,6 +174,7 @@ class OracleSpec:
             setattr(c, name, _ptr(k[name]))
         c.n_mods = len(t.mod_names)
         c.phy_n_tables = 0 if ph is None else ph.n_tables
+        c.phy_grooming = int(getattr(spec, "phy_grooming", 0))
         c.num_slots, c.num_cores, c.j = spec.num_slots, spec.num_cores, spec.j
         c.episode_length = spec.episode_length
         c.allow_rejection = int(spec.allow_rejection)
@@ -226,6 +229,11 @@ class OracleEnv:
         obs = np.zeros(n, np.uint8)
         self.L.oracle_matrix_observation(self.h, obs.ctypes.data)
         return obs
+
+    def phy_channel_state(self, max_entries=4096):
+        o = np.zeros((max_entries, 6), np.int32)
+        n = int(self.L.oracle_phy_channel_state(self.h, o.ctypes.data, max_entries))
+        return o[: min(n, max_entries)]
 
     def phy_stats(self):
         o = np.zeros(8, np.float64)

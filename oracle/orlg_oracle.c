@@ -119,13 +119,20 @@ typedef struct svc { /* a provisioned Service (utils.py:56-80), what release nee
   int32_t se; /* current_modulation.spectral_efficiency */
   int32_t nch;      /* PhyRMSA: service.channels */
   int16_t ch[8];
+  int8_t share[8], cap[8]; /* channel tuple fields [1] (capacity used by this service) and [3] (level), units of 100 Gb/s */
 } svc;
+
+/* one tuple of channel_state[src_id, dst_id, idp] (phy_rmsa_env.py:599-601): (channel, used, free, capacity);
+ * the per-key Python lists are kept as one list in append order (remove + append moves an entry to the end) */
+typedef struct chan_state { int32_t pair, idp, ch, used, free_, cap; } chan_state;
 
 struct oracle_env {
   oracle_config c;
   int64_t genv;
   uint8_t* avail; /* [cores][E][S], 1 = free: topology.graph["available_slots"] */
   svc* heap;      /* heapq list of (release_time, service) */
+  chan_state* cs; /* channel_state, all keys, append order */
+  int64_t cs_len, cs_cap;
   int64_t heap_len, heap_cap;
   double now;     /* current_time */
   oracle_request cur;
@@ -169,6 +176,7 @@ void oracle_destroy(oracle_env* e) {
   if (!e) return;
   free(e->avail);
   free(e->heap);
+  free(e->cs);
   free(e->link_of);
   free(e);
 }
@@ -269,13 +277,47 @@ static void provision_path(oracle_env* e, int pair, int path, int core, int star
   e->ep_br_provisioned += e->cur.bit_rate;
 }
 
+static int64_t cs_find(const oracle_env* e, int pair, int idp, int ch) {
+  for (int64_t i = 0; i < e->cs_len; i++)
+    if (e->cs[i].pair == pair && e->cs[i].idp == idp && e->cs[i].ch == ch) return i;
+  return -1;
+}
+static void cs_remove(oracle_env* e, int64_t at) {
+  memmove(e->cs + at, e->cs + at + 1, sizeof(chan_state) * (size_t)(e->cs_len - at - 1));
+  e->cs_len--;
+}
+static void cs_append(oracle_env* e, int pair, int idp, int ch, int used, int free_, int cap) {
+  if (e->cs_len == e->cs_cap) {
+    e->cs_cap = e->cs_cap ? 2 * e->cs_cap : 64;
+    e->cs = (chan_state*)realloc(e->cs, sizeof(chan_state) * (size_t)e->cs_cap);
+  }
+  chan_state r = {pair, idp, ch, used, free_, cap};
+  e->cs[e->cs_len++] = r;
+}
+
 /* _release_path rmsa_env.py:515-535 / rmcsa_env.py:536-558 */
 static void release_path(oracle_env* e, const svc* s) {
   const int16_t* L = links_of(e, s->pair, s->path, 0);
   int h = hops_of(e, s->pair, s->path);
-  if (e->c.env_kind == 3) { /* phy_rmsa_env.py:781-861 without grooming: every channel of the service is freed */
+  if (e->c.env_kind == 3 && !e->c.phy_grooming) { /* no channel_state: every channel of the service is freed */
     for (int i = 0; i < h; i++)
       for (int c = 0; c < s->nch; c++) AV(e, 0, L[i])[s->ch[c]] = 1;
+    return;
+  }
+  if (e->c.env_kind == 3) { /* phy_rmsa_env.py:781-861 */
+    for (int c = 0; c < s->nch; c++) {
+      int free_it = s->share[c] == s->cap[c]; /* :784 channel[1] == channel[3] */
+      if (!free_it) {                        /* :801-846 */
+        int64_t at = cs_find(e, s->pair, s->path, s->ch[c]);
+        if (at < 0) continue; /* the reference would raise IndexError; unreachable from step */
+        chan_state r = e->cs[at];
+        cs_remove(e, at);
+        if (r.used == s->share[c]) free_it = 1; /* :821 nobody else is on the channel */
+        else cs_append(e, r.pair, r.idp, r.ch, r.used - s->share[c], r.free_ + s->share[c], r.cap); /* :841-844 */
+      }
+      if (free_it)
+        for (int i = 0; i < h; i++) AV(e, 0, L[i])[s->ch[c]] = 1;
+    }
     return;
   }
   for (int i = 0; i < h; i++) memset(AV(e, s->core, L[i]) + s->initial_slot, 1, (size_t)s->number_slots);
@@ -358,6 +400,7 @@ void oracle_reset(oracle_env* e, int full) {
     }
     return;
   }
+  e->cs_len = 0;   /* channel_state phy_rmsa_env.py:455-461 */
   e->heap_len = 0; /* OpticalNetworkEnv.reset optical_network_env.py:216-222 */
   e->now = 0.0;
   e->services_processed = e->services_accepted = 0;
@@ -475,6 +518,8 @@ static double calculate_r_spatial(const oracle_env* e, int pair, int path, int c
   return after - before;
 }
 
+static int use_existing_channels(const oracle_env* e, int32_t* a);
+
 typedef struct phy_cand { int mod; double frag; int ch, idp; } phy_cand;
 
 /* sorted(row, key=...) is stable: insertion sort by the heuristic's key */
@@ -491,6 +536,11 @@ static void phy_heuristic(oracle_env* e, int hid, int32_t* a) {
   int k = e->c.k_paths, C = e->c.num_slots, pair = cur_pair(e);
   for (int i = 0; i < ORACLE_PHY_ADIM; i++) a[i] = -1;
   a[0] = -2; /* (-2, []) : blocked */
+  /* the virtual layer first: unconditionally in sapff/sapbm/bmff/faff/faff_rss, under env.grooming in bmfa/bmfa_rss */
+  if (e->c.phy_grooming == 1 || (e->c.phy_grooming == 2 && hid != 8 && hid != 11)) {
+    if (use_existing_channels(e, a)) return;
+    for (int i = 1; i < ORACLE_PHY_ADIM; i++) a[i] = -1;
+  }
   int table = e->c.phy_table_id[pair];
   if (table < 0) return;
   phy_cand* rows = (phy_cand*)malloc(sizeof(phy_cand) * (size_t)k * C);
@@ -543,27 +593,106 @@ static void phy_heuristic(oracle_env* e, int hid, int32_t* a) {
   free(rows); free(len); free(alive);
 }
 
-/* PhyRMSAEnv.step phy_rmsa_env.py:272-309 (physical path branch) */
+/* use_existing_channels phy_rmsa_env.py:1650-1673: first path whose partially used channels can carry the
+ * request; channels in list order, each gives all its free capacity, the last one what is still missing */
+static int use_existing_channels(const oracle_env* e, int32_t* a) {
+  int k = e->c.k_paths, pair = cur_pair(e), need = e->cur.bit_rate;
+  for (int idp = 0; idp < k; idp++) {
+    int sum = 0;
+    for (int64_t i = 0; i < e->cs_len; i++)
+      if (e->cs[i].pair == pair && e->cs[i].idp == idp) sum += e->cs[i].free_;
+    if (sum * 100 < need) continue; /* sum(free) >= unassigned_bitrate / 100 */
+    int n = 0;
+    for (int64_t i = 0; i < e->cs_len; i++) {
+      if (e->cs[i].pair != pair || e->cs[i].idp != idp || e->cs[i].free_ <= 0) continue;
+      need -= e->cs[i].free_ * 100;
+      if (n < ORACLE_PHY_ADIM - 1) a[1 + n] = e->cs[i].ch;
+      n++;
+      if (need <= 0) {
+        if (n > ORACLE_PHY_ADIM - 1) return 0; /* documented cap of 8 channels per action */
+        a[0] = idp + 20;
+        return 1;
+      }
+    }
+  }
+  return 0;
+}
+
+/* PhyRMSAEnv.step phy_rmsa_env.py:272-309.  The action carries channel numbers; the (used, free) fields of
+ * the reference's channel tuples are what its heuristics put there: every channel is used up to its capacity
+ * (physical) or its free part (virtual) until the bit rate is covered, the last one takes the remainder. */
 static int phy_decide(oracle_env* e, const int32_t* a, int32_t* alloc) {
   int k = e->c.k_paths, C = e->c.num_slots, pair = cur_pair(e);
   int path = a[0], nch = 0, accepted = 0;
+  const int groom = e->c.phy_grooming != 0;
   while (nch < ORACLE_PHY_ADIM - 1 && a[1 + nch] >= 0) nch++;
+  if (groom && path >= 20 && path < 20 + k && nch > 0) { /* virtual layer :280-288, _provision_virtual_path :625-659 */
+    int idp = path - 20, need = e->cur.bit_rate / 100, ok = 1, share[8];
+    for (int i = 0; ok && i < nch; i++) {
+      for (int q = 0; ok && q < i; q++) ok = a[1 + q] != a[1 + i];
+      int64_t at = ok ? cs_find(e, pair, idp, a[1 + i]) : -1;
+      ok = ok && at >= 0 && e->cs[at].free_ > 0 && need > 0;
+      if (ok) {
+        share[i] = e->cs[at].free_ < need ? e->cs[at].free_ : need;
+        need -= share[i];
+      }
+    }
+    if (ok) {
+      svc s = {e->cur.arrival + e->cur.holding, pair, idp, 0, a[1], nch, 0, nch, {0}, {0}, {0}};
+      for (int i = 0; i < nch; i++) {
+        int64_t at = cs_find(e, pair, idp, a[1 + i]);
+        chan_state r = e->cs[at];
+        cs_remove(e, at); /* :643-645 remove, then append the updated tuple */
+        cs_append(e, r.pair, r.idp, r.ch, r.used + share[i], r.free_ - share[i], r.cap);
+        s.ch[i] = (int16_t)a[1 + i];
+        s.share[i] = (int8_t)share[i];
+        s.cap[i] = (int8_t)r.cap;
+      }
+      e->services_accepted++; /* _service_acceptance(True) :767-778 */
+      e->ep_accepted++;
+      e->br_provisioned += e->cur.bit_rate;
+      e->ep_br_provisioned += e->cur.bit_rate;
+      heap_push(e, s);
+      accepted = 1;
+    }
+    if (alloc) {
+      alloc[0] = accepted;
+      alloc[1] = accepted ? path : -1;
+      alloc[2] = accepted ? a[1] : -1;
+      alloc[3] = accepted ? nch : 0;
+    }
+    return accepted;
+  }
   int ok = path >= 0 && path < k && nch > 0 && hops_of(e, pair, path) > 0 && e->c.phy_table_id[pair] >= 0;
   for (int i = 0; ok && i < nch; i++) {
     ok = a[1 + i] < C;
     for (int q = 0; ok && q < i; q++) ok = a[1 + q] != a[1 + i];
   }
   for (int i = 0; ok && i < nch; i++) ok = is_channel_free(e, pair, path, a[1 + i]); /* is_path_free_on_channels */
+  if (ok && groom) { /* with channel_state kept, every listed channel must carry part of the request */
+    int need = e->cur.bit_rate / 100, table = e->c.phy_table_id[pair];
+    for (int i = 0; ok && i < nch; i++) {
+      ok = need > 0;
+      need -= phy_level(e, table, a[1 + i], path);
+    }
+  }
   if (ok) {
     int table = e->c.phy_table_id[pair];
     const int16_t* L = links_of(e, pair, path, 0);
-    svc s = {e->cur.arrival + e->cur.holding, pair, path, 0, a[1], nch, 0, nch, {0}};
+    svc s = {e->cur.arrival + e->cur.holding, pair, path, 0, a[1], nch, 0, nch, {0}, {0}, {0}};
     for (int i = 0; i < hops_of(e, pair, path); i++)
       for (int c = 0; c < nch; c++) AV(e, 0, L[i])[a[1 + c]] = 0; /* _provision_path :576-590 */
+    int need = e->cur.bit_rate / 100;
     for (int c = 0; c < nch; c++) { /* :592-598 */
+      int level = phy_level(e, table, a[1 + c], path);
       s.ch[c] = (int16_t)a[1 + c];
+      s.cap[c] = (int8_t)level;
+      s.share[c] = (int8_t)(level < need ? level : need);
+      need -= s.share[c];
+      if (groom && s.share[c] != level) /* :599-601 channel[2] != 0 */
+        cs_append(e, pair, path, a[1 + c], s.share[c], level - s.share[c], level);
       e->total_gsnr_ep += e->c.phy_gsnr[((size_t)table * C + a[1 + c]) * k + path];
-      e->total_mod_level_ep += phy_level(e, table, a[1 + c], path);
+      e->total_mod_level_ep += level;
       e->channels_accepted_ep++;
     }
     e->services_accepted++; /* _service_acceptance(False) :767-778 */
@@ -583,6 +712,16 @@ static int phy_decide(oracle_env* e, const int32_t* a, int32_t* alloc) {
     alloc[3] = accepted ? nch : 0;
   }
   return accepted;
+}
+
+/* channel_state in append order: rows (pair, idp, channel, used, free, capacity); returns the number of entries */
+int64_t oracle_phy_channel_state(const oracle_env* e, int32_t* out, int64_t max_entries) {
+  for (int64_t i = 0; i < e->cs_len && i < max_entries; i++) {
+    const chan_state* r = &e->cs[i];
+    int32_t* o = out + i * 6;
+    o[0] = r->pair; o[1] = r->idp; o[2] = r->ch; o[3] = r->used; o[4] = r->free_; o[5] = r->cap;
+  }
+  return e->cs_len;
 }
 
 /* _calculate_total_cuts :1195-1203, calculate_total_r_spatial :1110-1121 */

@@ -57,7 +57,12 @@ typedef struct oracle_config {
   const double* src_cum;
   const double* dst_cum;
   /* PhyRMSA-v0 (env_kind 3, phy_rmsa_env.py): channels take the place of slots */
-  int32_t phy_n_tables, phy_pad;
+  int32_t phy_n_tables;
+  /* virtual layer (phy_rmsa_env.py:625-659, 1650-1673): 0 = channel_state not kept (physical layer only, the
+   * heuristics never groom), 1 = env.grooming True, 2 = env.grooming False with channel_state kept, which is what
+   * the reference does: sapff/sapbm/bmff/faff/faff_rss call use_existing_channels unconditionally (:1256,1321,1510,
+   * 1574,1678), bmfa/bmfa_rss only if env.grooming (:1377,1443) */
+  int32_t phy_grooming;
   const int32_t* phy_table_id;   /* [n_nodes*n_nodes] first connections_detail row of the unordered pair */
   const uint8_t* phy_mod_level;  /* [n_tables][num_slots][k_paths]  modulation_level[table][channel][idp] */
   const double* phy_gsnr;        /* [n_tables][num_slots][k_paths]  gsnr[table][channel][idp] */
@@ -99,6 +104,8 @@ int64_t oracle_rollout_many(const oracle_config* cfg, int64_t env0, int64_t n_en
  * number_cuts_total, rss_total_metric (phy_rmsa_env.py:313-348). */
 #define ORACLE_PHY_ADIM 9
 void oracle_phy_stats(const oracle_env* e, double* out8);
+/* channel_state (phy_rmsa_env.py:158-166) in append order, rows (src*N+dst, idp, channel, used, free, capacity) */
+int64_t oracle_phy_channel_state(const oracle_env* e, int32_t* out, int64_t max_entries);
 
 /* GN-model GSNR (examples/calculate_osnr.py:9-56); same parameter block as orlg_gsnr_params */
 typedef struct oracle_gsnr_params {

@@ -75,6 +75,7 @@ def run(name, topo_file, mat_key, heuristic, no_groom_stub, n_steps, **kw):
         reqs = np.zeros(n_steps + 1, REQ_DTYPE)
         actions = np.full((n_steps, ADIM), -1, np.int32)
         accepted = np.zeros(n_steps, np.uint8)
+        virtual = np.zeros(n_steps, np.uint8)
         reward = np.zeros(n_steps, np.int32)
         done = np.zeros(n_steps, np.uint8)
         counters = np.zeros((n_steps, 8), np.int64)
@@ -82,7 +83,8 @@ def run(name, topo_file, mat_key, heuristic, no_groom_stub, n_steps, **kw):
         reqs[0] = req_of(env)
         for t in range(n_steps):
             path, chans = heuristic(env)
-            assert path <= 10, "virtual-layer action in a no-grooming run"
+            assert path <= 10 or not no_groom_stub, "virtual-layer action although use_existing_channels is stubbed"
+            virtual[t] = int(path > 10)
             actions[t, 0] = path
             for i, c in enumerate(chans):
                 actions[t, 1 + i] = c[0]
@@ -98,7 +100,8 @@ def run(name, topo_file, mat_key, heuristic, no_groom_stub, n_steps, **kw):
                 env.reset()
             counters[t] = counters_of(env)
         out = dict(env_kind=3, topo_file=topo_file, requests=reqs, actions=actions, accepted=accepted, reward=reward,
-                   done=done, counters=counters, stats=stats,
+                   done=done, counters=counters, stats=stats, virtual=virtual,
+                   channel_state=np.int32(0 if no_groom_stub else (1 if kwargs.get("grooming") else 2)),
                    final_avail=np.asarray(env.topology.graph["available_channels"], np.uint8)[None],
                    kwargs_keys=np.array(sorted(kwargs)), tables_key=np.array(mat_key))
         tab = os.path.join(GOLDEN, f"phytab_{mat_key}.npz")
@@ -111,7 +114,7 @@ def run(name, topo_file, mat_key, heuristic, no_groom_stub, n_steps, **kw):
             out["kw_" + key] = np.asarray(v)
         path_ = os.path.join(GOLDEN, name + ".npz")
         np.savez_compressed(path_, **out)
-        print(f"{name}: {n_steps} steps, blocking {1 - accepted.mean():.3f}, episodes {int(done.sum())}, "
+        print(f"{name}: {n_steps} steps, blocking {1 - accepted.mean():.3f}, virtual {virtual.mean():.3f}, episodes {int(done.sum())}, "
               f"cuts {stats[-1, 6]:.3f} rss {stats[-1, 7]:.4f}, {os.path.getsize(path_) / 1024:.0f} KiB")
     finally:
         ref.use_existing_channels = saved
@@ -136,6 +139,14 @@ def main():
         episode_length=220, **small)
     run("phy_jpn12_faffrss_64ch", jpn, JPN, ref.phy_aware_faff_rss_rmsa, True, 1200, seed=18, load=1150,
         episode_length=180, **tiny)
+    # virtual layer: env.grooming=True, and the reference's grooming=False behaviour of the heuristics that call
+    # use_existing_channels unconditionally (no stub)
+    run("phy_us14_groom_bmfa_100ch", us, US, ref.phy_aware_bmfa_rmsa, False, 1500, seed=19, load=1900,
+        episode_length=230, grooming=True, **small)
+    run("phy_jpn12_groom_faffrss_64ch", jpn, JPN, ref.phy_aware_faff_rss_rmsa, False, 1200, seed=20, load=1500,
+        episode_length=170, grooming=True, **tiny)
+    run("phy_us14_cstate_sapff_100ch", us, US, ref.sapff_rmsa, False, 1500, seed=21, load=1900, episode_length=210,
+        **small)
     run("phy_jpn12_sapbm_64ch", jpn, JPN, ref.phy_aware_sapbm_rmsa, True, 1500, seed=14, load=1300,
         episode_length=100, **tiny)
 

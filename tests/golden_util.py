@@ -47,5 +47,7 @@ def load_case(name: str):
                   gsnr=z["phy_gsnr"])
         kw.pop("num_spectrum_resources", None)  # irrelevant to PhyRMSA's allocation
         kw.pop("bit_rate_selection", None)
+        if "channel_state" in g:  # 0: use_existing_channels stubbed out in the harness, 1: grooming=True, 2: unstubbed
+            kw["keep_channel_state"] = int(g["channel_state"]) != 0
     spec = S.make_spec(ENV_NAME[int(g["env_kind"])], tables, request_source=S.SRC_REPLAY, **kw)
     return g, spec

@@ -9,7 +9,7 @@ from optical_rl_gym_qot_aware_b200 import spec as S
 
 pytestmark = pytest.mark.gpu
 
-HEUR = {"bmfa_cut": S.H_PHY_BM_FA_CUT, "sapff": S.H_PHY_SAP_FF, "bmff": S.H_PHY_BM_FF, "sapbm": S.H_PHY_SAP_BM,
+HEUR = {"bmfa_cut": S.H_PHY_BM_FA_CUT, "bmfa": S.H_PHY_BM_FA_CUT, "sapff": S.H_PHY_SAP_FF, "bmff": S.H_PHY_BM_FF, "sapbm": S.H_PHY_SAP_BM,
         "faff": S.H_PHY_FA_FF, "bmfarss": S.H_PHY_BM_FA_RSS, "faffrss": S.H_PHY_FA_FF_RSS}
 
 
@@ -103,6 +103,54 @@ def test_phy_rollout_matches_oracle_on_philox(hid, channels, load):
             o.step(o.heuristic(hid))
         ost = o.phy_stats()
         assert np.array_equal(st[i, :6], ost[:6]), (i, st[i], ost)
+    eng.close()
+
+
+@pytest.mark.parametrize("hid,grooming,keep", [(S.H_PHY_BM_FA_CUT, True, False), (S.H_PHY_SAP_FF, False, True),
+                                               (S.H_PHY_BM_FA_CUT, False, True), (S.H_PHY_FA_FF_RSS, True, False)])
+def test_phy_virtual_layer_rollout_matches_oracle(hid, grooming, keep):
+    """Grooming (use_existing_channels + _provision_virtual_path + the partial-channel release rules): counters,
+    channel map and channel_state lists of 120 Philox envs against the oracle after 1 200 steps."""
+    import torch
+
+    import oracle_binding as OB
+    from optical_rl_gym_qot_aware_b200.engine import Engine
+
+    g, spec0 = G.load_case("phy_us14_bmfa_cut")
+    ph = np.load(G.os.path.join(G.GOLDEN, f"phytab_{str(g['tables_key'])}.npz"))
+    spec = S.make_spec("PhyRMSA-v0", spec0.tables, seed=91, load=1900, mean_service_holding_time=25, episode_length=130,
+                       auto_reset=True, modulation_level=ph["phy_mod"], connections_detail=ph["phy_conn"],
+                       gsnr=ph["phy_gsnr"], number_spectrum_channels=30, number_spectrum_channels_s_band=40,
+                       grooming=grooming, keep_channel_state=keep)
+    assert spec.phy_grooming == (1 if grooming else 2)
+    n_env, n_steps = 120, 1200
+    o_steps, o_cnt, o_state, o_rsum = OB.rollout_many(spec, 5, n_env, n_steps, hid, 8, want_state=True)
+    eng = Engine(spec, n_env, global_env_offset=5)
+    eng.reset(True)
+    rsum = torch.zeros(n_env, dtype=torch.int64, device=eng.device)
+    eng.rollout(hid, 500, rsum)
+    eng.rollout(hid, n_steps - 500, rsum)
+    cnt = eng.counters().cpu().numpy()
+    assert int(cnt[:, 10].max()) == 0
+    assert np.array_equal(cnt[:, :9], o_cnt[:, :9])
+    assert np.array_equal(rsum.cpu().numpy(), o_rsum)
+    assert np.array_equal(eng.export_state().cpu().numpy(), o_state)
+    cs, n_cs = eng.phy_channel_state(2048)
+    cs, n_cs = cs.cpu().numpy(), n_cs.cpu().numpy()
+    for i in (0, 17, n_env - 1):
+        o = OB.OracleEnv(spec, 5 + i)
+        o.reset(True)
+        virt = 0
+        for _ in range(n_steps):
+            a = o.heuristic(hid)
+            virt += int(a[0] >= 20)
+            o.step(a)
+        ocs = o.phy_channel_state()
+        if not grooming and hid in (S.H_PHY_BM_FA_CUT, S.H_PHY_BM_FA_RSS):
+            assert virt == 0  # bmfa asks env.grooming before it looks at the virtual layer (:1377)
+        else:
+            assert virt > 50, "the case should use the virtual layer"
+        assert n_cs[i] == len(ocs) and np.array_equal(cs[i, : n_cs[i]], ocs), (i, n_cs[i], len(ocs))
     eng.close()
 
 

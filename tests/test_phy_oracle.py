@@ -7,7 +7,7 @@ import pytest
 import golden_util as G
 import oracle_binding as OB
 
-HEUR = {"bmfa_cut": 8, "sapff": 5, "bmff": 7, "sapbm": 6, "faff": 10, "bmfarss": 11, "faffrss": 12}
+HEUR = {"bmfa_cut": 8, "bmfa": 8, "sapff": 5, "bmff": 7, "sapbm": 6, "faff": 10, "bmfarss": 11, "faffrss": 12}
 
 
 def heuristic_of(case):
