@@ -414,6 +414,16 @@ class GymEnv:
             ph, t, cs = self.spec.phy, self.tables, self._b.current_requests()[0]
             table = ph.table_id[int(cs["src"]) * t.n_nodes + int(cs["dst"])]
             un, out = int(cs["bit_rate"]), []
+            if a[0] >= 20:  # virtual layer: (idp + 20, [(channel, share, left over, capacity, True)]) :1380,1664-1670
+                rows, cnt = self._b.engine.phy_channel_state(4096)
+                rows = rows[0, : int(cnt[0])].cpu().numpy()
+                key = int(cs["src"]) * t.n_nodes + int(cs["dst"])
+                free = {int(r[2]): (int(r[4]), int(r[5])) for r in rows if r[0] == key and r[1] == a[0] - 20}
+                for ch in [int(c) for c in a[1:] if c >= 0]:
+                    fr, cap = free[ch]
+                    un -= fr * 100
+                    out.append((ch, fr + un / 100, un / -100, cap, True) if un <= 0 else (ch, fr, 0, cap, True))
+                return (int(a[0]), out)
             for ch in [int(c) for c in a[1:] if c >= 0]:
                 lvl = int(ph.mod_level[table, ch, int(a[0])])
                 un -= lvl * 100

@@ -177,6 +177,38 @@ def test_phy_scalar_env_five_tuple_and_info_reward():
     env.close()
 
 
+def test_phy_scalar_env_grooming_virtual_actions():
+    """grooming=True through the gym surface: the heuristic returns the reference's virtual-layer action
+    (idp + 20, [(channel, share, left over, capacity, True), ...]) (phy_rmsa_env.py:1380,1664-1670) and step takes it."""
+    import optical_rl_gym_qot_aware_b200 as pkg
+
+    g, spec = G.load_case("phy_us14_groom_bmfa_100ch")
+    assert spec.phy_grooming == 1
+    z = np.load(G.os.path.join(G.GOLDEN, f"phytab_{str(g['tables_key'])}.npz"))
+    kw = _kwargs(g)
+    kw.pop("num_spectrum_resources")
+    kw.pop("bit_rate_selection")
+    env = pkg.make("PhyRMSA-v0", topology=spec.tables, request_source="replay", modulation_level=z["phy_mod"],
+                   connections_detail=z["phy_conn"], gsnr=z["phy_gsnr"], **kw)
+    env.load_trace(g["requests"])
+    virt = 0
+    for t in range(400):
+        path, chans = env.heuristic("phy_aware_bmfa_rmsa")
+        want = g["actions"][t]
+        assert path == want[0] and [c[0] for c in chans] == [c for c in want[1:] if c >= 0], t
+        if path >= 20:
+            virt += 1
+            need = env.current_service.bit_rate / 100
+            assert all(c[4] is True for c in chans) and sum(c[1] for c in chans) == need
+            assert all(c[2] == 0 for c in chans[:-1]) and chans[-1][2] >= 0
+        _, r, d, _, info = env.step((path, chans))
+        assert info["accepted"] == int(g["accepted"][t]) and r == int(g["reward"][t]) and d == bool(g["done"][t])
+        if d:
+            env.reset()
+    assert virt > 50
+    env.close()
+
+
 def test_path_only_first_fit_action_wrapper():
     """PathOnlyFirstFitAction (rmsa_env.py:974-1008): path 0 + device first fit == the SP-FF golden trace."""
     import torch
