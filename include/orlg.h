@@ -143,7 +143,11 @@ typedef struct orlg_config {
    * under env.grooming.  A virtual action is (idp + 20, channels); shares are taken as the reference's
    * use_existing_channels takes them (all the free capacity of each channel, the last one the remainder). */
   int32_t phy_grooming;
-  int32_t reserved[5];
+  /* RMSA-v0 / DeepRMSA-v0: 1 = keep what the info dict of RMSAEnv.step needs (rmsa_env.py:276-332): the
+   * time-weighted link utilization / compactness of _update_link_stats :562-641, the per-bit-rate histograms
+   * and the running services' slots x hops; orlg_set_info_output then makes orlg_step write the dict */
+  int32_t info_stats;
+  int32_t reserved[4];
 
   /* PhyRMSA-v0 (phy_rmsa_env.py:51-53,93-95): num_slots = number of channels, num_cores = 1 */
   int32_t phy_n_tables;   /* rows of connections_detail */
@@ -255,6 +259,16 @@ int orlg_get_counters(orlg_engine* e, int64_t* dev_out /* [num_envs][ORLG_NUM_CO
  * physical_services_accepted_episode (phy_rmsa_env.py:431-439), then number_cuts_total and
  * rss_total_metric (:1195-1203, :1110-1121) of the CURRENT channel map. */
 int orlg_phy_get_stats(orlg_engine* e, double* dev_out, void* stream);
+
+/* The info dict of RMSAEnv.step (rmsa_env.py:293-332) for every following orlg_step, f64
+ * [num_envs][orlg_info_dim]: service_blocking_rate, episode_service_blocking_rate, bit_rate_blocking_rate,
+ * episode_bit_rate_blocking_rate, network_compactness (:806-851), network_compactness_difference,
+ * avg_link_compactness, avg_link_utilization (np.mean over the edges, numpy's summation order), fairness, then
+ * bit_rate_blocking_<b> for every configured bit rate — evaluated where the reference evaluates them: after the
+ * provisioning, before the next request is drawn and the releases are processed.  NULL switches it off.
+ * Needs info_stats = 1 (RMSA-v0 / DeepRMSA-v0). */
+int orlg_info_dim(const orlg_engine* e);
+int orlg_set_info_output(orlg_engine* e, double* dev_info);
 
 /* PhyRMSA-v0 channel_state (phy_rmsa_env.py:158-166,599-601): the partially used channels of every env in
  * append order, int32 [num_envs][max_entries][6] = (src_id * n_nodes + dst_id, idp, channel, used, free,

@@ -119,6 +119,16 @@ __device__ __forceinline__ int lowest_set(const Row<W>& x) {
   return r;
 }
 
+// index of the highest set bit, -1 if none
+template <int W>
+__device__ __forceinline__ int highest_set(const Row<W>& x) {
+  int r = -1;
+#pragma unroll
+  for (int i = 0; i < W; i++)
+    if (x.w[i]) r = 32 * i + 31 - __clz((int)x.w[i]);
+  return r;
+}
+
 // clear every bit below `pos`
 template <int W>
 __device__ __forceinline__ void clear_below(Row<W>& x, int pos) {

@@ -80,6 +80,11 @@ struct Params {
   const unsigned char* phy_cut_links;   // [N*N*k][phy_max_terms] neighbour link of every r_cut term
   const int* phy_cut_count;             // [N*N*k]
   int phy_max_terms, phy_mask_w;
+  // info dict of RMSAEnv.step (rmsa_env.py:276-332), RMSA-v0 / DeepRMSA-v0 with info_stats
+  int info_stats;
+  double* lnk_stat;       // [3][E][NP] topology[n1][n2]["last_update" | "utilization" | "compactness"] (:562-641)
+  int* br_hist;           // [2][n_bit_rates][NP] bit_rate_requested_histogram / bit_rate_provisioned_histogram
+  long long* slot_hops;   // [NP] sum of number_slots * hops over the running services (:809-812)
   // virtual layer (phy_rmsa_env.py:625-659, 1650-1673): channel_state of every env as one list in append order,
   // entry i of env e at phy_cs[i * NP + e] = {pair | idp << 16 | channel << 20, used | free << 8 | capacity << 16}
   int phy_grooming;                     // 0 off, 1 env.grooming, 2 channel_state kept with env.grooming False
@@ -102,6 +107,7 @@ struct StepIO {
   long long obs_es, obs_fs;  // element strides: env, feature
   int* alloc;
   long long* reward_sum;
+  double* info;        // optional f64 [num_envs][9 + n_bit_rates]: the step's info dict (needs info_stats)
   int* hint_actions;   // optional: the heuristic's action for the NEW pending request (fused next-action hint)
   int hint_heuristic;
 };

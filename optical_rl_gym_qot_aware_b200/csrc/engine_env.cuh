@@ -21,7 +21,9 @@ __device__ __forceinline__ int svc_start(unsigned long long s) { return (int)((s
 __device__ __forceinline__ int svc_slots(unsigned long long s) { return (int)((s >> 48) & 0x3FF); }
 __device__ __forceinline__ int svc_se(unsigned long long s) { return (int)((s >> 58) & 15); }
 
-template <int W, int BD, bool PHY = false>
+// INFO: the instantiation keeps the info-dict state of RMSAEnv.step (only the kernels launched for engines
+// created with info_stats carry that code)
+template <int W, int BD, bool PHY = false, bool INFO = false>
 struct Env {
   const Params& p;
   Tile<W, BD> tile;
@@ -33,6 +35,7 @@ struct Env {
   double fsum[2];      // PhyRMSA episode sums (phy_rmsa_env.py:431-439)
   long long isum[4];
   int cs_len, cs_dead; // PhyRMSA channel_state list: slots in use (tombstones included), tombstones
+  long long slot_hops; // info_stats: sum of number_slots * hops over the running services
 
   __device__ __forceinline__ Env(const Params& p_, uint32_t* smem, int tid, int e_)
       : p(p_), tile{smem, tid, p_.E}, e(e_) {
@@ -52,6 +55,8 @@ struct Env {
     heap_len = p.heap_len[e];
 #pragma unroll
     for (int i = 0; i < CNT_N; i++) cnt[i] = p.counters[(size_t)i * p.NP + e];
+    slot_hops = 0;
+    if constexpr (INFO) slot_hops = p.slot_hops[e];
     if constexpr (PHY) {
       fsum[0] = p.phy_f[e];
       fsum[1] = p.phy_f[(size_t)p.NP + e];
@@ -60,6 +65,105 @@ struct Env {
       load_cs_len();
     }
   }
+  // ---- info dict of RMSAEnv.step (rmsa_env.py:276-332), kept only with p.info_stats ----
+  __device__ __forceinline__ double& lnk(int f, int l) const { return p.lnk_stat[((size_t)f * p.E + l) * p.NP + e]; }
+  // used slots of a link row: bits [0, S) that are not free
+  __device__ __forceinline__ Row<W> used_row(int l) {
+    Row<W> u;
+#pragma unroll
+    for (int i = 0; i < W; i++) u.w[i] = ~tile.word(0, l, i) & mask_word(i, 0, p.S);
+    return u;
+  }
+  // _update_link_stats :562-641: time-weighted utilization and link compactness (the used blocks of a row are
+  // the runs of `used`; between lambda_min and lambda_max there are as many used runs as the row has)
+  __device__ __forceinline__ void info_update_link(int l) {
+    const double last_update = lnk(0, l);
+    const double time_diff = now - last_update;
+    if (now > 0) {
+      const Row<W> u = used_row(l);
+      const int used = popcount<W>(u), blocks = count_runs<W>(u);
+      const double cur_util = (double)used / (double)p.S;
+      lnk(1, l) = ((lnk(1, l) * last_update) + (cur_util * time_diff)) / now;
+      double cur = 0.0;
+      if (used < p.S) {  // np.sum(slot_allocation) > 0
+        cur = 1.0;
+        if (blocks > 1) {
+          const int span = highest_set<W>(u) + 1 - lowest_set<W>(u);
+          cur = ((double)span / (double)used) * (1.0 / (double)blocks);
+        }
+      }
+      lnk(2, l) = ((lnk(2, l) * last_update) + (cur * time_diff)) / now;
+    }
+    lnk(0, l) = now;
+  }
+  // _get_network_compactness :806-851
+  __device__ __forceinline__ double info_network_compactness() {
+    long long sum_occupied = 0, sum_unused_blocks = 0;
+    for (int l = 0; l < p.E; l++) {
+      const Row<W> u = used_row(l);
+      const int blocks = count_runs<W>(u);
+      if (blocks > 1) {
+        sum_occupied += highest_set<W>(u) + 1 - lowest_set<W>(u);
+        sum_unused_blocks += blocks - 1;  // one free run between two consecutive used blocks
+      }
+    }
+    if (sum_unused_blocks > 0)
+      return ((double)sum_occupied / (double)slot_hops) * ((double)p.E / (double)sum_unused_blocks);
+    return 1.0;
+  }
+  __device__ __forceinline__ int bit_rate_index(int br) const {
+    int idx = -1;
+    for (int i = 0; i < p.n_bit_rates; i++)
+      if (__ldg(p.bit_rates + i) == br) idx = idx < 0 ? i : idx;
+    return idx;
+  }
+  __device__ __forceinline__ void info_count(int which, int br) {
+    const int bi = bit_rate_index(br);
+    if (bi >= 0) p.br_hist[((size_t)which * p.n_bit_rates + bi) * p.NP + e]++;
+  }
+  // np.mean of the per-link values in edge order: numpy's pairwise summation (8 accumulators, n <= 128)
+  __device__ __forceinline__ double info_link_mean(int f) const {
+    const int n = p.E;
+    double res;
+    if (n < 8) {
+      res = 0.0;
+      for (int i = 0; i < n; i++) res += lnk(f, i);
+    } else {
+      double r[8];
+#pragma unroll
+      for (int j = 0; j < 8; j++) r[j] = lnk(f, j);
+      int i = 8;
+      for (; i < n - (n % 8); i += 8) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) r[j] += lnk(f, i + j);
+      }
+      res = ((r[0] + r[1]) + (r[2] + r[3])) + ((r[4] + r[5]) + (r[6] + r[7]));
+      for (; i < n; i++) res += lnk(f, i);
+    }
+    return res / (double)n;
+  }
+  // the info dict, taken after the provisioning and before _next_service (:276-332)
+  __device__ __forceinline__ void info_write(double* o, double previous_compactness) {
+    const double cur = info_network_compactness();
+    o[0] = (double)(cnt[CNT_PROC] - cnt[CNT_ACC]) / (double)cnt[CNT_PROC];
+    o[1] = (double)(cnt[CNT_EP_PROC] - cnt[CNT_EP_ACC]) / (double)cnt[CNT_EP_PROC];
+    o[2] = (double)(cnt[CNT_BR_REQ] - cnt[CNT_BR_PROV]) / (double)cnt[CNT_BR_REQ];
+    o[3] = (double)(cnt[CNT_EP_BR_REQ] - cnt[CNT_EP_BR_PROV]) / (double)cnt[CNT_EP_BR_REQ];
+    o[4] = cur;
+    o[5] = previous_compactness - cur;
+    o[6] = info_link_mean(2);
+    o[7] = info_link_mean(1);
+    double mx = 0.0, mn = 0.0;
+    for (int i = 0; i < p.n_bit_rates; i++) {  // :277-289, fairness :326-328
+      const int rq = p.br_hist[((size_t)i) * p.NP + e], pv = p.br_hist[((size_t)p.n_bit_rates + i) * p.NP + e];
+      const double b = rq > 0 ? (double)(rq - pv) / (double)rq : 0.0;
+      o[9 + i] = b;
+      if (i == 0 || b > mx) mx = b;
+      if (i == 0 || b < mn) mn = b;
+    }
+    o[8] = mx - mn;
+  }
+
   __device__ __forceinline__ void load_cs_len() {
     cs_len = cs_dead = 0;
     if (PHY && p.phy_grooming) {
@@ -84,6 +188,7 @@ struct Env {
     p.heap_len[e] = heap_len;
 #pragma unroll
     for (int i = 0; i < CNT_N; i++) p.counters[(size_t)i * p.NP + e] = cnt[i];
+    if constexpr (INFO) p.slot_hops[e] = slot_hops;
     if constexpr (PHY) {
       p.phy_f[e] = fsum[0];
       p.phy_f[(size_t)p.NP + e] = fsum[1];
@@ -279,6 +384,7 @@ struct Env {
     }
     cnt[CNT_BR_REQ] += bit_rate;  // rmsa_env.py:677-678, rmcsa_env.py:730-731
     cnt[CNT_EP_BR_REQ] += bit_rate;
+    if constexpr (INFO) info_count(0, bit_rate);  // bit_rate_requested_histogram :680
     while (next_rel <= now) {  // rmsa_env.py:689-695
       const double rel_key = next_rel;
       unsigned long long s = heap_pop();
@@ -311,6 +417,10 @@ struct Env {
       } else {
         PathRec rec = load_path(p, svc_pair(s), svc_path(s));
         tile.set_range(rec, svc_core(s), svc_start(s), svc_slots(s));
+        if constexpr (INFO) {  // _release_path :531-535 (current_time is already the new arrival)
+          for_each_link(rec, [&](int l) { info_update_link(l); });
+          slot_hops -= (long long)svc_slots(s) * rec.hops();
+        }
       }
     }
   }
@@ -344,6 +454,11 @@ struct Env {
   // _provision_path + _add_release (state and counters only)
   __device__ __forceinline__ void provision(const PathRec& rec, int path, int core, int start, int n, int se) {
     tile.clear_range(rec, core, start, n);
+    if constexpr (INFO) {  // _provision_path :494, :510
+      for_each_link(rec, [&](int l) { info_update_link(l); });
+      slot_hops += (long long)n * rec.hops();
+      info_count(1, bit_rate);
+    }
     cnt[CNT_ACC]++;
     cnt[CNT_EP_ACC]++;
     cnt[CNT_BR_PROV] += bit_rate;

@@ -58,7 +58,7 @@ __device__ __forceinline__ void fence_async_smem() {
 // same layout with a tile of one env) and every thread reads and writes its own rows in place
 // with vector loads.  This is the variant for envs whose occupancy is so large (multi-core, wide
 // spectra, many links) that only a warp or two of staged tiles would fit on an SM.
-template <int W, int BD, int MT, bool PHY, bool DIRECT = false>
+template <int W, int BD, int MT, bool PHY, bool DIRECT = false, bool INFO = false>
 __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t bar;
@@ -82,8 +82,8 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
     }
   }
 
-  Env<W, PS, PHY> env(p, tile_s, DIRECT ? 0 : tid, active ? e : 0);
-  typename Env<W, PS, PHY>::Req nx{};
+  Env<W, PS, PHY, INFO> env(p, tile_s, DIRECT ? 0 : tid, active ? e : 0);
+  typename Env<W, PS, PHY, INFO>::Req nx{};
   constexpr int ADIM = PHY ? PHY_ADIM : 4;
   int a[ADIM];
 #pragma unroll
@@ -97,6 +97,11 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
     env.bit_rate = env.src = env.dst = 0;
     env.heap_len = 0;
     env.cs_len = env.cs_dead = 0;  // channel_state phy_rmsa_env.py:455-461
+    env.slot_hops = 0;
+    if (INFO && active) {  // optical_network_env.py:257-260, rmsa_env.py:444-452
+      for (int l = 0; l < p.E; l++) env.lnk(0, l) = env.lnk(1, l) = env.lnk(2, l) = 0.0;
+      for (int i = 0; i < 2 * p.n_bit_rates; i++) p.br_hist[(size_t)i * p.NP + env.e] = 0;
+    }
     env.next_rel = __longlong_as_double(0x7FF0000000000000ll);
 #pragma unroll
     for (int i = 0; i < CNT_N; i++) env.cnt[i] = 0;
@@ -166,6 +171,10 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
           if (t > 0) nx = env.draw_request();
         }
         Decision d;
+        double prev_compactness = 0.0;
+        const bool want_info = INFO && mode == MODE_STEP && io.info != nullptr;
+        if constexpr (INFO)
+          if (want_info) prev_compactness = env.info_network_compactness();  // rmsa_env.py:227-229
         if constexpr (PHY) {
           d = phy_decide<W, PS>(env, a);
           // the info metrics are taken after the provisioning and before the releases (:313-314 vs :351)
@@ -178,6 +187,8 @@ __global__ void __launch_bounds__(BD) env_kernel(const Params p, const StepIO io
           else if (p.kind == ORLG_ENV_DEEPRMSA) d = deeprmsa_decide<W, PS>(env, a[0]);
           else d = rmcsa_decide<W, PS>(env, a[0], a[1], a[2], a[3]);
         }
+        if constexpr (INFO)
+          if (want_info) env.info_write(io.info + (size_t)e * (9 + p.n_bit_rates), prev_compactness);
         if (p.kind == ORLG_ENV_RMCSA) {  // rmcsa_env.py:292-295
           env.cnt[CNT_PROC]++;
           env.cnt[CNT_EP_PROC]++;

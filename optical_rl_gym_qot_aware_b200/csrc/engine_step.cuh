@@ -26,8 +26,8 @@ __device__ __forceinline__ int for_each_block(const Row<W>& avail, int n, int j,
 }
 
 // RMSAEnv.step decision (rmsa_env.py:233-271)
-template <int W, int BD>
-__device__ __forceinline__ Decision rmsa_decide(Env<W, BD>& env, int path, int slot) {
+template <int W, int BD, typename ENV>
+__device__ __forceinline__ Decision rmsa_decide(ENV& env, int path, int slot) {
   const Params& p = env.p;
   Decision d{0, -1, 0, -1, 0};
   if (path >= 0 && slot >= 0 && path < p.k && slot < p.S) {
@@ -47,8 +47,8 @@ __device__ __forceinline__ Decision rmsa_decide(Env<W, BD>& env, int path, int s
 }
 
 // DeepRMSAEnv.step (deeprmsa_env.py:48-58): action -> (route, block) -> start of that block
-template <int W, int BD>
-__device__ __forceinline__ Decision deeprmsa_decide(Env<W, BD>& env, int act) {
+template <int W, int BD, typename ENV>
+__device__ __forceinline__ Decision deeprmsa_decide(ENV& env, int act) {
   const Params& p = env.p;
   Decision d{0, -1, 0, -1, 0};
   if (act >= 0 && act < p.k * p.j) {
@@ -69,8 +69,8 @@ __device__ __forceinline__ Decision deeprmsa_decide(Env<W, BD>& env, int act) {
 }
 
 // RMCSAEnv.step decision (rmcsa_env.py:222-289)
-template <int W, int BD>
-__device__ __forceinline__ Decision rmcsa_decide(Env<W, BD>& env, int path, int mod, int core, int slot) {
+template <int W, int BD, typename ENV>
+__device__ __forceinline__ Decision rmcsa_decide(ENV& env, int path, int mod, int core, int slot) {
   const Params& p = env.p;
   Decision d{0, -1, 0, -1, 0};
   if (path >= 0 && mod >= 0 && core >= 0 && slot >= 0 && path < p.k && mod < p.n_mods &&
@@ -93,8 +93,8 @@ __device__ __forceinline__ Decision rmcsa_decide(Env<W, BD>& env, int path, int 
 }
 
 // Reference heuristics; `a` receives action_dim ints.
-template <int W, int BD>
-__device__ __forceinline__ void heuristic_action(Env<W, BD>& env, int hid, int* a, int in_path = 0) {
+template <int W, int BD, typename ENV>
+__device__ __forceinline__ void heuristic_action(ENV& env, int hid, int* a, int in_path = 0) {
   const Params& p = env.p;
   int pr = env.pair();
   if (p.kind == ORLG_ENV_RMSA && hid == ORLG_H_PATH_FF) {  // PathOnlyFirstFitAction rmsa_env.py:982-1005
@@ -182,8 +182,8 @@ __device__ __forceinline__ void heuristic_action(Env<W, BD>& env, int hid, int* 
 // operation order; OUT is double or float (one rounding at the store).
 // Returns the bitmask of paths that have at least one fitting block (what the K-SP-FF / SP-FF
 // heuristics of deeprmsa_env.py:135-155 decide on), so a fused next-action hint costs nothing extra.
-template <int W, int BD, typename OUT>
-__device__ __forceinline__ unsigned write_deeprmsa_obs(Env<W, BD>& env, OUT* o, long long fs) {
+template <int W, int BD, typename OUT, typename ENV>
+__device__ __forceinline__ unsigned write_deeprmsa_obs(ENV& env, OUT* o, long long fs) {
   unsigned fit_mask = 0u;
   const Params& p = env.p;
   const int N = p.n_nodes, S = p.S, j = p.j;

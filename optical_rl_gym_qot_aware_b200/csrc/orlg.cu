@@ -20,6 +20,7 @@ struct orlg_engine {
   Params p{};
   orlg_config cfg{};
   int W = 0, BD = 0, device = 0;  // BD = threads per CTA
+  double* info_out = nullptr;     // orlg_set_info_output
   int layout_bd = 0;              // envs per occupancy tile in HBM (1 = env-major, direct kernels)
   bool direct = false;
   size_t smem_bytes = 0;
@@ -92,7 +93,7 @@ extern "C" const char* orlg_last_error(const orlg_engine* e) {
 
 static int launch(orlg_engine* e, const StepIO& io, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
-  LaunchGeom g{e->BD, e->p.NP, e->device, e->smem_bytes, e->direct};
+  LaunchGeom g{e->BD, e->p.NP, e->device, e->smem_bytes, e->p.info_stats != 0, e->direct};
   cudaError_t rc;
   if (e->p.kind == ORLG_ENV_PHYRMSA) {
     switch (e->W) {
@@ -205,6 +206,10 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   // every row anyway; direct wins from 896 B/env (C5 +28 %/+64 %) to 4 760 B/env (C3, 4.2x)
   bool direct = !phy && bytes_per_env * 256 > 200 * 1024;
   if (const char* s = getenv("ORLG_DIRECT"); s && *s) direct = atoi(s) != 0;
+  if (c->info_stats) {  // the info-dict kernels exist for staged tiles of 128 envs and for direct rows
+    bd = 128;
+    if (bytes_per_env * bd > 100 * 1024) direct = true;
+  }
   if (!direct && bytes_per_env * bd > 220 * 1024) direct = true;
   e->direct = direct;
   e->BD = direct ? DIRECT_CTA : bd;
@@ -328,6 +333,15 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   const size_t NP = p.NP;
   if (phy && ((rc = dev_alloc(e, &p.phy_f, 2 * NP)) || (rc = dev_alloc(e, &p.phy_i, 4 * NP))))
     return fail_create(e, rc, e->err);
+  if (c->info_stats) {
+    if (c->env_kind != ORLG_ENV_RMSA && c->env_kind != ORLG_ENV_DEEPRMSA)
+      return fail_create(e, ORLG_EINVAL, "info_stats is built for RMSA-v0 / DeepRMSA-v0");
+    if (p.n_bit_rates <= 0 || p.n_bit_rates > 55) return fail_create(e, ORLG_EINVAL, "info_stats needs 1..55 discrete bit rates");
+    p.info_stats = 1;
+    if ((rc = dev_alloc(e, &p.lnk_stat, (size_t)3 * p.E * NP)) ||
+        (rc = dev_alloc(e, &p.br_hist, (size_t)2 * p.n_bit_rates * NP)) || (rc = dev_alloc(e, &p.slot_hops, NP)))
+      return fail_create(e, rc, e->err);
+  }
   if (phy && c->phy_grooming) {
     if (c->phy_grooming < 0 || c->phy_grooming > 2) return fail_create(e, ORLG_EINVAL, "phy_grooming must be 0, 1 or 2");
     if (npairs > 65536 || p.k > 8 || p.S > 4096) return fail_create(e, ORLG_EINVAL, "channel_state keys: pairs <= 65536, k <= 8, channels <= 4096");
@@ -439,6 +453,7 @@ extern "C" int orlg_step(orlg_engine* e, const int32_t* dev_actions, int32_t* de
   io.alloc = dev_alloc;
   io.hint_actions = e->hint_actions;
   io.hint_heuristic = e->hint_heuristic;
+  io.info = e->info_out;
   return launch(e, io, stream);
 }
 
@@ -609,6 +624,17 @@ extern "C" int orlg_gsnr(orlg_engine* e, const int32_t* dev_query, double* dev_o
       e->p, e->gp, dev_query, dev_out);
   CK(cudaGetLastError());
   e->launches++;
+  return ORLG_OK;
+}
+
+extern "C" int orlg_info_dim(const orlg_engine* e) { return (e && e->p.info_stats) ? 9 + e->p.n_bit_rates : 0; }
+extern "C" int orlg_set_info_output(orlg_engine* e, double* dev_info) {
+  if (!e) return ORLG_EINVAL;
+  if (dev_info && !e->p.info_stats) {
+    e->err = "orlg_set_info_output needs an engine created with info_stats = 1";
+    return ORLG_ESTATE;
+  }
+  e->info_out = dev_info;
   return ORLG_OK;
 }
 

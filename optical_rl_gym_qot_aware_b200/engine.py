@@ -34,7 +34,7 @@ EXPORTS = (
     "orlg_reset", "orlg_step", "orlg_step_host", "orlg_set_obs_layout", "orlg_observation",
     "orlg_heuristic", "orlg_rollout", "orlg_get_counters", "orlg_export_state", "orlg_get_requests",
     "orlg_launch_count", "orlg_gsnr_configure", "orlg_gsnr", "orlg_phy_get_stats", "orlg_path_first_fit", "orlg_set_next_action_hint", "orlg_step_host_async", "orlg_step_host_wait",
-    "orlg_phy_get_channel_state",
+    "orlg_phy_get_channel_state", "orlg_info_dim", "orlg_set_info_output",
 )
 
 
@@ -55,7 +55,7 @@ class OrlgConfig(C.Structure):
         ("bit_rates", C.c_void_p), ("bit_rate_cum", C.c_void_p),
         ("bit_rate_lo", C.c_int32), ("bit_rate_hi", C.c_int32),
         ("src_cum", C.c_void_p), ("dst_cum", C.c_void_p),
-        ("heap_capacity", C.c_int32), ("obs_kind", C.c_int32), ("phy_grooming", C.c_int32), ("reserved", C.c_int32 * 5),
+        ("heap_capacity", C.c_int32), ("obs_kind", C.c_int32), ("phy_grooming", C.c_int32), ("info_stats", C.c_int32), ("reserved", C.c_int32 * 4),
         ("phy_n_tables", C.c_int32), ("phy_max_terms", C.c_int32),
         ("phy_table_id", C.c_void_p), ("phy_mod_level", C.c_void_p), ("phy_gsnr", C.c_void_p),
         ("phy_cut_links", C.c_void_p), ("phy_cut_count", C.c_void_p),
@@ -109,6 +109,8 @@ def load_library():
         L.orlg_gsnr.argtypes = [vp, vp, vp, vp]
         L.orlg_phy_get_stats.argtypes = [vp, vp, vp]
         L.orlg_phy_get_channel_state.argtypes = [vp, vp, i32, vp, vp]
+        L.orlg_info_dim.argtypes = [vp]
+        L.orlg_set_info_output.argtypes = [vp, vp]
         L.orlg_path_first_fit.argtypes = [vp, vp, vp, vp]
         L.orlg_set_next_action_hint.argtypes = [vp, i32, vp]
         _lib = L
@@ -178,6 +180,7 @@ class Engine:
         c.bit_rate_lo, c.bit_rate_hi = spec.bit_rate_lo, spec.bit_rate_hi
         c.heap_capacity = heap_capacity
         c.obs_kind = spec.obs_kind
+        c.info_stats = int(bool(getattr(spec, "info_stats", False)))
         h = C.c_void_p()
         rc = self.L.orlg_create(C.byref(c), C.byref(h))
         if rc != 0:
@@ -297,6 +300,24 @@ class Engine:
         out = self.torch.empty((self.num_envs, REQUEST_DTYPE.itemsize), dtype=self.torch.uint8, device=self.device)
         self._ck(self.L.orlg_get_requests(self.h, self._p(out), self._stream()))
         return out.cpu().numpy().view(REQUEST_DTYPE).reshape(self.num_envs)
+
+    INFO_KEYS = ("service_blocking_rate", "episode_service_blocking_rate", "bit_rate_blocking_rate",
+                 "episode_bit_rate_blocking_rate", "network_compactness", "network_compactness_difference",
+                 "avg_link_compactness", "avg_link_utilization", "fairness")
+
+    def set_info_output(self, enable: bool = True):
+        """The info dict of RMSAEnv.step (rmsa_env.py:293-332) written by every following step; returns the
+        f64 tensor [num_envs, 9 + n_bit_rates] it lands in (columns: INFO_KEYS, then bit_rate_blocking_<b>)."""
+        if not enable:
+            self._ck(self.L.orlg_set_info_output(self.h, None))
+            self._info = None
+            return None
+        n = int(self.L.orlg_info_dim(self.h))
+        if n <= 0:
+            raise RuntimeError("engine was created without info_stats")
+        self._info = self.torch.zeros((self.num_envs, n), dtype=self.torch.float64, device=self.device)
+        self._ck(self.L.orlg_set_info_output(self.h, self._p(self._info)))
+        return self._info
 
     def phy_channel_state(self, max_entries: int = 256):
         """PhyRMSA-v0 channel_state: (int32 [num_envs, max_entries, 6], int32 [num_envs] counts); rows are

@@ -77,6 +77,9 @@ class EnvSpec:
     # 2 = grooming=False but channel_state kept, i.e. what the reference does: sapff/sapbm/bmff/faff/faff_rss
     # try use_existing_channels whatever env.grooming says (phy_rmsa_env.py:1256,1321,1510,1574,1678)
     phy_grooming: int = 0
+    # RMSA-v0 / DeepRMSA-v0: keep what the step's info dict needs (rmsa_env.py:276-332): time-weighted link
+    # statistics, per-bit-rate histograms, sum of slots x hops of the running services
+    info_stats: bool = False
 
     @property
     def action_dim(self) -> int:
@@ -157,6 +160,7 @@ def make_spec(
     s_band: bool = True,
     grooming: bool = False,
     keep_channel_state: bool = False,
+    info_stats: bool = False,
     defrag_period=None,
     number_moves=None,
     metric: str = "cut",
@@ -245,6 +249,7 @@ def make_spec(
         obs_kind = OBS_F64 if kind == ENV_DEEPRMSA else OBS_NONE
     spec.obs_kind = obs_kind
     spec.phy = phy_tables
+    spec.info_stats = bool(info_stats) and kind in (ENV_RMSA, ENV_DEEPRMSA)
     if kind == ENV_PHYRMSA:
         spec.phy_grooming = 1 if grooming else (2 if keep_channel_state else 0)
     assert spec.num_slots <= 1024 and tables.n_edges <= 128

@@ -70,6 +70,8 @@ class OracleConfig(C.Structure):
         ("phy_gsnr", C.c_void_p),
         ("path_nodes", C.c_void_p),
         ("edge_nodes", C.c_void_p),
+        ("info_stats", C.c_int32),
+        ("info_pad", C.c_int32),
     ]
 
 
@@ -118,6 +120,8 @@ def lib():
         L.oracle_phy_stats.argtypes = [C.c_void_p, C.c_void_p]
         L.oracle_phy_channel_state.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
         L.oracle_phy_channel_state.restype = C.c_int64
+        L.oracle_info.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+        L.oracle_info.restype = C.c_int
         L.oracle_gsnr.argtypes = [C.c_void_p, C.POINTER(OracleGsnrParams), C.c_void_p, C.c_void_p]
         L.oracle_services.restype = C.c_int64
         L.oracle_services.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
@@ -175,6 +179,7 @@ class OracleSpec:
         c.n_mods = len(t.mod_names)
         c.phy_n_tables = 0 if ph is None else ph.n_tables
         c.phy_grooming = int(getattr(spec, "phy_grooming", 0))
+        c.info_stats = int(bool(getattr(spec, "info_stats", False)))
         c.num_slots, c.num_cores, c.j = spec.num_slots, spec.num_cores, spec.j
         c.episode_length = spec.episode_length
         c.allow_rejection = int(spec.allow_rejection)
@@ -229,6 +234,12 @@ class OracleEnv:
         obs = np.zeros(n, np.uint8)
         self.L.oracle_matrix_observation(self.h, obs.ctypes.data)
         return obs
+
+    def info(self):
+        """info dict values of the last step (see oracle_info in orlg_oracle.h)."""
+        o = np.zeros(64, np.float64)
+        n = int(self.L.oracle_info(self.h, o.ctypes.data, 64))
+        return o[:n]
 
     def phy_channel_state(self, max_entries=4096):
         o = np.zeros((max_entries, 6), np.int32)

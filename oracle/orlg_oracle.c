@@ -131,6 +131,11 @@ struct oracle_env {
   int64_t genv;
   uint8_t* avail; /* [cores][E][S], 1 = free: topology.graph["available_slots"] */
   svc* heap;      /* heapq list of (release_time, service) */
+  /* info dict state (info_stats): topology[n1][n2]["last_update"|"utilization"|"compactness"], histograms */
+  double *lnk_last_update, *lnk_utilization, *lnk_compactness;
+  int64_t *hist_requested, *hist_provisioned; /* bit_rate_requested_histogram / _provisioned_ by bit-rate index */
+  double info[64];
+  int info_n;
   chan_state* cs; /* channel_state, all keys, append order */
   int64_t cs_len, cs_cap;
   int64_t heap_len, heap_cap;
@@ -160,6 +165,13 @@ oracle_env* oracle_create(const oracle_config* cfg, int64_t genv) {
   e->avail = (uint8_t*)malloc((size_t)e->c.num_cores * e->c.n_edges * e->c.num_slots);
   e->heap_cap = 64;
   e->heap = (svc*)malloc(sizeof(svc) * e->heap_cap);
+  if (e->c.info_stats) {
+    e->lnk_last_update = (double*)calloc((size_t)e->c.n_edges, sizeof(double));
+    e->lnk_utilization = (double*)calloc((size_t)e->c.n_edges, sizeof(double));
+    e->lnk_compactness = (double*)calloc((size_t)e->c.n_edges, sizeof(double));
+    e->hist_requested = (int64_t*)calloc((size_t)(e->c.n_bit_rates > 0 ? e->c.n_bit_rates : 1), sizeof(int64_t));
+    e->hist_provisioned = (int64_t*)calloc((size_t)(e->c.n_bit_rates > 0 ? e->c.n_bit_rates : 1), sizeof(int64_t));
+  }
   if (e->c.env_kind == 3 && e->c.edge_nodes) {
     int N = e->c.n_nodes;
     e->link_of = (int16_t*)malloc(sizeof(int16_t) * N * N);
@@ -177,6 +189,8 @@ void oracle_destroy(oracle_env* e) {
   free(e->avail);
   free(e->heap);
   free(e->cs);
+  free(e->lnk_last_update); free(e->lnk_utilization); free(e->lnk_compactness);
+  free(e->hist_requested); free(e->hist_provisioned);
   free(e->link_of);
   free(e);
 }
@@ -267,10 +281,133 @@ static int is_path_free(const oracle_env* e, int pair, int path, int core, int s
 
 /* _provision_path rmsa_env.py:462-513 / rmcsa_env.py:488-534 (state + counters;
  * the info-only link/network statistics are out of scope) */
+static int rle(const uint8_t* a, int n, int* pos, uint8_t* val, int* len);
+
+/* _get_network_compactness rmsa_env.py:806-851 */
+static double network_compactness(const oracle_env* e) {
+  int E = e->c.n_edges, S = e->c.num_slots;
+  int64_t sum_slots_paths = 0, sum_occupied = 0, sum_unused_spectrum_blocks = 0;
+  for (int64_t i = 0; i < e->heap_len; i++) /* running services = the release queue */
+    sum_slots_paths += (int64_t)e->heap[i].number_slots * hops_of(e, e->heap[i].pair, e->heap[i].path);
+  int pos[1024], len[1024], ipos[1024], ilen[1024];
+  uint8_t val[1024], ival[1024];
+  for (int l = 0; l < E; l++) {
+    const uint8_t* row = AV(e, 0, l);
+    int nr = rle(row, S, pos, val, len), first = -1, last = -1, used = 0;
+    for (int r = 0; r < nr; r++)
+      if (val[r] == 0) { if (first < 0) first = r; last = r; used++; }
+    if (used > 1) {
+      int lambda_min = pos[first], lambda_max = pos[last] + len[last];
+      sum_occupied += lambda_max - lambda_min;
+      int ni = rle(row + lambda_min, lambda_max - lambda_min, ipos, ival, ilen);
+      for (int r = 0; r < ni; r++) sum_unused_spectrum_blocks += ival[r]; /* np.sum(internal_values) */
+    }
+  }
+  if (sum_unused_spectrum_blocks > 0)
+    return ((double)sum_occupied / (double)sum_slots_paths) * ((double)E / (double)sum_unused_spectrum_blocks);
+  return 1.0;
+}
+
+/* _update_link_stats rmsa_env.py:562-641 (utilization and compactness; external_fragmentation is not in the info dict) */
+static void update_link_stats(oracle_env* e, int l) {
+  if (!e->c.info_stats) return;
+  int S = e->c.num_slots;
+  double last_update = e->lnk_last_update[l];
+  double time_diff = e->now - last_update;
+  if (e->now > 0) {
+    const uint8_t* row = AV(e, 0, l);
+    int64_t free_slots = 0;
+    for (int s = 0; s < S; s++) free_slots += row[s];
+    double last_util = e->lnk_utilization[l];
+    double cur_util = (double)(S - free_slots) / (double)S;
+    e->lnk_utilization[l] = ((last_util * last_update) + (cur_util * time_diff)) / e->now;
+    double last_compactness = e->lnk_compactness[l], cur_link_compactness = 0.0;
+    if (free_slots > 0) {
+      int pos[1024], len[1024], ipos[1024], ilen[1024];
+      uint8_t val[1024], ival[1024];
+      int nr = rle(row, S, pos, val, len), first = -1, last = -1, used = 0;
+      for (int r = 0; r < nr; r++)
+        if (val[r] == 0) { if (first < 0) first = r; last = r; used++; }
+      if (used > 1) {
+        int lambda_min = pos[first], lambda_max = pos[last] + len[last];
+        int ni = rle(row + lambda_min, lambda_max - lambda_min, ipos, ival, ilen);
+        int64_t unused_spectrum_slots = 0;
+        for (int r = 0; r < ni; r++) unused_spectrum_slots += 1 - ival[r]; /* np.sum(1 - internal_values) */
+        if (unused_spectrum_slots > 0)
+          cur_link_compactness = ((double)(lambda_max - lambda_min) / (double)(S - free_slots)) *
+                                 (1.0 / (double)unused_spectrum_slots);
+        else cur_link_compactness = 1.0;
+      } else cur_link_compactness = 1.0;
+    }
+    e->lnk_compactness[l] = ((last_compactness * last_update) + (cur_link_compactness * time_diff)) / e->now;
+  }
+  e->lnk_last_update[l] = e->now;
+}
+
+/* numpy's pairwise summation of a contiguous f64 array (what np.mean of a list runs), n < 128 */
+static double np_sum(const double* a, int n) {
+  if (n < 8) {
+    double res = 0.;
+    for (int i = 0; i < n; i++) res += a[i];
+    return res;
+  }
+  double r[8];
+  int i;
+  for (i = 0; i < 8; i++) r[i] = a[i];
+  for (i = 8; i < n - (n % 8); i += 8)
+    for (int j = 0; j < 8; j++) r[j] += a[i + j];
+  double res = ((r[0] + r[1]) + (r[2] + r[3])) + ((r[4] + r[5]) + (r[6] + r[7]));
+  for (; i < n; i++) res += a[i];
+  return res;
+}
+
+static int bit_rate_index(const oracle_env* e, int bit_rate) {
+  for (int i = 0; i < e->c.n_bit_rates; i++)
+    if (e->c.bit_rates[i] == bit_rate) return i;
+  return -1;
+}
+
+/* the info dict of RMSAEnv.step rmsa_env.py:276-332, taken after the provisioning and before _next_service */
+static void make_info(oracle_env* e, double previous_network_compactness) {
+  double* o = e->info;
+  int E = e->c.n_edges, nb = e->c.n_bit_rates;
+  double cur = network_compactness(e);
+  o[0] = (double)(e->services_processed - e->services_accepted) / (double)e->services_processed;
+  o[1] = (double)(e->ep_processed - e->ep_accepted) / (double)e->ep_processed;
+  o[2] = (double)(e->br_requested - e->br_provisioned) / (double)e->br_requested;
+  o[3] = (double)(e->ep_br_requested - e->ep_br_provisioned) / (double)e->ep_br_requested;
+  o[4] = cur;
+  o[5] = previous_network_compactness - cur;
+  o[6] = np_sum(e->lnk_compactness, E) / (double)E;
+  o[7] = np_sum(e->lnk_utilization, E) / (double)E;
+  double mx = 0, mn = 0;
+  for (int i = 0; i < nb && i < 50; i++) { /* :277-289 */
+    double b = e->hist_requested[i] > 0
+                   ? (double)(e->hist_requested[i] - e->hist_provisioned[i]) / (double)e->hist_requested[i] : 0.0;
+    o[9 + i] = b;
+    if (i == 0 || b > mx) mx = b;
+    if (i == 0 || b < mn) mn = b;
+  }
+  o[8] = mx - mn; /* fairness :326-328 */
+  e->info_n = 9 + (nb < 50 ? nb : 50);
+}
+
+int oracle_info(const oracle_env* e, double* out, int max_values) {
+  for (int i = 0; i < e->info_n && i < max_values; i++) out[i] = e->info[i];
+  return e->info_n;
+}
+
 static void provision_path(oracle_env* e, int pair, int path, int core, int start, int n) {
   const int16_t* L = links_of(e, pair, path, 0);
   int h = hops_of(e, pair, path);
-  for (int i = 0; i < h; i++) memset(AV(e, core, L[i]) + start, 0, (size_t)n);
+  for (int i = 0; i < h; i++) {
+    memset(AV(e, core, L[i]) + start, 0, (size_t)n);
+    if (e->c.env_kind <= 1) update_link_stats(e, L[i]); /* rmsa_env.py:494 */
+  }
+  if (e->c.info_stats && e->c.env_kind <= 1) {
+    int bi = bit_rate_index(e, e->cur.bit_rate);
+    if (bi >= 0) e->hist_provisioned[bi]++; /* :510 */
+  }
   e->services_accepted++;
   e->ep_accepted++;
   e->br_provisioned += e->cur.bit_rate;
@@ -320,7 +457,10 @@ static void release_path(oracle_env* e, const svc* s) {
     }
     return;
   }
-  for (int i = 0; i < h; i++) memset(AV(e, s->core, L[i]) + s->initial_slot, 1, (size_t)s->number_slots);
+  for (int i = 0; i < h; i++) {
+    memset(AV(e, s->core, L[i]) + s->initial_slot, 1, (size_t)s->number_slots);
+    if (e->c.env_kind <= 1) update_link_stats(e, L[i]); /* rmsa_env.py:531-533 */
+  }
 }
 
 /* get_available_slots rmsa_env.py:745-756 (rows by edge "id", F9); core 0 plane
@@ -379,6 +519,10 @@ static void next_service(oracle_env* e) {
   }
   e->br_requested += rq.bit_rate; /* rmsa_env.py:677-678 ; rmcsa_env.py:730-731 */
   e->ep_br_requested += rq.bit_rate;
+  if (e->c.info_stats && e->c.env_kind <= 1) {
+    int bi = bit_rate_index(e, rq.bit_rate);
+    if (bi >= 0) e->hist_requested[bi]++; /* :680 */
+  }
   while (e->heap_len > 0) { /* rmsa_env.py:689-695 */
     if (e->heap[0].release_time <= e->now) {
       svc s = heap_pop(e);
@@ -401,6 +545,10 @@ void oracle_reset(oracle_env* e, int full) {
     return;
   }
   e->cs_len = 0;   /* channel_state phy_rmsa_env.py:455-461 */
+  if (e->c.info_stats) { /* optical_network_env.py:257-260, rmsa_env.py:444-452 */
+    for (int l = 0; l < e->c.n_edges; l++) e->lnk_last_update[l] = e->lnk_utilization[l] = e->lnk_compactness[l] = 0.0;
+    for (int i = 0; i < e->c.n_bit_rates; i++) e->hist_requested[i] = e->hist_provisioned[i] = 0;
+  }
   e->heap_len = 0; /* OpticalNetworkEnv.reset optical_network_env.py:216-222 */
   e->now = 0.0;
   e->services_processed = e->services_accepted = 0;
@@ -786,6 +934,8 @@ void oracle_step(oracle_env* e, const int32_t* a, int32_t* reward, uint8_t* done
                  int32_t* alloc) {
   int accepted = 0;
   int k = e->c.k_paths, S = e->c.num_slots;
+  const int want_info = e->c.info_stats && e->c.env_kind <= 1;
+  double previous_network_compactness = want_info ? network_compactness(e) : 0.0; /* rmsa_env.py:227-229 */
   if (e->c.env_kind == 0) {
     accepted = rmsa_decide(e, a[0], a[1], alloc);
   } else if (e->c.env_kind == 1) { /* DeepRMSAEnv.step deeprmsa_env.py:48-58 */
@@ -825,6 +975,7 @@ void oracle_step(oracle_env* e, const int32_t* a, int32_t* reward, uint8_t* done
       alloc[3] = accepted ? n : 0;
     }
   }
+  if (want_info) make_info(e, previous_network_compactness);
   finish_step(e, accepted, reward, done);
   if (obs && e->c.env_kind == 1) oracle_observation(e, obs);
 }

@@ -68,6 +68,9 @@ typedef struct oracle_config {
   const double* phy_gsnr;        /* [n_tables][num_slots][k_paths]  gsnr[table][channel][idp] */
   const int16_t* path_nodes;     /* [n_nodes*n_nodes][k_paths][max_hops+1] node ids, -1 padded */
   const int32_t* edge_nodes;     /* [n_edges][2] */
+  /* 1: keep what the info dict of RMSAEnv.step needs (rmsa_env.py:276-332): time-weighted link statistics
+   * (_update_link_stats :562-641), per-bit-rate histograms; RMSA-v0 / DeepRMSA-v0 */
+  int32_t info_stats, info_pad;
 } oracle_config;
 
 typedef struct oracle_env oracle_env;
@@ -104,6 +107,11 @@ int64_t oracle_rollout_many(const oracle_config* cfg, int64_t env0, int64_t n_en
  * number_cuts_total, rss_total_metric (phy_rmsa_env.py:313-348). */
 #define ORACLE_PHY_ADIM 9
 void oracle_phy_stats(const oracle_env* e, double* out8);
+/* info dict of the LAST step (rmsa_env.py:293-332): service_blocking_rate, episode_service_blocking_rate,
+ * bit_rate_blocking_rate, episode_bit_rate_blocking_rate, network_compactness, network_compactness_difference,
+ * avg_link_compactness, avg_link_utilization, fairness, then bit_rate_blocking_<b> for every bit rate.
+ * Returns the number of values (9 + n_bit_rates).  Needs info_stats = 1. */
+int oracle_info(const oracle_env* e, double* out, int max_values);
 /* channel_state (phy_rmsa_env.py:158-166) in append order, rows (src*N+dst, idp, channel, used, free, capacity) */
 int64_t oracle_phy_channel_state(const oracle_env* e, int32_t* out, int64_t max_entries);
 

@@ -56,7 +56,15 @@ def counters_of(env):
          env.episode_bit_rate_requested, env.episode_bit_rate_provisioned], np.int64)
 
 
-def run_case(name, env_id, topo_file, kwargs, policy, n_steps, action_seed=0):
+INFO_KEYS = ("service_blocking_rate", "episode_service_blocking_rate", "bit_rate_blocking_rate",
+             "episode_bit_rate_blocking_rate", "network_compactness", "network_compactness_difference",
+             "avg_link_compactness", "avg_link_utilization")
+ONLY = set(sys.argv[1:])  # optional: names of the cases to (re)generate
+
+
+def run_case(name, env_id, topo_file, kwargs, policy, n_steps, action_seed=0, want_info=False):
+    if ONLY and name not in ONLY:
+        return
     topo = refenv.load_topology(topo_file)
     env = gym.make(env_id, topology=topo, **kwargs)
     kind = {"RMSA-v0": 0, "DeepRMSA-v0": 1, "RMCSA-v0": 2}[env_id]
@@ -71,6 +79,9 @@ def run_case(name, env_id, topo_file, kwargs, policy, n_steps, action_seed=0):
     counters = np.zeros((n_steps, 8), np.int64)
     obs = None
     obs0 = None
+    info_main = np.zeros((n_steps, len(INFO_KEYS)), np.float64)
+    info_fair = np.zeros(n_steps, np.float64)
+    info_br = np.zeros((n_steps, len(getattr(env, "bit_rates", []))), np.float64)
     if kind == 1:
         obs0 = np.asarray(env.observation(), np.float64)
         obs = np.zeros((n_steps, obs0.size), np.float64)
@@ -94,6 +105,10 @@ def run_case(name, env_id, topo_file, kwargs, policy, n_steps, action_seed=0):
         svc = env.current_service
         out = env.step(a[0] if kind == 1 else a)
         o, r, d = out[0], out[1], out[2]
+        if want_info:  # the info dict of rmsa_env.py:293-332, f64 as computed
+            info_main[t] = [out[3][key] for key in INFO_KEYS]
+            info_fair[t] = out[3]["fairness"]
+            info_br[t] = [out[3][f"bit_rate_blocking_{b}"] for b in env.bit_rates]
         accepted[t] = 1 if svc.accepted else 0
         reward[t] = r
         done[t] = 1 if d else 0
@@ -119,6 +134,8 @@ def run_case(name, env_id, topo_file, kwargs, policy, n_steps, action_seed=0):
     for key, v in kwargs.items():
         if key != "topology" and v is not None:
             out["kw_" + key] = np.asarray(v)
+    if want_info:
+        out.update(info_main=info_main, info_fairness=info_fair, info_bit_rate_blocking=info_br)
     if obs is not None:
         out["obs"] = obs
         out["obs0"] = obs0
@@ -145,7 +162,8 @@ TOPOLOGIES = {
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
     for short, f in TOPOLOGIES.items():
-        tables_from_topology(refenv.load_topology(f)).save(os.path.join(GOLDEN, f"topology_{short}.npz"))
+        if not ONLY:
+            tables_from_topology(refenv.load_topology(f)).save(os.path.join(GOLDEN, f"topology_{short}.npz"))
     nsf, spn, jpn = TOPOLOGIES["nsfnet"], TOPOLOGIES["spn"], TOPOLOGIES["jpn12_k5"]
     c1 = dict(seed=10, load=50, num_spectrum_resources=100, episode_length=1000)
     run_case("rmsa_nsfnet_sapff", "RMSA-v0", nsf, c1, rmsa_env.shortest_available_path_first_fit, 2500)
@@ -163,6 +181,15 @@ def main():
              dict(c2, seed=21, j=3, allow_rejection=True, episode_length=70), "random", 1000, 3)
     run_case("deeprmsa_nsfnet_spff", "DeepRMSA-v0", nsf, dict(c2, seed=22, allow_rejection=True),
              deeprmsa_env.shortest_path_first_fit, 600)
+    # the info dict: compactness, time-weighted link statistics, per-bit-rate blocking
+    run_case("info_rmsa_nsfnet_sapff", "RMSA-v0", nsf, dict(c1, seed=14, load=45, mean_service_holding_time=25,
+                                                             episode_length=150),
+             rmsa_env.shortest_available_path_first_fit, 700, want_info=True)
+    run_case("info_rmsa_nsfnet_random", "RMSA-v0", nsf,
+             dict(c1, seed=15, load=30, mean_service_holding_time=25, episode_length=90, allow_rejection=True),
+             "random", 600, 9, want_info=True)
+    run_case("info_deeprmsa_nsfnet_kspff", "DeepRMSA-v0", nsf, dict(c2, seed=23),
+             deeprmsa_env.shortest_available_path_first_fit, 600, want_info=True)
     c5 = dict(seed=30, load=100, mean_service_holding_time=25, num_spectrum_resources=100, episode_length=400)
     run_case("rmsa_spn_sapff", "RMSA-v0", spn, c5, rmsa_env.shortest_available_path_first_fit, 1500)
     run_case("rmsa_spn320_sapff", "RMSA-v0", spn, dict(c5, seed=31, load=400, num_spectrum_resources=320),

@@ -166,3 +166,39 @@ def test_fused_next_action_hint_equals_heuristic_launch(env_id, topo, kw, hid):
     before = act_a.clone()
     a.step(act_a)
     assert torch.equal(act_a, before)
+
+
+INFO_CASES = [c for c in G.CASES if c.startswith("info_")]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", INFO_CASES)
+def test_engine_info_dict_matches_reference(case):
+    """the step's info dict (rmsa_env.py:293-332) written by the step kernel — blocking rates,
+    network compactness (+ difference), time-weighted link compactness / utilization means, fairness, per-bit-rate
+    blocking — bit for bit against the golden trace of the unmodified reference."""
+    import torch
+
+    from optical_rl_gym_qot_aware_b200.engine import Engine
+
+    g, spec = G.load_case(case)
+    spec.info_stats = True
+    n_env = 3
+    eng = Engine(spec, n_env)
+    eng.load_trace(np.repeat(g["requests"][:, None], n_env, axis=1))
+    eng.reset(True)
+    info = eng.set_info_output()
+    dev = eng.device
+    reward = torch.zeros(n_env, dtype=torch.int32, device=dev)
+    done = torch.zeros(n_env, dtype=torch.uint8, device=dev)
+    act = torch.zeros((n_env, eng.action_dim), dtype=torch.int32, device=dev)
+    for t in range(len(g["actions"])):
+        act[:] = torch.as_tensor(g["actions"][t].astype(np.int32), device=dev)
+        eng.step(act, reward, done)
+        want = np.concatenate([g["info_main"][t], [g["info_fairness"][t]], g["info_bit_rate_blocking"][t]])
+        got = info.cpu().numpy()
+        assert np.array_equal(got[0], want) and np.array_equal(got[2], want), (case, t, np.flatnonzero(got[0] != want), got[0], want)
+        if bool(done.cpu().numpy()[0]):
+            eng.reset(False)
+    assert int(eng.counters()[:, 10].max()) == 0
+    eng.close()
