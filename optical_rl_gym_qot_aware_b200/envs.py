@@ -110,6 +110,8 @@ class BatchedEnv:
         self.engine = Engine(self.spec, num_envs, device=device, global_env_offset=global_env_offset)
         self.num_envs = int(num_envs)
         self.device = self.engine.device
+        # info_stats=True: the step's info dict of rmsa_env.py:293-332 comes from the step kernel itself
+        self._info = self.engine.set_info_output() if self.spec.info_stats else None
         t = tables
         # attributes the reference's drivers and heuristics read
         self.k_paths = t.k_paths
@@ -230,7 +232,14 @@ class BatchedEnv:
         return self.engine.requests()
 
     def info(self) -> Dict[str, Any]:
-        """Counter-derived entries of the reference's info dict (rmsa_env.py:293-307), per env."""
+        """The reference's info dict (rmsa_env.py:293-332), per env.  With ``info_stats=True`` every entry
+        (compactness, link statistics, fairness, per-bit-rate blocking) is the value the last step computed at
+        the reference's point in the step; otherwise only the counter-derived rates, from the current counters."""
+        if self._info is not None:
+            out = {k: self._info[:, i] for i, k in enumerate(self.engine.INFO_KEYS)}
+            for i, b in enumerate(np.asarray(self.spec.bit_rates).tolist()):
+                out[f"bit_rate_blocking_{b}"] = self._info[:, 9 + i]
+            return out
         c = self.counters().to(self.torch.float64)
         safe = lambda x: self.torch.clamp(x, min=1.0)  # noqa: E731
         return {

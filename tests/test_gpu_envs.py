@@ -177,6 +177,26 @@ def test_phy_scalar_env_five_tuple_and_info_reward():
     env.close()
 
 
+def test_scalar_env_info_dict_matches_reference():
+    """make(..., info_stats=True): env.step's info carries the reference's entries (rmsa_env.py:293-332)."""
+    import optical_rl_gym_qot_aware_b200 as pkg
+
+    g, spec = G.load_case("info_rmsa_nsfnet_sapff")
+    env = pkg.make("RMSA-v0", topology=spec.tables, request_source="replay", info_stats=True, **_kwargs(g))
+    env.load_trace(g["requests"])
+    keys = ("service_blocking_rate", "episode_service_blocking_rate", "bit_rate_blocking_rate",
+            "episode_bit_rate_blocking_rate", "network_compactness", "network_compactness_difference",
+            "avg_link_compactness", "avg_link_utilization")
+    for t in range(300):
+        _, r, d, info = env.step(env.heuristic("shortest_available_path_first_fit"))
+        assert [info[k] for k in keys] == list(g["info_main"][t]), t
+        assert info["fairness"] == g["info_fairness"][t]
+        assert info["bit_rate_blocking_200"] == g["info_bit_rate_blocking"][t][0]
+        if d:
+            env.reset()
+    env.close()
+
+
 def test_phy_scalar_env_grooming_virtual_actions():
     """grooming=True through the gym surface: the heuristic returns the reference's virtual-layer action
     (idp + 20, [(channel, share, left over, capacity, True), ...]) (phy_rmsa_env.py:1380,1664-1670) and step takes it."""
