@@ -23,12 +23,14 @@ __device__ __forceinline__ Row<W> row_ones() {
   return r;
 }
 
-// bits of [lo, hi) that fall into word `wi`
+// bits [0, len) that fall into word `wi`: the funnel shift clamps its amount to 32, so a prefix that covers
+// the whole word (or more) needs no special case
+__device__ __forceinline__ uint32_t prefix_word(int wi, int len) {
+  return ~__funnelshift_lc(0u, 0xFFFFFFFFu, (uint32_t)max(len - 32 * wi, 0));
+}
+// bits of [lo, hi) that fall into word `wi` (empty when hi <= lo)
 __device__ __forceinline__ uint32_t mask_word(int wi, int lo, int hi) {
-  int a = max(lo - 32 * wi, 0), b = min(hi - 32 * wi, 32);
-  if (b <= a) return 0u;
-  uint32_t m = (b - a == 32) ? 0xFFFFFFFFu : ((1u << (b - a)) - 1u);
-  return m << a;
+  return prefix_word(wi, hi) & ~prefix_word(wi, lo);
 }
 
 // logical right shift of the whole row by 2^B bits (zeros enter at the top)

@@ -62,6 +62,7 @@ struct Params {
   const double* br_cum;
   const double* src_cum;
   const double* dst_cum;
+  const unsigned char* guide;  // [2 + N][64] bisect guide tables: src, bit rate, dst given src (rng.cuh)
   uint32_t* occ;
   double* now;
   double* holding;

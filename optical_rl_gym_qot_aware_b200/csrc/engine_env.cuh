@@ -358,13 +358,13 @@ struct Env {
       q.holding = -det_log(1.0 - res53(R0.z, R0.w)) / lam_h;
       const double inv32 = 1.0 / 4294967296.0;
       int n = p.n_nodes;
-      q.src = bisect_right(p.src_cum, ((double)R1.x * inv32) * __ldg(p.src_cum + n - 1), n - 1);
+      q.src = bisect_right_guided(p.src_cum, p.guide, R1.x, ((double)R1.x * inv32) * __ldg(p.src_cum + n - 1), n - 1);
       const double* dc = p.dst_cum + (size_t)q.src * n;
-      q.dst = bisect_right(dc, ((double)R1.y * inv32) * __ldg(dc + n - 1), n - 1);
+      q.dst = bisect_right_guided(dc, p.guide + 64 * (2 + q.src), R1.y, ((double)R1.y * inv32) * __ldg(dc + n - 1), n - 1);
       double ub = (double)R1.z * inv32;
       if (p.n_bit_rates > 0) {
         int nb = p.n_bit_rates;
-        q.bit_rate = __ldg(p.bit_rates + bisect_right(p.br_cum, ub * __ldg(p.br_cum + nb - 1), nb - 1));
+        q.bit_rate = __ldg(p.bit_rates + bisect_right_guided(p.br_cum, p.guide + 64, R1.z, ub * __ldg(p.br_cum + nb - 1), nb - 1));
       } else {
         q.bit_rate = p.br_lo + (int)floor(ub * (double)(p.br_hi - p.br_lo + 1));
       }

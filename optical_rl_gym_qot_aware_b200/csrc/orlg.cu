@@ -276,7 +276,23 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
     const size_t o_brc = o_src + b_src, b_brc = have_br ? (size_t)c->n_bit_rates * 8 : 0;
     const size_t o_brv = o_brc + b_brc, b_brv = have_br ? (size_t)c->n_bit_rates * 4 : 0;
     const size_t o_dst = pad(o_brv + b_brv), b_dst = c->dst_cum ? npairs * 8 : 0;
-    std::vector<unsigned char> blob(pad(o_dst + b_dst), 0);
+    const size_t o_gd = pad(o_dst + b_dst), b_gd = (b_src && b_dst) ? (size_t)(2 + c->n_nodes) * 64 : 0;
+    std::vector<unsigned char> blob(pad(o_gd + b_gd), 0);
+    if (b_gd) {  // guide tables of bisect_right_guided: insertion point of the smallest value of each of 64 buckets
+      auto fill = [&](unsigned char* g, const double* cum, int n) {
+        if (n > 255) n = 255;
+        for (int b = 0; b < 64; b++) {
+          const double x = ((double)((unsigned long long)b << 26) * (1.0 / 4294967296.0)) * cum[n - 1];
+          int cnt = 0;
+          for (int i = 0; i < n - 1; i++) cnt += (x >= cum[i]) ? 1 : 0;
+          g[b] = (unsigned char)cnt;
+        }
+      };
+      unsigned char* g = blob.data() + o_gd;
+      fill(g, c->src_cum, c->n_nodes);
+      if (have_br) fill(g + 64, c->bit_rate_cum, c->n_bit_rates);
+      for (int s0 = 0; s0 < c->n_nodes; s0++) fill(g + 64 * (2 + s0), c->dst_cum + (size_t)s0 * c->n_nodes, c->n_nodes);
+    }
     memcpy(blob.data() + o_rec, rec.data(), b_rec);
     if (b_src) memcpy(blob.data() + o_src, c->src_cum, b_src);
     if (b_brc) memcpy(blob.data() + o_brc, c->bit_rate_cum, b_brc);
@@ -291,6 +307,7 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
     if (b_brc) p.br_cum = reinterpret_cast<const double*>(d + o_brc);
     if (b_brv) p.bit_rates = reinterpret_cast<const int*>(d + o_brv);
     if (b_dst) p.dst_cum = reinterpret_cast<const double*>(d + o_dst);
+    if (b_gd) p.guide = d + o_gd;
   }
   if ((rc = dev_upload(e, &p.path_length, c->path_length, npaths))) return fail_create(e, rc, e->err);
   if (c->mod_se && (rc = dev_upload(e, &p.mod_se, c->mod_se, c->n_mods))) return fail_create(e, rc, e->err);

@@ -76,4 +76,14 @@ __device__ __forceinline__ int bisect_right(const double* __restrict__ cum, doub
   return c;
 }
 
+// The same insertion point from a guide table: the 32-bit draw R selects bucket R >> 26, guide[bucket] is the
+// insertion point of the bucket's smallest value (so it is <= the answer for every x of the bucket, x being a
+// monotone function of R), and a short forward scan finishes.  One byte load and ~1 compare instead of `hi`.
+__device__ __forceinline__ int bisect_right_guided(const double* __restrict__ cum, const unsigned char* __restrict__ guide,
+                                                   uint32_t R, double x, int hi) {
+  int c = __ldg(guide + (R >> 26));
+  while (c < hi && x >= __ldg(cum + c)) c++;
+  return c;
+}
+
 }  // namespace orlg
