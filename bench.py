@@ -247,7 +247,7 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
         dist.init_process_group("nccl", device_id=dev)
     PREROLL = PREROLL_OF.get(wl, 600)
     n_env = args.envs
-    eng = Engine(spec, n_env, device=local, global_env_offset=rank * n_env)
+    eng = Engine(spec, n_env, device=local, global_env_offset=rank * n_env, heap_capacity=args.heap_capacity)
     eng.reset(True)
     eng.rollout(hid, PREROLL)
     act = torch.zeros((n_env, eng.action_dim), dtype=torch.int32, device=dev)
@@ -383,7 +383,7 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
         nh = n_env // 2
         halves = []
         for hi in range(2):
-            he = Engine(spec, nh, device=local, global_env_offset=rank * n_env + hi * nh)
+            he = Engine(spec, nh, device=local, global_env_offset=rank * n_env + hi * nh, heap_capacity=args.heap_capacity)
             he.reset(True)
             he.rollout(hid, PREROLL)
             dobs = he.new_obs()
@@ -426,6 +426,19 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
                 raise RuntimeError("device fault bits set in the pipelined e2e run")
             h["e"].close()
     clocks = sampler.stop() if rank == 0 else None
+    # what the host link can do with the same buffer: pinned D2H copies of the observation alone
+    pcie_gbs = None
+    if h_obs is not None:
+        dsrc = obs.t().contiguous() if obs.dim() == 2 else obs
+        for _ in range(3):
+            h_obs.copy_(dsrc, non_blocking=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(20):
+            h_obs.copy_(dsrc, non_blocking=True)
+        e1.record()
+        torch.cuda.synchronize()
+        pcie_gbs = 20 * h_obs.numel() * h_obs.element_size() / (e0.elapsed_time(e1) * 1e-3) / 1e9
     h2d = h_act.numel() * 4
     d2h = h_rew.numel() * 4 + h_done.numel() + (h_obs.numel() * h_obs.element_size() if h_obs is not None else 0)
 
@@ -481,6 +494,7 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
                 "d2h_bytes_per_step": d2h, "steps": Ke, "ms_per_step": e2e_ms / Ke, "mode": e2e_mode,
                 "serial_value": total_envs * Ke / (e2e_serial_ms * 1e-3),
                 "host_policy_ms_per_step": policy_s[0] * 1e3 / Ke,
+                "d2h_gbs": d2h * Ke / (e2e_ms * 1e-3) / 1e9, "pinned_d2h_copy_gbs": pcie_gbs,
                 "policy": "numpy K-SP-FF from the host observation" if use_obs_policy
                 else "device heuristic, actions D2H then H2D"},
         "gpu_launches": int(launches),
@@ -521,6 +535,8 @@ def main():
     ap.add_argument("--e2e-serial", action="store_true", help="no two-half pipelining of the e2e loop")
     ap.add_argument("--two-launch", action="store_true", help="orlg_heuristic + orlg_step instead of the fused hint")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--heap-capacity", type=int, default=0,
+                    help="release-queue entries per env (0 = the provable bound; overflow sets a fault bit, which fails the run)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     spec, hid, bytes_per_step, env_id = make_workload(args.workload)
