@@ -7,7 +7,10 @@ constructing an env without the built library or without a CUDA device raises.
 from .spec import ENV_IDS, EnvSpec, make_spec  # noqa: F401
 from .tables import TopologyTables, tables_from_topology  # noqa: F401
 
-__all__ = ["ENV_IDS", "EnvSpec", "make_spec", "TopologyTables", "tables_from_topology", "make", "register_all"]
+from .topology_builder import build_from_file, build_tables  # noqa: F401
+
+__all__ = ["ENV_IDS", "EnvSpec", "make_spec", "TopologyTables", "tables_from_topology", "build_from_file", "build_tables",
+           "make", "register_all"]
 
 
 def make(env_id, **kwargs):

@@ -47,6 +47,10 @@ def _as_tables(topology) -> TopologyTables:
     if isinstance(topology, TopologyTables):
         return topology
     if isinstance(topology, str):
+        if topology.endswith((".txt", ".xml")):  # a raw topology file: build the tables here (k via k_paths=)
+            from .topology_builder import build_from_file
+
+            return build_from_file(topology)
         return TopologyTables.load(topology)
     return tables_from_topology(topology)
 

@@ -110,3 +110,27 @@ def build_phy_tables(tables: TopologyTables, modulation_level, connections_detai
         gsnr=np.ascontiguousarray(gs[:, :channels, :k]),
         cut_links=cut_links, cut_count=cut_count,
     )
+
+
+def load_qot_mat(path: str, key: str = None):
+    """The precomputed QoT tables of a MATLAB ``Results_*.mat`` file as the reference's drivers unpack them
+    (tests/test_rmsa_us.py:43-49): the struct ``mat[key][0][0]`` holds ``connections_detail`` (field 0),
+    ``modulation_level`` (field 1, uint8 ``[pairs][channels][paths]``) and ``gsnr`` (field 2, f64).  ``key``
+    defaults to the file's stem (``Results_K3SP_FRP_SLC_CBG_USB14``).  Returns a dict with the three
+    constructor kwargs of PhyRMSA-v0 (phy_rmsa_env.py:51-53); the modulation levels are widened to int64
+    so that sums and sort keys cannot wrap in uint8, the node columns of
+    ``connections_detail`` are unwrapped to plain integers."""
+    import os
+
+    from scipy.io import loadmat
+
+    if key is None:
+        key = os.path.splitext(os.path.basename(path))[0]
+    mat = loadmat(path)
+    if key not in mat:
+        raise KeyError(f"{path}: no variable {key!r} (have {sorted(k for k in mat if not k.startswith('__'))})")
+    d = mat[key][0][0]
+    conn = d[0]
+    conn2 = np.array([[_scalar(conn[r, c]) for c in (0, 1)] for r in range(conn.shape[0])], np.int32)
+    return dict(connections_detail=conn2, modulation_level=np.asarray(d[1]).astype(np.int64),
+                gsnr=np.ascontiguousarray(np.asarray(d[2], np.float64)))
