@@ -222,6 +222,8 @@ class BatchedEnv:
             "total_path_length": st[:, 0] / (st[:, 5] + 1), "avrage_gsnr": st[:, 1] / (st[:, 4] + 1),
             "average_mod_level": st[:, 3] / (st[:, 4] + 1), "average_path_index": st[:, 2] / (st[:, 5] + 1),
             "path_index": st[:, 2], "physical_paths": st[:, 5],
+            # defrag_period=None (the only mode built): the reference's move counters stay 0
+            "num_moves": st[:, 0] * 0.0, "num_moves_groom": st[:, 0] * 0.0, "num_defrag_cycle": st[:, 0] * 0.0,
         }
 
     def available_channels(self):
