@@ -75,6 +75,7 @@ WORKLOADS["c4_phyrmsa_us14_320"] = ("PhyRMSA-v0", "us14", dict(load=1400, mean_s
                                                                episode_length=200, number_spectrum_channels=160,
                                                                s_band=False),
                                     S.H_PHY_BM_FA_CUT, S.OBS_PHY_CUTS, 1426)
+GSNR_WORKLOADS = {"c3_rmcsa_jpn12_320"}
 DEFAULT_WORKLOAD = "c2_deeprmsa_nsfnet_100"
 PREROLL = 600  # steps run before any timing so that the networks are in steady state
 PREROLL_OF = {"c4_phyrmsa_us14_320": 6000, "c3_rmcsa_jpn12_320": 1500}  # loads of 1400 / 250 Erlang fill up slowly
@@ -178,12 +179,14 @@ def host_policy_kspff(obs_fm, n_nodes, k, j, out=None):
     return out
 
 
-def cpu_arm(spec, hid, n_sample, min_seconds, threads, steps=None, warmup=0, preroll=PREROLL):
+def cpu_arm(spec, hid, n_sample, min_seconds, threads, steps=None, warmup=0, preroll=PREROLL, gsnr=False):
     """Times the oracle port on host threads.  Returns (steps/s, ms per pass, passes)."""
     import oracle_binding as OB
 
     pool = OB.OraclePool(spec, 0, n_sample)
     pool.rollout(preroll, hid, threads)
+    if gsnr:  # the GN model for every decision, like the GPU arm's orlg_gsnr_for_actions launch
+        pool.set_gsnr(S.gsnr_params(spec.tables, spec.channel_width))
     for _ in range(warmup):
         pool.rollout(1, hid, threads)
     done_steps, passes = 0, 0
@@ -211,7 +214,7 @@ def run_reference(args, spec, hid, env_id, wl):
     n_sample = args.ref_envs
     PREROLL = PREROLL_OF.get(wl, 600)
     v, ms, passes, blocking = cpu_arm(spec, hid, n_sample, 0, threads, steps=args.steps, warmup=args.warmup,
-                                      preroll=PREROLL)
+                                      preroll=PREROLL, gsnr=wl in GSNR_WORKLOADS and not args.no_gsnr)
     sample = (f"{n_sample} envs of the {args.envs}-env batch per pass, oracle C port (oracle/orlg_oracle.c) "
               f"with its own heuristic, {threads} pthreads, {PREROLL} pre-roll steps")
     line = {
@@ -261,6 +264,12 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
             dist.barrier()
         torch.cuda.synchronize()
 
+    # BASELINE configs[2] "QoT-aware RMCSA with GN-model GSNR": every decision's candidate lightpath and its
+    # neighbours are evaluated with the GN model (orlg_gsnr_for_actions on the action tensor, one more launch)
+    gs_out = None
+    if wl in GSNR_WORKLOADS and not args.no_gsnr:
+        eng.gsnr_configure()
+        gs_out = torch.zeros((n_env, 2), dtype=torch.float64, device=dev)
     fused = not args.two_launch
     eng.heuristic(hid, act)  # action for the first pending request
     if fused:  # every step also writes the heuristic's action for the next request into `act`
@@ -273,16 +282,22 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
             evs[0].record()
         if not fused:
             eng.heuristic(hid, act)
+            if gs_out is not None:
+                eng.gsnr_for_actions(act, gs_out)
         if evs is not None:
             evs[1].record()
         eng.step(act, rew, done, obs, None)
         if evs is not None:
             evs[2].record()
+        if fused and gs_out is not None:  # the hint is the action for the request that has just become pending
+            eng.gsnr_for_actions(act, gs_out)
+        if evs is not None:
+            evs[3].record()
 
     for _ in range(args.warmup):
         one_step()
     K = args.steps
-    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K)]
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(K)]
     sampler = ClockSampler(local)
     barrier()
     if rank == 0:
@@ -293,8 +308,11 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
         one_step(evs[t])
     barrier()
     launches = eng.launch_count - launches0
-    step_ms = sum(e[0].elapsed_time(e[2]) for e in evs)
+    step_ms = sum(e[0].elapsed_time(e[3]) for e in evs)
     kern_ms = sum(e[1].elapsed_time(e[2]) for e in evs)
+    gsnr_ms = sum(e[2].elapsed_time(e[3]) for e in evs) if (fused and gs_out is not None) else None
+    if gs_out is not None and not bool(torch.isfinite(gs_out[:, 0]).any()):
+        raise RuntimeError("GSNR evaluation produced no finite value")
 
     # warm-L2 variant (what a training loop sees when the state fits L2): one event pair around K steps
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -316,11 +334,11 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
         for _ in range(3):
             one_step()
         barrier()
-        ev2 = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K)]
+        ev2 = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(K)]
         for t in range(K):
             one_step(ev2[t])
         barrier()
-        two_ms = sum(e[0].elapsed_time(e[2]) for e in ev2)
+        two_ms = sum(e[0].elapsed_time(e[3]) for e in ev2)
         fused = True
         eng.heuristic(hid, act)
         eng.set_next_action_hint(hid, act)
@@ -337,6 +355,7 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
     h_act = torch.zeros((n_env, eng.action_dim), dtype=torch.int32).pin_memory()
     h_rew = torch.zeros(n_env, dtype=torch.int32).pin_memory()
     h_done = torch.zeros(n_env, dtype=torch.uint8).pin_memory()
+    h_gs = torch.zeros((n_env, 2), dtype=torch.float64).pin_memory() if gs_out is not None else None
     use_obs_policy = env_id == "DeepRMSA-v0" and eng.obs_dim > 0
     h_obs = None
     if eng.obs_dim:
@@ -359,6 +378,10 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
                 eng.heuristic(hid, act)
             h_act.copy_(act)
         eng.step_host(h_act, h_rew, h_done, h_obs, None)
+        if gs_out is not None:
+            if fused:
+                eng.gsnr_for_actions(act, gs_out)
+            h_gs.copy_(gs_out)  # synchronous D2H of the step's GSNR values
         return int(h_rew.numpy()[0])
 
     eng.heuristic(hid, act)  # the rollout above moved the envs on: refresh the pending actions
@@ -441,6 +464,7 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
         pcie_gbs = 20 * h_obs.numel() * h_obs.element_size() / (e0.elapsed_time(e1) * 1e-3) / 1e9
     h2d = h_act.numel() * 4
     d2h = h_rew.numel() * 4 + h_done.numel() + (h_obs.numel() * h_obs.element_size() if h_obs is not None else 0)
+    d2h += h_gs.numel() * 8 if h_gs is not None else 0
 
     # ---- episode statistics: the only collective on this path (NCCL all-reduce, off the step path) ----
     cnt = eng.counters()
@@ -487,6 +511,8 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
                      else "orlg_heuristic + orlg_step (2 launches)") + ", actions/obs/reward/done resident in HBM",
             "l2": ("flushed before every step by a 256 MiB fill outside the per-step event pairs"
                    if not args.no_flush else "not flushed (state may be L2 resident)"),
+            "qot": ("GN-model GSNR of every decision's candidate and its neighbours (orlg_gsnr_for_actions, +1 launch)"
+                    if gs_out is not None else "as the env defines it (tables / reach / crosstalk gate), no GN-model launch"),
             "preroll_steps": PREROLL, "parallelism": f"envs sharded x{world}, no data-path collective",
             "blocking": 1.0 - stats[1] / max(1, stats[0]), "episodes": stats[4],
         },
@@ -505,11 +531,13 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
         "extra": {"two_launch_env_steps_per_s": (total_envs * K / (two_ms * 1e-3)) if two_ms else None,
                   "warm_l2_env_steps_per_s": total_envs * K / (warm_ms * 1e-3),
                   "fused_rollout_env_steps_per_s": total_envs * K / (roll_ms * 1e-3),
+                  "gsnr_kernel_us": (gsnr_ms * 1e3 / K) if gsnr_ms is not None else None,
                   "hbm_bytes_per_gpu": eng.hbm_bytes},
     }
     if world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
-        v, ms, passes, blk = cpu_arm(spec, hid, args.ref_envs, args.cpu_seconds, threads, preroll=PREROLL)
+        v, ms, passes, blk = cpu_arm(spec, hid, args.ref_envs, args.cpu_seconds, threads, preroll=PREROLL,
+                                     gsnr=gs_out is not None)
         line["cpu_baseline"] = {
             "value": v, "unit": "env-steps/s", "cores": threads, "kind": "port",
             "sample": (f"{args.ref_envs} envs x {passes} steps of the same workload (blocking {blk:.3f}), oracle C port "
@@ -535,6 +563,7 @@ def main():
     ap.add_argument("--e2e-serial", action="store_true", help="no two-half pipelining of the e2e loop")
     ap.add_argument("--two-launch", action="store_true", help="orlg_heuristic + orlg_step instead of the fused hint")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-gsnr", action="store_true", help="c3 only: skip the per-decision GN-model launch")
     ap.add_argument("--heap-capacity", type=int, default=0,
                     help="release-queue entries per env (0 = the provable bound; overflow sets a fault bit, which fails the run)")
     args = ap.parse_args()

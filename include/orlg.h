@@ -311,6 +311,14 @@ int orlg_gsnr_configure(orlg_engine* e, const orlg_gsnr_params* params);
  * A query with path < 0 or path >= k_paths yields NaN in both. */
 int orlg_gsnr(orlg_engine* e, const int32_t* dev_query, double* dev_out, void* stream);
 
+/* The same two values for the candidate a step action describes: dev_actions is an action tensor in the
+ * env's own format for the pending request - RMSA-v0 int32[num_envs][2] (path, first slot) with the path's
+ * best modulation, RMCSA-v0 int32[num_envs][4] (path, modulation, core, first slot) - e.g. what
+ * orlg_heuristic or the fused next-action hint wrote; the slot count is get_number_slots of the pending
+ * bit rate (rmsa_env.py:708-719, rmcsa_env.py:753-765).  A rejection action yields NaN.  This is how the
+ * QoT-aware RMCSA configuration evaluates the GN model for every decision without a host round trip. */
+int orlg_gsnr_for_actions(orlg_engine* e, const int32_t* dev_actions, double* dev_out, void* stream);
+
 /* kernels launched by this engine so far (bench.py "gpu_launches") */
 int64_t orlg_launch_count(const orlg_engine* e);
 

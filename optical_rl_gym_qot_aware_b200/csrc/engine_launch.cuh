@@ -61,6 +61,10 @@ static cudaError_t launch_info(const LaunchGeom& g, const Params& p, const StepI
 #ifdef ORLG_INSTANTIATE_W
 template <int W>
 cudaError_t launch_w(const LaunchGeom& g, const Params& p, const StepIO& io, cudaStream_t st) {
+#ifdef ORLG_FAST_AB  // A/B builds (tools/build_variant_w4.sh): only the staged 128-env tile without info_stats
+  if (g.info || g.direct || g.BD != 128) return cudaErrorNotSupported;
+  return launch_m<W, 128, false>(g, p, io, st);
+#endif
   if (g.info) return g.direct ? launch_info<W, DIRECT_CTA, true>(g, p, io, st) : launch_info<W, 128, false>(g, p, io, st);
   if (g.direct) return launch_m<W, DIRECT_CTA, false, true>(g, p, io, st);
   switch (g.BD) {

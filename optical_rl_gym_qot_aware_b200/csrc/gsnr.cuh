@@ -91,22 +91,47 @@ __device__ double gsnr_target(const Params& p, const GsnrParams& g, const ulongl
   return 10.0 * log10(1.0 / acc);
 }
 
+// FROM_ACTION = false: `query` holds explicit candidates (path | core << 16, first slot, slots, se or 0).
+// FROM_ACTION = true : `query` holds the env's own step actions for the pending request — RMSA-v0 (path, first slot)
+// with the path's best modulation, RMCSA-v0 (path, modulation, core, first slot) — and the slot count comes from
+// the pending bit rate through get_number_slots, so a heuristic's (or the fused hint's) action tensor can be
+// evaluated as it is, without a host round trip.
+template <bool FROM_ACTION>
 __global__ void __launch_bounds__(128) gsnr_kernel(const Params p, const GsnrParams g, const int* __restrict__ query,
                                                    double* __restrict__ out) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= p.num_envs) return;
   const int e = warp;
-  const int4 q = reinterpret_cast<const int4*>(query)[e];
-  const int path = q.x & 0xFFFF, core = q.x >> 16;
   const double nan = __longlong_as_double(0x7FF8000000000000ll), inf = __longlong_as_double(0x7FF0000000000000ll);
   uint32_t m = p.meta[e];
   const int pair = (int)((m >> 16) & 0xFFu) * p.n_nodes + (int)(m >> 24);
+  int4 q;
+  int mod = -1;
+  if (FROM_ACTION) {
+    if (p.action_dim == 2) {
+      int2 a = reinterpret_cast<const int2*>(query)[e];
+      q = make_int4(a.x, a.y, 0, 0);
+    } else {
+      int4 a = reinterpret_cast<const int4*>(query)[e];
+      mod = a.y;
+      q = make_int4((a.x & 0xFFFF) | (a.z << 16), a.w, 0, 0);
+      if (a.x < 0 || a.x >= p.k || a.z < 0 || a.z >= p.cores || mod < 0 || mod >= p.n_mods) q.x = -1;
+    }
+  } else {
+    q = reinterpret_cast<const int4*>(query)[e];
+  }
+  const int path = q.x & 0xFFFF, core = q.x >> 16;
   PathRec crec{};
-  bool ok = q.x >= 0 && path < p.k && core < p.cores && q.y >= 0 && q.z >= 1 && q.y + q.z <= p.S;
+  bool ok = q.x >= 0 && path < p.k && core < p.cores;
   if (ok) {
     crec = load_path(p, pair, path);
     ok = crec.hops() > 0;
   }
+  if (ok && FROM_ACTION) {
+    q.w = mod >= 0 ? __ldg(p.mod_se + mod) : crec.se();
+    q.z = number_slots((int)(m & 0xFFFFu), q.w, p);
+  }
+  ok = ok && q.y >= 0 && q.z >= 1 && q.y + q.z <= p.S;
   if (!ok) {
     if (lane == 0) out[2 * (size_t)e] = out[2 * (size_t)e + 1] = nan;
     return;

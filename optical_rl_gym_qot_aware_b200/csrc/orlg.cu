@@ -637,8 +637,27 @@ extern "C" int orlg_gsnr(orlg_engine* e, const int32_t* dev_query, double* dev_o
   }
   cudaSetDevice(e->device);
   const int warps_per_cta = 4;
-  gsnr_kernel<<<(e->p.num_envs + warps_per_cta - 1) / warps_per_cta, warps_per_cta * 32, 0, (cudaStream_t)stream>>>(
+  gsnr_kernel<false><<<(e->p.num_envs + warps_per_cta - 1) / warps_per_cta, warps_per_cta * 32, 0, (cudaStream_t)stream>>>(
       e->p, e->gp, dev_query, dev_out);
+  CK(cudaGetLastError());
+  e->launches++;
+  return ORLG_OK;
+}
+
+extern "C" int orlg_gsnr_for_actions(orlg_engine* e, const int32_t* dev_actions, double* dev_out, void* stream) {
+  if (!e || !dev_actions || !dev_out) return ORLG_EINVAL;
+  if (!e->gsnr_ready) {
+    e->err = "orlg_gsnr_for_actions before orlg_gsnr_configure";
+    return ORLG_ESTATE;
+  }
+  if (e->p.kind != ORLG_ENV_RMSA && e->p.kind != ORLG_ENV_RMCSA) {
+    e->err = "orlg_gsnr_for_actions takes RMSA-v0 (path, slot) or RMCSA-v0 (path, modulation, core, slot) actions";
+    return ORLG_ESTATE;
+  }
+  cudaSetDevice(e->device);
+  const int warps_per_cta = 4;
+  gsnr_kernel<true><<<(e->p.num_envs + warps_per_cta - 1) / warps_per_cta, warps_per_cta * 32, 0, (cudaStream_t)stream>>>(
+      e->p, e->gp, dev_actions, dev_out);
   CK(cudaGetLastError());
   e->launches++;
   return ORLG_OK;

@@ -33,7 +33,7 @@ EXPORTS = (
     "orlg_action_dim", "orlg_obs_dim", "orlg_state_words", "orlg_hbm_bytes", "orlg_load_trace",
     "orlg_reset", "orlg_step", "orlg_step_host", "orlg_set_obs_layout", "orlg_observation",
     "orlg_heuristic", "orlg_rollout", "orlg_get_counters", "orlg_export_state", "orlg_get_requests",
-    "orlg_launch_count", "orlg_gsnr_configure", "orlg_gsnr", "orlg_phy_get_stats", "orlg_path_first_fit", "orlg_set_next_action_hint", "orlg_step_host_async", "orlg_step_host_wait",
+    "orlg_launch_count", "orlg_gsnr_configure", "orlg_gsnr", "orlg_gsnr_for_actions", "orlg_phy_get_stats", "orlg_path_first_fit", "orlg_set_next_action_hint", "orlg_step_host_async", "orlg_step_host_wait",
     "orlg_phy_get_channel_state", "orlg_info_dim", "orlg_set_info_output",
 )
 
@@ -107,6 +107,7 @@ def load_library():
         L.orlg_get_requests.argtypes = [vp, vp, vp]
         L.orlg_gsnr_configure.argtypes = [vp, C.POINTER(OrlgGsnrParams)]
         L.orlg_gsnr.argtypes = [vp, vp, vp, vp]
+        L.orlg_gsnr_for_actions.argtypes = [vp, vp, vp, vp]
         L.orlg_phy_get_stats.argtypes = [vp, vp, vp]
         L.orlg_phy_get_channel_state.argtypes = [vp, vp, i32, vp, vp]
         L.orlg_info_dim.argtypes = [vp]
@@ -353,6 +354,17 @@ class Engine:
         if out is None:
             out = torch.empty((self.num_envs, 2), dtype=torch.float64, device=self.device)
         self._ck(self.L.orlg_gsnr(self.h, self._p(query), self._p(out), self._stream()))
+        return out
+
+    def gsnr_for_actions(self, actions, out=None):
+        """actions: int32 device tensor in the env's own action format (RMSA-v0 [num_envs, 2], RMCSA-v0
+        [num_envs, 4]) for the pending requests.  Returns f64 [num_envs, 2] like :meth:`gsnr`."""
+        torch = self.torch
+        assert actions.dtype == torch.int32 and actions.is_cuda and actions.is_contiguous()
+        assert actions.numel() == self.num_envs * self.action_dim
+        if out is None:
+            out = torch.empty((self.num_envs, 2), dtype=torch.float64, device=self.device)
+        self._ck(self.L.orlg_gsnr_for_actions(self.h, self._p(actions), self._p(out), self._stream()))
         return out
 
     @property

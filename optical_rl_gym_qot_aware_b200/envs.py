@@ -43,14 +43,14 @@ HEURISTICS = {
 }
 
 
-def _as_tables(topology) -> TopologyTables:
+def _as_tables(topology, k_paths: Optional[int] = None) -> TopologyTables:
     if isinstance(topology, TopologyTables):
         return topology
     if isinstance(topology, str):
         if topology.endswith((".txt", ".xml")):  # a raw topology file: build the tables here (k via k_paths=)
             from .topology_builder import build_from_file
 
-            return build_from_file(topology)
+            return build_from_file(topology, k_paths=5 if k_paths is None else int(k_paths))
         return TopologyTables.load(topology)
     return tables_from_topology(topology)
 
@@ -98,7 +98,7 @@ class BatchedEnv:
 
         self.torch = torch
         self.env_id = env_id
-        tables = _as_tables(topology)
+        tables = _as_tables(topology, kwargs.pop("k_paths", None))  # k_paths only matters for raw topology files
         kind = S.ENV_IDS[env_id]
         obs_kind = None
         if kind == S.ENV_PHYRMSA and observation in ("info", "cuts"):

@@ -117,6 +117,9 @@ def lib():
         L.oracle_pool_env.argtypes = [C.c_void_p, C.c_int64]
         L.oracle_pool_reward_sum.restype = C.c_int64
         L.oracle_pool_reward_sum.argtypes = [C.c_void_p]
+        L.oracle_pool_set_gsnr.argtypes = [C.c_void_p, C.c_void_p]
+        L.oracle_pool_gsnr_sum.restype = C.c_double
+        L.oracle_pool_gsnr_sum.argtypes = [C.c_void_p]
         L.oracle_phy_stats.argtypes = [C.c_void_p, C.c_void_p]
         L.oracle_phy_channel_state.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
         L.oracle_phy_channel_state.restype = C.c_int64
@@ -326,6 +329,22 @@ class OraclePool:
 
     def rollout(self, nsteps: int, heuristic_id: int, threads: int) -> int:
         return int(self.L.oracle_pool_rollout(self.h, nsteps, heuristic_id, threads))
+
+    def set_gsnr(self, gp):
+        """Evaluate calculate_osnr for every decision of the following rollouts (gp: spec.GsnrParams or None)."""
+        if gp is None:
+            self._gs = None
+            self.L.oracle_pool_set_gsnr(self.h, None)
+            return
+        cnt = np.ascontiguousarray(gp.span_count, np.int32)
+        ln = np.ascontiguousarray(gp.span_length_km, np.float64)
+        c = OracleGsnrParams(gp.launch_power_w, gp.attenuation_per_m, gp.noise_figure_lin, gp.f0_hz, gp.slot_hz,
+                             cnt.ctypes.data, ln.ctypes.data)
+        self._gs = (cnt, ln, c)  # keep the buffers alive
+        self.L.oracle_pool_set_gsnr(self.h, C.byref(c))
+
+    def gsnr_sum(self) -> float:
+        return float(self.L.oracle_pool_gsnr_sum(self.h))
 
     def counters(self):
         out = np.zeros((self.n_envs, 12), np.int64)

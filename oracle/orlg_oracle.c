@@ -1187,6 +1187,8 @@ struct oracle_pool {
   int64_t next;
   int nsteps, hid;
   int64_t reward_sum;
+  const oracle_gsnr_params* gsnr; /* non-NULL: evaluate calculate_osnr for every decision (bench C3 arm) */
+  double gsnr_sum;
 };
 
 oracle_pool* oracle_pool_create(const oracle_config* cfg, int64_t env0, int64_t n_envs) {
@@ -1207,9 +1209,11 @@ void oracle_pool_destroy(oracle_pool* p) {
   free(p);
 }
 
+static pthread_mutex_t pool_sum_lock = PTHREAD_MUTEX_INITIALIZER;
 static void* pool_worker(void* arg) {
   oracle_pool* p = (oracle_pool*)arg;
   int64_t rs = 0;
+  double gs = 0.0;
   double obs[1024];
   for (;;) {
     int64_t i = __atomic_fetch_add(&p->next, 1, __ATOMIC_RELAXED);
@@ -1219,13 +1223,39 @@ static void* pool_worker(void* arg) {
     uint8_t d;
     for (int t = 0; t < p->nsteps; t++) {
       oracle_heuristic(e, p->hid, a);
+      if (p->gsnr && (e->c.env_kind == 0 || e->c.env_kind == 2)) {
+        /* the candidate the action describes, slot count from the pending bit rate (get_number_slots) */
+        int path = a[0], k = e->c.k_paths;
+        if (path >= 0 && path < k) {
+          int pair = e->cur.src * e->c.n_nodes + e->cur.dst, q[4];
+          double o2[2];
+          if (e->c.env_kind == 0) {
+            int se = e->c.path_se[(size_t)pair * k + path];
+            q[0] = path; q[1] = a[1]; q[2] = number_slots(e, se); q[3] = se;
+          } else {
+            int se = e->c.mod_se[a[1]];
+            q[0] = path | (a[2] << 16); q[1] = a[3]; q[2] = number_slots(e, se); q[3] = se;
+          }
+          oracle_gsnr(e, p->gsnr, q, o2);
+          if (o2[0] == o2[0]) gs += o2[0];
+        }
+      }
       oracle_step(e, a, &r, &d, e->c.env_kind == 1 ? obs : NULL, NULL);
       rs += r;
     }
   }
   __atomic_fetch_add(&p->reward_sum, rs, __ATOMIC_RELAXED);
+  if (p->gsnr) {
+    pthread_mutex_lock(&pool_sum_lock);
+    p->gsnr_sum += gs;
+    pthread_mutex_unlock(&pool_sum_lock);
+  }
   return NULL;
 }
+
+/* evaluate the GN model for every decision of the pool's rollouts (NULL switches it off); g must outlive them */
+void oracle_pool_set_gsnr(oracle_pool* p, const oracle_gsnr_params* g) { p->gsnr = g; }
+double oracle_pool_gsnr_sum(const oracle_pool* p) { return p->gsnr_sum; }
 
 int64_t oracle_pool_rollout(oracle_pool* p, int nsteps, int hid, int threads) {
   p->next = 0;

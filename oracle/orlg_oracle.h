@@ -133,6 +133,9 @@ void oracle_pool_destroy(oracle_pool* p);
 int64_t oracle_pool_rollout(oracle_pool* p, int nsteps, int heuristic_id, int threads);
 oracle_env* oracle_pool_env(oracle_pool* p, int64_t i);
 int64_t oracle_pool_reward_sum(const oracle_pool* p);
+/* pool rollouts that also evaluate the GN model for every decision's candidate (RMSA-v0 / RMCSA-v0 actions) */
+void oracle_pool_set_gsnr(oracle_pool* p, const oracle_gsnr_params* g);
+double oracle_pool_gsnr_sum(const oracle_pool* p);
 
 /* deterministic RNG pieces, exposed for tests */
 void oracle_philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,

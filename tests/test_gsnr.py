@@ -128,3 +128,48 @@ def test_engine_gsnr_matches_oracle_on_philox_envs():
             checked += 1
     assert checked >= 20
     eng.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("env_id", ["RMSA-v0", "RMCSA-v0"])
+def test_gsnr_for_actions_equals_explicit_queries(env_id):
+    """orlg_gsnr_for_actions on the heuristic's own action tensor == orlg_gsnr on the queries built on the
+    host from the same actions (slot count from the pending bit rate, rmsa_env.py:708-719 /
+    rmcsa_env.py:753-765): bit-identical outputs, NaN for rejections."""
+    import torch
+
+    from optical_rl_gym_qot_aware_b200.engine import Engine
+
+    if env_id == "RMSA-v0":
+        spec = S.make_spec(env_id, G.topology("spn"), seed=5, load=300, mean_service_holding_time=25,
+                           num_spectrum_resources=320, episode_length=500)
+        hid = S.H_SAP_FF
+    else:
+        spec = S.make_spec(env_id, G.topology("jpn12_k5"), seed=5, load=250, mean_service_holding_time=25,
+                           num_spectrum_resources=320, num_spatial_resources=7, worst_xt=-84.7, episode_length=500)
+        hid = S.H_SAP_BM_FC_FF
+    n_env = 300
+    eng = Engine(spec, n_env)
+    eng.gsnr_configure()
+    eng.reset(True)
+    eng.rollout(hid, 400)
+    act = torch.zeros((n_env, eng.action_dim), dtype=torch.int32, device=eng.device)
+    eng.heuristic(hid, act)
+    a = act.cpu().numpy()
+    a[::17, 0] = spec.tables.k_paths  # a few rejection actions
+    rq, t = eng.requests(), spec.tables
+    q = np.full((n_env, 4), -1, np.int32)
+    for i in range(n_env):
+        if a[i, 0] >= t.k_paths:
+            continue
+        pr = rq["src"][i] * t.n_nodes + rq["dst"][i]
+        if env_id == "RMSA-v0":
+            se, core, start = int(t.path_se[pr, a[i, 0]]), 0, a[i, 1]
+        else:
+            se, core, start = int(t.mod_se[a[i, 1]]), a[i, 2], a[i, 3]
+        q[i] = (a[i, 0] | (core << 16), start, int(np.ceil(rq["bit_rate"][i] / (se * spec.channel_width))) + 1, se)
+    want = eng.gsnr(torch.from_numpy(q).to(eng.device)).cpu().numpy()
+    got = eng.gsnr_for_actions(torch.from_numpy(a).to(eng.device)).cpu().numpy()
+    assert np.isnan(got[::17]).all() and np.isfinite(got[:, 0]).sum() >= n_env // 2
+    assert np.array_equal(got, want, equal_nan=True)
+    eng.close()

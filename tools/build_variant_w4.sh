@@ -6,7 +6,7 @@ name=$1; shift
 cd /root/repo/optical_rl_gym_qot_aware_b200/csrc
 mkdir -p /root/repo/build/variants
 obj=/root/repo/build/variants/orlg_w4_$name.o
-nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo --fmad=false -std=c++17 -Xcompiler -fPIC "$@" -c -o $obj orlg_w4.cu
+nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo --fmad=false -std=c++17 -Xcompiler -fPIC -DORLG_FAST_AB "$@" -c -o $obj orlg_w4.cu
 others=$(ls /root/repo/build/*.o | grep -v "/orlg_w4.o")
 nvcc -gencode arch=compute_100a,code=sm_100a -shared -o /root/repo/build/variants/liborlg_$name.so $obj $others
 ls -la /root/repo/build/variants/liborlg_$name.so
