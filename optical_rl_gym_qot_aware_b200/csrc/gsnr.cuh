@@ -26,6 +26,8 @@ struct GsnrParams {
   double P, alpha, nf, f0, slot_hz;
   const int* span_count;
   const double* span_km;
+  const ulonglong2* path_mask;  // [N*N*k] links of every path as a bit set (fast kernel; null when E > 128)
+  const double4* link_c;        // [E] (l_eff, l_eff / L, exp(2 a L) - 1, span count)
 };
 
 __device__ __forceinline__ bool path_has_link(const PathRec& r, int link) {
@@ -91,21 +93,15 @@ __device__ double gsnr_target(const Params& p, const GsnrParams& g, const ulongl
   return 10.0 * log10(1.0 / acc);
 }
 
-// FROM_ACTION = false: `query` holds explicit candidates (path | core << 16, first slot, slots, se or 0).
-// FROM_ACTION = true : `query` holds the env's own step actions for the pending request — RMSA-v0 (path, first slot)
-// with the path's best modulation, RMCSA-v0 (path, modulation, core, first slot) — and the slot count comes from
-// the pending bit rate through get_number_slots, so a heuristic's (or the fused hint's) action tensor can be
-// evaluated as it is, without a host round trip.
+// Candidate of env e: explicit query (path | core << 16, first slot, slots, se or 0), or — FROM_ACTION — the env's
+// own step action for the pending request: RMSA-v0 (path, first slot) with the path's best modulation, RMCSA-v0
+// (path, modulation, core, first slot); the slot count then comes from the pending bit rate through
+// get_number_slots, so a heuristic's (or the fused hint's) action tensor is evaluated as it is.
 template <bool FROM_ACTION>
-__global__ void __launch_bounds__(128) gsnr_kernel(const Params p, const GsnrParams g, const int* __restrict__ query,
-                                                   double* __restrict__ out) {
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (warp >= p.num_envs) return;
-  const int e = warp;
-  const double nan = __longlong_as_double(0x7FF8000000000000ll), inf = __longlong_as_double(0x7FF0000000000000ll);
+__device__ __forceinline__ bool resolve_candidate(const Params& p, const int* __restrict__ query, int e, int4& q,
+                                                  PathRec& crec, int& pair) {
   uint32_t m = p.meta[e];
-  const int pair = (int)((m >> 16) & 0xFFu) * p.n_nodes + (int)(m >> 24);
-  int4 q;
+  pair = (int)((m >> 16) & 0xFFu) * p.n_nodes + (int)(m >> 24);
   int mod = -1;
   if (FROM_ACTION) {
     if (p.action_dim == 2) {
@@ -121,7 +117,6 @@ __global__ void __launch_bounds__(128) gsnr_kernel(const Params p, const GsnrPar
     q = reinterpret_cast<const int4*>(query)[e];
   }
   const int path = q.x & 0xFFFF, core = q.x >> 16;
-  PathRec crec{};
   bool ok = q.x >= 0 && path < p.k && core < p.cores;
   if (ok) {
     crec = load_path(p, pair, path);
@@ -131,11 +126,26 @@ __global__ void __launch_bounds__(128) gsnr_kernel(const Params p, const GsnrPar
     q.w = mod >= 0 ? __ldg(p.mod_se + mod) : crec.se();
     q.z = number_slots((int)(m & 0xFFFFu), q.w, p);
   }
-  ok = ok && q.y >= 0 && q.z >= 1 && q.y + q.z <= p.S;
-  if (!ok) {
+  return ok && q.y >= 0 && q.z >= 1 && q.y + q.z <= p.S;
+}
+
+// Generic kernel (any number of links): lanes take targets round-robin, every target rescans the env's services
+// per hop.  Kept for topologies with more than 128 links; everything else runs gsnr_kernel_fast below.
+template <bool FROM_ACTION>
+__global__ void __launch_bounds__(128) gsnr_kernel_generic(const Params p, const GsnrParams g, const int* __restrict__ query,
+                                                           double* __restrict__ out) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= p.num_envs) return;
+  const int e = warp;
+  const double nan = __longlong_as_double(0x7FF8000000000000ll), inf = __longlong_as_double(0x7FF0000000000000ll);
+  int4 q;
+  PathRec crec{};
+  int pair;
+  if (!resolve_candidate<FROM_ACTION>(p, query, e, q, crec, pair)) {
     if (lane == 0) out[2 * (size_t)e] = out[2 * (size_t)e + 1] = nan;
     return;
   }
+  const int core = q.x >> 16;
   const Chan cch = chan_of(g, q.y, q.z, q.w > 0 ? q.w : crec.se());
   const ulonglong2* heap = p.heap + (size_t)e * p.heap_stride + HEAP_PAD;
   const int n_act = p.heap_len[e];
@@ -159,6 +169,181 @@ __global__ void __launch_bounds__(128) gsnr_kernel(const Params p, const GsnrPar
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) mine = fmin(mine, __shfl_xor_sync(0xFFFFFFFFu, mine, o));
   if (lane == 0) out[2 * (size_t)e + 1] = mine;
+}
+
+// ---- fast kernel -------------------------------------------------------------------------------------------
+// Static tables built once by gsnr_init_tables (orlg_gsnr_configure):
+//   path_mask[pair*k + path]  the links of a path as a 128-bit set, so "does service i use link l" and "do two
+//                             paths share a link" are bit tests instead of loops over path records;
+//   link_c[l] = (l_eff, l_eff / L, exp(2 a L) - 1, span count), the per-link factors of calculate_osnr.py:25,51.
+// The warp of an env walks its targets one at a time (the candidate, then every running service that shares a
+// link and core with it).  For one target the 32 lanes (1) scan the env's services 32 at a time and queue the
+// ones that interfere (same core, at least one common link) by ballot compaction, (2) whenever 32 are queued
+// evaluate their cross-channel terms with one lane per interferer — the two asinh of calculate_osnr.py:36-44 do
+// not depend on the link, only the last term scales with l_eff / L — and (3) lane h < hops adds, in service
+// order, the terms of the interferers present on the target's hop h.  Summation order per link is the order of
+// the services in the release heap, as in the generic kernel: results are bit-identical to it.
+constexpr int GS_WARPS = 4;
+struct GsnrWarpSmem {
+  double A[32], X[32];
+  unsigned hopmask[32];
+  unsigned queue[64];
+  int tlink[32];  // links of the current target, hop order
+};
+
+__global__ void gsnr_init_tables(const Params p, const GsnrParams g, int npaths, ulonglong2* path_mask, double4* link_c) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < npaths) {
+    PathRec r = load_path(p, i / p.k, i % p.k);
+    unsigned long long lo = 0ull, hi = 0ull;
+    for (int h = 0; h < r.hops(); h++) {
+      int l = r.link(h);
+      if (l < 64) lo |= 1ull << l;
+      else hi |= 1ull << (l & 63);
+    }
+    path_mask[i] = make_ulonglong2(lo, hi);
+  }
+  if (i < p.E) {
+    const double a = g.alpha, L = g.span_km[i] * 1e3;
+    const double l_eff = (1.0 - exp(-2.0 * a * L)) / (2.0 * a);
+    link_c[i] = make_double4(l_eff, l_eff / L, exp(2.0 * a * L) - 1.0, (double)g.span_count[i]);
+  }
+}
+
+__device__ __forceinline__ bool mask_has(ulonglong2 m, int l) { return (((l < 64) ? m.x : m.y) >> (l & 63)) & 1ull; }
+
+template <bool FROM_ACTION>
+__global__ void __launch_bounds__(GS_WARPS * 32) gsnr_kernel_fast(const Params p, const GsnrParams g,
+                                                                  const int* __restrict__ query, double* __restrict__ out) {
+  __shared__ GsnrWarpSmem smem[GS_WARPS];
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= p.num_envs) return;
+  GsnrWarpSmem& sm = smem[threadIdx.x >> 5];
+  const int e = warp;
+  const double nan = __longlong_as_double(0x7FF8000000000000ll), inf = __longlong_as_double(0x7FF0000000000000ll);
+  const double pi = 3.141592653589793, beta2 = 21.3e-27, gamma = 1.3e-3, h_planck = 6.626e-34;
+  int4 q;
+  PathRec crec{};
+  int pair;
+  if (!resolve_candidate<FROM_ACTION>(p, query, e, q, crec, pair)) {  // uniform per warp
+    if (lane == 0) out[2 * (size_t)e] = out[2 * (size_t)e + 1] = nan;
+    return;
+  }
+  const int ccore = q.x >> 16;
+  const Chan cch = chan_of(g, q.y, q.z, q.w > 0 ? q.w : crec.se());
+  const ulonglong2 cmask = __ldg(g.path_mask + (size_t)pair * p.k + (q.x & 0xFFFF));
+  const ulonglong2* heap = p.heap + (size_t)e * p.heap_stride + HEAP_PAD;
+  const int n_act = p.heap_len[e];
+  const double a = g.alpha, l_eff_a = 1.0 / (2.0 * a);
+  const double cxci = pi * pi * beta2 * l_eff_a;
+  double worst = inf;
+
+  for (int item = 0; item <= n_act; item++) {
+    // ---- the target (uniform over the warp) ----
+    PathRec trec;
+    Chan tch;
+    ulonglong2 tmask;
+    if (item == 0) {
+      trec = crec;
+      tch = cch;
+      tmask = cmask;
+    } else {
+      const unsigned long long s = heap[item - 1].y;
+      if (svc_core(s) != ccore) continue;
+      const size_t pi_ = (size_t)svc_pair(s) * p.k + svc_path(s);
+      tmask = __ldg(g.path_mask + pi_);
+      if (((tmask.x & cmask.x) | (tmask.y & cmask.y)) == 0ull) continue;
+      trec = load_path(p, svc_pair(s), svc_path(s));
+      tch = chan_of(g, svc_start(s), svc_slots(s), svc_se(s));
+    }
+    const int hops = trec.hops();
+    const int my_link = lane < hops ? trec.link(lane) : 0;
+    double4 lc = make_double4(0.0, 0.0, 0.0, 0.0);
+    if (lane < hops) lc = g.link_c[my_link];
+    sm.tlink[lane] = my_link;
+    __syncwarp();
+    double sum_phi = asinh(pi * pi * beta2 * tch.B * tch.B / (4.0 * a));  // SCI, calculate_osnr.py:30
+
+    // ---- interferers: queue by ballot compaction, evaluate 32 at a time ----
+    int queued = 0;
+    const int n_src = n_act + (item > 0 ? 1 : 0);  // neighbours also see the candidate, last (index n_act)
+    auto drain = [&](int count) {  // evaluate queue[0 .. count), count <= 32
+      if (lane < count) {
+        const int i = (int)sm.queue[lane];
+        Chan ic;
+        ulonglong2 im;
+        if (i == n_act) {
+          ic = cch;
+          im = cmask;
+        } else {
+          const unsigned long long s = heap[i].y;
+          ic = chan_of(g, svc_start(s), svc_slots(s), svc_se(s));
+          im = __ldg(g.path_mask + (size_t)svc_pair(s) * p.k + svc_path(s));
+        }
+        const double df = ic.f - tch.f;
+        const double c = cxci * ic.B;
+        const double pm = ic.se <= 2 ? 1.0 : ic.se == 3 ? 2.0 / 3.0 : ic.se == 4 ? 17.0 / 25.0 : ic.se == 5 ? 69.0 / 100.0 : 13.0 / 21.0;
+        sm.A[lane] = asinh(c * (df + ic.B / 2)) - asinh(c * (df - ic.B / 2));
+        sm.X[lane] = pm * (ic.B / fabs(df)) * 5.0 / 3.0;
+        unsigned hm = 0u;
+        for (int h = 0; h < hops; h++) hm |= mask_has(im, sm.tlink[h]) ? (1u << h) : 0u;
+        sm.hopmask[lane] = hm;
+      }
+      __syncwarp();
+      if (lane < hops)
+        for (int s = 0; s < count; s++)
+          if ((sm.hopmask[s] >> lane) & 1u) sum_phi += sm.A[s] - sm.X[s] * lc.y;
+      __syncwarp();
+    };
+    for (int base = 0; base < n_src; base += 32) {
+      const int i = base + lane;
+      bool hit = false;
+      if (i < n_act) {
+        if (i != item - 1) {
+          const unsigned long long s = heap[i].y;
+          if (svc_core(s) == ccore) {
+            const ulonglong2 im = __ldg(g.path_mask + (size_t)svc_pair(s) * p.k + svc_path(s));
+            hit = ((im.x & tmask.x) | (im.y & tmask.y)) != 0ull;
+          }
+        }
+      } else if (i == n_act && item > 0) {
+        hit = true;  // the candidate shares a link and the core with every neighbour by construction
+      }
+      const unsigned bal = __ballot_sync(0xFFFFFFFFu, hit);
+      if (hit) sm.queue[queued + __popc(bal & ((1u << lane) - 1u))] = (unsigned)i;
+      queued += __popc(bal);
+      __syncwarp();
+      if (queued >= 32) {
+        drain(32);
+        if (lane < queued - 32) sm.queue[lane] = sm.queue[32 + lane];  // keep the overflow, in order
+        queued -= 32;
+        __syncwarp();
+      }
+    }
+    if (queued > 0) drain(queued);
+
+    // ---- per link: P_NLI, P_ASE, one term per span (calculate_osnr.py:45-54), links in path order ----
+    double v = 0.0;
+    if (lane < hops) {
+      const double pr = g.P / tch.B;
+      const double p_nli = pr * pr * pr * (8.0 / (27.0 * pi * beta2)) * gamma * gamma * lc.x * sum_phi * tch.B;
+      const double p_ase = tch.B * h_planck * tch.f * lc.z * g.nf;
+      v = 1.0 / (g.P / (p_ase + p_nli));
+    }
+    double acc = 0.0;
+    for (int h = 0; h < hops; h++) {
+      const double vh = __shfl_sync(0xFFFFFFFFu, v, h);
+      const int ns = (int)__shfl_sync(0xFFFFFFFFu, lc.w, h);
+      for (int k = 0; k < ns; k++) acc += vh;
+    }
+    const double gs = 10.0 * log10(1.0 / acc);
+    if (item == 0) {
+      if (lane == 0) out[2 * (size_t)e] = gs;
+    } else {
+      worst = fmin(worst, gs);
+    }
+  }
+  if (lane == 0) out[2 * (size_t)e + 1] = worst;
 }
 
 }  // namespace orlg

@@ -625,8 +625,34 @@ extern "C" int orlg_gsnr_configure(orlg_engine* e, const orlg_gsnr_params* g) {
   e->gp.nf = g->noise_figure_lin;
   e->gp.f0 = g->f0_hz;
   e->gp.slot_hz = g->slot_hz;
+  e->gp.path_mask = nullptr;
+  e->gp.link_c = nullptr;
+  if (e->p.E <= 128) {  // tables of the fast kernel: link sets of the paths, per-link span factors
+    const int npaths = e->p.n_nodes * e->p.n_nodes * e->p.k;
+    ulonglong2* pm = nullptr;
+    double4* lc = nullptr;
+    if ((rc = dev_alloc(e, &pm, (size_t)npaths, false))) return rc;
+    if ((rc = dev_alloc(e, &lc, (size_t)e->p.E, false))) return rc;
+    const int n = npaths > e->p.E ? npaths : e->p.E;
+    gsnr_init_tables<<<(n + 127) / 128, 128>>>(e->p, e->gp, npaths, pm, lc);
+    CK(cudaGetLastError());
+    CK(cudaDeviceSynchronize());
+    e->gp.path_mask = pm;
+    e->gp.link_c = lc;
+  }
   e->gsnr_ready = true;
   return ORLG_OK;
+}
+
+template <bool FROM_ACTION>
+static cudaError_t launch_gsnr(orlg_engine* e, const int32_t* dev_in, double* dev_out, cudaStream_t st) {
+  const int grid = (e->p.num_envs + GS_WARPS - 1) / GS_WARPS;
+  const char* force = getenv("ORLG_GSNR_GENERIC");  // A/B: the previous kernel
+  if (e->gp.path_mask && !(force && *force == '1'))
+    gsnr_kernel_fast<FROM_ACTION><<<grid, GS_WARPS * 32, 0, st>>>(e->p, e->gp, dev_in, dev_out);
+  else
+    gsnr_kernel_generic<FROM_ACTION><<<grid, GS_WARPS * 32, 0, st>>>(e->p, e->gp, dev_in, dev_out);
+  return cudaGetLastError();
 }
 
 extern "C" int orlg_gsnr(orlg_engine* e, const int32_t* dev_query, double* dev_out, void* stream) {
@@ -636,10 +662,7 @@ extern "C" int orlg_gsnr(orlg_engine* e, const int32_t* dev_query, double* dev_o
     return ORLG_ESTATE;
   }
   cudaSetDevice(e->device);
-  const int warps_per_cta = 4;
-  gsnr_kernel<false><<<(e->p.num_envs + warps_per_cta - 1) / warps_per_cta, warps_per_cta * 32, 0, (cudaStream_t)stream>>>(
-      e->p, e->gp, dev_query, dev_out);
-  CK(cudaGetLastError());
+  CK(launch_gsnr<false>(e, dev_query, dev_out, (cudaStream_t)stream));
   e->launches++;
   return ORLG_OK;
 }
@@ -655,10 +678,7 @@ extern "C" int orlg_gsnr_for_actions(orlg_engine* e, const int32_t* dev_actions,
     return ORLG_ESTATE;
   }
   cudaSetDevice(e->device);
-  const int warps_per_cta = 4;
-  gsnr_kernel<true><<<(e->p.num_envs + warps_per_cta - 1) / warps_per_cta, warps_per_cta * 32, 0, (cudaStream_t)stream>>>(
-      e->p, e->gp, dev_actions, dev_out);
-  CK(cudaGetLastError());
+  CK(launch_gsnr<true>(e, dev_actions, dev_out, (cudaStream_t)stream));
   e->launches++;
   return ORLG_OK;
 }

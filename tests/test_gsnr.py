@@ -172,4 +172,14 @@ def test_gsnr_for_actions_equals_explicit_queries(env_id):
     got = eng.gsnr_for_actions(torch.from_numpy(a).to(eng.device)).cpu().numpy()
     assert np.isnan(got[::17]).all() and np.isfinite(got[:, 0]).sum() >= n_env // 2
     assert np.array_equal(got, want, equal_nan=True)
+    # the warp-cooperative kernel (link bit sets, ballot-compacted interferers) against the generic one it
+    # replaced: same summation order per link, so the two must agree bit for bit
+    import os
+
+    os.environ["ORLG_GSNR_GENERIC"] = "1"
+    try:
+        generic = eng.gsnr_for_actions(torch.from_numpy(a).to(eng.device)).cpu().numpy()
+    finally:
+        os.environ.pop("ORLG_GSNR_GENERIC")
+    assert np.array_equal(got, generic, equal_nan=True)
     eng.close()
