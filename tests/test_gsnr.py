@@ -172,8 +172,8 @@ def test_gsnr_for_actions_equals_explicit_queries(env_id):
     got = eng.gsnr_for_actions(torch.from_numpy(a).to(eng.device)).cpu().numpy()
     assert np.isnan(got[::17]).all() and np.isfinite(got[:, 0]).sum() >= n_env // 2
     assert np.array_equal(got, want, equal_nan=True)
-    # the warp-cooperative kernel (link bit sets, ballot-compacted interferers) against the generic one it
-    # replaced: same summation order per link, so the two must agree bit for bit
+    # the warp-cooperative kernel (link bit sets, ballot-compacted interferers, one log per asinh pair, butterfly
+    # sums) against the generic one it replaced (literal formula, sequential sums): 1e-9 dB, far inside 1e-4 dB
     import os
 
     os.environ["ORLG_GSNR_GENERIC"] = "1"
@@ -181,5 +181,7 @@ def test_gsnr_for_actions_equals_explicit_queries(env_id):
         generic = eng.gsnr_for_actions(torch.from_numpy(a).to(eng.device)).cpu().numpy()
     finally:
         os.environ.pop("ORLG_GSNR_GENERIC")
-    assert np.array_equal(got, generic, equal_nan=True)
+    assert np.array_equal(np.isnan(got), np.isnan(generic)) and np.array_equal(np.isinf(got), np.isinf(generic))
+    fin = np.isfinite(got)
+    assert np.abs(got[fin] - generic[fin]).max() < 1e-9
     eng.close()
