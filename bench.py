@@ -276,6 +276,8 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
         eng.set_next_action_hint(hid, act)
 
     def one_step(evs=None):
+        """evs = [start, after the heuristic launch, after the step launch, end]; only the events that separate
+        launches of this configuration are recorded (an event record costs GPU front-end time too)."""
         if flush is not None:
             flush.fill_(1)  # evict the 126 MB L2 (untimed: outside the event pairs)
         if evs is not None:
@@ -284,15 +286,22 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
             eng.heuristic(hid, act)
             if gs_out is not None:
                 eng.gsnr_for_actions(act, gs_out)
-        if evs is not None:
-            evs[1].record()
+            if evs is not None:
+                evs[1].record()
         eng.step(act, rew, done, obs, None)
         if evs is not None:
             evs[2].record()
         if fused and gs_out is not None:  # the hint is the action for the request that has just become pending
             eng.gsnr_for_actions(act, gs_out)
-        if evs is not None:
-            evs[3].record()
+            if evs is not None:
+                evs[3].record()
+
+    def ev_times(evs):
+        """(whole step, step kernel, GN-model kernel or None) in ms summed over the recorded steps"""
+        k0 = 0 if fused else 1
+        end = 3 if (fused and gs_out is not None) else 2
+        return (sum(e[0].elapsed_time(e[end]) for e in evs), sum(e[k0].elapsed_time(e[2]) for e in evs),
+                sum(e[2].elapsed_time(e[3]) for e in evs) if end == 3 else None)
 
     for _ in range(args.warmup):
         one_step()
@@ -308,9 +317,7 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
         one_step(evs[t])
     barrier()
     launches = eng.launch_count - launches0
-    step_ms = sum(e[0].elapsed_time(e[3]) for e in evs)
-    kern_ms = sum(e[1].elapsed_time(e[2]) for e in evs)
-    gsnr_ms = sum(e[2].elapsed_time(e[3]) for e in evs) if (fused and gs_out is not None) else None
+    step_ms, kern_ms, gsnr_ms = ev_times(evs)
     if gs_out is not None and not bool(torch.isfinite(gs_out[:, 0]).any()):
         raise RuntimeError("GSNR evaluation produced no finite value")
 
@@ -338,7 +345,7 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
         for t in range(K):
             one_step(ev2[t])
         barrier()
-        two_ms = sum(e[0].elapsed_time(e[3]) for e in ev2)
+        two_ms = ev_times(ev2)[0]
         fused = True
         eng.heuristic(hid, act)
         eng.set_next_action_hint(hid, act)

@@ -58,11 +58,13 @@ __device__ __forceinline__ void fence_async_smem() {
 // same layout with a tile of one env) and every thread reads and writes its own rows in place
 // with vector loads.  This is the variant for envs whose occupancy is so large (multi-core, wide
 // spectra, many links) that only a warp or two of staged tiles would fit on an SM.
-#ifndef ORLG_MIN_CTAS  // A/B knob: resident CTAs per SM the register allocation must allow
-#define ORLG_MIN_CTAS 1
+#ifdef ORLG_MIN_CTAS  // A/B knob: resident CTAs per SM the register allocation must allow
+#define ORLG_LAUNCH_BOUNDS(BD) __launch_bounds__(BD, ORLG_MIN_CTAS)
+#else
+#define ORLG_LAUNCH_BOUNDS(BD) __launch_bounds__(BD)
 #endif
 template <int W, int BD, int MT, bool PHY, bool DIRECT = false, bool INFO = false>
-__global__ void __launch_bounds__(BD, ORLG_MIN_CTAS) env_kernel(const Params p, const StepIO io) {
+__global__ void ORLG_LAUNCH_BOUNDS(BD) env_kernel(const Params p, const StepIO io) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t bar;
   constexpr int PS = DIRECT ? 1 : BD;  // plane stride of the occupancy this thread sees
