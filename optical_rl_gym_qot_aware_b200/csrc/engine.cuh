@@ -233,6 +233,15 @@ struct Tile {
         if (m[wi]) q[wi * BD] = set ? (q[wi * BD] | m[wi]) : (q[wi * BD] & ~m[wi]);
     });
   }
+  // one slot / channel on every link of the path (PhyRMSA allocates whole channels): one word per link
+  __device__ __forceinline__ void apply_bit(const PathRec& r, int core, int pos, bool set) {
+    const uint32_t m = 1u << (pos & 31);
+    uint32_t* base = s + (size_t)core * E * W * BD + tid + (pos >> 5) * BD;
+    for_each_link(r, [&](int l) {
+      uint32_t* q = base + l * (W * BD);
+      *q = set ? (*q | m) : (*q & ~m);
+    });
+  }
   __device__ __forceinline__ void clear_range(const PathRec& r, int core, int start, int n) {
     apply_range(r, core, start, n, false);
   }

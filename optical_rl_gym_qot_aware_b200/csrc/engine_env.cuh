@@ -255,7 +255,7 @@ struct Env {
     }
     if (free_it) {
       PathRec rec = load_path(p, svc_pair(s), svc_path(s));
-      tile.set_range(rec, 0, ch, 1);
+      tile.apply_bit(rec, 0, ch, true);
     }
   }
 

@@ -75,14 +75,21 @@ __device__ __forceinline__ void count_terms(ENV& env, int pathg, CutPlanes<W>& c
   const unsigned char* links = p.phy_cut_links + (size_t)pathg * p.phy_max_terms;
   for (int t = 0; t < T; t++) {
     const int l = __ldg(links + t);
+    // before term t every counter is <= t, so only planes 0 .. bits(t + 1) - 1 can change: the ripple stops
+    // there (t is the loop counter, hence the bound is the same for every lane still in the loop)
+    const int np = 32 - __clz(t + 1);
+    uint32_t carry[W];
 #pragma unroll
-    for (int i = 0; i < W; i++) {
-      uint32_t carry = env.tile.word(0, l, i);
+    for (int i = 0; i < W; i++) carry[i] = env.tile.word(0, l, i);
 #pragma unroll
-      for (int q = 0; q < PHY_PLANES; q++) {
-        uint32_t t2 = c.b[q].w[i] & carry;
-        c.b[q].w[i] ^= carry;
-        carry = t2;
+    for (int q = 0; q < PHY_PLANES; q++) {
+      if (q < np) {
+#pragma unroll
+        for (int i = 0; i < W; i++) {
+          uint32_t t2 = c.b[q].w[i] & carry[i];
+          c.b[q].w[i] ^= carry[i];
+          carry[i] = t2;
+        }
       }
     }
   }
@@ -465,7 +472,7 @@ __device__ Decision phy_decide(ENV& env, const int* a) {
   need = env.bit_rate / 100;
   for (int i = 0; i < nch; i++) {  // _provision_path :576-601
     const int ch = a[1 + i];
-    env.tile.clear_range(rec, 0, ch, 1);
+    env.tile.apply_bit(rec, 0, ch, false);
     const size_t tix = ((size_t)table * p.S + ch) * p.k + path;
     const int level = __ldg(p.phy_mod + tix);
     env.fsum[1] += __ldg(p.phy_gsnr + tix);

@@ -211,8 +211,11 @@ __global__ void gsnr_init_tables(const Params p, const GsnrParams g, int npaths,
 
 __device__ __forceinline__ bool mask_has(ulonglong2 m, int l) { return (((l < 64) ? m.x : m.y) >> (l & 63)) & 1ull; }
 
+#ifndef GS_MIN_CTAS  // resident CTAs per SM the register allocation must allow (A/B knob)
+#define GS_MIN_CTAS 6
+#endif
 template <bool FROM_ACTION>
-__global__ void __launch_bounds__(GS_WARPS * 32) gsnr_kernel_fast(const Params p, const GsnrParams g,
+__global__ void __launch_bounds__(GS_WARPS * 32, GS_MIN_CTAS) gsnr_kernel_fast(const Params p, const GsnrParams g,
                                                                   const int* __restrict__ query, double* __restrict__ out) {
   __shared__ GsnrWarpSmem smem[GS_WARPS];
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
