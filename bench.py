@@ -156,6 +156,7 @@ class ClockSampler:
 
 
 _KSPFF_LUT = {}
+_KSPFF_WS = {}
 
 
 def host_policy_kspff(obs_fm, n_nodes, k, j, out=None):
@@ -170,12 +171,21 @@ def host_policy_kspff(obs_fm, n_nodes, k, j, out=None):
     if lut is None:
         lut = np.array([next((p * j for p in range(k) if c >> p & 1), k * j) for c in range(1 << k)], np.int32)
         _KSPFF_LUT[(k, j)] = lut
-    code = (obs_fm[base + 1] != -1.0).view(np.uint8).copy()
-    for p in range(1, k):
-        code |= (obs_fm[base + p * rowlen + 1] != -1.0).view(np.uint8) << p
+    n = obs_fm.shape[1]
+    ws = _KSPFF_WS.get(n)
+    if ws is None:  # per batch size: bit scratch, packed code, index scratch (no allocation in the loop)
+        ws = _KSPFF_WS[n] = (np.empty(n, np.bool_), np.empty(n, np.uint8), np.empty(n, np.intp))
+    bit, code, idx = ws
+    # Horner over the paths, highest first: code = 2*code | (path p has a fitting block)
+    np.not_equal(obs_fm[base + (k - 1) * rowlen + 1], -1.0, out=code.view(np.bool_))
+    for p in range(k - 2, -1, -1):
+        np.not_equal(obs_fm[base + p * rowlen + 1], -1.0, out=bit)
+        np.add(code, code, out=code)
+        np.bitwise_or(code, bit.view(np.uint8), out=code)
+    np.copyto(idx, code)
     if out is None:
-        return lut[code].reshape(-1, 1)
-    np.take(lut, code, out=out.reshape(-1))
+        return lut.take(idx).reshape(-1, 1)
+    np.take(lut, idx, out=out.reshape(-1), mode="clip")  # codes are < 2**k by construction
     return out
 
 
@@ -409,10 +419,11 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
 
     # ---- e2e, pipelined: the batch as two VecEnv halves on two streams (step_async / step_wait);
     # the host policy of one half overlaps the copies and the kernel of the other ----
-    if use_obs_policy and n_env % 2 == 0 and not args.e2e_serial:
-        nh = n_env // 2
+    parts = max(2, args.e2e_parts)
+    if use_obs_policy and n_env % parts == 0 and not args.e2e_serial:
+        nh = n_env // parts
         halves = []
-        for hi in range(2):
+        for hi in range(parts):
             he = Engine(spec, nh, device=local, global_env_offset=rank * n_env + hi * nh, heap_capacity=args.heap_capacity)
             he.reset(True)
             he.rollout(hid, PREROLL)
@@ -450,7 +461,8 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
         e1.record()
         barrier()
         e2e_ms = max(e0.elapsed_time(e1), (time.perf_counter() - w0) * 1e3)
-        e2e_mode = "two VecEnv halves on two streams, orlg_step_host_async / _wait (policy overlaps copies)"
+        e2e_mode = (f"{parts} VecEnv shards of {nh} envs on {parts} streams, orlg_step_host_async / _wait "
+                    "(the host policy of one shard overlaps the copies and kernels of the others)")
         for h in halves:
             if int(h["e"].counters()[:, 10].max()) != 0:
                 raise RuntimeError("device fault bits set in the pipelined e2e run")
@@ -567,7 +579,8 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--e2e-steps", type=int, default=100)
     ap.add_argument("--no-flush", action="store_true")
-    ap.add_argument("--e2e-serial", action="store_true", help="no two-half pipelining of the e2e loop")
+    ap.add_argument("--e2e-serial", action="store_true", help="no pipelining of the e2e loop")
+    ap.add_argument("--e2e-parts", type=int, default=4, help="VecEnv shards (streams) the pipelined e2e loop cycles through")
     ap.add_argument("--two-launch", action="store_true", help="orlg_heuristic + orlg_step instead of the fused hint")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gsnr", action="store_true", help="c3 only: skip the per-decision GN-model launch")
