@@ -420,11 +420,16 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
     # ---- e2e, pipelined: the batch as two VecEnv halves on two streams (step_async / step_wait);
     # the host policy of one half overlaps the copies and the kernel of the other ----
     parts = max(2, args.e2e_parts)
+    # ranks x (a waiting main thread + the driver's helper threads) against the host's cores: spin-waiting is the
+    # fastest when every rank has cores to spare, and it starves the policy when it has not
+    ncpu = os.cpu_count() or 1
+    block_wait = {"spin": False, "block": True}.get(args.host_wait, world * 4 > ncpu)
     if use_obs_policy and n_env % parts == 0 and not args.e2e_serial:
         nh = n_env // parts
         halves = []
         for hi in range(parts):
             he = Engine(spec, nh, device=local, global_env_offset=rank * n_env + hi * nh, heap_capacity=args.heap_capacity)
+            he.set_host_wait(block_wait)
             he.reset(True)
             he.rollout(hid, PREROLL)
             dobs = he.new_obs()
@@ -538,7 +543,8 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
         "e2e": {"value": total_envs * Ke / (e2e_ms * 1e-3), "unit": "env-steps/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "steps": Ke, "ms_per_step": e2e_ms / Ke, "mode": e2e_mode,
                 "serial_value": total_envs * Ke / (e2e_serial_ms * 1e-3),
-                "host_policy_ms_per_step": policy_s[0] * 1e3 / Ke,
+                "host_policy_ms_per_step": policy_s[0] * 1e3 / Ke, "host_cores": ncpu,
+                "host_wait": "sleep on a blocking-sync event" if block_wait else "cudaStreamSynchronize (spin)",
                 "d2h_gbs": d2h * Ke / (e2e_ms * 1e-3) / 1e9, "pinned_d2h_copy_gbs": pcie_gbs,
                 "policy": "numpy K-SP-FF from the host observation" if use_obs_policy
                 else "device heuristic, actions D2H then H2D"},
@@ -580,6 +586,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=100)
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--e2e-serial", action="store_true", help="no pipelining of the e2e loop")
+    ap.add_argument("--host-wait", default="auto", choices=["auto", "spin", "block"],
+                    help="orlg_step_host_wait: spin on the stream, sleep on an event, or decide from ranks x 4 > cores")
     ap.add_argument("--e2e-parts", type=int, default=4, help="VecEnv shards (streams) the pipelined e2e loop cycles through")
     ap.add_argument("--two-launch", action="store_true", help="orlg_heuristic + orlg_step instead of the fused hint")
     ap.add_argument("--no-cpu-baseline", action="store_true")

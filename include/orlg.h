@@ -220,6 +220,11 @@ int orlg_step_host(orlg_engine* e, const int32_t* host_actions, int32_t* host_re
 int orlg_step_host_async(orlg_engine* e, const int32_t* host_actions, int32_t* host_reward,
                          uint8_t* host_done, void* host_obs, int32_t* host_alloc, void* stream);
 int orlg_step_host_wait(orlg_engine* e, void* stream);
+/* How orlg_step_host_wait waits: 0 (default) = cudaStreamSynchronize (the driver spins: lowest latency when
+ * every engine's host thread has a core to itself), 1 = sleep on a blocking-sync event recorded by the _async
+ * call (for hosts with fewer cores than busy threads, e.g. eight per-GPU processes on a 16-thread box, where
+ * spinning waiters take the cores the policy needs). */
+int orlg_set_host_wait(orlg_engine* e, int blocking);
 
 /* Layout of dev_obs for orlg_step / orlg_observation, in elements: feature f of
  * env i is written at dev_obs[i*env_stride + f*feat_stride].  Default (obs_dim, 1)

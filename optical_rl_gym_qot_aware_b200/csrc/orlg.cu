@@ -39,6 +39,8 @@ struct orlg_engine {
   long long obs_es = 0, obs_fs = 1;  // 0 = row-major default
   GsnrParams gp{};
   bool gsnr_ready = false;
+  cudaEvent_t host_ev = nullptr;  // end of the last orlg_step_host_async (blocking-sync event)
+  bool blocking_wait = false;
   int* hint_actions = nullptr;
   int hint_heuristic = 0;
 };
@@ -398,6 +400,7 @@ extern "C" int orlg_destroy(orlg_engine* e) {
   if (!e) return ORLG_EINVAL;
   cudaSetDevice(e->device);
   for (void* a : e->allocs) cudaFree(a);
+  if (e->host_ev) cudaEventDestroy(e->host_ev);
   delete e;
   return ORLG_OK;
 }
@@ -588,13 +591,26 @@ extern "C" int orlg_step_host_async(orlg_engine* e, const int32_t* h_actions, in
   if (h_alloc) CK(cudaMemcpyAsync(h_alloc, e->d_alloc, n * 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
   if (h_obs && e->d_obs)
     CK(cudaMemcpyAsync(h_obs, e->d_obs, n * e->obs_dim * e->obs_elem, cudaMemcpyDeviceToHost, st));
+  if (e->blocking_wait) {
+    if (!e->host_ev) CK(cudaEventCreateWithFlags(&e->host_ev, cudaEventBlockingSync | cudaEventDisableTiming));
+    CK(cudaEventRecord(e->host_ev, st));
+  }
   return ORLG_OK;
 }
 
 extern "C" int orlg_step_host_wait(orlg_engine* e, void* stream) {
   if (!e) return ORLG_EINVAL;
   cudaSetDevice(e->device);
-  CK(cudaStreamSynchronize((cudaStream_t)stream));
+  if (e->blocking_wait && e->host_ev)
+    CK(cudaEventSynchronize(e->host_ev));  // the thread sleeps instead of spinning on the stream
+  else
+    CK(cudaStreamSynchronize((cudaStream_t)stream));
+  return ORLG_OK;
+}
+
+extern "C" int orlg_set_host_wait(orlg_engine* e, int blocking) {
+  if (!e) return ORLG_EINVAL;
+  e->blocking_wait = blocking != 0;
   return ORLG_OK;
 }
 

@@ -33,7 +33,7 @@ EXPORTS = (
     "orlg_action_dim", "orlg_obs_dim", "orlg_state_words", "orlg_hbm_bytes", "orlg_load_trace",
     "orlg_reset", "orlg_step", "orlg_step_host", "orlg_set_obs_layout", "orlg_observation",
     "orlg_heuristic", "orlg_rollout", "orlg_get_counters", "orlg_export_state", "orlg_get_requests",
-    "orlg_launch_count", "orlg_gsnr_configure", "orlg_gsnr", "orlg_gsnr_for_actions", "orlg_phy_get_stats", "orlg_path_first_fit", "orlg_set_next_action_hint", "orlg_step_host_async", "orlg_step_host_wait",
+    "orlg_launch_count", "orlg_gsnr_configure", "orlg_gsnr", "orlg_gsnr_for_actions", "orlg_phy_get_stats", "orlg_path_first_fit", "orlg_set_next_action_hint", "orlg_step_host_async", "orlg_step_host_wait", "orlg_set_host_wait",
     "orlg_phy_get_channel_state", "orlg_info_dim", "orlg_set_info_output",
 )
 
@@ -98,6 +98,7 @@ def load_library():
         L.orlg_step_host.argtypes = [vp, vp, vp, vp, vp, vp, vp]
         L.orlg_step_host_async.argtypes = [vp, vp, vp, vp, vp, vp, vp]
         L.orlg_step_host_wait.argtypes = [vp, vp]
+        L.orlg_set_host_wait.argtypes = [vp, i32]
         L.orlg_set_obs_layout.argtypes = [vp, i64, i64]
         L.orlg_observation.argtypes = [vp, i32, vp, vp]
         L.orlg_heuristic.argtypes = [vp, i32, vp, vp]
@@ -355,6 +356,10 @@ class Engine:
             out = torch.empty((self.num_envs, 2), dtype=torch.float64, device=self.device)
         self._ck(self.L.orlg_gsnr(self.h, self._p(query), self._p(out), self._stream()))
         return out
+
+    def set_host_wait(self, blocking: bool):
+        """step_host_wait sleeps on an event (True) instead of spinning on the stream (False, default)."""
+        self._ck(self.L.orlg_set_host_wait(self.h, int(bool(blocking))))
 
     def gsnr_for_actions(self, actions, out=None):
         """actions: int32 device tensor in the env's own action format (RMSA-v0 [num_envs, 2], RMCSA-v0

@@ -249,3 +249,34 @@ def test_path_only_first_fit_action_wrapper():
         if bool(d[0]):
             env.reset()
     env.close()
+
+
+def test_host_wait_modes_give_the_same_step():
+    """orlg_set_host_wait: sleeping on the blocking-sync event and spinning on the stream are two ways to wait
+    for the same orlg_step_host_async work; host buffers must hold identical results afterwards."""
+    import torch
+
+    from optical_rl_gym_qot_aware_b200.engine import Engine
+
+    spec = S.make_spec("DeepRMSA-v0", G.topology("nsfnet"), seed=11, mean_service_holding_time=7.5,
+                       mean_service_inter_arrival_time=1 / 12.0, episode_length=50, auto_reset=True, obs_kind=S.OBS_F32)
+    n, outs = 512, []
+    for blocking in (False, True):
+        eng = Engine(spec, n)
+        eng.set_host_wait(blocking)
+        eng.reset(True)
+        st = torch.cuda.Stream()
+        act = torch.zeros((n, 1), dtype=torch.int32).pin_memory()
+        rew = torch.zeros(n, dtype=torch.int32).pin_memory()
+        done = torch.zeros(n, dtype=torch.uint8).pin_memory()
+        obs = torch.zeros((eng.obs_dim, n), dtype=torch.float32).pin_memory()
+        trace = []
+        for t in range(60):
+            act[:, 0] = t % 6
+            eng.step_host_async(act, rew, done, obs, None, stream=st)
+            eng.step_host_wait(stream=st)
+            trace.append((rew.numpy().copy(), done.numpy().copy(), obs.numpy().copy()))
+        outs.append(trace)
+        eng.close()
+    for a, b in zip(*outs):
+        assert all(np.array_equal(x, y) for x, y in zip(a, b))
