@@ -423,7 +423,7 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
     # ranks x (a waiting main thread + the driver's helper threads) against the host's cores: spin-waiting is the
     # fastest when every rank has cores to spare, and it starves the policy when it has not
     ncpu = os.cpu_count() or 1
-    block_wait = {"spin": False, "block": True}.get(args.host_wait, world * 4 > ncpu)
+    block_wait = {"spin": False, "block": True}.get(args.host_wait, world * 2 > ncpu)
     if use_obs_policy and n_env % parts == 0 and not args.e2e_serial:
         nh = n_env // parts
         halves = []
@@ -587,7 +587,7 @@ def main():
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--e2e-serial", action="store_true", help="no pipelining of the e2e loop")
     ap.add_argument("--host-wait", default="auto", choices=["auto", "spin", "block"],
-                    help="orlg_step_host_wait: spin on the stream, sleep on an event, or decide from ranks x 4 > cores")
+                    help="orlg_step_host_wait: spin on the stream, sleep on an event, or decide from ranks x 2 > cores")
     ap.add_argument("--e2e-parts", type=int, default=4, help="VecEnv shards (streams) the pipelined e2e loop cycles through")
     ap.add_argument("--two-launch", action="store_true", help="orlg_heuristic + orlg_step instead of the fused hint")
     ap.add_argument("--no-cpu-baseline", action="store_true")
