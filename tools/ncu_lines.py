@@ -4,7 +4,10 @@
 ncu's source page is per SASS instruction; this joins it with `nvdisasm -g` line markers of the same
 cubin so samples / executed instructions / stall reasons can be summed per file:line.
 
-  python tools/ncu_lines.py REPORT.ncu-rep build/orlg_w4.o KERNEL_MANGLED_SUBSTRING [--by inst|samples|long_sb] [--top N]
+  python tools/ncu_lines.py REPORT.ncu-rep build/orlg_w4.o KERNEL_MANGLED_SUBSTRING [--by inst|samples|long_sb|idle_lanes] [--top N]
+
+`lanes` = average active threads of the line's instructions, `idle%` = the line's share of all idle lane slots
+(32 x instructions - thread instructions): where divergence costs.
 """
 import argparse
 import collections
@@ -74,19 +77,24 @@ def main():
             base = addr
         key, _ = lines.get(addr - base, (("?", 0), ""))
         vals = {"samples": r[h["# Samples"]], "inst": r[h["Instructions Executed"]],
+                "thread_inst": r[h["Thread Instructions Executed"]],
                 "long_sb": r[h["stall_long_sb"]], "wait": r[h["stall_wait"]], "short_sb": r[h["stall_short_sb"]],
                 "no_inst": r[h["stall_no_inst"]], "branch": r[h["stall_branch_resolving"]]}
         for k, v in vals.items():
             v = float(v.replace(",", "") or 0)
             agg[key][k] += v
             tot[k] += v
+    for c in list(agg.values()) + [tot]:  # lane slots an instruction issued for but no thread used
+        c["idle_lanes"] = 32 * c["inst"] - c["thread_inst"]
     print(sec["name"])
     print("totals:", {k: int(v) for k, v in tot.items()})
-    print(f"{'file:line':34s} {'samples%':>8s} {'inst%':>7s} {'long_sb':>8s} {'wait':>6s} {'short':>6s} {'noinst':>6s}")
+    print(f"average active threads per instruction: {tot['thread_inst'] / max(tot['inst'], 1):.2f}")
+    print(f"{'file:line':34s} {'samples%':>8s} {'inst%':>7s} {'long_sb':>8s} {'wait':>6s} {'short':>6s} {'noinst':>6s} {'lanes':>6s} {'idle%':>6s}")
     for key, c in sorted(agg.items(), key=lambda kv: -kv[1][a.by])[: a.top]:
         print(f"{key[0] + ':' + str(key[1]):34s} {100 * c['samples'] / max(tot['samples'], 1):8.2f} "
               f"{100 * c['inst'] / max(tot['inst'], 1):7.2f} {int(c['long_sb']):8d} {int(c['wait']):6d} "
-              f"{int(c['short_sb']):6d} {int(c['no_inst']):6d}")
+              f"{int(c['short_sb']):6d} {int(c['no_inst']):6d} {c['thread_inst'] / max(c['inst'], 1):6.1f} "
+              f"{100 * c['idle_lanes'] / max(tot['idle_lanes'], 1):6.2f}")
 
 
 if __name__ == "__main__":
