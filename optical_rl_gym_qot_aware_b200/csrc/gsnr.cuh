@@ -28,6 +28,12 @@ struct GsnrParams {
   const double* span_km;
   const ulonglong2* path_mask;  // [N*N*k] links of every path as a bit set (fast kernel; null when E > 128)
   const double4* link_c;        // [E] (l_eff, l_eff / L, exp(2 a L) - 1, span count)
+  // [S + 1][4 S + 1]: the asinh pair of calculate_osnr.py:36-44 for an interferer of n slots whose centre lies
+  // d half-slots from the target's (column d + 2 S).  Channels live on the slot grid, so the pair only depends on
+  // (n, d); null when the table would exceed 16 MB.
+  const double2* xci_tab;  // (asinh pair, (B / |df|) * 5 / 3)
+  const double* sci_tab;   // [S + 1] self-channel term asinh(pi^2 |b2| B^2 / (4 a)) of an n-slot channel (:30)
+  int tab_S;
 };
 
 __device__ __forceinline__ bool path_has_link(const PathRec& r, int link) {
@@ -40,12 +46,15 @@ __device__ __forceinline__ bool path_has_link(const PathRec& r, int link) {
 struct Chan {  // a lightpath as the GN model sees it
   double B, f;
   int se;
+  int n, pos2;  // slots, and twice the centre position in slots (2 * first + n): the integer grid behind B and f
 };
 __device__ __forceinline__ Chan chan_of(const GsnrParams& g, int start, int n, int se) {
   Chan c;
   c.B = (double)n * g.slot_hz;
   c.f = g.f0 + ((double)start + 0.5 * (double)n) * g.slot_hz;
   c.se = se;
+  c.n = n;
+  c.pos2 = 2 * start + n;
   return c;
 }
 
@@ -188,6 +197,7 @@ constexpr int GS_WARPS = 4;
 struct GsnrWarpSmem {
   unsigned queue[64];
   int tlink[32];  // links of the current target, hop order
+  unsigned char hop_of[128];  // link -> hop of the current target (valid for the target's links only)
 };
 
 __global__ void gsnr_init_tables(const Params p, const GsnrParams g, int npaths, ulonglong2* path_mask, double4* link_c) {
@@ -207,6 +217,21 @@ __global__ void gsnr_init_tables(const Params p, const GsnrParams g, int npaths,
     const double l_eff = (1.0 - exp(-2.0 * a * L)) / (2.0 * a);
     link_c[i] = make_double4(l_eff, l_eff / L, exp(2.0 * a * L) - 1.0, (double)g.span_count[i]);
   }
+}
+
+__global__ void gsnr_init_xci(const GsnrParams g, int S, double2* tab, double* sci) {
+  const int cols = 4 * S + 1;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i <= S) {
+    const double Bn = (double)i * g.slot_hz;
+    sci[i] = asinh(3.141592653589793 * 3.141592653589793 * 21.3e-27 * Bn * Bn / (4.0 * g.alpha));
+  }
+  if (i >= (long long)(S + 1) * cols) return;
+  const int n = (int)(i / cols), d = (int)(i % cols) - 2 * S;
+  const double pi = 3.141592653589793, beta2 = 21.3e-27;
+  const double B = (double)n * g.slot_hz, df = (double)d * (0.5 * g.slot_hz);
+  const double c = pi * pi * beta2 * (1.0 / (2.0 * g.alpha)) * B;
+  tab[i] = make_double2(asinh(c * (df + B / 2)) - asinh(c * (df - B / 2)), (B / fabs(df)) * 5.0 / 3.0);
 }
 
 __device__ __forceinline__ bool mask_has(ulonglong2 m, int l) { return (((l < 64) ? m.x : m.y) >> (l & 63)) & 1ull; }
@@ -263,8 +288,10 @@ __global__ void __launch_bounds__(GS_WARPS * 32, GS_MIN_CTAS) gsnr_kernel_fast(c
     double4 lc = make_double4(0.0, 0.0, 0.0, 0.0);
     if (lane < hops) lc = g.link_c[my_link];
     sm.tlink[lane] = my_link;
+    if (lane < hops) sm.hop_of[my_link] = (unsigned char)lane;
     __syncwarp();
-    double sum_phi = asinh(pi * pi * beta2 * tch.B * tch.B / (4.0 * a));  // SCI, calculate_osnr.py:30
+    double sum_phi = g.sci_tab ? __ldg(g.sci_tab + tch.n)  // SCI, calculate_osnr.py:30
+                               : asinh(pi * pi * beta2 * tch.B * tch.B / (4.0 * a));
 
     // ---- interferers: queue by ballot compaction, evaluate 32 at a time ----
     int queued = 0;
@@ -284,25 +311,40 @@ __global__ void __launch_bounds__(GS_WARPS * 32, GS_MIN_CTAS) gsnr_kernel_fast(c
           ic = chan_of(g, svc_start(s), svc_slots(s), svc_se(s));
           im = __ldg(g.path_mask + (size_t)svc_pair(s) * p.k + svc_path(s));
         }
-        const double df = ic.f - tch.f;
-        const double c = cxci * ic.B;
         const double pm = ic.se <= 2 ? 1.0 : ic.se == 3 ? 2.0 / 3.0 : ic.se == 4 ? 17.0 / 25.0 : ic.se == 5 ? 69.0 / 100.0 : 13.0 / 21.0;
         // asinh(u) - asinh(v), calculate_osnr.py:36-44.  Channels that share a link and core do not overlap, so
         // u and v have one sign and the difference is log((|u'| + sqrt(u'^2 + 1)) / (|v'| + sqrt(v'^2 + 1)))
         // with u' the larger magnitude: one log instead of two asinh (agreement ~1e-15 relative).
-        double u = c * (df + ic.B / 2), v = c * (df - ic.B / 2);
-        if (u > 0.0 && v < 0.0) {
-          A = asinh(u) - asinh(v);  // overlapping spectra (a candidate that is not free): literal form
+        if (g.xci_tab != nullptr) {  // both channels sit on the slot grid: the pair and B/|df| are a table entry
+          const double2 t = __ldg(g.xci_tab + (size_t)ic.n * (4 * g.tab_S + 1) + (ic.pos2 - tch.pos2 + 2 * g.tab_S));
+          A = t.x;
+          X = pm * t.y;
         } else {
-          if (u <= 0.0) {
-            const double t = -u;
-            u = -v;
-            v = t;
+          const double df = ic.f - tch.f;
+          const double c = cxci * ic.B;
+          double u = c * (df + ic.B / 2), v = c * (df - ic.B / 2);
+          if (u > 0.0 && v < 0.0) {
+            A = asinh(u) - asinh(v);  // overlapping spectra (a candidate that is not free): literal form
+          } else {
+            if (u <= 0.0) {
+              const double t = -u;
+              u = -v;
+              v = t;
+            }
+            A = log((u + sqrt(u * u + 1.0)) / (v + sqrt(v * v + 1.0)));
           }
-          A = log((u + sqrt(u * u + 1.0)) / (v + sqrt(v * v + 1.0)));
+          X = pm * (ic.B / fabs(df)) * 5.0 / 3.0;
         }
-        X = pm * (ic.B / fabs(df)) * 5.0 / 3.0;
-        for (int h = 0; h < hops; h++) hm |= mask_has(im, sm.tlink[h]) ? (1u << h) : 0u;
+        // hops of the target the interferer is on: walk the common links (usually one or two)
+        unsigned long long c0 = im.x & tmask.x, c1 = im.y & tmask.y;
+        while (c0) {
+          hm |= 1u << sm.hop_of[__ffsll((long long)c0) - 1];
+          c0 &= c0 - 1;
+        }
+        while (c1) {
+          hm |= 1u << sm.hop_of[64 + __ffsll((long long)c1) - 1];
+          c1 &= c1 - 1;
+        }
       }
       // per hop of the target: sum over the 32 lanes (fixed butterfly order), lane h keeps the link's total
       for (int h = 0; h < hops; h++) {

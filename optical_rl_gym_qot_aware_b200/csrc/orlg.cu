@@ -643,6 +643,8 @@ extern "C" int orlg_gsnr_configure(orlg_engine* e, const orlg_gsnr_params* g) {
   e->gp.slot_hz = g->slot_hz;
   e->gp.path_mask = nullptr;
   e->gp.link_c = nullptr;
+  e->gp.xci_tab = nullptr;
+  e->gp.sci_tab = nullptr;
   if (e->p.E <= 128) {  // tables of the fast kernel: link sets of the paths, per-link span factors
     const int npaths = e->p.n_nodes * e->p.n_nodes * e->p.k;
     ulonglong2* pm = nullptr;
@@ -655,6 +657,21 @@ extern "C" int orlg_gsnr_configure(orlg_engine* e, const orlg_gsnr_params* g) {
     CK(cudaDeviceSynchronize());
     e->gp.path_mask = pm;
     e->gp.link_c = lc;
+    e->gp.xci_tab = nullptr;
+    e->gp.tab_S = e->p.S;
+    const long long entries = (long long)(e->p.S + 1) * (4 * e->p.S + 1);
+    const char* notab = getenv("ORLG_GSNR_NO_TABLE");  // A/B: evaluate the asinh pair instead of reading it
+    if (entries * 16 <= (16ll << 20) && !(notab && *notab == '1')) {
+      double2* tab = nullptr;
+      if ((rc = dev_alloc(e, &tab, (size_t)entries, false))) return rc;
+      double* sci = nullptr;
+      if ((rc = dev_alloc(e, &sci, (size_t)e->p.S + 1, false))) return rc;
+      gsnr_init_xci<<<(unsigned)((entries + 255) / 256), 256>>>(e->gp, e->p.S, tab, sci);
+      CK(cudaGetLastError());
+      CK(cudaDeviceSynchronize());
+      e->gp.xci_tab = tab;
+      e->gp.sci_tab = sci;
+    }
   }
   e->gsnr_ready = true;
   return ORLG_OK;

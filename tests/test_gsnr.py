@@ -173,7 +173,7 @@ def test_gsnr_for_actions_equals_explicit_queries(env_id):
     assert np.isnan(got[::17]).all() and np.isfinite(got[:, 0]).sum() >= n_env // 2
     assert np.array_equal(got, want, equal_nan=True)
     # the warp-cooperative kernel (link bit sets, ballot-compacted interferers, one log per asinh pair, butterfly
-    # sums) against the generic one it replaced (literal formula, sequential sums): 1e-9 dB, far inside 1e-4 dB
+    # sums, tabulated asinh pair) against the generic one it replaced (literal formula, sequential sums): 1e-7 dB
     import os
 
     os.environ["ORLG_GSNR_GENERIC"] = "1"
@@ -183,5 +183,5 @@ def test_gsnr_for_actions_equals_explicit_queries(env_id):
         os.environ.pop("ORLG_GSNR_GENERIC")
     assert np.array_equal(np.isnan(got), np.isnan(generic)) and np.array_equal(np.isinf(got), np.isinf(generic))
     fin = np.isfinite(got)
-    assert np.abs(got[fin] - generic[fin]).max() < 1e-9
+    assert np.abs(got[fin] - generic[fin]).max() < 1e-7  # the tabulated asinh pair uses exact grid distances
     eng.close()
