@@ -127,3 +127,37 @@ def test_stats_all_reduce_gloo_world2(tmp_path):
     assert res[0]["reward_sum"] == int((g * 3 - 10).sum())
     assert res[0]["envs"] == 37 and res[0]["fault"] == 2
     assert abs(res[0]["service_blocking_rate"] - (1 - (40 + g % 7).sum() / (100 + g).sum())) < 1e-15
+
+
+def test_bench_reference_arm_and_host_policy():
+    """`bench.py --impl reference` runs without a GPU (it times the oracle port) and prints the contract's line;
+    the host K-SP-FF policy of the e2e loop picks the first path whose block-length feature is not -1."""
+    import json
+    import subprocess
+    import sys
+
+    import numpy as np
+
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(repo, "bench.py"), "--impl", "reference", "--steps", "2",
+                          "--warmup", "3", "--ref-envs", "64"], capture_output=True, text=True, timeout=300, cwd=repo)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["unit"] == "env-steps/s" and line["value"] > 0
+    assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] >= 1
+    assert line["e2e"] == {"value": line["value"], "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert line["config"]["workload"] == "c2_deeprmsa_nsfnet_100" and line["gpu_launches"] == 0
+
+    sys.path.insert(0, repo)
+    import bench
+
+    n, k, j, nodes = 1000, 5, 1, 14
+    rng = np.random.default_rng(0)
+    obs = rng.random((1 + 2 * nodes + (2 * j + 3) * k, n), dtype=np.float32)
+    blocked = rng.random((k, n)) < 0.6
+    for p in range(k):
+        obs[1 + 2 * nodes + p * (2 * j + 3) + 1][blocked[p]] = -1.0
+    want = np.array([next((p * j for p in range(k) if not blocked[p, i]), k * j) for i in range(n)])
+    out_buf = np.zeros((n, 1), np.int32)
+    assert np.array_equal(bench.host_policy_kspff(obs, nodes, k, j, out=out_buf)[:, 0], want)
+    assert np.array_equal(bench.host_policy_kspff(obs, nodes, k, j)[:, 0], want)
