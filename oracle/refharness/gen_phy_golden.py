@@ -80,6 +80,11 @@ def run(name, topo_file, mat_key, heuristic, no_groom_stub, n_steps, **kw):
         done = np.zeros(n_steps, np.uint8)
         counters = np.zeros((n_steps, 8), np.int64)
         stats = np.zeros((n_steps, 8), np.float64)
+        # periodic defragmentation (phy_rmsa_env.py:355-417): cumulative move counters and a checksum of
+        # available_channels after every step, so that each reallocation is pinned, not only the final map
+        moves = np.zeros((n_steps, 3), np.int64)
+        avail_sum = np.zeros(n_steps, np.int64)
+        weights = None
         reqs[0] = req_of(env)
         for t in range(n_steps):
             path, chans = heuristic(env)
@@ -96,11 +101,16 @@ def run(name, topo_file, mat_key, heuristic, no_groom_stub, n_steps, **kw):
                         env.total_modulation_level_episode, env.channels_accepted_episode,
                         env.physical_services_accepted_episode, info["number_cuts_total"], info["rss_total_metric"])
             reqs[t + 1] = req_of(env)
+            moves[t] = (env.counted_moves, env.counted_moves_groom, env.counted_defrag_cycles)
+            av = np.asarray(env.topology.graph["available_channels"], np.int64).ravel()
+            if weights is None:
+                weights = np.arange(1, av.size + 1, dtype=np.int64)
+            avail_sum[t] = int(np.dot(av, weights))
             if d:
                 env.reset()
             counters[t] = counters_of(env)
         out = dict(env_kind=3, topo_file=topo_file, requests=reqs, actions=actions, accepted=accepted, reward=reward,
-                   done=done, counters=counters, stats=stats, virtual=virtual,
+                   done=done, counters=counters, stats=stats, virtual=virtual, moves=moves, avail_sum=avail_sum,
                    channel_state=np.int32(0 if no_groom_stub else (1 if kwargs.get("grooming") else 2)),
                    final_avail=np.asarray(env.topology.graph["available_channels"], np.uint8)[None],
                    kwargs_keys=np.array(sorted(kwargs)), tables_key=np.array(mat_key))
@@ -147,6 +157,13 @@ def main():
         episode_length=170, grooming=True, **tiny)
     run("phy_us14_cstate_sapff_100ch", us, US, ref.sapff_rmsa, False, 1500, seed=21, load=1900, episode_length=210,
         **small)
+    # periodic defragmentation: targets for the round-2 kernel; no engine path consumes them yet
+    run("defrag_phy_us14_defrag_cut_100ch", us, US, ref.phy_aware_bmfa_rmsa, False, 1200, seed=22, load=1700,
+        episode_length=240, defrag_period=10, number_moves=10, metric="cut", **small)
+    run("defrag_phy_us14_defrag_groom_cut_100ch", us, US, ref.phy_aware_bmfa_rmsa, False, 1200, seed=23, load=1900,
+        episode_length=240, grooming=True, defrag_period=10, number_moves=10, metric="cut", **small)
+    run("defrag_phy_jpn12_defrag_rss_64ch", jpn, JPN, ref.phy_aware_bmfa_rss_rmsa, False, 900, seed=24, load=1300,
+        episode_length=190, defrag_period=20, number_moves=5, metric="rss", **tiny)
     run("phy_jpn12_sapbm_64ch", jpn, JPN, ref.phy_aware_sapbm_rmsa, True, 1500, seed=14, load=1300,
         episode_length=100, **tiny)
 

@@ -18,7 +18,7 @@ TOPO_SHORT = {
 }
 
 CASES = sorted(f[:-4] for f in os.listdir(GOLDEN)
-               if f.endswith(".npz") and not f.startswith(("topology_", "gsnr_", "phy_", "phytab_")))
+               if f.endswith(".npz") and not f.startswith(("topology_", "gsnr_", "phy_", "phytab_", "defrag_")))
 PHY_CASES = sorted(f[:-4] for f in os.listdir(GOLDEN) if f.startswith("phy_") and f.endswith(".npz"))
 GSNR_CASES = sorted(f[:-4] for f in os.listdir(GOLDEN) if f.startswith("gsnr_") and f.endswith(".npz"))
 ENV_NAME = {0: "RMSA-v0", 1: "DeepRMSA-v0", 2: "RMCSA-v0", 3: "PhyRMSA-v0"}

@@ -60,3 +60,23 @@ def test_phy_tables_first_match_and_cut_terms():
         adj[b].add(a)
     expect = sum((1 if i in (0, h) else 2) * len(adj[v] - on) for i, v in enumerate(nodes))
     assert ph.cut_count[pr * t.k_paths + ip] == expect
+
+
+def test_defragmentation_is_refused_and_its_pins_exist():
+    """PhyRMSA periodic defragmentation is not built: asking for it must fail loudly, never
+    run without it.  The traces of the unmodified reference that the round-2 kernel has to reproduce are already
+    committed (`defrag_phy_*.npz`: per step the cumulative move counters and a checksum of available_channels)."""
+    import os
+
+    from optical_rl_gym_qot_aware_b200 import spec as S
+
+    g, spec = G.load_case("phy_us14_bmfa_cut_100ch")
+    with pytest.raises(NotImplementedError):
+        S.make_spec("PhyRMSA-v0", spec.tables, defrag_period=10, number_moves=10, modulation_level=spec.phy.mod_level,
+                    connections_detail=np.zeros((1, 2), np.int32), gsnr=spec.phy.gsnr)
+    pins = sorted(f for f in os.listdir(G.GOLDEN) if f.startswith("defrag_phy_"))
+    assert len(pins) == 3
+    for f in pins:
+        z = np.load(os.path.join(G.GOLDEN, f))
+        assert z["moves"].shape == (len(z["actions"]), 3) and z["moves"][:, 0].max() > 0 and z["moves"][:, 2].max() > 0
+        assert int(z["kw_defrag_period"]) in (10, 20) and z["avail_sum"].shape == (len(z["actions"]),)
