@@ -329,9 +329,10 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
     launches = eng.launch_count - launches0
     step_ms, kern_ms, gsnr_ms = ev_times(evs)
     bytes_note = "SURVEY.md 8(d): every row of the k candidate paths read once, chosen path written, one release"
-    if spec.env_kind == S.ENV_RMCSA and fused:
-        # first-core-first-fit stops at the first (path, core) that fits, so the rows it has to read follow from
-        # the decisions actually taken (SURVEY's 6 454 B assumes all k paths x all cores every step)
+    if fused and ((spec.env_kind == S.ENV_RMCSA and hid == S.H_SAP_BM_FC_FF) or
+                  (spec.env_kind == S.ENV_RMSA and hid == S.H_SAP_FF)):
+        # shortest-available-path first-fit stops at the first path (RMCSA: first (path, core)) that fits, so the rows
+        # it has to read follow from the decisions actually taken; SURVEY 8(d)'s figures assume all k paths (x all cores)
         a = act.cpu().numpy()
         rq, t = eng.requests(), spec.tables
         k, cores = t.k_paths, spec.num_cores
@@ -340,15 +341,17 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
         idx = np.arange(n_env)
         ok = (a[:, 0] >= 0) & (a[:, 0] < k)
         pth = np.where(ok, a[:, 0], 0)
-        rows_read = np.where(ok, cum[idx, pth] * cores + hops[idx, pth] * (a[:, 2] + 1), cum[:, k] * cores)
+        core = a[:, 2] if spec.env_kind == S.ENV_RMCSA else np.zeros(n_env, a.dtype)
+        rows_read = np.where(ok, cum[idx, pth] * cores + hops[idx, pth] * (core + 1), cum[:, k] * cores)
         cnt_now = eng.counters()
         accept = float(cnt_now[:, 1].sum()) / max(1.0, float(cnt_now[:, 0].sum()))
         rows_rw = accept * 3.0 * float(np.where(ok, hops[idx, pth], 0).mean())  # write the chosen rows, read+write a release
         words = (spec.num_slots + 31) // 32
+        upper = bytes_per_step
         bytes_per_step = int(round(4 * words * (float(rows_read.mean()) + rows_rw) + 168))
-        bytes_note = (f"rows of the (path, core) pairs first-core-first-fit examined for the decisions taken "
+        bytes_note = (f"rows of the paths{' x cores' if cores > 1 else ''} first-fit examined for the decisions taken "
                       f"({float(rows_read.mean()):.2f} rows read per step on average), chosen rows written, one release "
-                      f"per accepted service, 168 B fixed (SURVEY.md 8(d) upper bound: 6 454 B)")
+                      f"per accepted service, 168 B fixed (SURVEY.md 8(d) upper bound: {upper} B)")
     if gs_out is not None and not bool(torch.isfinite(gs_out[:, 0]).any()):
         raise RuntimeError("GSNR evaluation produced no finite value")
 
@@ -572,7 +575,10 @@ def run_b200(args, spec, hid, bytes_per_step, env_id, wl):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": traffic, "kernel": "env_kernel (MODE_STEP)", "peak_source": peak_src,
+                     "traffic": traffic, "peak_source": peak_src,
+                     "kernel": "env_kernel (MODE_STEP)" + ("; this workload's step is dominated by the GN-model launch "
+                                                           "(extra.gsnr_kernel_us, fp64 issue bound, DESIGN.md section 6)"
+                                                           if gsnr_ms is not None else ""),
                      "bytes_per_env_step": bytes_per_step, "bytes_definition": bytes_note,
                      "kernel_ms": kern_avg_s * 1e3},
         "extra": {"two_launch_env_steps_per_s": (total_envs * K / (two_ms * 1e-3)) if two_ms else None,
