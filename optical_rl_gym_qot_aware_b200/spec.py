@@ -27,6 +27,12 @@ H_SP_FF, H_SAP_FF, H_LLP_FF, H_SAP_BM_FC_FF, H_RANDOM = 0, 1, 2, 3, 4
 H_PHY_SAP_FF, H_PHY_SAP_BM, H_PHY_BM_FF, H_PHY_BM_FA_CUT = 5, 6, 7, 8  # phy_rmsa_env.py:1676,1254,1317,1375
 H_PATH_FF, H_PHY_FA_FF = 9, 10  # rmsa_env.py:974-1008, phy_rmsa_env.py:1508-1569
 H_PHY_BM_FA_RSS, H_PHY_FA_FF_RSS = 11, 12  # phy_rmsa_env.py:1441-1505, :1572-1633
+H_SAP_GN_FF = 13  # shortest available path, first fit, first candidate that passes the GN-model QoT gate
+
+# SD-FEC SNR thresholds by spectral efficiency 1..6 (target_SNR_dB_vec, examples/create_topology_gn.py:65): the
+# minimum_osnr the GN topology builder attaches to BPSK .. 64QAM (:68-110)
+SD_FEC_SNR_DB = (3.71925646843142, 6.72955642507124, 10.8453935345953, 13.2406469649752, 16.1608982942870,
+                 19.0134649345090)
 
 ENV_IDS = {
     "RMSA-v0": ENV_RMSA,
@@ -80,6 +86,13 @@ class EnvSpec:
     # RMSA-v0 / DeepRMSA-v0: keep what the step's info dict needs (rmsa_env.py:276-332): time-weighted link
     # statistics, per-bit-rate histograms, sum of slots x hops of the running services
     info_stats: bool = False
+    # GN-model QoT gate (RMSA-v0 / RMCSA-v0; include/orlg.h "QoT gate"): the GSNR of the candidate and of its
+    # neighbours (examples/calculate_osnr.py:9-56) must meet the SD-FEC threshold of their modulations
+    qot_gate: bool = False
+    qot_adaptive: bool = False
+    qot_thr_db: Optional[np.ndarray] = None   # [16] threshold in dB by spectral efficiency
+    qot_se: Optional[np.ndarray] = None       # spectral efficiencies an adaptive RMSA-v0 env tries, descending
+    qot_gsnr: Optional[object] = None         # GsnrParams
 
     @property
     def action_dim(self) -> int:
@@ -164,6 +177,10 @@ def make_spec(
     defrag_period=None,
     number_moves=None,
     metric: str = "cut",
+    qot: Optional[str] = None,
+    qot_adaptive: bool = False,
+    qot_thresholds_db=None,
+    qot_gsnr_params=None,
 ) -> EnvSpec:
     kind = ENV_IDS[env_id] if isinstance(env_id, str) else int(env_id)
     n = tables.n_nodes
@@ -252,6 +269,19 @@ def make_spec(
     spec.info_stats = bool(info_stats) and kind in (ENV_RMSA, ENV_DEEPRMSA)
     if kind == ENV_PHYRMSA:
         spec.phy_grooming = 1 if grooming else (2 if keep_channel_state else 0)
+    if qot:
+        if qot != "gn" or kind not in (ENV_RMSA, ENV_RMCSA):
+            raise ValueError("qot='gn' (GN-model QoT gate) is defined for RMSA-v0 and RMCSA-v0")
+        spec.qot_gate, spec.qot_adaptive = True, bool(qot_adaptive)
+        thr = np.full(16, np.inf, np.float64)  # a spectral efficiency without a threshold can never pass
+        thr[0] = -np.inf
+        src = dict(enumerate(SD_FEC_SNR_DB, start=1)) if qot_thresholds_db is None else dict(qot_thresholds_db)
+        for se, v in src.items():
+            thr[int(se)] = float(v)
+        spec.qot_thr_db = thr
+        ses = sorted({int(x) for x in tables.mod_se}, reverse=True)[:8]
+        spec.qot_se = np.array(ses, np.int32)
+        spec.qot_gsnr = qot_gsnr_params if qot_gsnr_params is not None else gsnr_params(tables, float(channel_width))
     assert spec.num_slots <= 1024 and tables.n_edges <= 128
     return spec
 

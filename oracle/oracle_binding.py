@@ -72,6 +72,13 @@ class OracleConfig(C.Structure):
         ("edge_nodes", C.c_void_p),
         ("info_stats", C.c_int32),
         ("info_pad", C.c_int32),
+        ("qot_gate", C.c_int32),
+        ("qot_adaptive", C.c_int32),
+        ("qot_n_se", C.c_int32),
+        ("qot_pad", C.c_int32),
+        ("qot_se", C.c_int32 * 8),
+        ("qot_thr_db", C.c_double * 16),
+        ("qot_gsnr", C.c_void_p),
     ]
 
 
@@ -126,6 +133,7 @@ def lib():
         L.oracle_info.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
         L.oracle_info.restype = C.c_int
         L.oracle_gsnr.argtypes = [C.c_void_p, C.POINTER(OracleGsnrParams), C.c_void_p, C.c_void_p]
+        L.oracle_qot_last.argtypes = [C.c_void_p, C.c_void_p]
         L.oracle_services.restype = C.c_int64
         L.oracle_services.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
         L.oracle_dlog.restype = C.c_double
@@ -192,6 +200,19 @@ class OracleSpec:
         c.n_bit_rates = 0 if spec.bit_rates is None else len(spec.bit_rates)
         c.seed = spec.seed & 0xFFFFFFFFFFFFFFFF
         c.bit_rate_lo, c.bit_rate_hi = spec.bit_rate_lo, spec.bit_rate_hi
+        if getattr(spec, "qot_gate", False):
+            gp = spec.qot_gsnr
+            k["qot_span_count"] = np.ascontiguousarray(gp.span_count, np.int32)
+            k["qot_span_km"] = np.ascontiguousarray(gp.span_length_km, np.float64)
+            self.qot_gp = OracleGsnrParams(gp.launch_power_w, gp.attenuation_per_m, gp.noise_figure_lin, gp.f0_hz,
+                                           gp.slot_hz, k["qot_span_count"].ctypes.data, k["qot_span_km"].ctypes.data)
+            c.qot_gate, c.qot_adaptive = 1, int(spec.qot_adaptive)
+            c.qot_n_se = len(spec.qot_se)
+            for i, v in enumerate(spec.qot_se):
+                c.qot_se[i] = int(v)
+            for i, v in enumerate(spec.qot_thr_db):
+                c.qot_thr_db[i] = float(v)
+            c.qot_gsnr = C.cast(C.pointer(self.qot_gp), C.c_void_p)
         self.spec = spec
 
 
@@ -285,6 +306,12 @@ class OracleEnv:
         out = np.zeros(2, np.float64)
         self.L.oracle_gsnr(self.h, C.byref(c), q.ctypes.data, out.ctypes.data)
         return out
+
+    def qot_last(self):
+        """(candidate GSNR dB, lowest neighbour GSNR dB) of the last candidate the QoT gate evaluated."""
+        o = np.zeros(2, np.float64)
+        self.L.oracle_qot_last(self.h, o.ctypes.data)
+        return o
 
     def services(self):
         """Live services: rows (pair, path, core, initial_slot, number_slots, se)."""

@@ -149,6 +149,7 @@ struct oracle_env {
   double total_path_length_ep, total_gsnr_ep;
   int64_t total_path_index_ep, total_mod_level_ep, channels_accepted_ep, physical_accepted_ep;
   double info_cuts, info_rss; /* number_cuts_total / rss_total_metric of the last step's info (:313-314) */
+  double qot_last[2];         /* QoT gate: GSNR of the last candidate evaluated, lowest neighbour GSNR with it present */
   int16_t* link_of; /* [N][N] edge index or -1 (topology[a][b]["index"]) */
   const oracle_request* trace;
   int64_t trace_len, trace_stride;
@@ -561,6 +562,10 @@ void oracle_reset(oracle_env* e, int full) {
 }
 
 /* ------------------------------------------------------------- stepping -- */
+/* GN-model QoT gate (defined with the GN model at the end of this file) */
+static int qot_gate_eval(oracle_env* e, int pair, int path, int core, int start, int n, int se);
+static int qot_alone_ok(const oracle_env* e, int pair, int path, int start, int n, int se);
+static int mods_by_se_desc(const oracle_env* e, int* order);
 /* _crosstalk_is_acceptable rmcsa_env.py:341-384.  The modulation-only factors
  * (10**x terms) are evaluated by the caller in Python with the reference's own
  * expression order and arrive as mod_snr_coeff / mod_reach. */
@@ -910,6 +915,33 @@ void oracle_phy_stats(const oracle_env* e, double* out) {
 /* RMSAEnv.step rmsa_env.py:222-341 (decision part) */
 static int rmsa_decide(oracle_env* e, int path, int slot, int32_t* alloc) {
   int pair = cur_pair(e), accepted = 0, n = 0;
+  if (e->c.qot_gate && e->c.env_kind == 0) {
+    /* RMSA-v0 with the GN-model QoT gate: the modulation is path.best_modulation (rmsa_env.py:708-719) or,
+     * with qot_adaptive, the most efficient one whose candidate passes the gate at (path, slot) */
+    e->qot_last[0] = e->qot_last[1] = NAN;
+    if (path >= 0 && slot >= 0 && path < e->c.k_paths && slot < e->c.num_slots && hops_of(e, pair, path) > 0) {
+      int nse = e->c.qot_adaptive ? e->c.qot_n_se : 1;
+      for (int t = 0; t < nse && !accepted; t++) {
+        int se = e->c.qot_adaptive ? e->c.qot_se[t] : e->c.path_se[(size_t)pair * e->c.k_paths + path];
+        n = number_slots(e, se);
+        if (!is_path_free(e, pair, path, 0, slot, n)) break; /* a wider channel does not fit either */
+        if (e->c.qot_adaptive && !qot_alone_ok(e, pair, path, slot, n, se)) continue;
+        if (qot_gate_eval(e, pair, path, 0, slot, n, se)) {
+          provision_path(e, pair, path, 0, slot, n);
+          accepted = 1;
+          svc s = {e->cur.arrival + e->cur.holding, pair, path, 0, slot, n, se};
+          heap_push(e, s);
+        }
+      }
+    }
+    if (alloc) {
+      alloc[0] = accepted;
+      alloc[1] = accepted ? path : -1;
+      alloc[2] = accepted ? slot : -1;
+      alloc[3] = accepted ? n : 0;
+    }
+    return accepted;
+  }
   if (path >= 0 && slot >= 0 && path < e->c.k_paths && slot < e->c.num_slots &&
       hops_of(e, pair, path) > 0) {
     n = number_slots(e, e->c.path_se[(size_t)pair * e->c.k_paths + path]);
@@ -957,11 +989,13 @@ void oracle_step(oracle_env* e, const int32_t* a, int32_t* reward, uint8_t* done
   } else { /* RMCSAEnv.step rmcsa_env.py:209-339 */
     int path = a[0], mod = a[1], core = a[2], slot = a[3], n = 0;
     int pair = cur_pair(e);
+    if (e->c.qot_gate) e->qot_last[0] = e->qot_last[1] = NAN;
     if (path >= 0 && mod >= 0 && core >= 0 && slot >= 0 && path < k && mod < e->c.n_mods &&
         core < e->c.num_cores && slot < S && hops_of(e, pair, path) > 0) {
       n = number_slots(e, e->c.mod_se[mod]);
       if (is_path_free(e, pair, path, core, slot, n) &&
-          crosstalk_ok(e, mod, e->c.path_length[(size_t)pair * k + path])) {
+          crosstalk_ok(e, mod, e->c.path_length[(size_t)pair * k + path]) &&
+          (!e->c.qot_gate || qot_gate_eval(e, pair, path, core, slot, n, e->c.mod_se[mod]))) {
         provision_path(e, pair, path, core, slot, n);
         accepted = 1;
         svc s = {e->cur.arrival + e->cur.holding, pair, path, core, slot, n, e->c.mod_se[mod]};
@@ -1035,8 +1069,59 @@ static int first_fit(const oracle_env* e, int pair, int path, int core, int n) {
   return -1;
 }
 
+/* Shortest available path, first fit, GN-model QoT (heuristic id 13): the first candidate, in the order the
+ * reference's first-fit heuristics walk them (rmsa_env.py:901-913, rmcsa_env.py:882-911), that passes the QoT
+ * gate.  RMSA-v0: per path the modulation is path.best_modulation or, adaptive, every spectral efficiency in
+ * descending order; RMCSA-v0: per path the best modulation by reach (utils.py:105-117) or, adaptive, every
+ * modulation by descending spectral efficiency, on the first core that has room. */
+static void qot_heuristic(oracle_env* e, int32_t* a) {
+  int k = e->c.k_paths, S = e->c.num_slots, pair = cur_pair(e);
+  e->qot_last[0] = e->qot_last[1] = NAN;
+  if (e->c.env_kind == 0) {
+    a[0] = k; a[1] = S;
+    int nse = e->c.qot_adaptive ? e->c.qot_n_se : 1;
+    for (int p = 0; p < k; p++) {
+      if (hops_of(e, pair, p) <= 0) continue;
+      for (int t = 0; t < nse; t++) {
+        int se = e->c.qot_adaptive ? e->c.qot_se[t] : e->c.path_se[(size_t)pair * k + p];
+        int n = number_slots(e, se);
+        int s = first_fit(e, pair, p, 0, n);
+        if (s < 0) break;
+        if (e->c.qot_adaptive && !qot_alone_ok(e, pair, p, s, n, se)) continue;
+        if (qot_gate_eval(e, pair, p, 0, s, n, se)) { a[0] = p; a[1] = s; return; }
+      }
+    }
+    return;
+  }
+  a[0] = k; a[1] = e->c.n_mods; a[2] = e->c.num_cores; a[3] = S;
+  int order[64];
+  int nm = mods_by_se_desc(e, order);
+  for (int p = 0; p < k; p++) {
+    if (hops_of(e, pair, p) <= 0) continue;
+    double len = e->c.path_length[(size_t)pair * k + p];
+    int first = -1; /* get_best_modulation_format: the first in SE-descending order that reaches */
+    for (int i = 0; i < nm && first < 0; i++)
+      if (len <= e->c.mod_max_length[order[i]]) first = i;
+    int lo = e->c.qot_adaptive ? 0 : first, hi = e->c.qot_adaptive ? nm : first + 1;
+    if (lo < 0) continue;
+    for (int i = lo; i < hi; i++) {
+      int m = order[i], se = e->c.mod_se[m];
+      int n = number_slots(e, se), core = -1, s = -1;
+      for (int c = 0; c < e->c.num_cores && s < 0; c++) {
+        s = first_fit(e, pair, p, c, n);
+        if (s >= 0) core = c;
+      }
+      if (s < 0) break; /* no core has room; a wider channel does not fit either */
+      if (!crosstalk_ok(e, m, len)) continue;
+      if (e->c.qot_adaptive && !qot_alone_ok(e, pair, p, s, n, se)) continue;
+      if (qot_gate_eval(e, pair, p, core, s, n, se)) { a[0] = p; a[1] = m; a[2] = core; a[3] = s; return; }
+    }
+  }
+}
+
 void oracle_heuristic(oracle_env* e, int hid, int32_t* a) {
   if (e->c.env_kind == 3) { phy_heuristic(e, hid, a); return; }
+  if (hid == 13 && e->c.qot_gate && (e->c.env_kind == 0 || e->c.env_kind == 2)) { qot_heuristic(e, a); return; }
   int k = e->c.k_paths, S = e->c.num_slots, pair = cur_pair(e);
   if (e->c.env_kind == 0) {
     a[0] = k; a[1] = S;
@@ -1405,3 +1490,72 @@ int64_t oracle_services(const oracle_env* e, int32_t* out6, int64_t max_rows) {
   }
   return e->heap_len;
 }
+
+/* ---- GN-model QoT gate (oracle_config.qot_gate) ---------------------------------------------------
+ * accept iff the candidate's GSNR meets the threshold of its modulation and every neighbour's GSNR,
+ * re-evaluated with the candidate present, still meets its own.  Each GSNR is one literal call of
+ * calculate_osnr; nothing is cached.  qot_last = (candidate, lowest neighbour; NaN when the candidate
+ * itself failed and the neighbours were not looked at). */
+static int qot_gate_eval(oracle_env* e, int pair, int path, int core, int start, int n, int se) {
+  const oracle_gsnr_params* g = e->c.qot_gsnr;
+  gn_service cand = gn_service_of(g, -1, start, n, se);
+  double gc = gsnr_of(e, g, pair, path, core, &cand, 0, pair, path, core, &cand);
+  e->qot_last[0] = gc;
+  e->qot_last[1] = NAN;
+  if (!(gc >= e->c.qot_thr_db[se])) return 0;
+  int ok = 1;
+  double mn = INFINITY;
+  const int16_t* CL = links_of(e, pair, path, 0);
+  for (int64_t i = 0; i < e->heap_len; i++) {
+    const svc* s = &e->heap[i];
+    if (s->core != core) continue;
+    int shares = 0;
+    for (int h = 0; h < hops_of(e, pair, path); h++) shares |= path_uses(e, s->pair, s->path, CL[h]);
+    if (!shares) continue;
+    gn_service t = gn_service_of(g, (int)i, s->initial_slot, s->number_slots, s->se);
+    double v = gsnr_of(e, g, s->pair, s->path, s->core, &t, 1, pair, path, core, &cand);
+    if (v < mn) mn = v;
+    if (!(v >= e->c.qot_thr_db[s->se])) ok = 0;
+  }
+  e->qot_last[1] = mn;
+  return ok;
+}
+
+/* the channel alone on its path (no interferer): ASE and self-channel NLI only */
+static int qot_alone_ok(const oracle_env* e, int pair, int path, int start, int n, int se) {
+  const oracle_gsnr_params* g = e->c.qot_gsnr;
+  gn_service cand = gn_service_of(g, -1, start, n, se);
+  int hops = hops_of(e, pair, path);
+  const int16_t* L = links_of(e, pair, path, 0);
+  gn_span* spans[64] = {0};
+  const gn_service* running[64] = {0};
+  int n_spans[64] = {0}, n_running[64] = {0};
+  for (int h = 0; h < hops; h++) {
+    int l = L[h];
+    n_spans[h] = g->span_count[l];
+    spans[h] = (gn_span*)malloc(sizeof(gn_span) * n_spans[h]);
+    for (int s = 0; s < n_spans[h]; s++) {
+      spans[h][s].length = g->span_length_km[l];
+      spans[h][s].attenuation_normalized = g->attenuation_per_m;
+      spans[h][s].noise_figure_normalized = g->noise_figure_lin;
+    }
+    running[h] = NULL;
+    n_running[h] = 0;
+  }
+  double v = gn_calculate_osnr(&cand, hops, (const gn_span* const*)spans, n_spans, running, n_running);
+  for (int h = 0; h < hops; h++) free(spans[h]);
+  return v >= e->c.qot_thr_db[se];
+}
+
+/* modulation rows by descending spectral efficiency, stable (the order get_best_modulation_format walks, utils.py:105-117) */
+static int mods_by_se_desc(const oracle_env* e, int* order) {
+  int nm = e->c.n_mods < 64 ? e->c.n_mods : 64;
+  for (int m = 0; m < nm; m++) order[m] = m;
+  for (int a = 1; a < nm; a++)
+    for (int b = a; b > 0 && e->c.mod_se[order[b]] > e->c.mod_se[order[b - 1]]; b--) {
+      int t = order[b]; order[b] = order[b - 1]; order[b - 1] = t;
+    }
+  return nm;
+}
+
+void oracle_qot_last(const oracle_env* e, double* out2) { out2[0] = e->qot_last[0]; out2[1] = e->qot_last[1]; }

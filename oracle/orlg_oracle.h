@@ -33,6 +33,13 @@ typedef struct oracle_request { /* same layout as orlg_request */
   int16_t dst;
 } oracle_request;
 
+/* GN-model GSNR (examples/calculate_osnr.py:9-56); same parameter block as orlg_gsnr_params */
+typedef struct oracle_gsnr_params {
+  double launch_power_w, attenuation_per_m, noise_figure_lin, f0_hz, slot_hz;
+  const int32_t* span_count;
+  const double* span_length_km;
+} oracle_gsnr_params;
+
 typedef struct oracle_config {
   int32_t env_kind; /* 0 RMSA, 1 DeepRMSA, 2 RMCSA, 3 PhyRMSA */
   int32_t n_nodes, n_edges, k_paths, max_hops;
@@ -71,6 +78,19 @@ typedef struct oracle_config {
   /* 1: keep what the info dict of RMSAEnv.step needs (rmsa_env.py:276-332): time-weighted link statistics
    * (_update_link_stats :562-641), per-bit-rate histograms; RMSA-v0 / DeepRMSA-v0 */
   int32_t info_stats, info_pad;
+  /* GN-model QoT gate (RMSA-v0 / RMCSA-v0).  The reference has no env that calls calculate_osnr;
+   * the gate is what BASELINE.json's north_star describes: the GN-model GSNR of the candidate lightpath and of
+   * its neighbours (running services sharing a link and core with it, re-evaluated with the candidate present)
+   * feeds the QoT feasibility check - accept iff every one of them meets the SD-FEC threshold of its own
+   * modulation (minimum_osnr = target_SNR_dB_vec, examples/create_topology_gn.py:65-110) - and, with
+   * qot_adaptive, the modulation-format choice (RMSA-v0: the env assigns the most efficient modulation that
+   * passes, spectral efficiencies qot_se[] in descending order; a modulation is tried only if the channel's
+   * interference-free GSNR meets its threshold).  Every GSNR is one literal call of calculate_osnr
+   * (examples/calculate_osnr.py:9-56). */
+  int32_t qot_gate, qot_adaptive, qot_n_se, qot_pad;
+  int32_t qot_se[8];
+  double qot_thr_db[16];             /* by spectral efficiency */
+  const oracle_gsnr_params* qot_gsnr;
 } oracle_config;
 
 typedef struct oracle_env oracle_env;
@@ -115,15 +135,12 @@ int oracle_info(const oracle_env* e, double* out, int max_values);
 /* channel_state (phy_rmsa_env.py:158-166) in append order, rows (src*N+dst, idp, channel, used, free, capacity) */
 int64_t oracle_phy_channel_state(const oracle_env* e, int32_t* out, int64_t max_entries);
 
-/* GN-model GSNR (examples/calculate_osnr.py:9-56); same parameter block as orlg_gsnr_params */
-typedef struct oracle_gsnr_params {
-  double launch_power_w, attenuation_per_m, noise_figure_lin, f0_hz, slot_hz;
-  const int32_t* span_count;
-  const double* span_length_km;
-} oracle_gsnr_params;
 /* query[4] = (path | core << 16, first_slot, n_slots, se or 0); out2 = (candidate dB, min neighbour dB) */
 void oracle_gsnr(const oracle_env* e, const oracle_gsnr_params* g, const int32_t* query, double* out2);
 int64_t oracle_services(const oracle_env* e, int32_t* out6, int64_t max_rows);
+/* QoT gate of the last step / heuristic call: out2 = (candidate GSNR dB, lowest neighbour GSNR dB with the
+ * candidate present) of the last candidate evaluated; NaN where nothing was evaluated */
+void oracle_qot_last(const oracle_env* e, double* out2);
 
 /* persistent pool of envs stepped with a heuristic on host threads (the envs keep
  * their state between calls); the timed CPU arm of bench.py */

@@ -18,8 +18,9 @@ TOPO_SHORT = {
 }
 
 CASES = sorted(f[:-4] for f in os.listdir(GOLDEN)
-               if f.endswith(".npz") and not f.startswith(("topology_", "gsnr_", "phy_", "phytab_", "defrag_")))
+               if f.endswith(".npz") and not f.startswith(("topology_", "gsnr_", "phy_", "phytab_", "defrag_", "qot_")))
 PHY_CASES = sorted(f[:-4] for f in os.listdir(GOLDEN) if f.startswith("phy_") and f.endswith(".npz"))
+QOT_CASES = sorted(f[:-4] for f in os.listdir(GOLDEN) if f.startswith("qot_") and f.endswith(".npz"))
 GSNR_CASES = sorted(f[:-4] for f in os.listdir(GOLDEN) if f.startswith("gsnr_") and f.endswith(".npz"))
 ENV_NAME = {0: "RMSA-v0", 1: "DeepRMSA-v0", 2: "RMCSA-v0", 3: "PhyRMSA-v0"}
 
@@ -49,5 +50,7 @@ def load_case(name: str):
         kw.pop("bit_rate_selection", None)
         if "channel_state" in g:  # 0: use_existing_channels stubbed out in the harness, 1: grooming=True, 2: unstubbed
             kw["keep_channel_state"] = int(g["channel_state"]) != 0
+    if "adaptive" in g and "gsnr" in g:  # GN-model QoT gate traces (oracle/refharness/gen_qot_golden.py)
+        kw.update(qot="gn", qot_adaptive=bool(int(g["adaptive"])))
     spec = S.make_spec(ENV_NAME[int(g["env_kind"])], tables, request_source=S.SRC_REPLAY, **kw)
     return g, spec
