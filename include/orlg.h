@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define ORLG_ABI_VERSION 1
+#define ORLG_ABI_VERSION 2
 
 enum {
   ORLG_OK = 0,
@@ -70,7 +70,11 @@ enum {
   ORLG_H_PATH_FF = 9,        /* PathOnlyFirstFitAction rmsa_env.py:974-1008 (orlg_path_first_fit only) */
   ORLG_H_PHY_FA_FF = 10,     /* phy_aware_faff_rmsa  phy_rmsa_env.py:1508-1569 */
   ORLG_H_PHY_BM_FA_RSS = 11, /* phy_aware_bmfa_rss_rmsa phy_rmsa_env.py:1441-1505 (calculate_r_spatial :1085-1108; <= 64 links) */
-  ORLG_H_PHY_FA_FF_RSS = 12  /* phy_aware_faff_rss_rmsa phy_rmsa_env.py:1572-1633 */
+  ORLG_H_PHY_FA_FF_RSS = 12, /* phy_aware_faff_rss_rmsa phy_rmsa_env.py:1572-1633 */
+  /* engines with the GN-model QoT gate (orlg_config.qot_gate): the walk of shortest_available_path_first_fit
+   * (rmsa_env.py:901-913) / ..._best_modulation_first_core_first_fit (rmcsa_env.py:882-911) that returns the
+   * first candidate passing the gate; with qot_adaptive every modulation is tried per path, most efficient first */
+  ORLG_H_SAP_GN_FF = 13
 };
 
 enum {
@@ -93,6 +97,23 @@ typedef struct orlg_request {
   int16_t src; /* node ids in graph["node_indices"] order */
   int16_t dst;
 } orlg_request; /* 24 bytes */
+
+/* ---- GN-model GSNR: calculate_osnr, examples/calculate_osnr.py:9-56 --------------------
+ * Physical inputs the reference leaves undefined (SURVEY.md F2) are explicit here.  Every
+ * link is split into span_count[l] equal spans of span_length_km[l]
+ * (examples/create_topology_gn.py:122-134: int(length // 80) + 1 spans).  A service that
+ * occupies slots [first, first+n) has bandwidth n*slot_hz and centre frequency
+ * f0_hz + (first + n/2)*slot_hz. */
+typedef struct orlg_gsnr_params {
+  double launch_power_w;    /* per-channel launch power (1e-3 = 0 dBm) */
+  double attenuation_per_m; /* field attenuation alpha [1/m]: power falls as exp(-2*alpha*L) */
+  double noise_figure_lin;  /* amplifier noise figure, linear */
+  double f0_hz;             /* lower edge of slot 0 */
+  double slot_hz;           /* slot width in Hz (channel_width * 1e9) */
+  const int32_t* span_count;    /* host, [n_edges] */
+  const double* span_length_km; /* host, [n_edges] */
+} orlg_gsnr_params;
+
 
 typedef struct orlg_config {
   int32_t abi_version; /* = ORLG_ABI_VERSION */
@@ -157,6 +178,27 @@ typedef struct orlg_config {
   const double* phy_gsnr;        /* [phy_n_tables][num_slots][k_paths] dB */
   const uint8_t* phy_cut_links;  /* [n_nodes*n_nodes*k_paths][phy_max_terms] neighbour link per r_cut term */
   const int32_t* phy_cut_count;  /* [n_nodes*n_nodes*k_paths] */
+
+  /* ---- QoT gate: GN-model GSNR feeding the QoT feasibility and modulation-format check (RMSA-v0, RMCSA-v0) ----
+   * The reference ships the GN model (examples/calculate_osnr.py:9-56) and the SD-FEC thresholds it is meant to be
+   * compared with (minimum_osnr = target_SNR_dB_vec, examples/create_topology_gn.py:65-110) but no env that calls
+   * them.  With qot_gate = 1 a step accepts a lightpath iff, beyond the env's own checks
+   * (rmsa_env.py:233-252; rmcsa_env.py:222-258 incl. _crosstalk_is_acceptable), (a) its GSNR given the running
+   * services on its links (and core) is >= qot_thr_db[its spectral efficiency] and (b) the GSNR of every
+   * neighbour - a running service sharing a link and core with it - re-evaluated with the candidate present is
+   * >= qot_thr_db[the neighbour's spectral efficiency].
+   * RMSA-v0: the modulation is path.best_modulation as in get_number_slots (rmsa_env.py:708-719), or with
+   * qot_adaptive = 1 the env assigns the most efficient modulation that passes at (path, initial_slot): spectral
+   * efficiencies qot_se[0..qot_n_se) in that (descending) order; one whose slot count does not fit ends the
+   * search (wider ones fit even less); one whose interference-free GSNR (ASE + self-channel NLI only) misses its
+   * threshold is skipped.  RMCSA-v0: the action names the modulation; qot_adaptive only changes ORLG_H_SAP_GN_FF.
+   * The engine keeps per running service the cross-channel sums of calculate_osnr.py:31-46 up to date (one term
+   * per shared link enters / leaves when a lightpath is provisioned / released), so a decision costs
+   * O(running services) instead of O(neighbours x interferers); the occupancy of such engines is env-major. */
+  int32_t qot_gate, qot_adaptive, qot_n_se, qot_pad;
+  int32_t qot_se[8];
+  double qot_thr_db[16];               /* by spectral efficiency; +inf = never acceptable */
+  const orlg_gsnr_params* qot_gsnr;    /* physical inputs of the GN model */
 } orlg_config;
 
 typedef struct orlg_engine orlg_engine;
@@ -289,22 +331,7 @@ int orlg_export_state(orlg_engine* e, uint8_t* dev_out, void* stream);
 /* Pending request of every env (current_service). */
 int orlg_get_requests(orlg_engine* e, orlg_request* dev_out, void* stream);
 
-/* ---- GN-model GSNR: calculate_osnr, examples/calculate_osnr.py:9-56 --------------------
- * Physical inputs the reference leaves undefined (SURVEY.md F2) are explicit here.  Every
- * link is split into span_count[l] equal spans of span_length_km[l]
- * (examples/create_topology_gn.py:122-134: int(length // 80) + 1 spans).  A service that
- * occupies slots [first, first+n) has bandwidth n*slot_hz and centre frequency
- * f0_hz + (first + n/2)*slot_hz. */
-typedef struct orlg_gsnr_params {
-  double launch_power_w;    /* per-channel launch power (1e-3 = 0 dBm) */
-  double attenuation_per_m; /* field attenuation alpha [1/m]: power falls as exp(-2*alpha*L) */
-  double noise_figure_lin;  /* amplifier noise figure, linear */
-  double f0_hz;             /* lower edge of slot 0 */
-  double slot_hz;           /* slot width in Hz (channel_width * 1e9) */
-  const int32_t* span_count;    /* host, [n_edges] */
-  const double* span_length_km; /* host, [n_edges] */
-} orlg_gsnr_params;
-
+/* ---- GN-model GSNR calls (parameter block: orlg_gsnr_params above) ---- */
 int orlg_gsnr_configure(orlg_engine* e, const orlg_gsnr_params* params);
 
 /* For every env: dev_query int32[num_envs][4] = (path | core << 16, first_slot, n_slots,
@@ -323,6 +350,21 @@ int orlg_gsnr(orlg_engine* e, const int32_t* dev_query, double* dev_out, void* s
  * bit rate (rmsa_env.py:708-719, rmcsa_env.py:753-765).  A rejection action yields NaN.  This is how the
  * QoT-aware RMCSA configuration evaluates the GN model for every decision without a host round trip. */
 int orlg_gsnr_for_actions(orlg_engine* e, const int32_t* dev_actions, double* dev_out, void* stream);
+
+/* One step with the device heuristic as the policy - one iteration of utils.evaluate_heuristic's loop
+ * (utils.py:124-162): the action `heuristic_id` takes for the pending request is written to dev_actions_out
+ * (optional) and stepped; outputs as orlg_step.  Engines with the QoT gate and ORLG_H_SAP_GN_FF evaluate the gate
+ * once for both (2 launches); everything else is orlg_heuristic + orlg_step. */
+int orlg_step_auto(orlg_engine* e, int heuristic_id, int32_t* dev_actions_out, int32_t* dev_reward, uint8_t* dev_done,
+                   void* dev_obs, int32_t* dev_alloc, void* stream);
+
+/* QoT gate: f64 [num_envs][2] = (GSNR in dB of the last candidate the gate evaluated for the env, lowest GSNR among
+ * its neighbours with the candidate present; +inf without neighbours); NaN where nothing was evaluated (invalid
+ * action, no free spectrum) and, for [1], where the candidate itself missed its threshold. */
+int orlg_qot_get(orlg_engine* e, double* dev_out, void* stream);
+/* QoT gate self-check (tests): dev_out int64 [num_envs] = number of (running service, hop) rows whose running sums
+ * differ from a from-scratch evaluation over the release queue; 0 everywhere unless the engine is broken. */
+int orlg_qot_check(orlg_engine* e, int64_t* dev_out, void* stream);
 
 /* kernels launched by this engine so far (bench.py "gpu_launches") */
 int64_t orlg_launch_count(const orlg_engine* e);

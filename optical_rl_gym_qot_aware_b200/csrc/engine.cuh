@@ -94,6 +94,18 @@ struct Params {
   uint32_t* phy_cs_len;                 // [NP] entries in use | tombstones << 16
   double* phy_f;                        // [2][NP] episode sums: path length, gsnr
   long long* phy_i;                     // [4][NP] episode sums: path index, modulation level, channels, physical services
+  // GN-model QoT gate (qot.cuh): RMSA-v0 / RMCSA-v0, env-major occupancy
+  int qot, qot_adaptive, qot_n_se, qot_hops, qot_slot_cap;
+  int qot_se[8];                        // adaptive RMSA-v0: spectral efficiencies tried, descending
+  int qot_mod_order[16];                // adaptive RMCSA-v0: modulation rows by descending spectral efficiency (stable)
+  double qot_thr[16];                   // GSNR threshold in dB by spectral efficiency
+  longlong2* qot_sums;                  // [NP][qot_slot_cap][qot_hops] running (S_A, S_X) of every service row, 2^-44 fixed point
+  unsigned short* qot_free;             // [NP][qot_slot_cap] stack of free rows
+  int* qot_free_n;                      // [NP]
+  unsigned long long* qot_rel;          // [NP][QOT_REL_CAP] payloads of the services the last step released
+  int* qot_rel_n;                       // [NP]
+  int4* qot_verdict;                    // [NP][2] (accept, path | core << 16, first slot, slots), (se, row, modulation, 0)
+  double* qot_g;                        // [NP][2] GSNR of the last candidate evaluated, lowest neighbour GSNR with it present
 };
 constexpr int PHY_LEVELS = 8;   // modulation levels 1..8 (100 Gb/s per level per channel, phy_rmsa_env.py:1424)
 constexpr int PHY_ADIM = 9;     // action = (path, 8 channel numbers, -1 terminated)

@@ -6,20 +6,26 @@ namespace orlg {
 
 constexpr int HEAP_D = 8;    // 8-ary implicit min-heap keyed by release time: one 128 B line per child group
 constexpr int HEAP_PAD = 7;  // logical index i lives in slot i+7 -> the children of i are slots 8i+8..8i+15 (line aligned)
+constexpr int QOT_REL_CAP_ = 32;  // = QOT_REL_CAP (qot.cuh)
 constexpr int HEAP_TAIL = 8; // slack after the last entry so that a whole child group can be read unconditionally
 
-// payload of a heap entry: what _release_path needs (rmsa_env.py:515-535) plus the spectral
-// efficiency of the service's modulation (the GN model's per-interferer correction needs it)
-__device__ __forceinline__ unsigned long long pack_service(int pair, int path, int core, int start, int n, int se) {
-  return (unsigned long long)pair | ((unsigned long long)path << 16) | ((unsigned long long)core << 24) |
-         ((unsigned long long)start << 32) | ((unsigned long long)n << 48) | ((unsigned long long)(se & 15) << 58);
+// payload of a heap entry: what _release_path needs (rmsa_env.py:515-535) plus the spectral efficiency of
+// the service's modulation (the GN model's per-interferer correction needs it) and, for engines with the
+// GN-model QoT gate, the service's row in the per-env table of running cross-channel sums (qot.cuh).
+// bits: pair 0-15 | path 16-19 | core 20-24 | first slot 25-33 | slots 34-42 | se 43-46 | row 47-60
+__device__ __forceinline__ unsigned long long pack_service(int pair, int path, int core, int start, int n, int se,
+                                                           int row = 0) {
+  return (unsigned long long)pair | ((unsigned long long)(path & 15) << 16) | ((unsigned long long)(core & 31) << 20) |
+         ((unsigned long long)(start & 511) << 25) | ((unsigned long long)(n & 511) << 34) |
+         ((unsigned long long)(se & 15) << 43) | ((unsigned long long)(row & 0x3FFF) << 47);
 }
 __device__ __forceinline__ int svc_pair(unsigned long long s) { return (int)(s & 0xFFFF); }
-__device__ __forceinline__ int svc_path(unsigned long long s) { return (int)((s >> 16) & 0xFF); }
-__device__ __forceinline__ int svc_core(unsigned long long s) { return (int)((s >> 24) & 0xFF); }
-__device__ __forceinline__ int svc_start(unsigned long long s) { return (int)((s >> 32) & 0xFFFF); }
-__device__ __forceinline__ int svc_slots(unsigned long long s) { return (int)((s >> 48) & 0x3FF); }
-__device__ __forceinline__ int svc_se(unsigned long long s) { return (int)((s >> 58) & 15); }
+__device__ __forceinline__ int svc_path(unsigned long long s) { return (int)((s >> 16) & 15); }
+__device__ __forceinline__ int svc_core(unsigned long long s) { return (int)((s >> 20) & 31); }
+__device__ __forceinline__ int svc_start(unsigned long long s) { return (int)((s >> 25) & 511); }
+__device__ __forceinline__ int svc_slots(unsigned long long s) { return (int)((s >> 34) & 511); }
+__device__ __forceinline__ int svc_se(unsigned long long s) { return (int)((s >> 43) & 15); }
+__device__ __forceinline__ int svc_slot(unsigned long long s) { return (int)((s >> 47) & 0x3FFF); }
 
 // INFO: the instantiation keeps the info-dict state of RMSAEnv.step (only the kernels launched for engines
 // created with info_stats carry that code)
@@ -36,6 +42,7 @@ struct Env {
   long long isum[4];
   int cs_len, cs_dead; // PhyRMSA channel_state list: slots in use (tombstones included), tombstones
   long long slot_hops; // info_stats: sum of number_slots * hops over the running services
+  int rel_n = 0;       // QoT gate: services released by this step, handed to the next qot_kernel launch
 
   __device__ __forceinline__ Env(const Params& p_, uint32_t* smem, int tid, int e_)
       : p(p_), tile{smem, tid, p_.E}, e(e_) {
@@ -56,6 +63,7 @@ struct Env {
 #pragma unroll
     for (int i = 0; i < CNT_N; i++) cnt[i] = p.counters[(size_t)i * p.NP + e];
     slot_hops = 0;
+    rel_n = p.qot ? p.qot_rel_n[e] : 0;  // releases not yet seen by qot_kernel survive an episode reset
     if constexpr (INFO) slot_hops = p.slot_hops[e];
     if constexpr (PHY) {
       fsum[0] = p.phy_f[e];
@@ -189,6 +197,7 @@ struct Env {
 #pragma unroll
     for (int i = 0; i < CNT_N; i++) p.counters[(size_t)i * p.NP + e] = cnt[i];
     if constexpr (INFO) p.slot_hops[e] = slot_hops;
+    if (p.qot) p.qot_rel_n[e] = rel_n;
     if constexpr (PHY) {
       p.phy_f[e] = fsum[0];
       p.phy_f[(size_t)p.NP + e] = fsum[1];
@@ -417,6 +426,10 @@ struct Env {
       } else {
         PathRec rec = load_path(p, svc_pair(s), svc_path(s));
         tile.set_range(rec, svc_core(s), svc_start(s), svc_slots(s));
+        if (p.qot) {  // its neighbours' running sums are corrected by the next qot_kernel launch (qot.cuh)
+          if (rel_n < QOT_REL_CAP_) p.qot_rel[(size_t)e * QOT_REL_CAP_ + rel_n++] = s;
+          else cnt[CNT_FAULT] |= 16;
+        }
         if constexpr (INFO) {  // _release_path :531-535 (current_time is already the new arrival)
           for_each_link(rec, [&](int l) { info_update_link(l); });
           slot_hops -= (long long)svc_slots(s) * rec.hops();
@@ -452,7 +465,7 @@ struct Env {
   }
 
   // _provision_path + _add_release (state and counters only)
-  __device__ __forceinline__ void provision(const PathRec& rec, int path, int core, int start, int n, int se) {
+  __device__ __forceinline__ void provision(const PathRec& rec, int path, int core, int start, int n, int se, int row = 0) {
     tile.clear_range(rec, core, start, n);
     if constexpr (INFO) {  // _provision_path :494, :510
       for_each_link(rec, [&](int l) { info_update_link(l); });
@@ -463,7 +476,7 @@ struct Env {
     cnt[CNT_EP_ACC]++;
     cnt[CNT_BR_PROV] += bit_rate;
     cnt[CNT_EP_BR_PROV] += bit_rate;
-    heap_push(now + holding, pack_service(pair(), path, core, start, n, se));
+    heap_push(now + holding, pack_service(pair(), path, core, start, n, se, row));
   }
 
   // _crosstalk_is_acceptable rmcsa_env.py:341-384 (modulation-only factors precomputed on host)

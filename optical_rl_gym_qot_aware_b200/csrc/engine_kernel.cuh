@@ -108,6 +108,11 @@ __global__ void ORLG_LAUNCH_BOUNDS(BD) env_kernel(const Params p, const StepIO i
       for (int i = 0; i < 2 * p.n_bit_rates; i++) p.br_hist[(size_t)i * p.NP + env.e] = 0;
     }
     env.next_rel = __longlong_as_double(0x7FF0000000000000ll);
+    if (p.qot && active) {  // every row of the service table is free, nothing waits to leave the sums
+      for (int i = 0; i < p.qot_slot_cap; i++)
+        p.qot_free[(size_t)env.e * p.qot_slot_cap + i] = (unsigned short)(p.qot_slot_cap - 1 - i);
+      p.qot_free_n[env.e] = p.qot_slot_cap;
+    }
 #pragma unroll
     for (int i = 0; i < CNT_N; i++) env.cnt[i] = 0;
     env.fsum[0] = env.fsum[1] = 0.0;
@@ -187,6 +192,17 @@ __global__ void ORLG_LAUNCH_BOUNDS(BD) env_kernel(const Params p, const StepIO i
               (io.obs_kind == ORLG_OBS_PHY_INFO || io.obs_kind == ORLG_OBS_PHY_CUTS))
             phy_info<W, PS>(env, reinterpret_cast<double*>(io.obs) + (long long)e * io.obs_es, io.obs_fs,
                             io.obs_kind == ORLG_OBS_PHY_INFO);
+        } else if (p.qot) {
+          // GN-model QoT gate: qot_kernel has taken the decision (validity, free spectrum, RMCSA's closed-form
+          // gate, GSNR of the candidate and its neighbours); apply its verdict
+          const int4 v0 = p.qot_verdict[2 * (size_t)e], v1 = p.qot_verdict[2 * (size_t)e + 1];
+          d = Decision{0, -1, 0, -1, 0};
+          if (v0.x) {
+            const int path = v0.y & 0xFFFF, core = v0.y >> 16;
+            PathRec rec = load_path(p, env.pair(), path);
+            env.provision(rec, path, core, v0.z, v0.w, v1.x, v1.y);
+            d = Decision{1, path, core, v0.z, v0.w};
+          }
         } else {
           if (p.kind == ORLG_ENV_RMSA) d = rmsa_decide<W, PS>(env, a[0], a[1]);
           else if (p.kind == ORLG_ENV_DEEPRMSA) d = deeprmsa_decide<W, PS>(env, a[0]);

@@ -13,6 +13,7 @@
 #include "engine_launch.cuh"
 #include "engine_util.cuh"
 #include "gsnr.cuh"
+#include "qot.cuh"
 
 using namespace orlg;
 
@@ -43,6 +44,8 @@ struct orlg_engine {
   bool blocking_wait = false;
   int* hint_actions = nullptr;
   int hint_heuristic = 0;
+  int* auto_actions = nullptr;          // orlg_step_auto without a caller buffer
+  long long* auto_reward_sum = nullptr; // set by orlg_rollout around its orlg_step_auto loop
 };
 
 static thread_local std::string g_create_error;
@@ -126,6 +129,8 @@ static int fail_create(orlg_engine* e, int code, const std::string& msg) {
   }
   return code;
 }
+
+static int configure_gsnr(orlg_engine* e, const orlg_gsnr_params* g);
 
 extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   if (!c || !out) return fail_create(nullptr, ORLG_EINVAL, "null argument");
@@ -213,6 +218,7 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
     if (bytes_per_env * bd > 100 * 1024) direct = true;
   }
   if (!direct && bytes_per_env * bd > 220 * 1024) direct = true;
+  if (c->qot_gate) direct = true;  // qot_kernel (one warp per env) reads the env's rows in place
   e->direct = direct;
   e->BD = direct ? DIRECT_CTA : bd;
   e->layout_bd = direct ? 1 : bd;
@@ -263,7 +269,17 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   if (phy) min_slots = 1;  // one queue entry per occupied channel
   long long bound = (long long)cores * p.E * (p.S / min_slots);
   const long long lightpaths = bound;  // PhyRMSA: occupied (link, channel) cells
-  if (phy && c->phy_grooming) bound *= 2;  // groomed services queue entries without holding spectrum of their own
+  if (phy && c->phy_grooming) bound *= PHY_LEVELS;  // a level-m channel can carry m groomed 100G services, one entry each
+  // Default capacity: the offered load is Poisson (M/G/inf): mean A = holding / inter-arrival services in the
+  // system if nothing were blocked, so A + 8 sqrt(A) + 32 entries are never exceeded in practice (8 sigma), and
+  // never more than the provable bound.  PhyRMSA queues one entry per channel: up to 8 per service.  Overflow
+  // raises the sticky fault bit (ORLG_C_FAULT), it never corrupts state silently.
+  {
+    const double A = c->mean_holding / c->mean_iat;
+    double est = A + 8.0 * std::sqrt(A) + 32.0;
+    if (phy) est *= (PHY_ADIM - 1);
+    if (c->request_source == ORLG_SRC_PHILOX && est < (double)bound) bound = (long long)std::ceil(est);
+  }
   p.heap_cap = c->heap_capacity > 0 ? c->heap_capacity : (int)(bound < 16 ? 16 : bound);
   p.heap_stride = (p.heap_cap + HEAP_PAD + HEAP_TAIL + 7) & ~7;  // 128 B multiples: child groups stay line aligned
 
@@ -378,6 +394,36 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
       (rc = dev_alloc(e, &p.counters, (size_t)CNT_N * NP)))
     return fail_create(e, rc, e->err);
 
+  if (c->qot_gate) {
+    if (c->env_kind != ORLG_ENV_RMSA && c->env_kind != ORLG_ENV_RMCSA)
+      return fail_create(e, ORLG_EINVAL, "qot_gate is defined for RMSA-v0 and RMCSA-v0");
+    if (!c->qot_gsnr || p.E > 128 || c->n_mods > 16 || c->qot_n_se < 0 || c->qot_n_se > 8 || c->info_stats)
+      return fail_create(e, ORLG_EINVAL, "qot_gate needs qot_gsnr, <= 128 links, <= 16 modulations, no info_stats");
+    if (p.heap_cap > 0x3FFF) return fail_create(e, ORLG_EINVAL, "qot_gate: release-queue capacity above 16383 rows");
+    if ((rc = configure_gsnr(e, c->qot_gsnr))) return fail_create(e, rc, e->err);
+    if (!e->gp.xci_tab) return fail_create(e, ORLG_EINVAL, "qot_gate: the cross-channel table does not fit (slots too many)");
+    p.qot = 1;
+    p.qot_adaptive = c->qot_adaptive ? 1 : 0;
+    p.qot_n_se = c->qot_n_se;
+    for (int i = 0; i < 8; i++) p.qot_se[i] = c->qot_se[i];
+    for (int i = 0; i < 16; i++) p.qot_thr[i] = c->qot_thr_db[i];
+    for (int i = 0; i < c->qot_n_se; i++)
+      if (c->qot_se[i] < 1 || c->qot_se[i] > 15) return fail_create(e, ORLG_EINVAL, "qot_se out of range");
+    if (p.qot_adaptive && c->env_kind == ORLG_ENV_RMSA && c->qot_n_se < 1)
+      return fail_create(e, ORLG_EINVAL, "qot_adaptive needs qot_se");
+    for (int m = 0; m < 16; m++) p.qot_mod_order[m] = m;
+    for (int a = 1; a < c->n_mods; a++)  // stable, by descending spectral efficiency (utils.py:105-117)
+      for (int b = a; b > 0 && c->mod_se[p.qot_mod_order[b]] > c->mod_se[p.qot_mod_order[b - 1]]; b--)
+        std::swap(p.qot_mod_order[b], p.qot_mod_order[b - 1]);
+    p.qot_hops = c->max_hops;
+    p.qot_slot_cap = p.heap_cap;
+    if ((rc = dev_alloc(e, &p.qot_sums, NP * (size_t)p.qot_slot_cap * p.qot_hops)) ||
+        (rc = dev_alloc(e, &p.qot_free, NP * (size_t)p.qot_slot_cap)) || (rc = dev_alloc(e, &p.qot_free_n, NP)) ||
+        (rc = dev_alloc(e, &p.qot_rel, NP * (size_t)QOT_REL_CAP)) || (rc = dev_alloc(e, &p.qot_rel_n, NP)) ||
+        (rc = dev_alloc(e, &p.qot_verdict, NP * 2)) || (rc = dev_alloc(e, &p.qot_g, NP * 2)))
+      return fail_create(e, rc, e->err);
+  }
+
   e->obs_kind = c->obs_kind;
   if (c->obs_kind == ORLG_OBS_F64 || c->obs_kind == ORLG_OBS_F32) {
     e->obs_dim = 1 + 2 * p.n_nodes + (2 * p.j + 3) * p.k;
@@ -438,7 +484,27 @@ static bool heuristic_ok(const orlg_engine* e, int hid) {
   if (e->p.kind == ORLG_ENV_PHYRMSA)
     return (hid >= ORLG_H_PHY_SAP_FF && hid <= ORLG_H_PHY_BM_FA_CUT) || hid == ORLG_H_PHY_FA_FF ||
            ((hid == ORLG_H_PHY_BM_FA_RSS || hid == ORLG_H_PHY_FA_FF_RSS) && e->p.E <= 64);  // columns are gathered into 64 bits
+  if (hid == ORLG_H_SAP_GN_FF) return e->p.qot != 0;
   return hid >= ORLG_H_SP_FF && hid <= ORLG_H_SAP_BM_FC_FF;
+}
+
+// qot_kernel launch (engines with the QoT gate): one warp per env
+static int launch_qot(orlg_engine* e, int mode, const int32_t* actions, int32_t* actions_out, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  QotIO q{mode, actions, actions_out};
+  const int grid = (e->p.num_envs + QOT_WARPS - 1) / QOT_WARPS;
+  switch (e->W) {
+    case 2: qot_kernel<2><<<grid, QOT_WARPS * 32, 0, st>>>(e->p, e->gp, q); break;
+    case 4: qot_kernel<4><<<grid, QOT_WARPS * 32, 0, st>>>(e->p, e->gp, q); break;
+    default: qot_kernel<10><<<grid, QOT_WARPS * 32, 0, st>>>(e->p, e->gp, q); break;
+  }
+  cudaError_t rc = cudaGetLastError();
+  if (rc != cudaSuccess) {
+    e->err = std::string("qot_kernel launch: ") + cudaGetErrorString(rc);
+    return ORLG_ECUDA;
+  }
+  e->launches++;
+  return ORLG_OK;
 }
 
 static StepIO make_io(orlg_engine* e, int mode) {
@@ -465,6 +531,8 @@ extern "C" int orlg_step(orlg_engine* e, const int32_t* dev_actions, int32_t* de
   if (!e || !dev_actions) return ORLG_EINVAL;
   if (int rc = check_source(e)) return rc;
   cudaSetDevice(e->device);
+  if (e->p.qot)  // the gate decides (verdict), the step kernel applies
+    if (int rc = launch_qot(e, QOT_VERDICT, dev_actions, nullptr, stream)) return rc;
   StepIO io = make_io(e, MODE_STEP);
   io.actions = dev_actions;
   io.reward = dev_reward;
@@ -474,6 +542,33 @@ extern "C" int orlg_step(orlg_engine* e, const int32_t* dev_actions, int32_t* de
   io.hint_actions = e->hint_actions;
   io.hint_heuristic = e->hint_heuristic;
   io.info = e->info_out;
+  return launch(e, io, stream);
+}
+
+extern "C" int orlg_step_auto(orlg_engine* e, int hid, int32_t* dev_actions_out, int32_t* dev_reward, uint8_t* dev_done,
+                              void* dev_obs, int32_t* dev_alloc, void* stream) {
+  if (!e || !heuristic_ok(e, hid)) return ORLG_EINVAL;
+  if (int rc = check_source(e)) return rc;
+  cudaSetDevice(e->device);
+  int rc;
+  if (!dev_actions_out) {  // the action still has to live somewhere between the two launches
+    if (!e->auto_actions && (rc = ::dev_alloc(e, &e->auto_actions, (size_t)e->p.num_envs * e->p.action_dim))) return rc;
+    dev_actions_out = e->auto_actions;
+  }
+  if (e->p.qot && hid == ORLG_H_SAP_GN_FF) {
+    if ((rc = launch_qot(e, QOT_HEUR_VERDICT, nullptr, dev_actions_out, stream))) return rc;
+  } else {
+    if ((rc = orlg_heuristic(e, hid, dev_actions_out, stream))) return rc;
+    if (e->p.qot && (rc = launch_qot(e, QOT_VERDICT, dev_actions_out, nullptr, stream))) return rc;
+  }
+  StepIO io = make_io(e, MODE_STEP);
+  io.actions = dev_actions_out;
+  io.reward = dev_reward;
+  io.done = dev_done;
+  io.obs = e->obs_kind ? dev_obs : nullptr;
+  io.alloc = dev_alloc;
+  io.info = e->info_out;
+  io.reward_sum = e->auto_reward_sum;
   return launch(e, io, stream);
 }
 
@@ -497,6 +592,7 @@ extern "C" int orlg_observation(orlg_engine* e, int obs_kind, void* dev_obs, voi
 extern "C" int orlg_heuristic(orlg_engine* e, int hid, int32_t* dev_actions, void* stream) {
   if (!e || !dev_actions || !heuristic_ok(e, hid)) return ORLG_EINVAL;
   cudaSetDevice(e->device);
+  if (hid == ORLG_H_SAP_GN_FF) return launch_qot(e, QOT_HEURISTIC, nullptr, dev_actions, stream);
   StepIO io = make_io(e, MODE_HEURISTIC);
   io.heuristic = hid;
   io.actions_out = dev_actions;
@@ -521,7 +617,7 @@ extern "C" int orlg_path_first_fit(orlg_engine* e, const int32_t* dev_paths, int
 
 extern "C" int orlg_set_next_action_hint(orlg_engine* e, int hid, int32_t* dev_next_actions) {
   if (!e) return ORLG_EINVAL;
-  if (dev_next_actions && (!heuristic_ok(e, hid) || hid == ORLG_H_PATH_FF)) return ORLG_EINVAL;
+  if (dev_next_actions && (!heuristic_ok(e, hid) || hid == ORLG_H_PATH_FF || hid == ORLG_H_SAP_GN_FF)) return ORLG_EINVAL;
   e->hint_actions = dev_next_actions;
   e->hint_heuristic = hid;
   return ORLG_OK;
@@ -531,6 +627,14 @@ extern "C" int orlg_rollout(orlg_engine* e, int hid, int nsteps, int64_t* dev_re
   if (!e || nsteps < 1 || !heuristic_ok(e, hid)) return ORLG_EINVAL;
   if (int rc = check_source(e)) return rc;
   cudaSetDevice(e->device);
+  if (e->p.qot) {  // the gate is a launch of its own: nsteps x orlg_step_auto
+    e->auto_reward_sum = (long long*)dev_reward_sum;
+    int rc = ORLG_OK;
+    for (int t = 0; t < nsteps && rc == ORLG_OK; t++)
+      rc = orlg_step_auto(e, hid, nullptr, nullptr, nullptr, nullptr, nullptr, stream);
+    e->auto_reward_sum = nullptr;
+    return rc;
+  }
   StepIO io = make_io(e, MODE_ROLLOUT);
   io.heuristic = hid;
   io.nsteps = nsteps;
@@ -621,6 +725,13 @@ extern "C" int orlg_step_host(orlg_engine* e, const int32_t* h_actions, int32_t*
 }
 
 extern "C" int orlg_gsnr_configure(orlg_engine* e, const orlg_gsnr_params* g) {
+  if (e && e->p.qot) {
+    e->err = "the GN model of an engine with the QoT gate is configured by orlg_create (orlg_config.qot_gsnr)";
+    return ORLG_ESTATE;
+  }
+  return configure_gsnr(e, g);
+}
+static int configure_gsnr(orlg_engine* e, const orlg_gsnr_params* g) {
   if (!e || !g || !g->span_count || !g->span_length_km) return ORLG_EINVAL;
   if (!(g->launch_power_w > 0) || !(g->attenuation_per_m > 0) || !(g->noise_figure_lin > 0) || !(g->slot_hz > 0) ||
       !(g->f0_hz > 0)) {
@@ -752,6 +863,37 @@ extern "C" int orlg_phy_get_stats(orlg_engine* e, double* dev_out, void* stream)
   const int warps_per_cta = 4;
   phy_stats_kernel<<<(e->p.num_envs + warps_per_cta - 1) / warps_per_cta, warps_per_cta * 32, 0, (cudaStream_t)stream>>>(
       e->p, e->W, e->layout_bd, dev_out);
+  CK(cudaGetLastError());
+  e->launches++;
+  return ORLG_OK;
+}
+
+extern "C" int orlg_qot_get(orlg_engine* e, double* dev_out, void* stream) {
+  if (!e || !dev_out) return ORLG_EINVAL;
+  if (!e->p.qot) {
+    e->err = "orlg_qot_get needs an engine created with qot_gate = 1";
+    return ORLG_ESTATE;
+  }
+  cudaSetDevice(e->device);
+  CK(cudaMemcpyAsync(dev_out, e->p.qot_g, (size_t)e->p.num_envs * 2 * sizeof(double), cudaMemcpyDeviceToDevice,
+                     (cudaStream_t)stream));
+  return ORLG_OK;
+}
+
+extern "C" int orlg_qot_check(orlg_engine* e, int64_t* dev_out, void* stream) {
+  if (!e || !dev_out) return ORLG_EINVAL;
+  if (!e->p.qot) {
+    e->err = "orlg_qot_check needs an engine created with qot_gate = 1";
+    return ORLG_ESTATE;
+  }
+  cudaSetDevice(e->device);
+  // the services released by the last step leave the sums first (heuristic mode changes nothing else)
+  if (!e->auto_actions) {
+    int rc = dev_alloc(e, &e->auto_actions, (size_t)e->p.num_envs * e->p.action_dim);
+    if (rc) return rc;
+  }
+  if (int rc = launch_qot(e, QOT_HEURISTIC, nullptr, e->auto_actions, stream)) return rc;
+  qot_check_kernel<<<(e->p.num_envs + 63) / 64, 64, 0, (cudaStream_t)stream>>>(e->p, e->gp, (long long*)dev_out);
   CK(cudaGetLastError());
   e->launches++;
   return ORLG_OK;

@@ -1,0 +1,399 @@
+// qot.cuh — GN-model QoT gate of RMSA-v0 / RMCSA-v0 (include/orlg.h "QoT gate"), one warp per env.
+//
+// The gate: a candidate lightpath is accepted iff its GSNR (calculate_osnr, examples/calculate_osnr.py:9-56)
+// meets the SD-FEC threshold of its modulation (minimum_osnr of examples/create_topology_gn.py:65-110) AND the
+// GSNR of every neighbour — a running service that shares a link and core with it — re-evaluated with the
+// candidate present still meets its own.  With qot_adaptive the modulation is chosen by the same check.
+//
+// Cost model.  Literally, calculate_osnr re-sums every interferer of every neighbour: ~neighbours x interferers
+// asinh pairs per decision (what gsnr_kernel_fast does, 15 ms per 65 536 decisions on the RMCSA workload).  Adding
+// or removing ONE lightpath changes the cross-channel sum of a neighbour by exactly one term per shared link, so
+// the engine keeps, for every running service and every hop of its path, the running sums
+//     S_A = sum_i [asinh(..(df + B_i/2)) - asinh(..(df - B_i/2))]      (calculate_osnr.py:36-41)
+//     S_X = sum_i Phi(SE_i) (B_i / |df|) 5/3                            (:43-45, without the per-link l_eff / L)
+// in a per-env service table next to the release queue (the queue payload carries the service's row).  A decision
+// is then one pass over the env's queue: O(services) membership tests, O(neighbours) table lookups.
+//
+// The sums are 64-bit fixed point (2^-44): integer addition is associative, so provision / release in any order
+// leave exactly the sums a from-scratch evaluation would give (qot_check_kernel verifies that bit for bit) and
+// there is no drift however long an env runs.  Quantisation is ~6e-14 per term against O(1) sums: ~1e-12 dB.
+#pragma once
+#include "gsnr.cuh"
+
+namespace orlg {
+
+enum { QOT_VERDICT = 0, QOT_HEUR_VERDICT = 1, QOT_HEURISTIC = 2 };
+constexpr int QOT_WARPS = 4;
+constexpr int QOT_REL_CAP = 32;  // services released by one step (overflow: sticky fault bit 16)
+constexpr double QOT_SCALE = 17592186044416.0;  // 2^44
+constexpr double QOT_INV_SCALE = 1.0 / 17592186044416.0;
+
+struct QotIO {
+  int mode;
+  const int* actions;  // QOT_VERDICT: the step's action tensor
+  int* actions_out;    // heuristic modes: the action chosen (may be null in QOT_HEUR_VERDICT)
+};
+
+struct QotWarpSmem {
+  unsigned long long cSA[32], cSX[32];  // the candidate's own sums, per hop
+  unsigned char hop_of[128];            // link -> hop of the candidate
+};
+
+__device__ __forceinline__ double phi_mod(int se) {  // phi_modulation_format[se - 1], calculate_osnr.py:20
+  return se <= 2 ? 1.0 : se == 3 ? 2.0 / 3.0 : se == 4 ? 17.0 / 25.0 : se == 5 ? 69.0 / 100.0 : 13.0 / 21.0;
+}
+__device__ __forceinline__ double4 ld_link(const GsnrParams& g, int l) {
+  const double2* q = reinterpret_cast<const double2*>(g.link_c + l);
+  const double2 a = __ldg(q), b = __ldg(q + 1);
+  return make_double4(a.x, a.y, b.x, b.y);
+}
+__device__ __forceinline__ long long qot_q(double x) { return __double2ll_rn(x * QOT_SCALE); }
+
+// one link of a lightpath of n slots centred at f: (P_ASE + P_NLI) / P for one span (calculate_osnr.py:45-52)
+__device__ __forceinline__ double qot_link_term(const GsnrParams& g, const double4& lc, double sum_phi, double B, double f) {
+  const double pi = 3.141592653589793, beta2 = 21.3e-27, gamma = 1.3e-3, h_planck = 6.626e-34;
+  const double pr = g.P / B;
+  const double p_nli = pr * pr * pr * (8.0 / (27.0 * pi * beta2)) * gamma * gamma * lc.x * sum_phi * B;
+  const double p_ase = B * h_planck * f * lc.z * g.nf;
+  return 1.0 / (g.P / (p_ase + p_nli));
+}
+__device__ __forceinline__ double qot_sum_phi(const GsnrParams& g, int n, long long SA, long long SX, double lol) {
+  return __ldg(g.sci_tab + n) + ((double)SA * QOT_INV_SCALE - ((double)SX * QOT_INV_SCALE) * lol);
+}
+
+struct QotCtx {
+  const Params& p;
+  const GsnrParams& g;
+  QotWarpSmem& sm;
+  int e, lane;
+  const ulonglong2* heap;
+  int heap_len;
+  longlong2* sums;  // this env's service table [slot][qot_hops]
+  int bit_rate, pair;
+
+  __device__ __forceinline__ longlong2* row(int slot) const { return sums + (size_t)slot * p.qot_hops; }
+
+  // GSNR in dB from per-hop terms: lane h < hops holds v (one span of link h) and the link's span count;
+  // spans are added one by one in path order like the reference's loops (:22-54)
+  __device__ __forceinline__ double finish(double v, double spans, int hops) const {
+    double acc = 0.0;
+    for (int h = 0; h < hops; h++) {
+      const double vh = __shfl_sync(0xFFFFFFFFu, v, h);
+      const int ns = (int)__shfl_sync(0xFFFFFFFFu, spans, h);
+      for (int k = 0; k < ns; k++) acc += vh;
+    }
+    return 10.0 * log10(1.0 / acc);
+  }
+
+  // the channel alone on its path: ASE and self-channel NLI only
+  __device__ __forceinline__ bool alone_ok(const PathRec& rec, int start, int n, int se) const {
+    const Chan c = chan_of(g, start, n, se);
+    const int hops = rec.hops();
+    double v = 0.0, spans = 0.0;
+    if (lane < hops) {
+      const double4 lc = ld_link(g, rec.link(lane));
+      v = qot_link_term(g, lc, __ldg(g.sci_tab + n), c.B, c.f);
+      spans = lc.w;
+    }
+    return finish(v, spans, hops) >= p.qot_thr[se];
+  }
+
+  // Walks the env's running services; `f(i, payload, common links)` runs on the lane that owns service i for
+  // every service on `core` that shares a link with `mask`.
+  template <typename F>
+  __device__ __forceinline__ void for_neighbours(int core, ulonglong2 mask, F f) const {
+    for (int base = 0; base < heap_len; base += 32) {
+      const int i = base + lane;
+      if (i < heap_len) {
+        const unsigned long long s = heap[i].y;
+        if (svc_core(s) == core) {
+          const ulonglong2 im = __ldg(g.path_mask + (size_t)svc_pair(s) * p.k + svc_path(s));
+          const ulonglong2 common = make_ulonglong2(im.x & mask.x, im.y & mask.y);
+          if ((common.x | common.y) != 0ull) f(i, s, common);
+        }
+      }
+    }
+  }
+
+  // the gate for one candidate; warp-collective.  Leaves the candidate's sums in sm.cSA / sm.cSX.
+  __device__ bool gate(const PathRec& rec, int path, int core, int start, int n, int se, double& gc, double& gmin) {
+    const Chan cch = chan_of(g, start, n, se);
+    const ulonglong2 cmask = __ldg(g.path_mask + (size_t)pair * p.k + path);
+    const int hops = rec.hops();
+    __syncwarp();
+    sm.cSA[lane] = 0ull;
+    sm.cSX[lane] = 0ull;
+    if (lane < hops) sm.hop_of[rec.link(lane)] = (unsigned char)lane;
+    __syncwarp();
+    const int cols = 4 * g.tab_S + 1;
+    const double pm_c = phi_mod(se);
+    bool fail = false;
+    double mn = __longlong_as_double(0x7FF0000000000000ll);
+    for_neighbours(core, cmask, [&](int, unsigned long long s, ulonglong2 common) {
+      const int ni = svc_slots(s), sei = svc_se(s);
+      const int d = (2 * svc_start(s) + ni) - cch.pos2;  // centre distance in half slots, interferer - candidate
+      const double2 t_ci = __ldg(g.xci_tab + (size_t)ni * cols + (d + 2 * g.tab_S));  // service i seen by the candidate
+      const double2 t_ic = __ldg(g.xci_tab + (size_t)n * cols + (-d + 2 * g.tab_S));  // the candidate seen by service i
+      const unsigned long long qa_ci = (unsigned long long)qot_q(t_ci.x),
+                               qx_ci = (unsigned long long)qot_q(phi_mod(sei) * t_ci.y);
+      const long long qa_ic = qot_q(t_ic.x), qx_ic = qot_q(pm_c * t_ic.y);
+      unsigned long long c0 = common.x, c1 = common.y;
+      while (c0) {
+        const int h = sm.hop_of[__ffsll((long long)c0) - 1];
+        atomicAdd(&sm.cSA[h], qa_ci);
+        atomicAdd(&sm.cSX[h], qx_ci);
+        c0 &= c0 - 1;
+      }
+      while (c1) {
+        const int h = sm.hop_of[64 + __ffsll((long long)c1) - 1];
+        atomicAdd(&sm.cSA[h], qa_ci);
+        atomicAdd(&sm.cSX[h], qx_ci);
+        c1 &= c1 - 1;
+      }
+      // the neighbour with the candidate present: its stored sums + the candidate's term on the shared links
+      const PathRec ri = load_path(p, svc_pair(s), svc_path(s));
+      const longlong2* rw = row(svc_slot(s));
+      const double Bi = (double)ni * g.slot_hz, fi = g.f0 + ((double)svc_start(s) + 0.5 * (double)ni) * g.slot_hz;
+      double acc = 0.0;
+      const int hi = ri.hops();
+      for (int h = 0; h < hi; h++) {
+        const int l = ri.link(h);
+        const double4 lc = ld_link(g, l);
+        longlong2 sv = rw[h];
+        if (mask_has(common, l)) {
+          sv.x += qa_ic;
+          sv.y += qx_ic;
+        }
+        const double v = qot_link_term(g, lc, qot_sum_phi(g, ni, sv.x, sv.y, lc.y), Bi, fi);
+        const int ns = (int)lc.w;
+        for (int k = 0; k < ns; k++) acc += v;
+      }
+      const double gi = 10.0 * log10(1.0 / acc);
+      mn = fmin(mn, gi);
+      if (!(gi >= p.qot_thr[sei])) fail = true;
+    });
+    fail = __any_sync(0xFFFFFFFFu, fail);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mn = fmin(mn, __shfl_xor_sync(0xFFFFFFFFu, mn, o));
+    __syncwarp();
+    double v = 0.0, spans = 0.0;
+    if (lane < hops) {
+      const double4 lc = ld_link(g, rec.link(lane));
+      v = qot_link_term(g, lc, qot_sum_phi(g, n, (long long)sm.cSA[lane], (long long)sm.cSX[lane], lc.y), cch.B, cch.f);
+      spans = lc.w;
+    }
+    gc = finish(v, spans, hops);
+    const bool cand_ok = gc >= p.qot_thr[se];
+    gmin = cand_ok ? mn : __longlong_as_double(0x7FF8000000000000ll);  // neighbours are not looked at when the candidate fails
+    return cand_ok && !fail;
+  }
+
+  // add (sign = +1) or remove (-1) lightpath (path mask, core, start, n, se) from the sums of its neighbours
+  __device__ void apply_to_neighbours(ulonglong2 mask, int core, int start, int n, int se, int sign) const {
+    const int cols = 4 * g.tab_S + 1;
+    const int pos2 = 2 * start + n;
+    const double pm = phi_mod(se);
+    for_neighbours(core, mask, [&](int, unsigned long long s, ulonglong2 common) {
+      const int d = (2 * svc_start(s) + svc_slots(s)) - pos2;
+      const double2 t = __ldg(g.xci_tab + (size_t)n * cols + (-d + 2 * g.tab_S));  // this lightpath seen by service i
+      const long long qa = sign * qot_q(t.x), qx = sign * qot_q(pm * t.y);
+      const PathRec ri = load_path(p, svc_pair(s), svc_path(s));
+      longlong2* rw = row(svc_slot(s));
+      const int hi = ri.hops();
+      for (int h = 0; h < hi; h++)
+        if (mask_has(common, ri.link(h))) {
+          longlong2 sv = rw[h];
+          sv.x += qa;
+          sv.y += qx;
+          rw[h] = sv;
+        }
+    });
+  }
+};
+
+__device__ __forceinline__ bool qot_crosstalk_ok(const Params& p, int bit_rate, int mod, double path_length) {
+  // _crosstalk_is_acceptable rmcsa_env.py:341-384 (as Env::crosstalk_ok)
+  double denom = __ldg(p.mod_coeff + mod) * ((double)bit_rate / (double)__ldg(p.mod_se + mod));
+  denom = denom * 1e9;
+  double lmax_snr = 100.0 / denom;
+  lmax_snr = lmax_snr / 1000.0;
+  return path_length < __ldg(p.mod_reach + mod) && path_length < lmax_snr;
+}
+
+// One warp per env: (1) the services the last step released leave their neighbours' sums, (2) the candidate(s)
+// of the action / of heuristic 13 are put through the gate, (3) an accepted candidate gets a row of the service
+// table and enters its neighbours' sums; the verdict tells the step kernel what to provision.
+template <int W>
+__global__ void __launch_bounds__(QOT_WARPS * 32) qot_kernel(const Params p, const GsnrParams g, const QotIO io) {
+  __shared__ QotWarpSmem smem[QOT_WARPS];
+  const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (e >= p.num_envs) return;
+  const uint32_t m = p.meta[e];
+  const int bit_rate = (int)(m & 0xFFFFu), src = (int)((m >> 16) & 0xFFu), dst = (int)(m >> 24);
+  QotCtx cx{p, g, smem[threadIdx.x >> 5], e, lane, p.heap + (size_t)e * p.heap_stride + HEAP_PAD, p.heap_len[e],
+            p.qot_sums + (size_t)e * p.qot_slot_cap * p.qot_hops, bit_rate, src * p.n_nodes + dst};
+  unsigned short* free_stack = p.qot_free + (size_t)e * p.qot_slot_cap;
+  int free_n = p.qot_free_n[e];
+
+  // (1) releases of the last step (the services are out of the queue already)
+  const int nrel = p.qot_rel_n[e];
+  for (int r = 0; r < nrel; r++) {
+    const unsigned long long s = p.qot_rel[(size_t)e * QOT_REL_CAP + r];
+    const ulonglong2 rm = __ldg(g.path_mask + (size_t)svc_pair(s) * p.k + svc_path(s));
+    cx.apply_to_neighbours(rm, svc_core(s), svc_start(s), svc_slots(s), svc_se(s), -1);
+    if (lane == 0) free_stack[free_n] = (unsigned short)svc_slot(s);
+    free_n++;
+  }
+  __syncwarp();
+
+  // (2) candidates, in the order the reference's first-fit heuristics walk them
+  Tile<W, 1> tile{p.occ + (size_t)e * p.planes, 0, p.E};
+  const double nan = __longlong_as_double(0x7FF8000000000000ll);
+  double gc = nan, gmin = nan;
+  bool accept = false;
+  int a_path = -1, a_core = 0, a_start = -1, a_n = 0, a_se = 0, a_mod = 0;
+  PathRec a_rec{};
+  const bool rmcsa = p.kind == ORLG_ENV_RMCSA;
+  if (io.mode == QOT_VERDICT) {
+    if (!rmcsa) {  // RMSAEnv.step behind the gate (rmsa_env.py:233-271)
+      const int2 a = reinterpret_cast<const int2*>(io.actions)[e];
+      if (a.x >= 0 && a.y >= 0 && a.x < p.k && a.y < p.S) {
+        const PathRec rec = load_path(p, cx.pair, a.x);
+        if (rec.hops() > 0) {
+          const Row<W> av = tile.path_avail(rec, 0);
+          const int nse = p.qot_adaptive ? p.qot_n_se : 1;
+          for (int t = 0; t < nse && !accept; t++) {
+            const int se = p.qot_adaptive ? p.qot_se[t] : rec.se();
+            const int n = number_slots(bit_rate, se, p);
+            if (a.y + n > p.S || !range_is_free<W>(av, a.y, n)) break;  // a wider channel does not fit either
+            if (p.qot_adaptive && !cx.alone_ok(rec, a.y, n, se)) continue;
+            a_rec = rec, a_path = a.x, a_start = a.y, a_n = n, a_se = se;
+            accept = cx.gate(rec, a.x, 0, a.y, n, se, gc, gmin);
+          }
+        }
+      }
+    } else {  // RMCSAEnv.step behind the gate (rmcsa_env.py:222-289)
+      const int4 a = reinterpret_cast<const int4*>(io.actions)[e];
+      if (a.x >= 0 && a.y >= 0 && a.z >= 0 && a.w >= 0 && a.x < p.k && a.y < p.n_mods && a.z < p.cores && a.w < p.S) {
+        const PathRec rec = load_path(p, cx.pair, a.x);
+        if (rec.hops() > 0) {
+          const int se = __ldg(p.mod_se + a.y), n = number_slots(bit_rate, se, p);
+          if (a.w + n <= p.S && range_is_free<W>(tile.path_avail(rec, a.z), a.w, n) &&
+              qot_crosstalk_ok(p, bit_rate, a.y, __ldg(p.path_length + (size_t)cx.pair * p.k + a.x))) {
+            a_rec = rec, a_path = a.x, a_core = a.z, a_start = a.w, a_n = n, a_se = se, a_mod = a.y;
+            accept = cx.gate(rec, a.x, a.z, a.w, n, se, gc, gmin);
+          }
+        }
+      }
+    }
+  } else if (!rmcsa) {  // heuristic 13 on RMSA-v0 (walk of rmsa_env.py:901-913)
+    for (int path = 0; path < p.k && !accept; path++) {
+      const PathRec rec = load_path(p, cx.pair, path);
+      if (rec.hops() <= 0) continue;
+      const Row<W> av = tile.path_avail(rec, 0);
+      const int nse = p.qot_adaptive ? p.qot_n_se : 1;
+      for (int t = 0; t < nse && !accept; t++) {
+        const int se = p.qot_adaptive ? p.qot_se[t] : rec.se();
+        const int n = number_slots(bit_rate, se, p);
+        const int s = first_fit<W>(av, n, p.S);
+        if (s < 0) break;
+        if (p.qot_adaptive && !cx.alone_ok(rec, s, n, se)) continue;
+        a_rec = rec, a_path = path, a_start = s, a_n = n, a_se = se;
+        accept = cx.gate(rec, path, 0, s, n, se, gc, gmin);
+      }
+    }
+  } else {  // heuristic 13 on RMCSA-v0 (walk of rmcsa_env.py:882-911)
+    for (int path = 0; path < p.k && !accept; path++) {
+      const PathRec rec = load_path(p, cx.pair, path);
+      if (rec.hops() <= 0) continue;
+      const double len = __ldg(p.path_length + (size_t)cx.pair * p.k + path);
+      const int nm = p.qot_adaptive ? p.n_mods : 1;
+      for (int t = 0; t < nm && !accept; t++) {
+        const int mod = p.qot_adaptive ? p.qot_mod_order[t] : rec.best_mod();
+        if (mod >= p.n_mods) break;  // no modulation reaches (get_best_modulation_format raises)
+        const int se = __ldg(p.mod_se + mod), n = number_slots(bit_rate, se, p);
+        int core = -1, s = -1;
+        for (int c = 0; c < p.cores && s < 0; c++) {
+          s = first_fit<W>(tile.path_avail(rec, c), n, p.S);
+          if (s >= 0) core = c;
+        }
+        if (s < 0) break;  // no core has room; a wider channel does not fit either
+        if (!qot_crosstalk_ok(p, bit_rate, mod, len)) continue;
+        if (p.qot_adaptive && !cx.alone_ok(rec, s, n, se)) continue;
+        a_rec = rec, a_path = path, a_core = core, a_start = s, a_n = n, a_se = se, a_mod = mod;
+        accept = cx.gate(rec, path, core, s, n, se, gc, gmin);
+      }
+    }
+  }
+
+  if (io.mode != QOT_VERDICT && io.actions_out != nullptr && lane == 0) {
+    if (!rmcsa)
+      reinterpret_cast<int2*>(io.actions_out)[e] = accept ? make_int2(a_path, a_start) : make_int2(p.k, p.S);
+    else
+      reinterpret_cast<int4*>(io.actions_out)[e] =
+          accept ? make_int4(a_path, a_mod, a_core, a_start) : make_int4(p.k, p.n_mods, p.cores, p.S);
+  }
+  if (lane == 0) {
+    p.qot_g[2 * (size_t)e] = gc;
+    p.qot_g[2 * (size_t)e + 1] = gmin;
+  }
+
+  // (3) the accepted candidate enters the service table
+  int slot = 0;
+  if (io.mode != QOT_HEURISTIC) {
+    if (accept && free_n == 0) {  // more running services than rows (the release queue is as full): refuse
+      accept = false;
+      if (lane == 0) atomicOr((unsigned long long*)&p.counters[(size_t)CNT_FAULT * p.NP + e], 32ull);
+    }
+    if (accept) {
+      slot = free_stack[--free_n];
+      if (lane < a_rec.hops())
+        cx.row(slot)[lane] = make_longlong2((long long)cx.sm.cSA[lane], (long long)cx.sm.cSX[lane]);
+      cx.apply_to_neighbours(__ldg(g.path_mask + (size_t)cx.pair * p.k + a_path), a_core, a_start, a_n, a_se, +1);
+    }
+    if (lane == 0) {
+      p.qot_verdict[2 * (size_t)e] = make_int4(accept ? 1 : 0, a_path | (a_core << 16), a_start, a_n);
+      p.qot_verdict[2 * (size_t)e + 1] = make_int4(a_se, slot, a_mod, 0);
+    }
+  }
+  if (lane == 0) {
+    p.qot_free_n[e] = free_n;
+    p.qot_rel_n[e] = 0;
+  }
+}
+
+// Test / debug: recompute every running service's sums from scratch and compare with the table (exact).
+// out[e] = number of (service, hop) rows that differ.  One thread per env.
+__global__ void qot_check_kernel(const Params p, const GsnrParams g, long long* out) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= p.num_envs) return;
+  const ulonglong2* heap = p.heap + (size_t)e * p.heap_stride + HEAP_PAD;
+  const int n_act = p.heap_len[e];
+  const longlong2* sums = p.qot_sums + (size_t)e * p.qot_slot_cap * p.qot_hops;
+  const int cols = 4 * g.tab_S + 1;
+  long long bad = 0;
+  for (int a = 0; a < n_act; a++) {
+    const unsigned long long t = heap[a].y;
+    const PathRec rt = load_path(p, svc_pair(t), svc_path(t));
+    const int pos2 = 2 * svc_start(t) + svc_slots(t);
+    for (int h = 0; h < rt.hops(); h++) {
+      const int l = rt.link(h);
+      long long SA = 0, SX = 0;
+      for (int i = 0; i < n_act; i++) {
+        if (i == a) continue;
+        const unsigned long long s = heap[i].y;
+        if (svc_core(s) != svc_core(t)) continue;
+        const ulonglong2 im = __ldg(g.path_mask + (size_t)svc_pair(s) * p.k + svc_path(s));
+        if (!mask_has(im, l)) continue;
+        const int d = (2 * svc_start(s) + svc_slots(s)) - pos2;
+        const double2 x = __ldg(g.xci_tab + (size_t)svc_slots(s) * cols + (d + 2 * g.tab_S));
+        SA += qot_q(x.x);
+        SX += qot_q(phi_mod(svc_se(s)) * x.y);
+      }
+      const longlong2 st = sums[(size_t)svc_slot(t) * p.qot_hops + h];
+      if (st.x != SA || st.y != SX) bad++;
+    }
+  }
+  out[e] = bad;
+}
+}  // namespace orlg

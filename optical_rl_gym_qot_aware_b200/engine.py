@@ -35,6 +35,7 @@ EXPORTS = (
     "orlg_heuristic", "orlg_rollout", "orlg_get_counters", "orlg_export_state", "orlg_get_requests",
     "orlg_launch_count", "orlg_gsnr_configure", "orlg_gsnr", "orlg_gsnr_for_actions", "orlg_phy_get_stats", "orlg_path_first_fit", "orlg_set_next_action_hint", "orlg_step_host_async", "orlg_step_host_wait", "orlg_set_host_wait",
     "orlg_phy_get_channel_state", "orlg_info_dim", "orlg_set_info_output",
+    "orlg_step_auto", "orlg_qot_get", "orlg_qot_check",
 )
 
 
@@ -59,6 +60,8 @@ class OrlgConfig(C.Structure):
         ("phy_n_tables", C.c_int32), ("phy_max_terms", C.c_int32),
         ("phy_table_id", C.c_void_p), ("phy_mod_level", C.c_void_p), ("phy_gsnr", C.c_void_p),
         ("phy_cut_links", C.c_void_p), ("phy_cut_count", C.c_void_p),
+        ("qot_gate", C.c_int32), ("qot_adaptive", C.c_int32), ("qot_n_se", C.c_int32), ("qot_pad", C.c_int32),
+        ("qot_se", C.c_int32 * 8), ("qot_thr_db", C.c_double * 16), ("qot_gsnr", C.c_void_p),
     ]
 
 
@@ -115,6 +118,9 @@ def load_library():
         L.orlg_set_info_output.argtypes = [vp, vp]
         L.orlg_path_first_fit.argtypes = [vp, vp, vp, vp]
         L.orlg_set_next_action_hint.argtypes = [vp, i32, vp]
+        L.orlg_step_auto.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
+        L.orlg_qot_get.argtypes = [vp, vp, vp]
+        L.orlg_qot_check.argtypes = [vp, vp, vp]
         _lib = L
     return _lib
 
@@ -183,6 +189,19 @@ class Engine:
         c.heap_capacity = heap_capacity
         c.obs_kind = spec.obs_kind
         c.info_stats = int(bool(getattr(spec, "info_stats", False)))
+        if getattr(spec, "qot_gate", False):  # GN-model QoT gate (include/orlg.h "QoT gate")
+            gp = spec.qot_gsnr
+            k["qot_span_count"] = np.ascontiguousarray(gp.span_count, np.int32)
+            k["qot_span_km"] = np.ascontiguousarray(gp.span_length_km, np.float64)
+            self._qot_gp = OrlgGsnrParams(gp.launch_power_w, gp.attenuation_per_m, gp.noise_figure_lin, gp.f0_hz,
+                                          gp.slot_hz, k["qot_span_count"].ctypes.data, k["qot_span_km"].ctypes.data)
+            c.qot_gate, c.qot_adaptive, c.qot_n_se = 1, int(spec.qot_adaptive), len(spec.qot_se)
+            for i, v in enumerate(spec.qot_se):
+                c.qot_se[i] = int(v)
+            for i, v in enumerate(spec.qot_thr_db):
+                c.qot_thr_db[i] = float(v)
+            c.qot_gsnr = C.cast(C.pointer(self._qot_gp), C.c_void_p)
+            self.gsnr_params = gp
         h = C.c_void_p()
         rc = self.L.orlg_create(C.byref(c), C.byref(h))
         if rc != 0:
@@ -285,6 +304,24 @@ class Engine:
 
     def rollout(self, heuristic_id, nsteps, reward_sum=None):
         self._ck(self.L.orlg_rollout(self.h, heuristic_id, int(nsteps), self._p(reward_sum), self._stream()))
+
+    def step_auto(self, heuristic_id, actions_out=None, reward=None, done=None, obs=None, alloc=None):
+        """One step with the device heuristic as the policy (orlg_step_auto)."""
+        self._ck(self.L.orlg_step_auto(self.h, int(heuristic_id), self._p(actions_out), self._p(reward), self._p(done),
+                                       self._obs_base(obs), self._p(alloc), self._stream()))
+
+    def qot_last(self, out=None):
+        """QoT gate: f64 [num_envs, 2] (candidate GSNR dB, lowest neighbour GSNR dB) of the last candidates evaluated."""
+        if out is None:
+            out = self.torch.empty((self.num_envs, 2), dtype=self.torch.float64, device=self.device)
+        self._ck(self.L.orlg_qot_get(self.h, self._p(out), self._stream()))
+        return out
+
+    def qot_check(self):
+        """QoT gate self-check: int64 [num_envs] rows whose running sums differ from a from-scratch evaluation."""
+        out = self.torch.empty(self.num_envs, dtype=self.torch.int64, device=self.device)
+        self._ck(self.L.orlg_qot_check(self.h, self._p(out), self._stream()))
+        return out
 
     def counters(self):
         out = self.torch.empty((self.num_envs, NUM_COUNTERS), dtype=self.torch.int64, device=self.device)

@@ -24,7 +24,7 @@ def test_library_exports_every_declared_symbol():
     missing = [n for n in sorted(declared) if not hasattr(L, n)]
     assert not missing, missing
     assert set(engine.EXPORTS) >= declared - {"orlg_engine"}
-    assert L.orlg_abi_version() == 1
+    assert L.orlg_abi_version() == 2
     assert b"sm_100a" in L.orlg_build_info()
 
 
