@@ -360,7 +360,9 @@ int orlg_step_auto(orlg_engine* e, int heuristic_id, int32_t* dev_actions_out, i
 
 /* QoT gate: f64 [num_envs][2] = (GSNR in dB of the last candidate the gate evaluated for the env, lowest GSNR among
  * its neighbours with the candidate present; +inf without neighbours); NaN where nothing was evaluated (invalid
- * action, no free spectrum) and, for [1], where the candidate itself missed its threshold. */
+ * action, no free spectrum) and, for [1], where the candidate itself missed its threshold.  After orlg_step_auto
+ * with ORLG_H_SAP_GN_FF (gate evaluated once for heuristic and step) a blocked request reports the last candidate
+ * the heuristic looked at. */
 int orlg_qot_get(orlg_engine* e, double* dev_out, void* stream);
 /* QoT gate self-check (tests): dev_out int64 [num_envs] = number of (running service, hop) rows whose running sums
  * differ from a from-scratch evaluation over the release queue; 0 everywhere unless the engine is broken. */

@@ -279,6 +279,8 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
     double est = A + 8.0 * std::sqrt(A) + 32.0;
     if (phy) est *= (PHY_ADIM - 1);
     if (c->request_source == ORLG_SRC_PHILOX && est < (double)bound) bound = (long long)std::ceil(est);
+    // engines with the QoT gate address a service's row with 14 bits: sized by load for every request source
+    if (c->qot_gate && bound > 0x3FFF) bound = est < 16383.0 ? (long long)std::ceil(est) : 0x3FFF;
   }
   p.heap_cap = c->heap_capacity > 0 ? c->heap_capacity : (int)(bound < 16 ? 16 : bound);
   p.heap_stride = (p.heap_cap + HEAP_PAD + HEAP_TAIL + 7) & ~7;  // 128 B multiples: child groups stay line aligned

@@ -300,6 +300,19 @@ __global__ void __launch_bounds__(QOT_WARPS * 32) qot_kernel(const Params p, con
         if (p.qot_adaptive && !cx.alone_ok(rec, s, n, se)) continue;
         a_rec = rec, a_path = path, a_start = s, a_n = n, a_se = se;
         accept = cx.gate(rec, path, 0, s, n, se, gc, gmin);
+        if (accept && t > 0 && io.mode == QOT_HEUR_VERDICT) {
+          // The RMSA-v0 action (path, slot) does not name the modulation: the step assigns the most efficient one
+          // that passes AT THIS SLOT, which can be better than the one that passed at its own first-fit slot.
+          // Walk the step's search (the chosen one is reached last and passes).
+          accept = false;
+          for (int t2 = 0; t2 <= t && !accept; t2++) {
+            const int se2 = p.qot_se[t2], n2 = number_slots(bit_rate, se2, p);
+            if (s + n2 > p.S || !range_is_free<W>(av, s, n2)) break;
+            if (!cx.alone_ok(rec, s, n2, se2)) continue;
+            a_n = n2, a_se = se2;
+            accept = cx.gate(rec, path, 0, s, n2, se2, gc, gmin);
+          }
+        }
       }
     }
   } else {  // heuristic 13 on RMCSA-v0 (walk of rmcsa_env.py:882-911)
