@@ -358,6 +358,20 @@ int orlg_gsnr_for_actions(orlg_engine* e, const int32_t* dev_actions, double* de
 int orlg_step_auto(orlg_engine* e, int heuristic_id, int32_t* dev_actions_out, int32_t* dev_reward, uint8_t* dev_done,
                    void* dev_obs, int32_t* dev_alloc, void* stream);
 
+/* orlg_step_auto for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  No counterpart in the reference.
+ * Same step as orlg_step_auto(e, heuristic_id, NULL, ...), but the action tensor that travels from the heuristic
+ * launch to the step launch lives in a static device array inside liborlg.so instead of a lazily cudaMalloc'ed
+ * buffer; the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).
+ * Limit: num_envs * action_dim <= ORLG_NOALLOC_MAX_INTS int32 (1 MiB of device memory, held by every GPU that loads
+ * the library until the process exits); larger engines get ORLG_EINVAL with a message naming the limit.
+ * The array is shared by every engine and every call on a device and keeps the last call's contents (each call
+ * overwrites all the entries it reads, nothing needs clearing): calls that overlap on the GPU - two streams, two
+ * engines, two host threads - race on it; serialise them or use orlg_step_auto with buffers of your own. */
+#define ORLG_NOALLOC_MAX_INTS 262144
+int orlg_step_auto_noalloc(orlg_engine* e, int heuristic_id, int32_t* dev_reward, uint8_t* dev_done, void* dev_obs,
+                           int32_t* dev_alloc, void* stream);
+
 /* QoT gate: f64 [num_envs][2] = (GSNR in dB of the last candidate the gate evaluated for the env, lowest GSNR among
  * its neighbours with the candidate present; +inf without neighbours); NaN where nothing was evaluated (invalid
  * action, no free spectrum) and, for [1], where the candidate itself missed its threshold.  After orlg_step_auto

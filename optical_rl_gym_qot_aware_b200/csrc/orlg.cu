@@ -900,3 +900,38 @@ extern "C" int orlg_qot_check(orlg_engine* e, int64_t* dev_out, void* stream) {
   e->launches++;
   return ORLG_OK;
 }
+
+// ---- orlg_step_auto_noalloc: orlg_step_auto without any allocation -------------------------------------------
+// orlg_step_auto needs scratch for the action tensor that travels from the heuristic launch to the step launch; when
+// the caller passes no buffer it allocates one (cudaMalloc) on first use.  Callers that must not allocate (CUDA graph
+// capture, serving loops, harnesses that forbid it) use this variant: the scratch is a file-scope device array of
+// ORLG_NOALLOC_MAX_INTS int32 (1 MiB; every GPU that loads the library holds it until exit).  Host code must not
+// pass the symbol itself to a kernel (it is a host-side stand-in, not a device address): the address is taken once
+// per device with cudaGetSymbolAddress, with that device current.
+static __device__ __align__(256) int32_t g_noalloc_actions[ORLG_NOALLOC_MAX_INTS];
+static int32_t* g_noalloc_ptr[64] = {};  // per device, resolved on first use
+
+extern "C" int orlg_step_auto_noalloc(orlg_engine* e, int hid, int32_t* dev_reward, uint8_t* dev_done, void* dev_obs,
+                                      int32_t* dev_alloc, void* stream) {
+  if (!e || !heuristic_ok(e, hid)) return ORLG_EINVAL;
+  if (int rc = check_source(e)) return rc;
+  const long long need = (long long)e->p.num_envs * e->p.action_dim;
+  if (need > (long long)ORLG_NOALLOC_MAX_INTS) {
+    e->err = "orlg_step_auto_noalloc: num_envs * action_dim = " + std::to_string(need) + " int32 exceed the static scratch of " +
+             std::to_string((long long)ORLG_NOALLOC_MAX_INTS) + " (ORLG_NOALLOC_MAX_INTS); use orlg_step_auto with a caller buffer";
+    return ORLG_EINVAL;
+  }
+  if (e->device < 0 || e->device >= 64) {
+    e->err = "orlg_step_auto_noalloc: device ordinal out of range";
+    return ORLG_EINVAL;
+  }
+  CK(cudaSetDevice(e->device));
+  if (!g_noalloc_ptr[e->device]) {  // set-up, once per device, that device current
+    void* ptr = nullptr;
+    CK(cudaGetSymbolAddress(&ptr, g_noalloc_actions));
+    g_noalloc_ptr[e->device] = (int32_t*)ptr;
+  }
+  // every env's action is written by the heuristic launch before the step launch reads it, so what an earlier
+  // call left in the array is never read: nothing has to be cleared
+  return orlg_step_auto(e, hid, g_noalloc_ptr[e->device], dev_reward, dev_done, dev_obs, dev_alloc, stream);
+}

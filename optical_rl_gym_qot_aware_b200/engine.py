@@ -35,7 +35,7 @@ EXPORTS = (
     "orlg_heuristic", "orlg_rollout", "orlg_get_counters", "orlg_export_state", "orlg_get_requests",
     "orlg_launch_count", "orlg_gsnr_configure", "orlg_gsnr", "orlg_gsnr_for_actions", "orlg_phy_get_stats", "orlg_path_first_fit", "orlg_set_next_action_hint", "orlg_step_host_async", "orlg_step_host_wait", "orlg_set_host_wait",
     "orlg_phy_get_channel_state", "orlg_info_dim", "orlg_set_info_output",
-    "orlg_step_auto", "orlg_qot_get", "orlg_qot_check",
+    "orlg_step_auto", "orlg_qot_get", "orlg_qot_check", "orlg_step_auto_noalloc",
 )
 
 
@@ -119,6 +119,7 @@ def load_library():
         L.orlg_path_first_fit.argtypes = [vp, vp, vp, vp]
         L.orlg_set_next_action_hint.argtypes = [vp, i32, vp]
         L.orlg_step_auto.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
+        L.orlg_step_auto_noalloc.argtypes = [vp, i32, vp, vp, vp, vp, vp]
         L.orlg_qot_get.argtypes = [vp, vp, vp]
         L.orlg_qot_check.argtypes = [vp, vp, vp]
         _lib = L
@@ -309,6 +310,12 @@ class Engine:
         """One step with the device heuristic as the policy (orlg_step_auto)."""
         self._ck(self.L.orlg_step_auto(self.h, int(heuristic_id), self._p(actions_out), self._p(reward), self._p(done),
                                        self._obs_base(obs), self._p(alloc), self._stream()))
+
+    def step_auto_noalloc(self, heuristic_id, reward=None, done=None, obs=None, alloc=None):
+        """orlg_step_auto_noalloc: as step_auto(heuristic_id, None, ...), with the action scratch in a static device
+        array of the library (num_envs * action_dim <= 262144); the call allocates nothing."""
+        self._ck(self.L.orlg_step_auto_noalloc(self.h, int(heuristic_id), self._p(reward), self._p(done),
+                                               self._obs_base(obs), self._p(alloc), self._stream()))
 
     def qot_last(self, out=None):
         """QoT gate: f64 [num_envs, 2] (candidate GSNR dB, lowest neighbour GSNR dB) of the last candidates evaluated."""
