@@ -382,6 +382,23 @@ int orlg_qot_get(orlg_engine* e, double* dev_out, void* stream);
  * differ from a from-scratch evaluation over the release queue; 0 everywhere unless the engine is broken. */
 int orlg_qot_check(orlg_engine* e, int64_t* dev_out, void* stream);
 
+/* The running services of every env (topology.graph["running_services"], rmsa_env.py:484-487; the owner map
+ * spectrum_slots_allocation :481-483 follows from it): int32 [num_envs][max_rows][6] = (src_id * n_nodes + dst_id,
+ * path, core, first slot, slots, spectral efficiency) in release-queue order, and their number per env in
+ * dev_count (rows past max_rows are counted, not written).  PhyRMSA: one row per (service, channel):
+ * (pair, path, share, channel, position in the action, level). */
+int orlg_export_services(orlg_engine* e, int32_t* dev_out, int32_t max_rows, int32_t* dev_count, void* stream);
+
+/* Measurement support (bench.py): nsteps steps - mode 0: orlg_step(dev_actions, ...) as configured (fused hint
+ * included); mode 1: orlg_step_auto(heuristic_id, dev_actions as its output or NULL, ...) - each bracketed by its own
+ * CUDA event pair, with an optional L2-evicting memset of dev_flush[flush_bytes] before every pair, issued from one C
+ * loop (no interpreter between an event record and the launch it times) or, with use_graph, captured into one CUDA
+ * graph and launched once.  ms_step[nsteps] = duration of every step; ms_first[nsteps] (optional) = duration of
+ * the step's first launch when it has two (gate / heuristic kernel), else 0.  Synchronous. */
+int orlg_timed_steps(orlg_engine* e, int mode, int heuristic_id, int32_t* dev_actions, int32_t* dev_reward,
+                     uint8_t* dev_done, void* dev_obs, int nsteps, void* dev_flush, size_t flush_bytes, int use_graph,
+                     float* ms_step, float* ms_first, void* stream);
+
 /* kernels launched by this engine so far (bench.py "gpu_launches") */
 int64_t orlg_launch_count(const orlg_engine* e);
 

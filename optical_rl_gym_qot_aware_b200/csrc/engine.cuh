@@ -99,6 +99,7 @@ struct Params {
   int qot_se[8];                        // adaptive RMSA-v0: spectral efficiencies tried, descending
   int qot_mod_order[16];                // adaptive RMCSA-v0: modulation rows by descending spectral efficiency (stable)
   double qot_thr[16];                   // GSNR threshold in dB by spectral efficiency
+  double qot_thr_lin[16];               // the same as the largest acceptable 1 / GSNR (linear): 10^(-thr / 10)
   longlong2* qot_sums;                  // [NP][qot_slot_cap][qot_hops] running (S_A, S_X) of every service row, 2^-44 fixed point
   unsigned short* qot_free;             // [NP][qot_slot_cap] stack of free rows
   int* qot_free_n;                      // [NP]

@@ -53,6 +53,28 @@ __global__ void requests_kernel(const Params p, orlg_request* out) {
 }
 
 
+// running services of every env = the entries of its release queue, in queue order: rows of
+// (src_id * n_nodes + dst_id, path, core, first slot, slots, spectral efficiency) - what the reference keeps as
+// topology.graph["running_services"] (rmsa_env.py:484-487); the owner map spectrum_slots_allocation (:481-483)
+// follows from it.  PhyRMSA: one row per (service, channel): (pair, path, share, channel, position, level).
+__global__ void services_kernel(const Params p, int* out, int max_rows, int* count) {
+  int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= p.num_envs) return;
+  const ulonglong2* heap = p.heap + (size_t)e * p.heap_stride + HEAP_PAD;
+  const int n = p.heap_len[e];
+  for (int i = 0; i < n && i < max_rows; i++) {
+    const unsigned long long s = heap[i].y;
+    int* o = out + ((size_t)e * max_rows + i) * 6;
+    o[0] = svc_pair(s);
+    o[1] = svc_path(s);
+    o[2] = svc_core(s);
+    o[3] = svc_start(s);
+    o[4] = svc_slots(s);
+    o[5] = svc_se(s);
+  }
+  count[e] = n;
+}
+
 // PhyRMSA-v0 channel_state without the tombstones, thread per env
 __global__ void phy_channel_state_kernel(const Params p, int* out, int max_entries, int* count) {
   int e = blockIdx.x * blockDim.x + threadIdx.x;

@@ -46,6 +46,8 @@ struct orlg_engine {
   int hint_heuristic = 0;
   int* auto_actions = nullptr;          // orlg_step_auto without a caller buffer
   long long* auto_reward_sum = nullptr; // set by orlg_rollout around its orlg_step_auto loop
+  cudaEvent_t mid_ev = nullptr;         // orlg_timed_steps: recorded between the launches of a multi-launch step
+  bool mid_external = false;
 };
 
 static thread_local std::string g_create_error;
@@ -408,7 +410,10 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
     p.qot_adaptive = c->qot_adaptive ? 1 : 0;
     p.qot_n_se = c->qot_n_se;
     for (int i = 0; i < 8; i++) p.qot_se[i] = c->qot_se[i];
-    for (int i = 0; i < 16; i++) p.qot_thr[i] = c->qot_thr_db[i];
+    for (int i = 0; i < 16; i++) {
+      p.qot_thr[i] = c->qot_thr_db[i];
+      p.qot_thr_lin[i] = std::pow(10.0, -c->qot_thr_db[i] / 10.0);  // +inf dB -> 0 (never), -inf dB -> inf (always)
+    }
     for (int i = 0; i < c->qot_n_se; i++)
       if (c->qot_se[i] < 1 || c->qot_se[i] > 15) return fail_create(e, ORLG_EINVAL, "qot_se out of range");
     if (p.qot_adaptive && c->env_kind == ORLG_ENV_RMSA && c->qot_n_se < 1)
@@ -490,6 +495,10 @@ static bool heuristic_ok(const orlg_engine* e, int hid) {
   return hid >= ORLG_H_SP_FF && hid <= ORLG_H_SAP_BM_FC_FF;
 }
 
+static void record_mid(orlg_engine* e, void* stream) {
+  if (e->mid_ev) cudaEventRecordWithFlags(e->mid_ev, (cudaStream_t)stream, e->mid_external ? cudaEventRecordExternal : cudaEventRecordDefault);
+}
+
 // qot_kernel launch (engines with the QoT gate): one warp per env
 static int launch_qot(orlg_engine* e, int mode, const int32_t* actions, int32_t* actions_out, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
@@ -533,8 +542,10 @@ extern "C" int orlg_step(orlg_engine* e, const int32_t* dev_actions, int32_t* de
   if (!e || !dev_actions) return ORLG_EINVAL;
   if (int rc = check_source(e)) return rc;
   cudaSetDevice(e->device);
-  if (e->p.qot)  // the gate decides (verdict), the step kernel applies
+  if (e->p.qot) {  // the gate decides (verdict), the step kernel applies
     if (int rc = launch_qot(e, QOT_VERDICT, dev_actions, nullptr, stream)) return rc;
+    record_mid(e, stream);
+  }
   StepIO io = make_io(e, MODE_STEP);
   io.actions = dev_actions;
   io.reward = dev_reward;
@@ -563,6 +574,7 @@ extern "C" int orlg_step_auto(orlg_engine* e, int hid, int32_t* dev_actions_out,
     if ((rc = orlg_heuristic(e, hid, dev_actions_out, stream))) return rc;
     if (e->p.qot && (rc = launch_qot(e, QOT_VERDICT, dev_actions_out, nullptr, stream))) return rc;
   }
+  record_mid(e, stream);
   StepIO io = make_io(e, MODE_STEP);
   io.actions = dev_actions_out;
   io.reward = dev_reward;
@@ -934,4 +946,81 @@ extern "C" int orlg_step_auto_noalloc(orlg_engine* e, int hid, int32_t* dev_rewa
   // every env's action is written by the heuristic launch before the step launch reads it, so what an earlier
   // call left in the array is never read: nothing has to be cleared
   return orlg_step_auto(e, hid, g_noalloc_ptr[e->device], dev_reward, dev_done, dev_obs, dev_alloc, stream);
+}
+
+extern "C" int orlg_export_services(orlg_engine* e, int32_t* dev_out, int32_t max_rows, int32_t* dev_count, void* stream) {
+  if (!e || !dev_count || max_rows < 0 || (max_rows > 0 && !dev_out)) return ORLG_EINVAL;
+  cudaSetDevice(e->device);
+  services_kernel<<<(e->p.num_envs + 127) / 128, 128, 0, (cudaStream_t)stream>>>(e->p, dev_out, max_rows, dev_count);
+  CK(cudaGetLastError());
+  e->launches++;
+  return ORLG_OK;
+}
+
+// ---- orlg_timed_steps: K steps timed on the device with nothing but C between the event records ----------------
+extern "C" int orlg_timed_steps(orlg_engine* e, int mode, int hid, int32_t* dev_actions, int32_t* dev_reward,
+                                uint8_t* dev_done, void* dev_obs, int nsteps, void* dev_flush, size_t flush_bytes,
+                                int use_graph, float* ms_step, float* ms_first, void* stream) {
+  if (!e || nsteps < 1 || nsteps > 100000 || !ms_step || (mode != 0 && mode != 1) || (mode == 0 && !dev_actions))
+    return ORLG_EINVAL;
+  if (mode == 1 && !heuristic_ok(e, hid)) return ORLG_EINVAL;
+  if (int rc = check_source(e)) return rc;
+  CK(cudaSetDevice(e->device));
+  cudaStream_t caller = (cudaStream_t)stream, st = caller;
+  std::vector<cudaEvent_t> ev(3 * (size_t)nsteps, nullptr);
+  for (auto& x : ev) CK(cudaEventCreate(&x));
+  int rc = ORLG_OK;
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  cudaStream_t own = nullptr;
+  if (mode == 1 && !dev_actions) {  // allocate the action scratch outside the timed / captured region
+    if (!e->auto_actions && (rc = ::dev_alloc(e, &e->auto_actions, (size_t)e->p.num_envs * e->p.action_dim))) return rc;
+    dev_actions = e->auto_actions;
+  }
+  if (use_graph) {  // the whole K-step sequence as one graph launch: no host work between the nodes
+    CK(cudaStreamSynchronize(caller));
+    CK(cudaStreamCreateWithFlags(&own, cudaStreamNonBlocking));
+    st = own;
+    CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+  }
+  const unsigned flag = use_graph ? cudaEventRecordExternal : cudaEventRecordDefault;
+  e->mid_external = use_graph != 0;
+  for (int t = 0; t < nsteps && rc == ORLG_OK; t++) {
+    if (dev_flush && flush_bytes) cudaMemsetAsync(dev_flush, t & 1, flush_bytes, st);  // evicts L2, outside the event pair
+    cudaEventRecordWithFlags(ev[3 * t], st, flag);
+    e->mid_ev = ev[3 * t + 1];
+    rc = mode == 0 ? orlg_step(e, dev_actions, dev_reward, dev_done, dev_obs, nullptr, st)
+                   : orlg_step_auto(e, hid, dev_actions, dev_reward, dev_done, dev_obs, nullptr, st);
+    cudaEventRecordWithFlags(ev[3 * t + 2], st, flag);
+  }
+  e->mid_ev = nullptr;
+  e->mid_external = false;
+  cudaError_t ce = cudaSuccess;
+  if (use_graph) {
+    ce = cudaStreamEndCapture(st, &graph);
+    if (ce == cudaSuccess && rc == ORLG_OK) ce = cudaGraphInstantiate(&exec, graph, 0);
+    if (ce == cudaSuccess && rc == ORLG_OK) ce = cudaGraphLaunch(exec, st);
+  }
+  if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);
+  if (ce == cudaSuccess && rc == ORLG_OK) {
+    const bool two = mode == 1 || e->p.qot;
+    for (int t = 0; t < nsteps && ce == cudaSuccess; t++) {
+      ce = cudaEventElapsedTime(&ms_step[t], ev[3 * t], ev[3 * t + 2]);
+      if (ms_first) {
+        ms_first[t] = 0.f;
+        if (two && ce == cudaSuccess) ce = cudaEventElapsedTime(&ms_first[t], ev[3 * t], ev[3 * t + 1]);
+      }
+    }
+  }
+  if (exec) cudaGraphExecDestroy(exec);
+  if (graph) cudaGraphDestroy(graph);
+  if (own) cudaStreamDestroy(own);
+  for (auto& x : ev) cudaEventDestroy(x);
+  if (rc != ORLG_OK) return rc;
+  if (ce != cudaSuccess) {
+    e->err = std::string("orlg_timed_steps: ") + cudaGetErrorString(ce);
+    cudaGetLastError();
+    return ORLG_ECUDA;
+  }
+  return ORLG_OK;
 }

@@ -34,28 +34,39 @@ struct QotIO {
   int* actions_out;    // heuristic modes: the action chosen (may be null in QOT_HEUR_VERDICT)
 };
 
+#ifndef QOT_MIN_CTAS  // resident CTAs per SM the register allocation must allow (A/B knob)
+#define QOT_MIN_CTAS 5
+#endif
+constexpr int QOT_CAP = 256;  // running services staged per window (an env with more is walked window by window)
+
 struct QotWarpSmem {
+  unsigned long long pay[QOT_CAP];      // release-queue payloads of the staged window
+  ulonglong2 mask[QOT_CAP];             // their paths as link sets
   unsigned long long cSA[32], cSX[32];  // the candidate's own sums, per hop
+  unsigned short nb[QOT_CAP];           // compacted neighbour list of the current pass
   unsigned char hop_of[128];            // link -> hop of the candidate
 };
 
 __device__ __forceinline__ double phi_mod(int se) {  // phi_modulation_format[se - 1], calculate_osnr.py:20
   return se <= 2 ? 1.0 : se == 3 ? 2.0 / 3.0 : se == 4 ? 17.0 / 25.0 : se == 5 ? 69.0 / 100.0 : 13.0 / 21.0;
 }
-__device__ __forceinline__ double4 ld_link(const GsnrParams& g, int l) {
-  const double2* q = reinterpret_cast<const double2*>(g.link_c + l);
-  const double2 a = __ldg(q), b = __ldg(q + 1);
-  return make_double4(a.x, a.y, b.x, b.y);
-}
 __device__ __forceinline__ long long qot_q(double x) { return __double2ll_rn(x * QOT_SCALE); }
 
-// one link of a lightpath of n slots centred at f: (P_ASE + P_NLI) / P for one span (calculate_osnr.py:45-52)
-__device__ __forceinline__ double qot_link_term(const GsnrParams& g, const double4& lc, double sum_phi, double B, double f) {
+// A lightpath of n slots centred at f, on one link: every span adds (P_ASE + P_NLI) / P (calculate_osnr.py:45-52).
+// The factors that do not depend on the link are hoisted: v = (ase * lc.z + nli * lc.x * sum_phi) / P.  The
+// reference adds span by span and divides twice (1 / (P / x)); here spans are a multiplication - the GSNR agrees to
+// ~1e-14 dB (tolerance of the path: 1e-4 dB).
+struct QotChan {
+  double ase, nli;  // B h f NF / P ;  (P / B)^3 8 / (27 pi |b2|) g^2 B / P
+};
+__device__ __forceinline__ QotChan qot_chan(const GsnrParams& g, int start, int n, double invP) {
   const double pi = 3.141592653589793, beta2 = 21.3e-27, gamma = 1.3e-3, h_planck = 6.626e-34;
+  const double B = (double)n * g.slot_hz, f = g.f0 + ((double)start + 0.5 * (double)n) * g.slot_hz;
   const double pr = g.P / B;
-  const double p_nli = pr * pr * pr * (8.0 / (27.0 * pi * beta2)) * gamma * gamma * lc.x * sum_phi * B;
-  const double p_ase = B * h_planck * f * lc.z * g.nf;
-  return 1.0 / (g.P / (p_ase + p_nli));
+  QotChan c;
+  c.ase = B * h_planck * f * g.nf * invP;
+  c.nli = pr * pr * pr * (8.0 / (27.0 * pi * beta2)) * gamma * gamma * B * invP;
+  return c;
 }
 __device__ __forceinline__ double qot_sum_phi(const GsnrParams& g, int n, long long SA, long long SX, double lol) {
   return __ldg(g.sci_tab + n) + ((double)SA * QOT_INV_SCALE - ((double)SX * QOT_INV_SCALE) * lol);
@@ -65,59 +76,87 @@ struct QotCtx {
   const Params& p;
   const GsnrParams& g;
   QotWarpSmem& sm;
+  const double4* link_c;  // per-link factors (l_eff, l_eff / L, exp(2 a L) - 1, spans), staged in shared memory
   int e, lane;
   const ulonglong2* heap;
   int heap_len;
   longlong2* sums;  // this env's service table [slot][qot_hops]
   int bit_rate, pair;
+  double invP;
+  int win;  // staged window of the release queue
 
   __device__ __forceinline__ longlong2* row(int slot) const { return sums + (size_t)slot * p.qot_hops; }
 
-  // GSNR in dB from per-hop terms: lane h < hops holds v (one span of link h) and the link's span count;
-  // spans are added one by one in path order like the reference's loops (:22-54)
-  __device__ __forceinline__ double finish(double v, double spans, int hops) const {
-    double acc = 0.0;
-    for (int h = 0; h < hops; h++) {
-      const double vh = __shfl_sync(0xFFFFFFFFu, v, h);
-      const int ns = (int)__shfl_sync(0xFFFFFFFFu, spans, h);
-      for (int k = 0; k < ns; k++) acc += vh;
+  __device__ __forceinline__ void stage(int w) {
+    __syncwarp();
+    const int base = w * QOT_CAP, n = min(QOT_CAP, heap_len - base);
+    for (int i = lane; i < n; i += 32) {
+      const unsigned long long s = heap[base + i].y;
+      sm.pay[i] = s;
+      sm.mask[i] = __ldg(g.path_mask + (size_t)svc_pair(s) * p.k + svc_path(s));
     }
-    return 10.0 * log10(1.0 / acc);
+    win = w;
+    __syncwarp();
   }
 
-  // the channel alone on its path: ASE and self-channel NLI only
-  __device__ __forceinline__ bool alone_ok(const PathRec& rec, int start, int n, int se) const {
-    const Chan c = chan_of(g, start, n, se);
-    const int hops = rec.hops();
-    double v = 0.0, spans = 0.0;
-    if (lane < hops) {
-      const double4 lc = ld_link(g, rec.link(lane));
-      v = qot_link_term(g, lc, __ldg(g.sci_tab + n), c.B, c.f);
-      spans = lc.w;
-    }
-    return finish(v, spans, hops) >= p.qot_thr[se];
-  }
-
-  // Walks the env's running services; `f(i, payload, common links)` runs on the lane that owns service i for
-  // every service on `core` that shares a link with `mask`.
+  // `f(payload, common links)` for every running service on `core` that shares a link with `mask`: the window's
+  // services are filtered 32 at a time from shared memory, the hits compacted (ballot), then visited with one lane
+  // each, so the per-neighbour work runs with full lanes.
   template <typename F>
-  __device__ __forceinline__ void for_neighbours(int core, ulonglong2 mask, F f) const {
-    for (int base = 0; base < heap_len; base += 32) {
-      const int i = base + lane;
-      if (i < heap_len) {
-        const unsigned long long s = heap[i].y;
-        if (svc_core(s) == core) {
-          const ulonglong2 im = __ldg(g.path_mask + (size_t)svc_pair(s) * p.k + svc_path(s));
-          const ulonglong2 common = make_ulonglong2(im.x & mask.x, im.y & mask.y);
-          if ((common.x | common.y) != 0ull) f(i, s, common);
+  __device__ __forceinline__ void for_neighbours(int core, ulonglong2 mask, F f) {
+    const int nwin = (heap_len + QOT_CAP - 1) / QOT_CAP;
+    for (int w = 0; w < nwin; w++) {
+      if (win != w) stage(w);
+      const int n = min(QOT_CAP, heap_len - w * QOT_CAP);
+      int cnt = 0;
+      for (int base = 0; base < n; base += 32) {
+        const int i = base + lane;
+        bool hit = false;
+        if (i < n && svc_core(sm.pay[i]) == core) {
+          const ulonglong2 im = sm.mask[i];
+          hit = ((im.x & mask.x) | (im.y & mask.y)) != 0ull;
         }
+        const unsigned bal = __ballot_sync(0xFFFFFFFFu, hit);
+        if (hit) sm.nb[cnt + __popc(bal & ((1u << lane) - 1u))] = (unsigned short)i;
+        cnt += __popc(bal);
       }
+      __syncwarp();
+      for (int j = lane; j < cnt; j += 32) {
+        const int i = sm.nb[j];
+        const ulonglong2 im = sm.mask[i];
+        f(sm.pay[i], make_ulonglong2(im.x & mask.x, im.y & mask.y));
+      }
+      __syncwarp();
     }
   }
 
-  // the gate for one candidate; warp-collective.  Leaves the candidate's sums in sm.cSA / sm.cSX.
-  __device__ bool gate(const PathRec& rec, int path, int core, int start, int n, int se, double& gc, double& gmin) {
-    const Chan cch = chan_of(g, start, n, se);
+  // sum over the hops of (spans x per-span term); lane h < hops holds link h's term
+  __device__ __forceinline__ double hop_sum(double v, int hops) const {
+    double acc = 0.0;
+    for (int h = 0; h < hops; h++) acc += __shfl_sync(0xFFFFFFFFu, v, h);
+    return acc;
+  }
+
+  // the channel alone on its path: ASE and self-channel NLI only.  1 / GSNR (linear).
+  __device__ __forceinline__ double alone_acc(const PathRec& rec, int start, int n) const {
+    const QotChan c = qot_chan(g, start, n, invP);
+    const int hops = rec.hops();
+    double v = 0.0;
+    if (lane < hops) {
+      const double4 lc = link_c[rec.link(lane)];
+      v = lc.w * (c.ase * lc.z + c.nli * lc.x * __ldg(g.sci_tab + n));
+    }
+    return hop_sum(v, hops);
+  }
+  __device__ __forceinline__ bool alone_ok(const PathRec& rec, int start, int n, int se) const {
+    return alone_acc(rec, start, n) <= p.qot_thr_lin[se];
+  }
+
+  // The gate for one candidate; warp-collective.  Returns pass / fail; acc_c = 1 / GSNR of the candidate,
+  // acc_w = the largest 1 / GSNR among its neighbours with the candidate present (0 without neighbours).
+  // Leaves the candidate's sums in sm.cSA / sm.cSX.
+  __device__ bool gate(const PathRec& rec, int path, int core, int start, int n, int se, double& acc_c, double& acc_w) {
+    const int cpos2 = 2 * start + n;
     const ulonglong2 cmask = __ldg(g.path_mask + (size_t)pair * p.k + path);
     const int hops = rec.hops();
     __syncwarp();
@@ -128,12 +167,14 @@ struct QotCtx {
     const int cols = 4 * g.tab_S + 1;
     const double pm_c = phi_mod(se);
     bool fail = false;
-    double mn = __longlong_as_double(0x7FF0000000000000ll);
-    for_neighbours(core, cmask, [&](int, unsigned long long s, ulonglong2 common) {
+    double worst = 0.0;
+    for_neighbours(core, cmask, [&](unsigned long long s, ulonglong2 common) {
       const int ni = svc_slots(s), sei = svc_se(s);
-      const int d = (2 * svc_start(s) + ni) - cch.pos2;  // centre distance in half slots, interferer - candidate
+      const int d = (2 * svc_start(s) + ni) - cpos2;  // centre distance in half slots, interferer - candidate
       const double2 t_ci = __ldg(g.xci_tab + (size_t)ni * cols + (d + 2 * g.tab_S));  // service i seen by the candidate
       const double2 t_ic = __ldg(g.xci_tab + (size_t)n * cols + (-d + 2 * g.tab_S));  // the candidate seen by service i
+      const PathRec ri = load_path(p, svc_pair(s), svc_path(s));
+      const longlong2* rw = row(svc_slot(s));
       const unsigned long long qa_ci = (unsigned long long)qot_q(t_ci.x),
                                qx_ci = (unsigned long long)qot_q(phi_mod(sei) * t_ci.y);
       const long long qa_ic = qot_q(t_ic.x), qx_ic = qot_q(pm_c * t_ic.y);
@@ -151,49 +192,50 @@ struct QotCtx {
         c1 &= c1 - 1;
       }
       // the neighbour with the candidate present: its stored sums + the candidate's term on the shared links
-      const PathRec ri = load_path(p, svc_pair(s), svc_path(s));
-      const longlong2* rw = row(svc_slot(s));
-      const double Bi = (double)ni * g.slot_hz, fi = g.f0 + ((double)svc_start(s) + 0.5 * (double)ni) * g.slot_hz;
+      const QotChan ci = qot_chan(g, svc_start(s), ni, invP);
+      const double sci = __ldg(g.sci_tab + ni);
       double acc = 0.0;
       const int hi = ri.hops();
-      for (int h = 0; h < hi; h++) {
-        const int l = ri.link(h);
-        const double4 lc = ld_link(g, l);
-        longlong2 sv = rw[h];
-        if (mask_has(common, l)) {
-          sv.x += qa_ic;
-          sv.y += qx_ic;
-        }
-        const double v = qot_link_term(g, lc, qot_sum_phi(g, ni, sv.x, sv.y, lc.y), Bi, fi);
-        const int ns = (int)lc.w;
-        for (int k = 0; k < ns; k++) acc += v;
+      for (int h0 = 0; h0 < hi; h0 += 4) {  // four independent row loads in flight
+        longlong2 sv[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) sv[u] = (h0 + u < hi) ? rw[h0 + u] : make_longlong2(0, 0);
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+          if (h0 + u < hi) {
+            const int l = ri.link(h0 + u);
+            const double4 lc = link_c[l];
+            if (mask_has(common, l)) {
+              sv[u].x += qa_ic;
+              sv[u].y += qx_ic;
+            }
+            const double sum_phi = sci + ((double)sv[u].x * QOT_INV_SCALE - ((double)sv[u].y * QOT_INV_SCALE) * lc.y);
+            acc += lc.w * (ci.ase * lc.z + ci.nli * lc.x * sum_phi);
+          }
       }
-      const double gi = 10.0 * log10(1.0 / acc);
-      mn = fmin(mn, gi);
-      if (!(gi >= p.qot_thr[sei])) fail = true;
+      worst = fmax(worst, acc);
+      if (!(acc <= p.qot_thr_lin[sei])) fail = true;
     });
     fail = __any_sync(0xFFFFFFFFu, fail);
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mn = fmin(mn, __shfl_xor_sync(0xFFFFFFFFu, mn, o));
-    __syncwarp();
-    double v = 0.0, spans = 0.0;
+    for (int o = 16; o > 0; o >>= 1) worst = fmax(worst, __shfl_xor_sync(0xFFFFFFFFu, worst, o));
+    const QotChan cc = qot_chan(g, start, n, invP);
+    double v = 0.0;
     if (lane < hops) {
-      const double4 lc = ld_link(g, rec.link(lane));
-      v = qot_link_term(g, lc, qot_sum_phi(g, n, (long long)sm.cSA[lane], (long long)sm.cSX[lane], lc.y), cch.B, cch.f);
-      spans = lc.w;
+      const double4 lc = link_c[rec.link(lane)];
+      v = lc.w * (cc.ase * lc.z + cc.nli * lc.x * qot_sum_phi(g, n, (long long)sm.cSA[lane], (long long)sm.cSX[lane], lc.y));
     }
-    gc = finish(v, spans, hops);
-    const bool cand_ok = gc >= p.qot_thr[se];
-    gmin = cand_ok ? mn : __longlong_as_double(0x7FF8000000000000ll);  // neighbours are not looked at when the candidate fails
-    return cand_ok && !fail;
+    acc_c = hop_sum(v, hops);
+    acc_w = worst;
+    return acc_c <= p.qot_thr_lin[se] && !fail;
   }
 
   // add (sign = +1) or remove (-1) lightpath (path mask, core, start, n, se) from the sums of its neighbours
-  __device__ void apply_to_neighbours(ulonglong2 mask, int core, int start, int n, int se, int sign) const {
+  __device__ void apply_to_neighbours(ulonglong2 mask, int core, int start, int n, int se, int sign) {
     const int cols = 4 * g.tab_S + 1;
     const int pos2 = 2 * start + n;
     const double pm = phi_mod(se);
-    for_neighbours(core, mask, [&](int, unsigned long long s, ulonglong2 common) {
+    for_neighbours(core, mask, [&](unsigned long long s, ulonglong2 common) {
       const int d = (2 * svc_start(s) + svc_slots(s)) - pos2;
       const double2 t = __ldg(g.xci_tab + (size_t)n * cols + (-d + 2 * g.tab_S));  // this lightpath seen by service i
       const long long qa = sign * qot_q(t.x), qx = sign * qot_q(pm * t.y);
@@ -224,16 +266,20 @@ __device__ __forceinline__ bool qot_crosstalk_ok(const Params& p, int bit_rate, 
 // of the action / of heuristic 13 are put through the gate, (3) an accepted candidate gets a row of the service
 // table and enters its neighbours' sums; the verdict tells the step kernel what to provision.
 template <int W>
-__global__ void __launch_bounds__(QOT_WARPS * 32) qot_kernel(const Params p, const GsnrParams g, const QotIO io) {
+__global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const Params p, const GsnrParams g, const QotIO io) {
   __shared__ QotWarpSmem smem[QOT_WARPS];
+  __shared__ double4 s_link[128];
+  for (int l = threadIdx.x; l < p.E; l += blockDim.x) s_link[l] = g.link_c[l];
+  __syncthreads();
   const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (e >= p.num_envs) return;
   const uint32_t m = p.meta[e];
   const int bit_rate = (int)(m & 0xFFFFu), src = (int)((m >> 16) & 0xFFu), dst = (int)(m >> 24);
-  QotCtx cx{p, g, smem[threadIdx.x >> 5], e, lane, p.heap + (size_t)e * p.heap_stride + HEAP_PAD, p.heap_len[e],
-            p.qot_sums + (size_t)e * p.qot_slot_cap * p.qot_hops, bit_rate, src * p.n_nodes + dst};
+  QotCtx cx{p, g, smem[threadIdx.x >> 5], s_link, e, lane, p.heap + (size_t)e * p.heap_stride + HEAP_PAD, p.heap_len[e],
+            p.qot_sums + (size_t)e * p.qot_slot_cap * p.qot_hops, bit_rate, src * p.n_nodes + dst, 1.0 / g.P, -1};
   unsigned short* free_stack = p.qot_free + (size_t)e * p.qot_slot_cap;
   int free_n = p.qot_free_n[e];
+  if (cx.heap_len > 0) cx.stage(0);
 
   // (1) releases of the last step (the services are out of the queue already)
   const int nrel = p.qot_rel_n[e];
@@ -249,7 +295,7 @@ __global__ void __launch_bounds__(QOT_WARPS * 32) qot_kernel(const Params p, con
   // (2) candidates, in the order the reference's first-fit heuristics walk them
   Tile<W, 1> tile{p.occ + (size_t)e * p.planes, 0, p.E};
   const double nan = __longlong_as_double(0x7FF8000000000000ll);
-  double gc = nan, gmin = nan;
+  double gc = -1.0, gmin = 0.0;  // 1 / GSNR (linear) of the last candidate evaluated (< 0: none) and of its worst neighbour
   bool accept = false;
   int a_path = -1, a_core = 0, a_start = -1, a_n = 0, a_se = 0, a_mod = 0;
   PathRec a_rec{};
@@ -346,9 +392,10 @@ __global__ void __launch_bounds__(QOT_WARPS * 32) qot_kernel(const Params p, con
       reinterpret_cast<int4*>(io.actions_out)[e] =
           accept ? make_int4(a_path, a_mod, a_core, a_start) : make_int4(p.k, p.n_mods, p.cores, p.S);
   }
-  if (lane == 0) {
-    p.qot_g[2 * (size_t)e] = gc;
-    p.qot_g[2 * (size_t)e + 1] = gmin;
+  if (lane == 0) {  // dB for the caller; the neighbours are not reported when the candidate itself missed its threshold
+    const bool cand_ok = gc >= 0.0 && gc <= p.qot_thr_lin[a_se];
+    p.qot_g[2 * (size_t)e] = gc >= 0.0 ? 10.0 * log10(1.0 / gc) : nan;
+    p.qot_g[2 * (size_t)e + 1] = cand_ok ? 10.0 * log10(1.0 / gmin) : nan;
   }
 
   // (3) the accepted candidate enters the service table

@@ -36,6 +36,7 @@ EXPORTS = (
     "orlg_launch_count", "orlg_gsnr_configure", "orlg_gsnr", "orlg_gsnr_for_actions", "orlg_phy_get_stats", "orlg_path_first_fit", "orlg_set_next_action_hint", "orlg_step_host_async", "orlg_step_host_wait", "orlg_set_host_wait",
     "orlg_phy_get_channel_state", "orlg_info_dim", "orlg_set_info_output",
     "orlg_step_auto", "orlg_qot_get", "orlg_qot_check", "orlg_step_auto_noalloc",
+    "orlg_export_services", "orlg_timed_steps",
 )
 
 
@@ -120,6 +121,8 @@ def load_library():
         L.orlg_set_next_action_hint.argtypes = [vp, i32, vp]
         L.orlg_step_auto.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
         L.orlg_step_auto_noalloc.argtypes = [vp, i32, vp, vp, vp, vp, vp]
+        L.orlg_export_services.argtypes = [vp, vp, i32, vp, vp]
+        L.orlg_timed_steps.argtypes = [vp, i32, i32, vp, vp, vp, vp, i32, vp, C.c_size_t, i32, vp, vp, vp]
         L.orlg_qot_get.argtypes = [vp, vp, vp]
         L.orlg_qot_check.argtypes = [vp, vp, vp]
         _lib = L
@@ -316,6 +319,28 @@ class Engine:
         array of the library (num_envs * action_dim <= 262144); the call allocates nothing."""
         self._ck(self.L.orlg_step_auto_noalloc(self.h, int(heuristic_id), self._p(reward), self._p(done),
                                                self._obs_base(obs), self._p(alloc), self._stream()))
+
+    def services(self, max_rows: int = 512):
+        """Running services of every env: (int32 [num_envs, max_rows, 6], int32 [num_envs] counts); rows are
+        (src_id * n_nodes + dst_id, path, core, first slot, slots, spectral efficiency) in release-queue order."""
+        torch = self.torch
+        out = torch.zeros((self.num_envs, max_rows, 6), dtype=torch.int32, device=self.device)
+        cnt = torch.zeros(self.num_envs, dtype=torch.int32, device=self.device)
+        self._ck(self.L.orlg_export_services(self.h, self._p(out), max_rows, self._p(cnt), self._stream()))
+        return out, cnt
+
+    def timed_steps(self, nsteps, actions=None, reward=None, done=None, obs=None, heuristic_id=None, flush=None,
+                    use_graph=True):
+        """orlg_timed_steps: (ms per step [nsteps], ms of the step's first launch [nsteps]) as numpy f32.
+        heuristic_id None: orlg_step(actions) as configured; else orlg_step_auto(heuristic_id, actions)."""
+        ms = np.zeros(nsteps, np.float32)
+        first = np.zeros(nsteps, np.float32)
+        mode = 0 if heuristic_id is None else 1
+        fb = 0 if flush is None else flush.numel() * flush.element_size()
+        self._ck(self.L.orlg_timed_steps(self.h, mode, int(heuristic_id or 0), self._p(actions), self._p(reward),
+                                         self._p(done), self._obs_base(obs), int(nsteps), self._p(flush), fb,
+                                         int(bool(use_graph)), ms.ctypes.data, first.ctypes.data, self._stream()))
+        return ms, first
 
     def qot_last(self, out=None):
         """QoT gate: f64 [num_envs, 2] (candidate GSNR dB, lowest neighbour GSNR dB) of the last candidates evaluated."""
