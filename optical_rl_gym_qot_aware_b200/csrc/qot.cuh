@@ -155,7 +155,7 @@ struct QotCtx {
   // The gate for one candidate; warp-collective.  Returns pass / fail; acc_c = 1 / GSNR of the candidate,
   // acc_w = the largest 1 / GSNR among its neighbours with the candidate present (0 without neighbours).
   // Leaves the candidate's sums in sm.cSA / sm.cSX.
-  __device__ bool gate(const PathRec& rec, int path, int core, int start, int n, int se, double& acc_c, double& acc_w) {
+  __device__ __noinline__ bool gate(const PathRec& rec, int path, int core, int start, int n, int se, double& acc_c, double& acc_w) {
     const int cpos2 = 2 * start + n;
     const ulonglong2 cmask = __ldg(g.path_mask + (size_t)pair * p.k + path);
     const int hops = rec.hops();
@@ -231,7 +231,7 @@ struct QotCtx {
   }
 
   // add (sign = +1) or remove (-1) lightpath (path mask, core, start, n, se) from the sums of its neighbours
-  __device__ void apply_to_neighbours(ulonglong2 mask, int core, int start, int n, int se, int sign) {
+  __device__ __noinline__ void apply_to_neighbours(ulonglong2 mask, int core, int start, int n, int se, int sign) {
     const int cols = 4 * g.tab_S + 1;
     const int pos2 = 2 * start + n;
     const double pm = phi_mod(se);
@@ -262,14 +262,54 @@ __device__ __forceinline__ bool qot_crosstalk_ok(const Params& p, int bit_rate, 
   return path_length < __ldg(p.mod_reach + mod) && path_length < lmax_snr;
 }
 
-// One warp per env: (1) the services the last step released leave their neighbours' sums, (2) the candidate(s)
-// of the action / of heuristic 13 are put through the gate, (3) an accepted candidate gets a row of the service
-// table and enters its neighbours' sums; the verdict tells the step kernel what to provision.
+// One lane's candidate lightpath for the pending request
+struct QotCand {
+  int path, core, start, n, se, mod;
+};
+__device__ __forceinline__ QotCand qot_cand_from(const QotCand& c, int src_lane) {
+  QotCand r;
+  r.path = __shfl_sync(0xFFFFFFFFu, c.path, src_lane);
+  r.core = __shfl_sync(0xFFFFFFFFu, c.core, src_lane);
+  r.start = __shfl_sync(0xFFFFFFFFu, c.start, src_lane);
+  r.n = __shfl_sync(0xFFFFFFFFu, c.n, src_lane);
+  r.se = __shfl_sync(0xFFFFFFFFu, c.se, src_lane);
+  r.mod = __shfl_sync(0xFFFFFFFFu, c.mod, src_lane);
+  return r;
+}
+
+// the channel alone on its path, evaluated by ONE lane (hops walked serially): lanes hold different candidates
+__device__ __forceinline__ bool qot_alone_ok_lane(const Params& p, const GsnrParams& g, const double4* link_c,
+                                                  const PathRec& rec, int start, int n, int se, double invP) {
+  const QotChan c = qot_chan(g, start, n, invP);
+  const double sci = __ldg(g.sci_tab + n);
+  double acc = 0.0;
+  for_each_link(rec, [&](int l) {
+    const double4 lc = link_c[l];
+    acc += lc.w * (c.ase * lc.z + c.nli * lc.x * sci);
+  });
+  return acc <= p.qot_thr_lin[se];
+}
+
+// One warp per env: (1) the services the last step released leave their neighbours' sums, (2) the candidates of the
+// action / of heuristic 13 are generated one per lane - (path, modulation) pairs: slot count, first fit, RMCSA's
+// closed-form gate, interference-free GSNR - and the viable ones put through the gate in the order the reference's
+// first-fit heuristics walk them, (3) an accepted candidate gets a row of the service table and enters its
+// neighbours' sums; the verdict tells the step kernel what to provision.
 template <int W>
-__global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const Params p, const GsnrParams g, const QotIO io) {
+__global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const Params p_, const GsnrParams g_, const QotIO io) {
   __shared__ QotWarpSmem smem[QOT_WARPS];
   __shared__ double4 s_link[128];
-  for (int l = threadIdx.x; l < p.E; l += blockDim.x) s_link[l] = g.link_c[l];
+  // the parameter blocks are handed to non-inlined helpers by reference: one shared copy per CTA instead of a
+  // local-memory copy per thread
+  __shared__ Params p;
+  __shared__ GsnrParams g;
+  {
+    const int* src = reinterpret_cast<const int*>(&p_);
+    int* dst = reinterpret_cast<int*>(&p);
+    for (int i = threadIdx.x; i < (int)(sizeof(Params) / 4); i += blockDim.x) dst[i] = src[i];
+    if (threadIdx.x == 0) g = g_;
+  }
+  for (int l = threadIdx.x; l < p_.E; l += blockDim.x) s_link[l] = g_.link_c[l];
   __syncthreads();
   const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (e >= p.num_envs) return;
@@ -292,110 +332,124 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
   }
   __syncwarp();
 
-  // (2) candidates, in the order the reference's first-fit heuristics walk them
+  // (2) candidates
   Tile<W, 1> tile{p.occ + (size_t)e * p.planes, 0, p.E};
-  const double nan = __longlong_as_double(0x7FF8000000000000ll);
+  const bool rmcsa = p.kind == ORLG_ENV_RMCSA;
+  const bool verdict = io.mode == QOT_VERDICT;
+  // modulations tried per path, most efficient first: RMSA-v0 adaptive qot_se[], RMCSA-v0 adaptive qot_mod_order[],
+  // else the path's best modulation; a verdict on an RMCSA action names its modulation
+  const int nt = (rmcsa && verdict) ? 1 : !p.qot_adaptive ? 1 : rmcsa ? p.n_mods : p.qot_n_se;
+  int act[4] = {0, 0, 0, 0};
+  bool act_ok = true;
+  if (verdict) {
+    if (!rmcsa) {
+      const int2 a = reinterpret_cast<const int2*>(io.actions)[e];
+      act[0] = a.x, act[3] = a.y;
+      act_ok = a.x >= 0 && a.y >= 0 && a.x < p.k && a.y < p.S;  // rmsa_env.py:233-235
+    } else {
+      const int4 a = reinterpret_cast<const int4*>(io.actions)[e];
+      act[0] = a.x, act[1] = a.y, act[2] = a.z, act[3] = a.w;
+      act_ok = a.x >= 0 && a.y >= 0 && a.z >= 0 && a.w >= 0 && a.x < p.k && a.y < p.n_mods && a.z < p.cores && a.w < p.S;
+    }
+  }
+  const int n_paths = verdict ? 1 : p.k;
+  const int ppr = max(1, 32 / nt);  // whole paths per round of 32 lanes
   double gc = -1.0, gmin = 0.0;  // 1 / GSNR (linear) of the last candidate evaluated (< 0: none) and of its worst neighbour
   bool accept = false;
-  int a_path = -1, a_core = 0, a_start = -1, a_n = 0, a_se = 0, a_mod = 0;
-  PathRec a_rec{};
-  const bool rmcsa = p.kind == ORLG_ENV_RMCSA;
-  if (io.mode == QOT_VERDICT) {
-    if (!rmcsa) {  // RMSAEnv.step behind the gate (rmsa_env.py:233-271)
-      const int2 a = reinterpret_cast<const int2*>(io.actions)[e];
-      if (a.x >= 0 && a.y >= 0 && a.x < p.k && a.y < p.S) {
-        const PathRec rec = load_path(p, cx.pair, a.x);
-        if (rec.hops() > 0) {
+  QotCand A{-1, 0, -1, 0, 0, 0};  // the last candidate evaluated
+  for (int p0 = 0; p0 < n_paths && !accept && act_ok; p0 += ppr) {
+    // ---- generation, one candidate per lane ----
+    QotCand c{-1, 0, -1, 0, 0, 0};
+    bool ok = false;
+    const int pl = lane / nt, t = lane - pl * nt;
+    if (pl < ppr && p0 + pl < n_paths) {
+      c.path = verdict ? act[0] : p0 + pl;
+      const PathRec rec = load_path(p, cx.pair, c.path);
+      if (rec.hops() > 0) {
+        if (!rmcsa) {
+          c.se = p.qot_adaptive ? p.qot_se[t] : rec.se();
+          c.n = number_slots(bit_rate, c.se, p);
           const Row<W> av = tile.path_avail(rec, 0);
-          const int nse = p.qot_adaptive ? p.qot_n_se : 1;
-          for (int t = 0; t < nse && !accept; t++) {
-            const int se = p.qot_adaptive ? p.qot_se[t] : rec.se();
-            const int n = number_slots(bit_rate, se, p);
-            if (a.y + n > p.S || !range_is_free<W>(av, a.y, n)) break;  // a wider channel does not fit either
-            if (p.qot_adaptive && !cx.alone_ok(rec, a.y, n, se)) continue;
-            a_rec = rec, a_path = a.x, a_start = a.y, a_n = n, a_se = se;
-            accept = cx.gate(rec, a.x, 0, a.y, n, se, gc, gmin);
+          if (verdict) {  // RMSAEnv.step: the slot is given
+            c.start = act[3];
+            ok = c.start + c.n <= p.S && range_is_free<W>(av, c.start, c.n);
+          } else {  // walk of rmsa_env.py:901-913
+            c.start = first_fit<W>(av, c.n, p.S);
+            ok = c.start >= 0;
+          }
+        } else {
+          c.mod = verdict ? act[1] : p.qot_adaptive ? p.qot_mod_order[t] : rec.best_mod();
+          if (c.mod < p.n_mods) {  // else: no modulation reaches (get_best_modulation_format raises)
+            c.se = __ldg(p.mod_se + c.mod);
+            c.n = number_slots(bit_rate, c.se, p);
+            if (verdict) {  // RMCSAEnv.step: core and slot are given
+              c.core = act[2], c.start = act[3];
+              ok = c.start + c.n <= p.S && range_is_free<W>(tile.path_avail(rec, c.core), c.start, c.n);
+            } else {  // walk of rmcsa_env.py:882-911: the first core with room
+              for (int core = 0; core < p.cores && !ok; core++) {
+                c.start = first_fit<W>(tile.path_avail(rec, core), c.n, p.S);
+                c.core = core;
+                ok = c.start >= 0;
+              }
+            }
+            ok = ok && qot_crosstalk_ok(p, bit_rate, c.mod, __ldg(p.path_length + (size_t)cx.pair * p.k + c.path));
           }
         }
-      }
-    } else {  // RMCSAEnv.step behind the gate (rmcsa_env.py:222-289)
-      const int4 a = reinterpret_cast<const int4*>(io.actions)[e];
-      if (a.x >= 0 && a.y >= 0 && a.z >= 0 && a.w >= 0 && a.x < p.k && a.y < p.n_mods && a.z < p.cores && a.w < p.S) {
-        const PathRec rec = load_path(p, cx.pair, a.x);
-        if (rec.hops() > 0) {
-          const int se = __ldg(p.mod_se + a.y), n = number_slots(bit_rate, se, p);
-          if (a.w + n <= p.S && range_is_free<W>(tile.path_avail(rec, a.z), a.w, n) &&
-              qot_crosstalk_ok(p, bit_rate, a.y, __ldg(p.path_length + (size_t)cx.pair * p.k + a.x))) {
-            a_rec = rec, a_path = a.x, a_core = a.z, a_start = a.w, a_n = n, a_se = se, a_mod = a.y;
-            accept = cx.gate(rec, a.x, a.z, a.w, n, se, gc, gmin);
-          }
-        }
-      }
-    }
-  } else if (!rmcsa) {  // heuristic 13 on RMSA-v0 (walk of rmsa_env.py:901-913)
-    for (int path = 0; path < p.k && !accept; path++) {
-      const PathRec rec = load_path(p, cx.pair, path);
-      if (rec.hops() <= 0) continue;
-      const Row<W> av = tile.path_avail(rec, 0);
-      const int nse = p.qot_adaptive ? p.qot_n_se : 1;
-      for (int t = 0; t < nse && !accept; t++) {
-        const int se = p.qot_adaptive ? p.qot_se[t] : rec.se();
-        const int n = number_slots(bit_rate, se, p);
-        const int s = first_fit<W>(av, n, p.S);
-        if (s < 0) break;
-        if (p.qot_adaptive && !cx.alone_ok(rec, s, n, se)) continue;
-        a_rec = rec, a_path = path, a_start = s, a_n = n, a_se = se;
-        accept = cx.gate(rec, path, 0, s, n, se, gc, gmin);
-        if (accept && t > 0 && io.mode == QOT_HEUR_VERDICT) {
-          // The RMSA-v0 action (path, slot) does not name the modulation: the step assigns the most efficient one
-          // that passes AT THIS SLOT, which can be better than the one that passed at its own first-fit slot.
-          // Walk the step's search (the chosen one is reached last and passes).
-          accept = false;
-          for (int t2 = 0; t2 <= t && !accept; t2++) {
-            const int se2 = p.qot_se[t2], n2 = number_slots(bit_rate, se2, p);
-            if (s + n2 > p.S || !range_is_free<W>(av, s, n2)) break;
-            if (!cx.alone_ok(rec, s, n2, se2)) continue;
-            a_n = n2, a_se = se2;
-            accept = cx.gate(rec, path, 0, s, n2, se2, gc, gmin);
-          }
-        }
+        // a slot count that does not fit ends a path's search in the reference walk; wider channels (later t) fit even
+        // less, so dropping every candidate without room is the same thing
+        if (ok && p.qot_adaptive) ok = qot_alone_ok_lane(p, g, s_link, rec, c.start, c.n, c.se, cx.invP);
       }
     }
-  } else {  // heuristic 13 on RMCSA-v0 (walk of rmcsa_env.py:882-911)
-    for (int path = 0; path < p.k && !accept; path++) {
-      const PathRec rec = load_path(p, cx.pair, path);
-      if (rec.hops() <= 0) continue;
-      const double len = __ldg(p.path_length + (size_t)cx.pair * p.k + path);
-      const int nm = p.qot_adaptive ? p.n_mods : 1;
-      for (int t = 0; t < nm && !accept; t++) {
-        const int mod = p.qot_adaptive ? p.qot_mod_order[t] : rec.best_mod();
-        if (mod >= p.n_mods) break;  // no modulation reaches (get_best_modulation_format raises)
-        const int se = __ldg(p.mod_se + mod), n = number_slots(bit_rate, se, p);
-        int core = -1, s = -1;
-        for (int c = 0; c < p.cores && s < 0; c++) {
-          s = first_fit<W>(tile.path_avail(rec, c), n, p.S);
-          if (s >= 0) core = c;
+    // ---- the gate, in candidate order, until one passes ----
+    unsigned viable = __ballot_sync(0xFFFFFFFFu, ok);
+    while (viable && !accept) {
+      const int L = __ffs((int)viable) - 1;
+      viable &= viable - 1;
+      A = qot_cand_from(c, L);
+      const PathRec rec = load_path(p, cx.pair, A.path);
+      accept = cx.gate(rec, A.path, A.core, A.start, A.n, A.se, gc, gmin);
+      if (accept && !rmcsa && io.mode == QOT_HEUR_VERDICT && (L % nt) > 0) {
+        // The RMSA-v0 action (path, slot) does not name the modulation: the step assigns the most efficient one that
+        // passes AT THIS SLOT, which can be better than the one that passed at its own first-fit slot.  Walk the
+        // step's search over the more efficient ones; the chosen one is evaluated again last if none passes.
+        const QotCand chosen = A;
+        const int tc = L % nt;
+        QotCand c2 = chosen;
+        bool ok2 = false;
+        if (lane < tc) {
+          c2.se = p.qot_se[lane];
+          c2.n = number_slots(bit_rate, c2.se, p);  // narrower than the chosen channel: it fits where that one fits
+          ok2 = qot_alone_ok_lane(p, g, s_link, rec, c2.start, c2.n, c2.se, cx.invP);
         }
-        if (s < 0) break;  // no core has room; a wider channel does not fit either
-        if (!qot_crosstalk_ok(p, bit_rate, mod, len)) continue;
-        if (p.qot_adaptive && !cx.alone_ok(rec, s, n, se)) continue;
-        a_rec = rec, a_path = path, a_core = core, a_start = s, a_n = n, a_se = se, a_mod = mod;
-        accept = cx.gate(rec, path, core, s, n, se, gc, gmin);
+        unsigned v2 = __ballot_sync(0xFFFFFFFFu, ok2);
+        accept = false;
+        while (v2 && !accept) {
+          const int L2 = __ffs((int)v2) - 1;
+          v2 &= v2 - 1;
+          A = qot_cand_from(c2, L2);
+          accept = cx.gate(rec, A.path, A.core, A.start, A.n, A.se, gc, gmin);
+        }
+        if (!accept) {
+          A = chosen;
+          accept = cx.gate(rec, A.path, A.core, A.start, A.n, A.se, gc, gmin);
+        }
       }
     }
   }
 
-  if (io.mode != QOT_VERDICT && io.actions_out != nullptr && lane == 0) {
+  const double nan = __longlong_as_double(0x7FF8000000000000ll);
+  if (!verdict && io.actions_out != nullptr && lane == 0) {
     if (!rmcsa)
-      reinterpret_cast<int2*>(io.actions_out)[e] = accept ? make_int2(a_path, a_start) : make_int2(p.k, p.S);
+      reinterpret_cast<int2*>(io.actions_out)[e] = accept ? make_int2(A.path, A.start) : make_int2(p.k, p.S);
     else
       reinterpret_cast<int4*>(io.actions_out)[e] =
-          accept ? make_int4(a_path, a_mod, a_core, a_start) : make_int4(p.k, p.n_mods, p.cores, p.S);
+          accept ? make_int4(A.path, A.mod, A.core, A.start) : make_int4(p.k, p.n_mods, p.cores, p.S);
   }
-  if (lane == 0) {  // dB for the caller; the neighbours are not reported when the candidate itself missed its threshold
-    const bool cand_ok = gc >= 0.0 && gc <= p.qot_thr_lin[a_se];
-    p.qot_g[2 * (size_t)e] = gc >= 0.0 ? 10.0 * log10(1.0 / gc) : nan;
-    p.qot_g[2 * (size_t)e + 1] = cand_ok ? 10.0 * log10(1.0 / gmin) : nan;
+  if (lane < 2) {  // dB for the caller; the neighbours are not reported when the candidate itself missed its threshold
+    const bool cand_ok = gc >= 0.0 && gc <= p.qot_thr_lin[A.se];
+    const double x = lane == 0 ? gc : gmin;
+    const bool have = lane == 0 ? gc >= 0.0 : cand_ok;
+    p.qot_g[2 * (size_t)e + lane] = have ? 10.0 * log10(1.0 / x) : nan;
   }
 
   // (3) the accepted candidate enters the service table
@@ -407,13 +461,14 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
     }
     if (accept) {
       slot = free_stack[--free_n];
-      if (lane < a_rec.hops())
+      const PathRec rec = load_path(p, cx.pair, A.path);
+      if (lane < rec.hops())
         cx.row(slot)[lane] = make_longlong2((long long)cx.sm.cSA[lane], (long long)cx.sm.cSX[lane]);
-      cx.apply_to_neighbours(__ldg(g.path_mask + (size_t)cx.pair * p.k + a_path), a_core, a_start, a_n, a_se, +1);
+      cx.apply_to_neighbours(__ldg(g.path_mask + (size_t)cx.pair * p.k + A.path), A.core, A.start, A.n, A.se, +1);
     }
     if (lane == 0) {
-      p.qot_verdict[2 * (size_t)e] = make_int4(accept ? 1 : 0, a_path | (a_core << 16), a_start, a_n);
-      p.qot_verdict[2 * (size_t)e + 1] = make_int4(a_se, slot, a_mod, 0);
+      p.qot_verdict[2 * (size_t)e] = make_int4(accept ? 1 : 0, A.path | (A.core << 16), A.start, A.n);
+      p.qot_verdict[2 * (size_t)e + 1] = make_int4(A.se, slot, A.mod, 0);
     }
   }
   if (lane == 0) {
