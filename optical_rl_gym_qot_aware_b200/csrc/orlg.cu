@@ -46,6 +46,7 @@ struct orlg_engine {
   int hint_heuristic = 0;
   int* auto_actions = nullptr;          // orlg_step_auto without a caller buffer
   long long* auto_reward_sum = nullptr; // set by orlg_rollout around its orlg_step_auto loop
+  int qot_cap = 64;                     // services staged per window by qot_kernel (64 / 128 / 256)
   cudaEvent_t mid_ev = nullptr;         // orlg_timed_steps: recorded between the launches of a multi-launch step
   bool mid_external = false;
 };
@@ -422,6 +423,13 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
     for (int a = 1; a < c->n_mods; a++)  // stable, by descending spectral efficiency (utils.py:105-117)
       for (int b = a; b > 0 && c->mod_se[p.qot_mod_order[b]] > c->mod_se[p.qot_mod_order[b - 1]]; b--)
         std::swap(p.qot_mod_order[b], p.qot_mod_order[b - 1]);
+    {  // window of the release queue qot_kernel stages in shared memory: the offered load + 1 sigma covers the
+       // queue nearly always (blocking keeps it below the offered load); a longer queue costs a second window
+      const double A = c->mean_holding / c->mean_iat;
+      int cap = (int)std::ceil(A + std::sqrt(A));
+      if (const char* s = getenv("ORLG_QOT_CAP"); s && *s) cap = atoi(s);
+      e->qot_cap = cap <= 64 ? 64 : cap <= 128 ? 128 : 256;
+    }
     p.qot_hops = c->max_hops;
     p.qot_slot_cap = p.heap_cap;
     if ((rc = dev_alloc(e, &p.qot_sums, NP * (size_t)p.qot_slot_cap * p.qot_hops)) ||
@@ -504,11 +512,18 @@ static int launch_qot(orlg_engine* e, int mode, const int32_t* actions, int32_t*
   cudaStream_t st = (cudaStream_t)stream;
   QotIO q{mode, actions, actions_out};
   const int grid = (e->p.num_envs + QOT_WARPS - 1) / QOT_WARPS;
+#define ORLG_QOT_LAUNCH(WW)                                                                         \
+  do {                                                                                              \
+    if (e->qot_cap <= 64) qot_kernel<WW, 64><<<grid, QOT_WARPS * 32, 0, st>>>(e->p, e->gp, q);       \
+    else if (e->qot_cap <= 128) qot_kernel<WW, 128><<<grid, QOT_WARPS * 32, 0, st>>>(e->p, e->gp, q); \
+    else qot_kernel<WW, 256><<<grid, QOT_WARPS * 32, 0, st>>>(e->p, e->gp, q);                        \
+  } while (0)
   switch (e->W) {
-    case 2: qot_kernel<2><<<grid, QOT_WARPS * 32, 0, st>>>(e->p, e->gp, q); break;
-    case 4: qot_kernel<4><<<grid, QOT_WARPS * 32, 0, st>>>(e->p, e->gp, q); break;
-    default: qot_kernel<10><<<grid, QOT_WARPS * 32, 0, st>>>(e->p, e->gp, q); break;
+    case 2: ORLG_QOT_LAUNCH(2); break;
+    case 4: ORLG_QOT_LAUNCH(4); break;
+    default: ORLG_QOT_LAUNCH(10); break;
   }
+#undef ORLG_QOT_LAUNCH
   cudaError_t rc = cudaGetLastError();
   if (rc != cudaSuccess) {
     e->err = std::string("qot_kernel launch: ") + cudaGetErrorString(rc);

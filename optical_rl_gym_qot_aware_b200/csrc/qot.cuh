@@ -35,10 +35,12 @@ struct QotIO {
 };
 
 #ifndef QOT_MIN_CTAS  // resident CTAs per SM the register allocation must allow (A/B knob)
-#define QOT_MIN_CTAS 5
+#define QOT_MIN_CTAS 8
 #endif
-constexpr int QOT_CAP = 256;  // running services staged per window (an env with more is walked window by window)
-
+// QOT_CAP = running services staged per window (an env with more is walked window by window); the kernel is
+// instantiated for 64 / 128 / 256 and the launch picks the smallest that covers the offered load + 1 sigma, because
+// shared memory per CTA is what bounds the resident warps here
+template <int QOT_CAP>
 struct QotWarpSmem {
   unsigned long long pay[QOT_CAP];      // release-queue payloads of the staged window
   ulonglong2 mask[QOT_CAP];             // their paths as link sets
@@ -72,10 +74,11 @@ __device__ __forceinline__ double qot_sum_phi(const GsnrParams& g, int n, long l
   return __ldg(g.sci_tab + n) + ((double)SA * QOT_INV_SCALE - ((double)SX * QOT_INV_SCALE) * lol);
 }
 
+template <int QOT_CAP>
 struct QotCtx {
   const Params& p;
   const GsnrParams& g;
-  QotWarpSmem& sm;
+  QotWarpSmem<QOT_CAP>& sm;
   const double4* link_c;  // per-link factors (l_eff, l_eff / L, exp(2 a L) - 1, spans), staged in shared memory
   int e, lane;
   const ulonglong2* heap;
@@ -86,6 +89,9 @@ struct QotCtx {
   int win;  // staged window of the release queue
 
   __device__ __forceinline__ longlong2* row(int slot) const { return sums + (size_t)slot * p.qot_hops; }
+  __device__ __forceinline__ const unsigned char* path_bytes(int pr, int path) const {
+    return reinterpret_cast<const unsigned char*>(p.path_rec + ((size_t)pr * p.k + path) * p.rec_u4);
+  }
 
   __device__ __forceinline__ void stage(int w) {
     __syncwarp();
@@ -173,7 +179,7 @@ struct QotCtx {
       const int d = (2 * svc_start(s) + ni) - cpos2;  // centre distance in half slots, interferer - candidate
       const double2 t_ci = __ldg(g.xci_tab + (size_t)ni * cols + (d + 2 * g.tab_S));  // service i seen by the candidate
       const double2 t_ic = __ldg(g.xci_tab + (size_t)n * cols + (-d + 2 * g.tab_S));  // the candidate seen by service i
-      const PathRec ri = load_path(p, svc_pair(s), svc_path(s));
+      const unsigned char* ri = path_bytes(svc_pair(s), svc_path(s));  // byte 0 hops, bytes 4.. link per hop
       const longlong2* rw = row(svc_slot(s));
       const unsigned long long qa_ci = (unsigned long long)qot_q(t_ci.x),
                                qx_ci = (unsigned long long)qot_q(phi_mod(sei) * t_ci.y);
@@ -195,7 +201,7 @@ struct QotCtx {
       const QotChan ci = qot_chan(g, svc_start(s), ni, invP);
       const double sci = __ldg(g.sci_tab + ni);
       double acc = 0.0;
-      const int hi = ri.hops();
+      const int hi = __ldg(ri);
       for (int h0 = 0; h0 < hi; h0 += 4) {  // four independent row loads in flight
         longlong2 sv[4];
 #pragma unroll
@@ -203,7 +209,7 @@ struct QotCtx {
 #pragma unroll
         for (int u = 0; u < 4; u++)
           if (h0 + u < hi) {
-            const int l = ri.link(h0 + u);
+            const int l = __ldg(ri + 4 + h0 + u);
             const double4 lc = link_c[l];
             if (mask_has(common, l)) {
               sv[u].x += qa_ic;
@@ -239,11 +245,11 @@ struct QotCtx {
       const int d = (2 * svc_start(s) + svc_slots(s)) - pos2;
       const double2 t = __ldg(g.xci_tab + (size_t)n * cols + (-d + 2 * g.tab_S));  // this lightpath seen by service i
       const long long qa = sign * qot_q(t.x), qx = sign * qot_q(pm * t.y);
-      const PathRec ri = load_path(p, svc_pair(s), svc_path(s));
+      const unsigned char* ri = path_bytes(svc_pair(s), svc_path(s));
       longlong2* rw = row(svc_slot(s));
-      const int hi = ri.hops();
+      const int hi = __ldg(ri);
       for (int h = 0; h < hi; h++)
-        if (mask_has(common, ri.link(h))) {
+        if (mask_has(common, __ldg(ri + 4 + h))) {
           longlong2 sv = rw[h];
           sv.x += qa;
           sv.y += qx;
@@ -295,9 +301,9 @@ __device__ __forceinline__ bool qot_alone_ok_lane(const Params& p, const GsnrPar
 // closed-form gate, interference-free GSNR - and the viable ones put through the gate in the order the reference's
 // first-fit heuristics walk them, (3) an accepted candidate gets a row of the service table and enters its
 // neighbours' sums; the verdict tells the step kernel what to provision.
-template <int W>
+template <int W, int QOT_CAP>
 __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const Params p_, const GsnrParams g_, const QotIO io) {
-  __shared__ QotWarpSmem smem[QOT_WARPS];
+  __shared__ QotWarpSmem<QOT_CAP> smem[QOT_WARPS];
   __shared__ double4 s_link[128];
   // the parameter blocks are handed to non-inlined helpers by reference: one shared copy per CTA instead of a
   // local-memory copy per thread
@@ -315,7 +321,7 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
   if (e >= p.num_envs) return;
   const uint32_t m = p.meta[e];
   const int bit_rate = (int)(m & 0xFFFFu), src = (int)((m >> 16) & 0xFFu), dst = (int)(m >> 24);
-  QotCtx cx{p, g, smem[threadIdx.x >> 5], s_link, e, lane, p.heap + (size_t)e * p.heap_stride + HEAP_PAD, p.heap_len[e],
+  QotCtx<QOT_CAP> cx{p, g, smem[threadIdx.x >> 5], s_link, e, lane, p.heap + (size_t)e * p.heap_stride + HEAP_PAD, p.heap_len[e],
             p.qot_sums + (size_t)e * p.qot_slot_cap * p.qot_hops, bit_rate, src * p.n_nodes + dst, 1.0 / g.P, -1};
   unsigned short* free_stack = p.qot_free + (size_t)e * p.qot_slot_cap;
   int free_n = p.qot_free_n[e];
