@@ -106,7 +106,8 @@ struct Params {
   unsigned long long* qot_rel;          // [NP][QOT_REL_CAP] payloads of the services the last step released
   int* qot_rel_n;                       // [NP]
   int4* qot_verdict;                    // [NP][2] (accept, path | core << 16, first slot, slots), (se, row, modulation, 0)
-  double* qot_g;                        // [NP][2] GSNR of the last candidate evaluated, lowest neighbour GSNR with it present
+  double* qot_g;                        // [NP][2] 1 / GSNR (linear) of the last candidate evaluated and of its worst neighbour with it present; < 0 = none
+  const double2* qot_chan;              // [S + 1] per slot count: (B h NF / P, (P / B)^3 8 / (27 pi |b2|) g^2 B / P)
 };
 constexpr int PHY_LEVELS = 8;   // modulation levels 1..8 (100 Gb/s per level per channel, phy_rmsa_env.py:1424)
 constexpr int PHY_ADIM = 9;     // action = (path, 8 channel numbers, -1 terminated)

@@ -430,6 +430,19 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
       if (const char* s = getenv("ORLG_QOT_CAP"); s && *s) cap = atoi(s);
       e->qot_cap = cap <= 64 ? 64 : cap <= 128 ? 128 : 256;
     }
+    {  // the link-independent factors of P_ASE / P and P_NLI / P (calculate_osnr.py:45-52) per slot count
+      const double pi = 3.141592653589793, beta2 = 21.3e-27, gamma = 1.3e-3, h_planck = 6.626e-34;
+      const orlg_gsnr_params* gq = c->qot_gsnr;
+      std::vector<double> tab(2 * ((size_t)p.S + 1), 0.0);
+      for (int n = 1; n <= p.S; n++) {
+        const double B = (double)n * gq->slot_hz, pr = gq->launch_power_w / B;
+        tab[2 * n] = B * h_planck * gq->noise_figure_lin / gq->launch_power_w;
+        tab[2 * n + 1] = pr * pr * pr * (8.0 / (27.0 * pi * beta2)) * gamma * gamma * B / gq->launch_power_w;
+      }
+      const double* d = nullptr;
+      if ((rc = dev_upload(e, &d, tab.data(), tab.size()))) return fail_create(e, rc, e->err);
+      p.qot_chan = reinterpret_cast<const double2*>(d);
+    }
     p.qot_hops = c->max_hops;
     p.qot_slot_cap = p.heap_cap;
     if ((rc = dev_alloc(e, &p.qot_sums, NP * (size_t)p.qot_slot_cap * p.qot_hops)) ||
@@ -904,8 +917,10 @@ extern "C" int orlg_qot_get(orlg_engine* e, double* dev_out, void* stream) {
     return ORLG_ESTATE;
   }
   cudaSetDevice(e->device);
-  CK(cudaMemcpyAsync(dev_out, e->p.qot_g, (size_t)e->p.num_envs * 2 * sizeof(double), cudaMemcpyDeviceToDevice,
-                     (cudaStream_t)stream));
+  const long long n = 2ll * e->p.num_envs;
+  qot_db_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(e->p.qot_g, dev_out, n);
+  CK(cudaGetLastError());
+  e->launches++;
   return ORLG_OK;
 }
 

@@ -61,13 +61,11 @@ __device__ __forceinline__ long long qot_q(double x) { return __double2ll_rn(x *
 struct QotChan {
   double ase, nli;  // B h f NF / P ;  (P / B)^3 8 / (27 pi |b2|) g^2 B / P
 };
-__device__ __forceinline__ QotChan qot_chan(const GsnrParams& g, int start, int n, double invP) {
-  const double pi = 3.141592653589793, beta2 = 21.3e-27, gamma = 1.3e-3, h_planck = 6.626e-34;
-  const double B = (double)n * g.slot_hz, f = g.f0 + ((double)start + 0.5 * (double)n) * g.slot_hz;
-  const double pr = g.P / B;
+__device__ __forceinline__ QotChan qot_chan(const Params& p, const GsnrParams& g, int start, int n) {
+  const double2 t = __ldg(p.qot_chan + n);  // per slot count: (B h NF / P, (P / B)^3 8 / (27 pi |b2|) g^2 B / P), built at create
   QotChan c;
-  c.ase = B * h_planck * f * g.nf * invP;
-  c.nli = pr * pr * pr * (8.0 / (27.0 * pi * beta2)) * gamma * gamma * B * invP;
+  c.ase = t.x * (g.f0 + ((double)start + 0.5 * (double)n) * g.slot_hz);
+  c.nli = t.y;
   return c;
 }
 __device__ __forceinline__ double qot_sum_phi(const GsnrParams& g, int n, long long SA, long long SX, double lol) {
@@ -145,7 +143,7 @@ struct QotCtx {
 
   // the channel alone on its path: ASE and self-channel NLI only.  1 / GSNR (linear).
   __device__ __forceinline__ double alone_acc(const PathRec& rec, int start, int n) const {
-    const QotChan c = qot_chan(g, start, n, invP);
+    const QotChan c = qot_chan(p, g, start, n);
     const int hops = rec.hops();
     double v = 0.0;
     if (lane < hops) {
@@ -198,7 +196,7 @@ struct QotCtx {
         c1 &= c1 - 1;
       }
       // the neighbour with the candidate present: its stored sums + the candidate's term on the shared links
-      const QotChan ci = qot_chan(g, svc_start(s), ni, invP);
+      const QotChan ci = qot_chan(p, g, svc_start(s), ni);
       const double sci = __ldg(g.sci_tab + ni);
       double acc = 0.0;
       const int hi = __ldg(ri);
@@ -225,7 +223,7 @@ struct QotCtx {
     fail = __any_sync(0xFFFFFFFFu, fail);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) worst = fmax(worst, __shfl_xor_sync(0xFFFFFFFFu, worst, o));
-    const QotChan cc = qot_chan(g, start, n, invP);
+    const QotChan cc = qot_chan(p, g, start, n);
     double v = 0.0;
     if (lane < hops) {
       const double4 lc = link_c[rec.link(lane)];
@@ -286,7 +284,7 @@ __device__ __forceinline__ QotCand qot_cand_from(const QotCand& c, int src_lane)
 // the channel alone on its path, evaluated by ONE lane (hops walked serially): lanes hold different candidates
 __device__ __forceinline__ bool qot_alone_ok_lane(const Params& p, const GsnrParams& g, const double4* link_c,
                                                   const PathRec& rec, int start, int n, int se, double invP) {
-  const QotChan c = qot_chan(g, start, n, invP);
+  const QotChan c = qot_chan(p, g, start, n);
   const double sci = __ldg(g.sci_tab + n);
   double acc = 0.0;
   for_each_link(rec, [&](int l) {
@@ -451,11 +449,9 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
       reinterpret_cast<int4*>(io.actions_out)[e] =
           accept ? make_int4(A.path, A.mod, A.core, A.start) : make_int4(p.k, p.n_mods, p.cores, p.S);
   }
-  if (lane < 2) {  // dB for the caller; the neighbours are not reported when the candidate itself missed its threshold
-    const bool cand_ok = gc >= 0.0 && gc <= p.qot_thr_lin[A.se];
-    const double x = lane == 0 ? gc : gmin;
-    const bool have = lane == 0 ? gc >= 0.0 : cand_ok;
-    p.qot_g[2 * (size_t)e + lane] = have ? 10.0 * log10(1.0 / x) : nan;
+  if (lane == 0) {  // 1 / GSNR (linear); orlg_qot_get converts to dB on demand (no log10 on the step path)
+    p.qot_g[2 * (size_t)e] = gc;  // < 0: nothing evaluated
+    p.qot_g[2 * (size_t)e + 1] = (gc >= 0.0 && gc <= p.qot_thr_lin[A.se]) ? gmin : -1.0;  // not reported when the candidate failed
   }
 
   // (3) the accepted candidate enters the service table
@@ -481,6 +477,12 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
     p.qot_free_n[e] = free_n;
     p.qot_rel_n[e] = 0;
   }
+}
+
+// 1 / GSNR (linear, < 0 = none) -> dB (NaN = none) for orlg_qot_get
+__global__ void qot_db_kernel(const double* in, double* out, long long n) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i < n) out[i] = in[i] >= 0.0 ? 10.0 * log10(1.0 / in[i]) : __longlong_as_double(0x7FF8000000000000ll);
 }
 
 // Test / debug: recompute every running service's sums from scratch and compare with the table (exact).
