@@ -161,3 +161,23 @@ def tables_from_topology(topology) -> TopologyTables:
         mod_inband_xt=np.array([_f(m.inband_xt) for m in mods], np.float64),
         path_links_by_id=path_links_by_id,
     )
+
+
+DATA_DIR = __import__("os").path.join(__import__("os").path.dirname(__import__("os").path.abspath(__file__)), "data")
+
+
+def builtin_topology(short: str) -> TopologyTables:
+    """Tables of the topologies the reference ships (examples/topologies/*.h5), flattened once and kept with the
+    package: nsfnet, us14, jpn12_k3, jpn12_k5, spn, germany50."""
+    import os
+
+    return TopologyTables.load(os.path.join(DATA_DIR, f"topology_{short}.npz"))
+
+
+def builtin_qot_tables(name: str = "Results_K3SP_FRP_SLC_CBG_USB14"):
+    """The QoT tables of examples/phy_frag_rmsa/inputs/*.mat as numpy arrays: (modulation_level, gsnr,
+    connections_detail), as tests/test_rmsa_us.py:43-49 unpacks them."""
+    import os
+
+    z = np.load(os.path.join(DATA_DIR, f"phytab_{name}.npz"), allow_pickle=False)
+    return z["phy_mod"], z["phy_gsnr"], z["phy_conn"]

@@ -115,7 +115,8 @@ def test_other_bench_workloads_at_full_size(workload, steps):
     from optical_rl_gym_qot_aware_b200.engine import Engine
     from optical_rl_gym_qot_aware_b200.sharding import shard_bounds
 
-    spec, hid, _, _ = bench.make_workload(workload)
+    spec, w = bench.make_workload(workload)
+    hid = w["hid"]
     dev = torch.device("cuda", 0)
     eng = Engine(spec, N_ENV)
     eng.reset(True)

@@ -146,7 +146,8 @@ def test_bench_reference_arm_and_host_policy():
     assert line["impl"] == "reference" and line["unit"] == "env-steps/s" and line["value"] > 0
     assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] >= 1
     assert line["e2e"] == {"value": line["value"], "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
-    assert line["config"]["workload"] == "c2_deeprmsa_nsfnet_100" and line["gpu_launches"] == 0
+    # the default workload is the QoT configuration BASELINE.json's metric is quoted on
+    assert line["config"]["workload"] == "c6_rmsa_us14_320_gn" and line["gpu_launches"] == 0
 
     sys.path.insert(0, repo)
     import bench
