@@ -88,6 +88,10 @@ class EnvSpec:
     info_stats: bool = False
     # GN-model QoT gate (RMSA-v0 / RMCSA-v0; include/orlg.h "QoT gate"): the GSNR of the candidate and of its
     # neighbours (examples/calculate_osnr.py:9-56) must meet the SD-FEC threshold of their modulations
+    # PhyRMSA periodic defragmentation (phy_rmsa_env.py:355-417): every phy_defrag_period processed services
+    phy_defrag_period: int = 0
+    phy_number_moves: int = 0
+    phy_metric: int = 0  # 0 "cut" (calculate_r_cut), 1 "rss" (calculate_r_spatial)
     qot_gate: bool = False
     qot_adaptive: bool = False
     qot_thr_db: Optional[np.ndarray] = None   # [16] threshold in dB by spectral efficiency
@@ -197,9 +201,8 @@ def make_spec(
     if kind == ENV_PHYRMSA:
         from . import phy as P
 
-        if defrag_period:
-            raise NotImplementedError("PhyRMSA periodic defragmentation is not built yet (SURVEY.md 8f N2); "
-                                      "pass defrag_period=None")
+        if defrag_period and (number_moves is None or metric not in ("cut", "rss")):
+            raise ValueError("defrag_period needs number_moves and metric in ('cut', 'rss') (phy_rmsa_env.py:54-56)")
         if modulation_level is None or connections_detail is None or gsnr is None:
             raise ValueError("PhyRMSA-v0 needs modulation_level, connections_detail and gsnr")
         channels = P.num_channels(number_spectrum_channels, number_spectrum_channels_s_band, l_band, s_band)
@@ -269,6 +272,11 @@ def make_spec(
     spec.info_stats = bool(info_stats) and kind in (ENV_RMSA, ENV_DEEPRMSA)
     if kind == ENV_PHYRMSA:
         spec.phy_grooming = 1 if grooming else (2 if keep_channel_state else 0)
+        if defrag_period:
+            spec.phy_defrag_period, spec.phy_number_moves = int(defrag_period), int(number_moves)
+            spec.phy_metric = 0 if metric == "cut" else 1
+            if spec.phy_grooming == 0:  # _groom_defragmentation and the release rules read channel_state
+                spec.phy_grooming = 2
     if qot:
         if qot != "gn" or kind not in (ENV_RMSA, ENV_RMCSA):
             raise ValueError("qot='gn' (GN-model QoT gate) is defined for RMSA-v0 and RMCSA-v0")

@@ -79,6 +79,10 @@ class OracleConfig(C.Structure):
         ("qot_se", C.c_int32 * 8),
         ("qot_thr_db", C.c_double * 16),
         ("qot_gsnr", C.c_void_p),
+        ("phy_defrag_period", C.c_int32),
+        ("phy_number_moves", C.c_int32),
+        ("phy_metric", C.c_int32),
+        ("phy_pad", C.c_int32),
     ]
 
 
@@ -128,6 +132,7 @@ def lib():
         L.oracle_pool_gsnr_sum.restype = C.c_double
         L.oracle_pool_gsnr_sum.argtypes = [C.c_void_p]
         L.oracle_phy_stats.argtypes = [C.c_void_p, C.c_void_p]
+        L.oracle_phy_moves.argtypes = [C.c_void_p, C.c_void_p]
         L.oracle_phy_channel_state.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
         L.oracle_phy_channel_state.restype = C.c_int64
         L.oracle_info.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
@@ -200,6 +205,9 @@ class OracleSpec:
         c.n_bit_rates = 0 if spec.bit_rates is None else len(spec.bit_rates)
         c.seed = spec.seed & 0xFFFFFFFFFFFFFFFF
         c.bit_rate_lo, c.bit_rate_hi = spec.bit_rate_lo, spec.bit_rate_hi
+        c.phy_defrag_period = int(getattr(spec, "phy_defrag_period", 0) or 0)
+        c.phy_number_moves = int(getattr(spec, "phy_number_moves", 0) or 0)
+        c.phy_metric = int(getattr(spec, "phy_metric", 0) or 0)
         if getattr(spec, "qot_gate", False):
             gp = spec.qot_gsnr
             k["qot_span_count"] = np.ascontiguousarray(gp.span_count, np.int32)
@@ -269,6 +277,12 @@ class OracleEnv:
         o = np.zeros((max_entries, 6), np.int32)
         n = int(self.L.oracle_phy_channel_state(self.h, o.ctypes.data, max_entries))
         return o[: min(n, max_entries)]
+
+    def phy_moves(self):
+        """(counted_moves, counted_moves_groom, counted_defrag_cycles) of the current episode."""
+        o = np.zeros(3, np.int64)
+        self.L.oracle_phy_moves(self.h, o.ctypes.data)
+        return o
 
     def phy_stats(self):
         o = np.zeros(8, np.float64)

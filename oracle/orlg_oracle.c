@@ -120,6 +120,8 @@ typedef struct svc { /* a provisioned Service (utils.py:56-80), what release nee
   int32_t nch;      /* PhyRMSA: service.channels */
   int16_t ch[8];
   int8_t share[8], cap[8]; /* channel tuple fields [1] (capacity used by this service) and [3] (level), units of 100 Gb/s */
+  int64_t uid;    /* identity of the Service object (service_id repeats across episodes, F7) */
+  double arrival; /* service.arrival_time (age of a defragmentation candidate, phy_rmsa_env.py:372) */
 } svc;
 
 /* one tuple of channel_state[src_id, dst_id, idp] (phy_rmsa_env.py:599-601): (channel, used, free, capacity);
@@ -149,6 +151,9 @@ struct oracle_env {
   double total_path_length_ep, total_gsnr_ep;
   int64_t total_path_index_ep, total_mod_level_ep, channels_accepted_ep, physical_accepted_ep;
   double info_cuts, info_rss; /* number_cuts_total / rss_total_metric of the last step's info (:313-314) */
+  int64_t* run; /* topology.graph["running_services"] in list order (uids): PhyRMSA defragmentation walks it */
+  int64_t run_len, run_cap, next_uid;
+  int64_t counted_moves, counted_moves_groom, counted_defrag_cycles; /* phy_rmsa_env.py:110-112 */
   double qot_last[2];         /* QoT gate: GSNR of the last candidate evaluated, lowest neighbour GSNR with it present */
   int16_t* link_of; /* [N][N] edge index or -1 (topology[a][b]["index"]) */
   const oracle_request* trace;
@@ -193,6 +198,7 @@ void oracle_destroy(oracle_env* e) {
   free(e->lnk_last_update); free(e->lnk_utilization); free(e->lnk_compactness);
   free(e->hist_requested); free(e->hist_provisioned);
   free(e->link_of);
+  free(e->run);
   free(e);
 }
 
@@ -433,8 +439,26 @@ static void cs_append(oracle_env* e, int pair, int idp, int ch, int used, int fr
   e->cs[e->cs_len++] = r;
 }
 
+/* topology.graph["running_services"]: list.append / list.remove */
+static void run_append(oracle_env* e, int64_t uid) {
+  if (e->run_len == e->run_cap) {
+    e->run_cap = e->run_cap ? 2 * e->run_cap : 256;
+    e->run = (int64_t*)realloc(e->run, sizeof(int64_t) * (size_t)e->run_cap);
+  }
+  e->run[e->run_len++] = uid;
+}
+static void run_remove(oracle_env* e, int64_t uid) {
+  for (int64_t i = 0; i < e->run_len; i++)
+    if (e->run[i] == uid) {
+      memmove(e->run + i, e->run + i + 1, sizeof(int64_t) * (size_t)(e->run_len - i - 1));
+      e->run_len--;
+      return;
+    }
+}
+
 /* _release_path rmsa_env.py:515-535 / rmcsa_env.py:536-558 */
 static void release_path(oracle_env* e, const svc* s) {
+  if (e->c.env_kind == 3) run_remove(e, s->uid); /* phy_rmsa_env.py:861 (order of this line does not matter) */
   const int16_t* L = links_of(e, s->pair, s->path, 0);
   int h = hops_of(e, s->pair, s->path);
   if (e->c.env_kind == 3 && !e->c.phy_grooming) { /* no channel_state: every channel of the service is freed */
@@ -538,6 +562,7 @@ void oracle_reset(oracle_env* e, int full) {
   e->ep_processed = e->ep_accepted = 0;
   e->total_path_length_ep = e->total_gsnr_ep = 0.0; /* phy_rmsa_env.py:431-439 */
   e->total_path_index_ep = e->total_mod_level_ep = e->channels_accepted_ep = e->physical_accepted_ep = 0;
+  e->counted_moves = e->counted_moves_groom = e->counted_defrag_cycles = 0; /* phy_rmsa_env.py:433-435 */
   if (!full) {
     if (e->new_service) { /* pending service is re-counted, rmsa_env.py:370-374 */
       e->ep_processed++;
@@ -546,6 +571,7 @@ void oracle_reset(oracle_env* e, int full) {
     return;
   }
   e->cs_len = 0;   /* channel_state phy_rmsa_env.py:455-461 */
+  e->run_len = 0;
   if (e->c.info_stats) { /* optical_network_env.py:257-260, rmsa_env.py:444-452 */
     for (int l = 0; l < e->c.n_edges; l++) e->lnk_last_update[l] = e->lnk_utilization[l] = e->lnk_compactness[l] = 0.0;
     for (int i = 0; i < e->c.n_bit_rates; i++) e->hist_requested[i] = e->hist_provisioned[i] = 0;
@@ -578,6 +604,7 @@ static int crosstalk_ok(const oracle_env* e, int mod, double path_length) {
   return path_length < lmax_xt && path_length < lmax_snr;
 }
 
+static void phy_defragmentation(oracle_env* e);
 static void finish_step(oracle_env* e, int accepted, int32_t* reward, uint8_t* done) {
   if (e->c.env_kind == 2) { /* rmcsa_env.py:292-295 (bit rate counted a second time) */
     e->services_processed++;
@@ -589,6 +616,8 @@ static void finish_step(oracle_env* e, int accepted, int32_t* reward, uint8_t* d
   int r = e->c.env_kind == 1 ? (accepted ? 1 : -1) : (accepted ? 1 : 0);
   e->new_service = 0;
   next_service(e);
+  if (e->c.env_kind == 3 && e->c.phy_defrag_period > 0 && e->services_processed % e->c.phy_defrag_period == 0)
+    phy_defragmentation(e); /* phy_rmsa_env.py:355-417 */
   int d = e->ep_processed == e->c.episode_length; /* rmsa_env.py:339 */
   if (d) {
     e->episodes++;
@@ -618,7 +647,7 @@ static int is_channel_free(const oracle_env* e, int pair, int path, int ch) {
 }
 
 /* calculate_r_cut(channel, links, defrag_flag=False, path, modified=True) phy_rmsa_env.py:1140-1193 */
-static int calculate_r_cut(const oracle_env* e, int pair, int path, int ch) {
+static int calculate_r_cut_flag(const oracle_env* e, int pair, int path, int ch, int defrag_flag) {
   int N = e->c.n_nodes, E = e->c.n_edges, h = hops_of(e, pair, path);
   const int16_t* nl = nodes_of(e, pair, path);
   const int16_t* L = links_of(e, pair, path, 0);
@@ -627,7 +656,7 @@ static int calculate_r_cut(const oracle_env* e, int pair, int path, int ch) {
   int result[2];
   for (int pass = 0; pass < 2; pass++) {
     for (int l = 0; l < E; l++) tmp[l] = AV(e, 0, l)[ch];
-    if (pass == 1) for (int i = 0; i < h; i++) tmp[L[i]] = 0; /* temporary_channels2[i] = 0 */
+    if (pass == 1) for (int i = 0; i < h; i++) tmp[L[i]] = defrag_flag ? 1 : 0; /* temporary_channels2[i] = 1 / 0 (:1167-1172) */
     int cut = 0;
     for (int i = 0; i < nn; i++) {
       for (int key = 0; key < N; key++) { /* for node_key in self.topology[path.node_list[i]] */
@@ -647,6 +676,8 @@ static int calculate_r_cut(const oracle_env* e, int pair, int path, int ch) {
   return result[0] - result[1];
 }
 
+static int calculate_r_cut(const oracle_env* e, int pair, int path, int ch) { return calculate_r_cut_flag(e, pair, path, ch, 0); }
+
 /* sqrt(sum len^2) / (sum len + 1) over the runs of free links of a channel column, link-index order
  * (the summand of calculate_r_spatial / calculate_total_r_spatial phy_rmsa_env.py:1085-1121) */
 static double column_rss(const uint8_t* col, int E) {
@@ -660,15 +691,18 @@ static double column_rss(const uint8_t* col, int E) {
 }
 
 /* calculate_r_spatial(channel, links, defrag_flag=False) phy_rmsa_env.py:1085-1108 */
-static double calculate_r_spatial(const oracle_env* e, int pair, int path, int ch) {
+static double calculate_r_spatial_flag(const oracle_env* e, int pair, int path, int ch, int defrag_flag) {
   int E = e->c.n_edges, h = hops_of(e, pair, path);
   const int16_t* L = links_of(e, pair, path, 0);
   uint8_t tmp[256];
   for (int l = 0; l < E; l++) tmp[l] = AV(e, 0, l)[ch];
   double before = column_rss(tmp, E);
-  for (int i = 0; i < h; i++) tmp[L[i]] = 0;
+  for (int i = 0; i < h; i++) tmp[L[i]] = defrag_flag ? 1 : 0; /* :1095-1100 */
   double after = column_rss(tmp, E);
   return after - before;
+}
+static double calculate_r_spatial(const oracle_env* e, int pair, int path, int ch) {
+  return calculate_r_spatial_flag(e, pair, path, ch, 0);
 }
 
 static int use_existing_channels(const oracle_env* e, int32_t* a);
@@ -805,6 +839,9 @@ static int phy_decide(oracle_env* e, const int32_t* a, int32_t* alloc) {
       e->ep_accepted++;
       e->br_provisioned += e->cur.bit_rate;
       e->ep_br_provisioned += e->cur.bit_rate;
+      s.uid = e->next_uid++;
+      s.arrival = e->cur.arrival;
+      run_append(e, s.uid); /* :656 */
       heap_push(e, s);
       accepted = 1;
     }
@@ -855,6 +892,9 @@ static int phy_decide(oracle_env* e, const int32_t* a, int32_t* alloc) {
     e->physical_accepted_ep++;
     e->br_provisioned += e->cur.bit_rate;
     e->ep_br_provisioned += e->cur.bit_rate;
+    s.uid = e->next_uid++;
+    s.arrival = e->cur.arrival;
+    run_append(e, s.uid); /* :620 */
     heap_push(e, s);
     accepted = 1;
   }
@@ -865,6 +905,140 @@ static int phy_decide(oracle_env* e, const int32_t* a, int32_t* alloc) {
     alloc[3] = accepted ? nch : 0;
   }
   return accepted;
+}
+
+/* ---- PhyRMSA periodic defragmentation: phy_rmsa_env.py:355-417 (step), _groom_defragmentation :703-733,
+ * _move_virtual :735-764, _move :662-697.  Python iterates its lists by index while the loop bodies remove and
+ * re-append elements; the loops below do the same on arrays, so the elements skipped / visited twice are the same. */
+static svc* svc_by_uid(oracle_env* e, int64_t uid) {
+  for (int64_t i = 0; i < e->heap_len; i++)
+    if (e->heap[i].uid == uid) return &e->heap[i];
+  return NULL;
+}
+static void svc_channel_remove(svc* s, int ci) { /* service.channels.remove(old_channel) */
+  for (int i = ci; i + 1 < s->nch; i++) { s->ch[i] = s->ch[i + 1]; s->share[i] = s->share[i + 1]; s->cap[i] = s->cap[i + 1]; }
+  s->nch--;
+}
+static void svc_channel_append(svc* s, int ch, int share, int cap) {
+  s->ch[s->nch] = (int16_t)ch; s->share[s->nch] = (int8_t)share; s->cap[s->nch] = (int8_t)cap;
+  s->nch++;
+}
+static void set_channel_on_path(oracle_env* e, const svc* s, int ch, int value) {
+  const int16_t* L = links_of(e, s->pair, s->path, 0);
+  for (int i = 0; i < hops_of(e, s->pair, s->path); i++) AV(e, 0, L[i])[ch] = (uint8_t)value;
+}
+
+/* _groom_defragmentation :703-733 */
+static int groom_defragmentation(oracle_env* e) {
+  int grooming_moves = 0;
+  for (int64_t i = 0; i < e->run_len; i++) {       /* for service in running_services (live list) */
+    const int64_t uid = e->run[i];
+    svc* s = svc_by_uid(e, uid);
+    if (!s) continue;
+    for (int ci = 0; ci < s->nch; ci++) {          /* for channel in service.channels (live list) */
+      const int c_ch = s->ch[ci], c_share = s->share[ci], c_cap = s->cap[ci];
+      if (c_share != c_cap) {
+        int64_t at = cs_find(e, s->pair, s->path, c_ch); /* corresponding_channel = [t for t in ... if t[0] == channel[0]][0] */
+        if (at >= 0 && e->cs[at].used == c_share) {      /* nobody else uses the channel: it can move */
+          for (int64_t j = 0; j < e->cs_len; j++) {      /* for target_channel in channel_state[key] */
+            chan_state t = e->cs[j];
+            if (t.pair != s->pair || t.idp != s->path) continue;
+            if (j == at) continue;                       /* target_channel != corresponding_channel */
+            if (t.free_ >= c_share) {
+              /* two tuples removed, one appended (:717-724) */
+              if (j > at) { cs_remove(e, j); cs_remove(e, at); } else { cs_remove(e, at); cs_remove(e, j); }
+              cs_append(e, t.pair, t.idp, t.ch, t.used + c_share, t.free_ - c_share, t.cap);
+              /* _move_virtual(service, (target[0], channel[1], updated[2], target[3], True), channel) */
+              set_channel_on_path(e, s, c_ch, 1);
+              run_remove(e, uid);
+              run_append(e, uid);
+              svc_channel_remove(s, ci);
+              svc_channel_append(s, t.ch, c_share, t.cap);
+              grooming_moves++;
+              break;
+            }
+          }
+        }
+      }
+      if (grooming_moves == e->c.phy_number_moves) return grooming_moves;
+    }
+  }
+  return grooming_moves;
+}
+
+typedef struct defrag_cand { double diff, age; int ch; int64_t uid; int share, cap; } defrag_cand;
+
+static void phy_defragmentation(oracle_env* e) {
+  const int C = e->c.num_slots, k = e->c.k_paths, N = e->c.n_nodes;
+  e->counted_moves_groom = groom_defragmentation(e); /* :357 */
+  if (e->counted_moves_groom > e->c.phy_number_moves) return;
+  /* candidates :360-380, in running_services order, then sorted by (-gain, -age), stable */
+  int64_t cap = 64, n = 0;
+  defrag_cand* cand = (defrag_cand*)malloc(sizeof(defrag_cand) * (size_t)cap);
+  for (int64_t i = 0; i < e->run_len; i++) {
+    const svc* s = svc_by_uid(e, e->run[i]);
+    if (!s) continue;
+    for (int ci = 0; ci < s->nch; ci++) {
+      if (s->share[ci] != s->cap[ci]) continue; /* only whole channels are reallocated */
+      double diff = e->c.phy_metric == 0 ? (double)calculate_r_cut_flag(e, s->pair, s->path, s->ch[ci], 1)
+                                         : calculate_r_spatial_flag(e, s->pair, s->path, s->ch[ci], 1);
+      if (diff > 0) {
+        if (n == cap) { cap *= 2; cand = (defrag_cand*)realloc(cand, sizeof(defrag_cand) * (size_t)cap); }
+        defrag_cand c = {diff, e->now - s->arrival, s->ch[ci], s->uid, s->share[ci], s->cap[ci]};
+        int64_t pos = n++;
+        while (pos > 0 && (c.diff > cand[pos - 1].diff || (c.diff == cand[pos - 1].diff && c.age > cand[pos - 1].age))) {
+          cand[pos] = cand[pos - 1];
+          pos--;
+        }
+        cand[pos] = c;
+      }
+    }
+  }
+  int num_moves = 0;
+  const int cur_a = e->cur.src, cur_b = e->cur.dst;
+  for (int64_t i = 0; i < n; i++) {
+    svc* s = svc_by_uid(e, cand[i].uid);
+    if (!s) continue;
+    const int sa = s->pair / N, sb = s->pair % N;
+    /* idp: the index of the candidate's path among the CURRENT request's k paths (dataclass equality), which is
+     * the path's own index when both are between the same two nodes and otherwise the last value of the loop
+     * variable, k - 1 (:386-391) */
+    const int same_pair = (sa == cur_a && sb == cur_b) || (sa == cur_b && sb == cur_a);
+    const int idp = same_pair ? s->path : k - 1;
+    const int table = e->c.phy_table_id[s->pair];
+    int have = 0, best_ch = -1;
+    double best_metric = 0;
+    for (int ch = 0; ch < C; ch++) { /* reallocation options :382-399, best of sorted(key=(-metric, channel)) */
+      if (!is_channel_free(e, s->pair, s->path, ch)) continue;
+      if (phy_level(e, table, ch, idp) != phy_level(e, table, cand[i].ch, idp)) continue;
+      double metric = e->c.phy_metric == 0 ? (double)calculate_r_cut(e, s->pair, s->path, ch)
+                                           : calculate_r_spatial(e, s->pair, s->path, ch);
+      if (!have || metric > best_metric) { have = 1; best_metric = metric; best_ch = ch; }
+    }
+    if (have && -1 * best_metric < cand[i].diff) { /* :401-405 */
+      /* _move(service, new_channel_number, old_channel) :662-697 */
+      int ci = -1;
+      for (int q = 0; q < s->nch; q++)
+        if (s->ch[q] == cand[i].ch && s->share[q] == cand[i].share && s->cap[q] == cand[i].cap) { ci = q; break; }
+      if (ci >= 0) {
+        set_channel_on_path(e, s, best_ch, 0);
+        set_channel_on_path(e, s, cand[i].ch, 1);
+        run_remove(e, s->uid);
+        run_append(e, s->uid);
+        svc_channel_remove(s, ci);
+        svc_channel_append(s, best_ch, cand[i].share, cand[i].cap);
+        num_moves++;
+        e->counted_moves++;
+      }
+    }
+    if (num_moves + e->counted_moves_groom > e->c.phy_number_moves) break; /* :414 */
+  }
+  if (num_moves != 0) e->counted_defrag_cycles++;
+  free(cand);
+}
+
+void oracle_phy_moves(const oracle_env* e, int64_t* out3) {
+  out3[0] = e->counted_moves; out3[1] = e->counted_moves_groom; out3[2] = e->counted_defrag_cycles;
 }
 
 /* channel_state in append order: rows (pair, idp, channel, used, free, capacity); returns the number of entries */

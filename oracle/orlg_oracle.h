@@ -91,6 +91,10 @@ typedef struct oracle_config {
   int32_t qot_se[8];
   double qot_thr_db[16];             /* by spectral efficiency */
   const oracle_gsnr_params* qot_gsnr;
+  /* PhyRMSA-v0 periodic defragmentation (phy_rmsa_env.py:355-417, 662-764): every phy_defrag_period processed
+   * services, grooming moves (_groom_defragmentation) then up to phy_number_moves channel reallocations ranked by the
+   * fragmentation gain (phy_metric 0 = "cut", 1 = "rss"); 0 = off */
+  int32_t phy_defrag_period, phy_number_moves, phy_metric, phy_pad;
 } oracle_config;
 
 typedef struct oracle_env oracle_env;
@@ -127,6 +131,8 @@ int64_t oracle_rollout_many(const oracle_config* cfg, int64_t env0, int64_t n_en
  * number_cuts_total, rss_total_metric (phy_rmsa_env.py:313-348). */
 #define ORACLE_PHY_ADIM 9
 void oracle_phy_stats(const oracle_env* e, double* out8);
+/* out3 = counted_moves, counted_moves_groom, counted_defrag_cycles (phy_rmsa_env.py:110-112; per episode :433-435) */
+void oracle_phy_moves(const oracle_env* e, int64_t* out3);
 /* info dict of the LAST step (rmsa_env.py:293-332): service_blocking_rate, episode_service_blocking_rate,
  * bit_rate_blocking_rate, episode_bit_rate_blocking_rate, network_compactness, network_compactness_difference,
  * avg_link_compactness, avg_link_utilization, fairness, then bit_rate_blocking_<b> for every bit rate.

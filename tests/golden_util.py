@@ -21,6 +21,7 @@ CASES = sorted(f[:-4] for f in os.listdir(GOLDEN)
                if f.endswith(".npz") and not f.startswith(("topology_", "gsnr_", "phy_", "phytab_", "defrag_", "qot_")))
 PHY_CASES = sorted(f[:-4] for f in os.listdir(GOLDEN) if f.startswith("phy_") and f.endswith(".npz"))
 QOT_CASES = sorted(f[:-4] for f in os.listdir(GOLDEN) if f.startswith("qot_") and f.endswith(".npz"))
+DEFRAG_CASES = sorted(f[:-4] for f in os.listdir(GOLDEN) if f.startswith("defrag_phy_") and f.endswith(".npz"))
 GSNR_CASES = sorted(f[:-4] for f in os.listdir(GOLDEN) if f.startswith("gsnr_") and f.endswith(".npz"))
 ENV_NAME = {0: "RMSA-v0", 1: "DeepRMSA-v0", 2: "RMCSA-v0", 3: "PhyRMSA-v0"}
 

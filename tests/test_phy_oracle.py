@@ -62,21 +62,33 @@ def test_phy_tables_first_match_and_cut_terms():
     assert ph.cut_count[pr * t.k_paths + ip] == expect
 
 
-def test_defragmentation_is_refused_and_its_pins_exist():
-    """PhyRMSA periodic defragmentation is not built: asking for it must fail loudly, never
-    run without it.  The traces of the unmodified reference that the round-2 kernel has to reproduce are already
-    committed (`defrag_phy_*.npz`: per step the cumulative move counters and a checksum of available_channels)."""
-    import os
+def avail_checksum(state):
+    """the checksum of available_channels the golden generator stores after every step (gen_phy_golden.py)"""
+    av = np.asarray(state, np.int64).ravel()
+    return int(np.dot(av, np.arange(1, av.size + 1, dtype=np.int64)))
 
-    from optical_rl_gym_qot_aware_b200 import spec as S
 
-    g, spec = G.load_case("phy_us14_bmfa_cut_100ch")
-    with pytest.raises(NotImplementedError):
-        S.make_spec("PhyRMSA-v0", spec.tables, defrag_period=10, number_moves=10, modulation_level=spec.phy.mod_level,
-                    connections_detail=np.zeros((1, 2), np.int32), gsnr=spec.phy.gsnr)
-    pins = sorted(f for f in os.listdir(G.GOLDEN) if f.startswith("defrag_phy_"))
-    assert len(pins) == 3
-    for f in pins:
-        z = np.load(os.path.join(G.GOLDEN, f))
-        assert z["moves"].shape == (len(z["actions"]), 3) and z["moves"][:, 0].max() > 0 and z["moves"][:, 2].max() > 0
-        assert int(z["kw_defrag_period"]) in (10, 20) and z["avail_sum"].shape == (len(z["actions"]),)
+@pytest.mark.parametrize("case", G.DEFRAG_CASES)
+def test_oracle_replays_defragmentation_golden(case):
+    """Periodic defragmentation (phy_rmsa_env.py:355-417, 662-764): the unmodified reference ran with defrag_period /
+    number_moves / metric; per step its heuristic action, accept / block, counters, the cumulative move counters
+    (counted_moves, counted_moves_groom, counted_defrag_cycles) and a checksum of available_channels are pinned, so
+    every grooming move and every reallocation has to land on the channel the reference chose."""
+    g, spec = G.load_case(case)
+    assert spec.phy_defrag_period == int(g["kw_defrag_period"]) and spec.phy_number_moves == int(g["kw_number_moves"])
+    hid = heuristic_of(case.replace("defrag_", "").replace("_cut_", "_bmfa_cut_").replace("_rss_", "_bmfarss_"))
+    env = OB.OracleEnv(spec, 0, trace=g["requests"])
+    env.reset(full=True)
+    for t in range(len(g["actions"])):
+        a = env.heuristic(hid)
+        assert np.array_equal(a, g["actions"][t]), (case, t, a, g["actions"][t])
+        _, r, d, alloc = env.step(g["actions"][t])
+        assert alloc[0] == g["accepted"][t] and r == g["reward"][t] and d == bool(g["done"][t]), (case, t)
+        assert np.array_equal(env.phy_moves(), g["moves"][t]), (case, t, env.phy_moves(), g["moves"][t])
+        assert avail_checksum(env.state()) == int(g["avail_sum"][t]), (case, t)
+        if d:
+            env.reset(full=False)
+        assert np.array_equal(env.counters()[:8], g["counters"][t]), (case, t)
+    assert np.array_equal(env.state(), g["final_avail"])
+    assert g["moves"][:, 0].max() > 0 and g["moves"][:, 2].max() > 0
+    env.close()
