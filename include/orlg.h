@@ -199,6 +199,13 @@ typedef struct orlg_config {
   int32_t qot_se[8];
   double qot_thr_db[16];               /* by spectral efficiency; +inf = never acceptable */
   const orlg_gsnr_params* qot_gsnr;    /* physical inputs of the GN model */
+
+  /* PhyRMSA-v0 periodic defragmentation (phy_rmsa_env.py:54-56, 355-417): every phy_defrag_period processed
+   * services the step also runs _groom_defragmentation (:703-733) and then reallocates up to phy_number_moves whole
+   * channels, candidates ranked by the gain in the fragmentation metric (phy_metric 0 = "cut" calculate_r_cut
+   * :1123-1193, 1 = "rss" calculate_r_spatial :1085-1108; "rss" needs <= 64 links) and by age (_move :662-697).
+   * 0 = off.  Needs phy_grooming != 0 (the grooming moves read channel_state). */
+  int32_t phy_defrag_period, phy_number_moves, phy_metric, phy_pad;
 } orlg_config;
 
 typedef struct orlg_engine orlg_engine;
@@ -316,6 +323,11 @@ int orlg_phy_get_stats(orlg_engine* e, double* dev_out, void* stream);
  * Needs info_stats = 1 (RMSA-v0 / DeepRMSA-v0). */
 int orlg_info_dim(const orlg_engine* e);
 int orlg_set_info_output(orlg_engine* e, double* dev_info);
+
+/* PhyRMSA-v0 defragmentation counters of the current episode, int64 [num_envs][3]: counted_moves,
+ * counted_moves_groom, counted_defrag_cycles (phy_rmsa_env.py:110-112; info keys num_moves = [0] / 2 + [1],
+ * num_moves_groom, num_defrag_cycle :340-342). */
+int orlg_phy_get_moves(orlg_engine* e, int64_t* dev_out, void* stream);
 
 /* PhyRMSA-v0 channel_state (phy_rmsa_env.py:158-166,599-601): the partially used channels of every env in
  * append order, int32 [num_envs][max_entries][6] = (src_id * n_nodes + dst_id, idp, channel, used, free,

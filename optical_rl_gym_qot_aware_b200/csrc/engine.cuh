@@ -94,6 +94,18 @@ struct Params {
   uint32_t* phy_cs_len;                 // [NP] entries in use | tombstones << 16
   double* phy_f;                        // [2][NP] episode sums: path length, gsnr
   long long* phy_i;                     // [4][NP] episode sums: path index, modulation level, channels, physical services
+  // PhyRMSA service table (engine_env.cuh PhySvc): one 48-byte record per running service
+  uint4* phy_svc;                       // [NP][phy_svc_cap][3]
+  unsigned short* phy_free;             // [NP][phy_svc_cap] stack of free rows
+  int* phy_free_n;                      // [NP]
+  int phy_svc_cap;
+  // periodic defragmentation (phy_rmsa_env.py:355-417): order list of the running services, move counters, candidates
+  int phy_defrag_period, phy_number_moves, phy_metric, phy_run_cap, phy_cand_cap;
+  unsigned short* phy_run;              // [NP][phy_run_cap] running_services in list order, 0xFFFF = removed
+  uint32_t* phy_run_len;                // [NP] slots in use | tombstones << 16
+  long long* phy_moves;                 // [3][NP] counted_moves, counted_moves_groom, counted_defrag_cycles
+  double2* phy_cand;                    // [NP][phy_cand_cap] (gain, age) of the defragmentation candidates
+  uint32_t* phy_cand_id;                // [NP][phy_cand_cap] service row | channel << 16
   // GN-model QoT gate (qot.cuh): RMSA-v0 / RMCSA-v0, env-major occupancy
   int qot, qot_adaptive, qot_n_se, qot_hops, qot_slot_cap;
   int qot_se[8];                        // adaptive RMSA-v0: spectral efficiencies tried, descending

@@ -43,6 +43,10 @@ struct Env {
   int cs_len, cs_dead; // PhyRMSA channel_state list: slots in use (tombstones included), tombstones
   long long slot_hops; // info_stats: sum of number_slots * hops over the running services
   int rel_n = 0;       // QoT gate: services released by this step, handed to the next qot_kernel launch
+  // PhyRMSA service table (one queue entry per service; its channels live in the service's record)
+  int sv_free_n = 0;            // free rows of the table
+  int run_len = 0, run_dead = 0;  // running_services order list (defragmentation only): slots in use, tombstones
+  long long mv[3] = {0, 0, 0};  // counted_moves, counted_moves_groom, counted_defrag_cycles (phy_rmsa_env.py:110-112)
 
   __device__ __forceinline__ Env(const Params& p_, uint32_t* smem, int tid, int e_)
       : p(p_), tile{smem, tid, p_.E}, e(e_) {
@@ -71,6 +75,14 @@ struct Env {
 #pragma unroll
       for (int i = 0; i < 4; i++) isum[i] = p.phy_i[(size_t)i * p.NP + e];
       load_cs_len();
+      sv_free_n = p.phy_free_n[e];
+      if (p.phy_defrag_period > 0) {
+        const uint32_t v = p.phy_run_len[e];
+        run_len = (int)(v & 0xFFFFu);
+        run_dead = (int)(v >> 16);
+#pragma unroll
+        for (int i = 0; i < 3; i++) mv[i] = p.phy_moves[(size_t)i * p.NP + e];
+      }
     }
   }
   // ---- info dict of RMSAEnv.step (rmsa_env.py:276-332), kept only with p.info_stats ----
@@ -204,6 +216,12 @@ struct Env {
 #pragma unroll
       for (int i = 0; i < 4; i++) p.phy_i[(size_t)i * p.NP + e] = isum[i];
       if (p.phy_grooming) p.phy_cs_len[e] = (uint32_t)cs_len | ((uint32_t)cs_dead << 16);
+      p.phy_free_n[e] = sv_free_n;
+      if (p.phy_defrag_period > 0) {
+        p.phy_run_len[e] = (uint32_t)run_len | ((uint32_t)run_dead << 16);
+#pragma unroll
+        for (int i = 0; i < 3; i++) p.phy_moves[(size_t)i * p.NP + e] = mv[i];
+      }
     }
   }
 
@@ -245,27 +263,137 @@ struct Env {
     }
     cs_at(cs_len++) = make_uint2(key, (uint32_t)used | ((uint32_t)free_ << 8) | ((uint32_t)cap << 16));
   }
-  // _release_path :781-861 for one channel tuple (ch, share, ., cap) of a service on (pair, path)
-  __device__ void phy_release(unsigned long long s) {
-    const int share = svc_core(s), cap = svc_se(s), ch = svc_start(s);
-    bool free_it = !p.phy_grooming || share == cap;  // :784 channel[1] == channel[3]
-    if (!free_it) {
-      const uint32_t key = cs_key(svc_pair(s), svc_path(s), ch);
-      const int at = cs_find(key);
-      if (at < 0) {  // unreachable from step (the reference would raise)
-        cnt[CNT_FAULT] |= 8;
-        return;
+  // ---- PhyRMSA service table: Service objects with their channel tuples (phy_rmsa_env.py:610-621) ----
+  // 48-byte records [slot][3 x uint4]: arrival f64 | pair u16, path u8, nch u8 | position in the order list;
+  // channel number u16 x 8; share u8 x 8 (tuple field [1]) and capacity u8 x 8 (field [3]), units of 100 Gb/s.
+  struct PhySvc {
+    double arrival;
+    int pair, path, nch, run_pos;
+    int ch[8], share[8], cap[8];
+    __device__ __forceinline__ void remove_channel(int ci) {  // service.channels.remove(old_channel)
+#pragma unroll
+      for (int i = 0; i < 7; i++)
+        if (i >= ci) {
+          ch[i] = ch[i + 1];
+          share[i] = share[i + 1];
+          cap[i] = cap[i + 1];
+        }
+      nch--;
+    }
+    __device__ __forceinline__ void append_channel(int c, int sh, int cp) {  // service.channels.append(new_channel)
+#pragma unroll
+      for (int i = 0; i < 8; i++)
+        if (i == nch) {
+          ch[i] = c;
+          share[i] = sh;
+          cap[i] = cp;
+        }
+      nch++;
+    }
+  };
+  __device__ __forceinline__ uint4* svc_rec(int slot) const { return p.phy_svc + ((size_t)e * p.phy_svc_cap + slot) * 3; }
+  __device__ PhySvc svc_load(int slot) const {
+    const uint4* r = svc_rec(slot);
+    const uint4 a = r[0], b = r[1], c = r[2];
+    PhySvc v;
+    v.arrival = __hiloint2double((int)a.y, (int)a.x);
+    v.pair = (int)(a.z & 0xFFFFu);
+    v.path = (int)((a.z >> 16) & 0xFFu);
+    v.nch = (int)(a.z >> 24);
+    v.run_pos = (int)a.w;
+    const uint32_t cw[4] = {b.x, b.y, b.z, b.w}, sw[2] = {c.x, c.y}, pw[2] = {c.z, c.w};
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      v.ch[i] = (int)((cw[i >> 1] >> (16 * (i & 1))) & 0xFFFFu);
+      v.share[i] = (int)((sw[i >> 2] >> (8 * (i & 3))) & 0xFFu);
+      v.cap[i] = (int)((pw[i >> 2] >> (8 * (i & 3))) & 0xFFu);
+    }
+    return v;
+  }
+  __device__ void svc_store(int slot, const PhySvc& v) const {
+    uint32_t cw[4] = {0, 0, 0, 0}, sw[2] = {0, 0}, pw[2] = {0, 0};
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      cw[i >> 1] |= (uint32_t)(v.ch[i] & 0xFFFF) << (16 * (i & 1));
+      sw[i >> 2] |= (uint32_t)(v.share[i] & 0xFF) << (8 * (i & 3));
+      pw[i >> 2] |= (uint32_t)(v.cap[i] & 0xFF) << (8 * (i & 3));
+    }
+    uint4* r = svc_rec(slot);
+    r[0] = make_uint4((uint32_t)__double2loint(v.arrival), (uint32_t)__double2hiint(v.arrival),
+                      (uint32_t)v.pair | ((uint32_t)v.path << 16) | ((uint32_t)v.nch << 24), (uint32_t)v.run_pos);
+    r[1] = make_uint4(cw[0], cw[1], cw[2], cw[3]);
+    r[2] = make_uint4(sw[0], sw[1], pw[0], pw[1]);
+  }
+  __device__ __forceinline__ unsigned short& run_at(int i) const { return p.phy_run[(size_t)e * p.phy_run_cap + i]; }
+  // topology.graph["running_services"] as an append-only list with tombstones (kept for defragmentation only)
+  __device__ void run_squeeze() {
+    int j = 0;
+    for (int i = 0; i < run_len; i++) {
+      const unsigned short sl = run_at(i);
+      if (sl != 0xFFFFu) {
+        if (j != i) {
+          run_at(j) = sl;
+          svc_rec(sl)[0].w = (uint32_t)j;
+        }
+        j++;
       }
-      const uint32_t y = cs_at(at).y;
-      const int used = (int)(y & 0xFFu), fr = (int)((y >> 8) & 0xFFu);
-      cs_remove(at);
-      if (used == share) free_it = true;                              // :821 nobody else is on the channel
-      else cs_append(key, used - share, fr + share, (int)(y >> 16));  // :841-844
     }
-    if (free_it) {
-      PathRec rec = load_path(p, svc_pair(s), svc_path(s));
-      tile.apply_bit(rec, 0, ch, true);
+    run_len = j;
+    run_dead = 0;
+  }
+  __device__ int run_append(int slot) {  // returns the position
+    if (run_len == p.phy_run_cap) run_squeeze();
+    if (run_len == p.phy_run_cap) {
+      cnt[CNT_FAULT] |= 64;
+      return 0;
     }
+    run_at(run_len) = (unsigned short)slot;
+    return run_len++;
+  }
+  __device__ __forceinline__ void run_remove(int pos) {
+    run_at(pos) = 0xFFFFu;
+    run_dead++;
+  }
+  // a new Service enters the table, the release queue and (defragmentation) the order list; false = table full
+  __device__ bool svc_provision(PhySvc& v, double key) {
+    if (sv_free_n == 0 || heap_len >= p.heap_cap) {
+      cnt[CNT_FAULT] |= 1;
+      return false;
+    }
+    const int slot = p.phy_free[(size_t)e * p.phy_svc_cap + --sv_free_n];
+    v.run_pos = p.phy_defrag_period > 0 ? run_append(slot) : 0;
+    svc_store(slot, v);
+    heap_push(key, (unsigned long long)slot);
+    return true;
+  }
+  // _release_path :781-861: the channels of the service in the order of service.channels
+  __device__ void phy_release(int slot) {
+    const PhySvc v = svc_load(slot);
+    PathRec rec = load_path(p, v.pair, v.path);
+#pragma unroll 1
+    for (int i = 0; i < v.nch; i++) {
+      const int share = v.share[i], cap = v.cap[i], ch = v.ch[i];
+      bool free_it = !p.phy_grooming || share == cap;  // :784 channel[1] == channel[3]
+      if (!free_it) {
+        const uint32_t key = cs_key(v.pair, v.path, ch);
+        const int at = cs_find(key);
+        if (at < 0) {  // unreachable from step (the reference would raise)
+          cnt[CNT_FAULT] |= 8;
+          continue;
+        }
+        const uint32_t y = cs_at(at).y;
+        const int used = (int)(y & 0xFFu), fr = (int)((y >> 8) & 0xFFu);
+        cs_remove(at);
+        if (used == share) free_it = true;                              // :821 nobody else is on the channel
+        else cs_append(key, used - share, fr + share, (int)(y >> 16));  // :841-844
+      }
+      if (free_it) tile.apply_bit(rec, 0, ch, true);
+    }
+    if (p.phy_defrag_period > 0) {
+      run_remove(v.run_pos);  // running_services.remove(service) :861
+      if (run_dead >= 64 + ((run_len - run_dead) >> 1)) run_squeeze();
+    }
+    p.phy_free[(size_t)e * p.phy_svc_cap + sv_free_n++] = (unsigned short)slot;
   }
 
   // ---- release queue: heapq of (arrival+holding, service), optical_network_env.py:178-189 ----
@@ -395,34 +523,9 @@ struct Env {
     cnt[CNT_EP_BR_REQ] += bit_rate;
     if constexpr (INFO) info_count(0, bit_rate);  // bit_rate_requested_histogram :680
     while (next_rel <= now) {  // rmsa_env.py:689-695
-      const double rel_key = next_rel;
       unsigned long long s = heap_pop();
       if constexpr (PHY) {
-        if (!p.phy_grooming) {
-          phy_release(s);
-        } else {
-          // the queue entries of one service (one per channel, same key) come out of the heap in any order;
-          // _release_path walks service.channels in order, and that order decides where the updated
-          // channel_state tuples are appended: regroup by the channel's position in the action
-          unsigned long long grp[8];
-          unsigned have = 0u;
-          const double key = rel_key;
-          for (;;) {
-            const int idx = svc_slots(s) & 7;
-            if (have & (1u << idx)) phy_release(s);  // two services released at the same instant
-            else {
-#pragma unroll
-              for (int q = 0; q < 8; q++)
-                if (idx == q) grp[q] = s;
-              have |= 1u << idx;
-            }
-            if (heap_len == 0 || next_rel != key) break;
-            s = heap_pop();
-          }
-#pragma unroll
-          for (int q = 0; q < 8; q++)
-            if (have & (1u << q)) phy_release(grp[q]);
-        }
+        phy_release((int)s);  // the payload is the service's row
       } else {
         PathRec rec = load_path(p, svc_pair(s), svc_path(s));
         tile.set_range(rec, svc_core(s), svc_start(s), svc_slots(s));
@@ -461,6 +564,7 @@ struct Env {
     if constexpr (PHY) {
       fsum[0] = fsum[1] = 0.0;
       isum[0] = isum[1] = isum[2] = isum[3] = 0;
+      mv[0] = mv[1] = mv[2] = 0;  // phy_rmsa_env.py:433-435
     }
   }
 

@@ -108,6 +108,13 @@ __global__ void ORLG_LAUNCH_BOUNDS(BD) env_kernel(const Params p, const StepIO i
       for (int i = 0; i < 2 * p.n_bit_rates; i++) p.br_hist[(size_t)i * p.NP + env.e] = 0;
     }
     env.next_rel = __longlong_as_double(0x7FF0000000000000ll);
+    if (PHY && active) {  // every row of the service table is free; empty order list
+      for (int i = 0; i < p.phy_svc_cap; i++)
+        p.phy_free[(size_t)env.e * p.phy_svc_cap + i] = (unsigned short)(p.phy_svc_cap - 1 - i);
+      env.sv_free_n = p.phy_svc_cap;
+      env.run_len = env.run_dead = 0;
+      env.mv[0] = env.mv[1] = env.mv[2] = 0;
+    }
     if (p.qot && active) {  // every row of the service table is free, nothing waits to leave the sums
       for (int i = 0; i < p.qot_slot_cap; i++)
         p.qot_free[(size_t)env.e * p.qot_slot_cap + i] = (unsigned short)(p.qot_slot_cap - 1 - i);
@@ -219,6 +226,8 @@ __global__ void ORLG_LAUNCH_BOUNDS(BD) env_kernel(const Params p, const StepIO i
         // reward: optical_network_env.py:213-214 ; deeprmsa_env.py:123-124
         int r = (p.kind == ORLG_ENV_DEEPRMSA) ? (d.accepted ? 1 : -1) : (d.accepted ? 1 : 0);
         env.commit_request(nx);
+        if constexpr (PHY)  // periodic defragmentation, after _next_service (phy_rmsa_env.py:355-417)
+          if (p.phy_defrag_period > 0 && env.cnt[CNT_PROC] % p.phy_defrag_period == 0) phy_defragmentation<W, PS>(env);
         int dn = env.cnt[CNT_EP_PROC] == (long long)p.episode_length;  // rmsa_env.py:339
         if (dn) {
           env.cnt[CNT_EPISODES]++;

@@ -394,6 +394,198 @@ __device__ void phy_heuristic(ENV& env, int hid, int* a) {
   }
 }
 
+// ---- periodic defragmentation: phy_rmsa_env.py:355-417 (step), _groom_defragmentation :703-733, _move_virtual
+// :735-764, _move :662-697 --------------------------------------------------------------------------------------
+// Runs inside the step kernel after _next_service, every phy_defrag_period processed services (all envs of a batch
+// reach that count in the same step, so the warp does not diverge on it).  running_services is the order list
+// with tombstones kept next to the service table; Python's index-based list iteration over a list whose current
+// element is removed and re-appended (the next element is skipped, the moved one is met again at the end) is
+// reproduced on it.
+
+// number of r_cut terms of the path whose neighbour link has the channel free
+template <int W, int BD, typename ENV>
+__device__ int count_terms_at(ENV& env, int pathg, int ch) {
+  const Params& p = env.p;
+  const int T = __ldg(p.phy_cut_count + pathg), wi = ch >> 5, b = ch & 31;
+  const unsigned char* links = p.phy_cut_links + (size_t)pathg * p.phy_max_terms;
+  int c = 0;
+  for (int t = 0; t < T; t++) c += (int)((env.tile.word(0, __ldg(links + t), wi) >> b) & 1u);
+  return c;
+}
+
+template <int W, int BD, typename CT, typename ENV>
+__device__ double defrag_gain_rss(ENV& env, int ch, CT path_links) {  // calculate_r_spatial(ch, links, True) :1085-1108
+  CT col = 0;
+  const int wi = ch >> 5, b = ch & 31;
+  for (int l = 0; l < env.p.E; l++) col |= (CT)((env.tile.word(0, l, wi) >> b) & 1u) << l;
+  return column_rss<CT>(col | path_links) - column_rss<CT>(col);
+}
+
+template <int W, int BD, typename CT, typename ENV>
+__device__ __noinline__ void phy_defragmentation_t(ENV& env) {
+  const Params& p = env.p;
+  typedef typename ENV::PhySvc Svc;
+  if (p.phy_run_cap - env.run_len < 2 * p.phy_number_moves + 8) env.run_squeeze();  // room for this cycle's re-appends
+  // ---- _groom_defragmentation :703-733 ----
+  int gm = 0;
+  bool full = false;
+  for (int pos = 0; pos < env.run_len && !full; pos++) {  // for service in running_services (live list)
+    const int slot = env.run_at(pos);
+    if (slot == 0xFFFF) continue;
+    Svc sv = env.svc_load(slot);
+    bool moved = false;
+    for (int ci = 0; ci < sv.nch && !full; ci++) {  // for channel in service.channels (live list)
+      const int c_ch = sv.ch[ci], c_share = sv.share[ci], c_cap = sv.cap[ci];
+      if (c_share != c_cap) {
+        const int at = env.cs_find(ENV::cs_key(sv.pair, sv.path, c_ch));  // corresponding_channel
+        if (at >= 0 && (int)(env.cs_at(at).y & 0xFFu) == c_share) {      // nobody else uses it: it can move
+          const uint32_t want = (uint32_t)sv.pair | ((uint32_t)sv.path << 16);
+          for (int j = 0; j < env.cs_len; j++) {  // for target_channel in channel_state[key]
+            const uint2 v = env.cs_at(j);
+            if (v.x == ENV::CS_DEAD || (v.x & 0xFFFFFu) != want || j == at) continue;
+            const int used = (int)(v.y & 0xFFu), fr = (int)((v.y >> 8) & 0xFFu), cap = (int)(v.y >> 16), tch = (int)(v.x >> 20);
+            if (fr >= c_share) {
+              env.cs_remove(j);  // two tuples removed, one appended :717-724
+              env.cs_remove(at);
+              env.cs_append(ENV::cs_key(sv.pair, sv.path, tch), used + c_share, fr - c_share, cap);
+              PathRec rec = load_path(p, sv.pair, sv.path);  // _move_virtual :735-764
+              env.tile.apply_bit(rec, 0, c_ch, true);
+              env.run_remove(sv.run_pos);
+              sv.run_pos = env.run_append(slot);
+              sv.remove_channel(ci);
+              sv.append_channel(tch, c_share, cap);
+              moved = true;
+              gm++;
+              break;
+            }
+          }
+        }
+      }
+      if (gm == p.phy_number_moves) full = true;  // :731
+    }
+    if (moved) {
+      env.svc_store(slot, sv);
+      if (!full) {  // the element that slid into this index is skipped by Python's list iterator
+        int q = pos + 1;
+        while (q < env.run_len && env.run_at(q) == 0xFFFFu) q++;
+        pos = q;
+      }
+    }
+  }
+  env.mv[1] = gm;  // counted_moves_groom :357
+  if (gm > p.phy_number_moves) return;
+  // ---- candidates :360-380: whole channels whose release gains fragmentation metric, running_services order ----
+  double2* cd = p.phy_cand + (size_t)env.e * p.phy_cand_cap;
+  uint32_t* cid = p.phy_cand_id + (size_t)env.e * p.phy_cand_cap;
+  int ncand = 0;
+  for (int pos = 0; pos < env.run_len; pos++) {
+    const int slot = env.run_at(pos);
+    if (slot == 0xFFFF) continue;
+    const Svc sv = env.svc_load(slot);
+    const int pathg = sv.pair * p.k + sv.path;
+    CT links = 0;
+    if (p.phy_metric != 0) {
+      PathRec rec = load_path(p, sv.pair, sv.path);
+      for_each_link(rec, [&](int l) { links |= (CT)1 << l; });
+    }
+    for (int ci = 0; ci < sv.nch; ci++) {
+      if (sv.share[ci] != sv.cap[ci]) continue;
+      const double diff = p.phy_metric == 0
+                              ? (double)(2 * count_terms_at<W, BD>(env, pathg, sv.ch[ci]) - __ldg(p.phy_cut_count + pathg))
+                              : defrag_gain_rss<W, BD, CT>(env, sv.ch[ci], links);
+      if (diff > 0) {
+        if (ncand < p.phy_cand_cap) {
+          cd[ncand] = make_double2(diff, env.now - sv.arrival);
+          cid[ncand] = (uint32_t)slot | ((uint32_t)sv.ch[ci] << 16);
+          ncand++;
+        } else {
+          env.cnt[CNT_FAULT] |= 128;
+        }
+      }
+    }
+  }
+  // ---- reallocation in sorted(key=(-gain, -age)) order (stable: the earliest of equal keys first) :381-415 ----
+  int num_moves = 0;
+  for (;;) {
+    int best = -1;
+    double bx = 0.0, by = 0.0;
+    for (int i = 0; i < ncand; i++) {
+      const double2 d = cd[i];
+      if (d.x > 0.0 && (best < 0 || d.x > bx || (d.x == bx && d.y > by))) {
+        best = i;
+        bx = d.x;
+        by = d.y;
+      }
+    }
+    if (best < 0) break;
+    cd[best].x = -1.0;  // taken
+    const int slot = (int)(cid[best] & 0xFFFFu), cch = (int)(cid[best] >> 16);
+    Svc sv = env.svc_load(slot);
+    int ci = -1;
+    for (int q = 0; q < sv.nch; q++)
+      if (ci < 0 && sv.ch[q] == cch && sv.share[q] == sv.cap[q]) ci = q;
+    if (ci >= 0) {
+      // idp: the candidate's path looked up among the CURRENT request's k paths (dataclass equality): its own index
+      // when both connect the same two nodes, else the loop variable's last value k - 1 (:386-391)
+      const int sa = sv.pair / p.n_nodes, sb = sv.pair % p.n_nodes;
+      const bool same = (sa == env.src && sb == env.dst) || (sa == env.dst && sb == env.src);
+      const int idp = same ? sv.path : p.k - 1;
+      const int table = __ldg(p.phy_table_id + sv.pair);
+      const int level = (int)__ldg(p.phy_mod + ((size_t)table * p.S + cch) * p.k + idp);
+      const int pathg = sv.pair * p.k + sv.path;
+      PathRec rec = load_path(p, sv.pair, sv.path);
+      Row<W> opt = level_mask<W>(p, table, idp, level);
+      and_into(opt, env.tile.path_avail(rec, 0));  // free on the path and of the same modulation level
+      if (row_any<W>(opt)) {
+        int nch_ = -1;
+        double metric = 0.0;
+        if (p.phy_metric == 0) {  // best of sorted(key=(-r_cut, channel)): fewest free neighbours, lowest channel
+          CutPlanes<W> cp;
+          count_terms<W, BD>(env, pathg, cp);
+          nch_ = lowest_set<W>(min_count_subset<W>(opt, cp));
+          metric = (double)(__ldg(p.phy_cut_count + pathg) - 2 * count_at<W>(cp, nch_));
+        } else {
+          CT links = 0;
+          for_each_link(rec, [&](int l) { links |= (CT)1 << l; });
+#pragma unroll 1
+          for (int i = 0; i < W; i++) {
+            uint32_t mword = opt.w[i];
+            while (mword) {
+              const int ch = 32 * i + (__ffs((int)mword) - 1);
+              mword &= mword - 1;
+              const double f = r_spatial<W, BD, CT>(env, ch, links);
+              if (nch_ < 0 || f > metric) {
+                nch_ = ch;
+                metric = f;
+              }
+            }
+          }
+        }
+        if (-1.0 * metric < bx) {  // :401-405 it pays: _move :662-697
+          env.tile.apply_bit(rec, 0, nch_, false);
+          env.tile.apply_bit(rec, 0, cch, true);
+          env.run_remove(sv.run_pos);
+          sv.run_pos = env.run_append(slot);
+          const int sh = sv.share[ci], cpv = sv.cap[ci];
+          sv.remove_channel(ci);
+          sv.append_channel(nch_, sh, cpv);
+          env.svc_store(slot, sv);
+          num_moves++;
+          env.mv[0]++;
+        }
+      }
+    }
+    if ((long long)num_moves + env.mv[1] > (long long)p.phy_number_moves) break;  // :414
+  }
+  if (num_moves != 0) env.mv[2]++;
+}
+
+template <int W, int BD, typename ENV>
+__device__ __forceinline__ void phy_defragmentation(ENV& env) {
+  if (env.p.E <= 32) phy_defragmentation_t<W, BD, uint32_t>(env);
+  else phy_defragmentation_t<W, BD, unsigned long long>(env);
+}
+
 // PhyRMSAEnv.step (phy_rmsa_env.py:272-309).  The action carries channel numbers; the (used, free) fields of
 // the reference's channel tuples are what its heuristics put there: every channel is used up to its capacity
 // (physical layer) or its free part (virtual layer) until the bit rate is covered, the last one takes the rest.
@@ -436,6 +628,18 @@ __device__ Decision phy_decide(ENV& env, const int* a) {
         need -= share[i];
       }
     if (!ok) return d;
+    if (env.sv_free_n == 0 || env.heap_len >= p.heap_cap) {  // no row for the service: refuse, state untouched
+      env.cnt[CNT_FAULT] |= 1;
+      return d;
+    }
+    typename ENV::PhySvc sv;
+    sv.arrival = env.now;
+    sv.pair = pr;
+    sv.path = idp;
+    sv.nch = nch;
+    sv.run_pos = 0;
+#pragma unroll
+    for (int i = 0; i < PHY_ADIM - 1; i++) sv.ch[i] = sv.share[i] = sv.cap[i] = 0;
 #pragma unroll
     for (int i = 0; i < PHY_ADIM - 1; i++)
       if (i < nch) env.cs_remove(at[i]);
@@ -444,8 +648,11 @@ __device__ Decision phy_decide(ENV& env, const int* a) {
       if (i < nch) {  // :643-645 the updated tuple goes to the end of the list
         const int used = (int)(yv[i] & 0xFFu), fr = (int)((yv[i] >> 8) & 0xFFu), cap = (int)(yv[i] >> 16);
         env.cs_append(ENV::cs_key(pr, idp, a[1 + i]), used + share[i], fr - share[i], cap);
-        env.heap_push(key, pack_service(pr, idp, share[i], a[1 + i], i, cap));
+        sv.ch[i] = a[1 + i];
+        sv.share[i] = share[i];
+        sv.cap[i] = cap;
       }
+    env.svc_provision(sv, key);
     env.cnt[CNT_ACC]++;  // _service_acceptance(True) :767-778
     env.cnt[CNT_EP_ACC]++;
     env.cnt[CNT_BR_PROV] += env.bit_rate;
@@ -469,6 +676,18 @@ __device__ Decision phy_decide(ENV& env, const int* a) {
     }
   }
   if (!ok) return d;
+  if (env.sv_free_n == 0 || env.heap_len >= p.heap_cap) {  // no row for the service: refuse, state untouched
+    env.cnt[CNT_FAULT] |= 1;
+    return d;
+  }
+  typename ENV::PhySvc sv;
+  sv.arrival = env.now;
+  sv.pair = pr;
+  sv.path = path;
+  sv.nch = nch;
+  sv.run_pos = 0;
+#pragma unroll
+  for (int i = 0; i < PHY_ADIM - 1; i++) sv.ch[i] = sv.share[i] = sv.cap[i] = 0;
   need = env.bit_rate / 100;
   for (int i = 0; i < nch; i++) {  // _provision_path :576-601
     const int ch = a[1 + i];
@@ -484,8 +703,15 @@ __device__ Decision phy_decide(ENV& env, const int* a) {
       need -= share;
       if (share != level) env.cs_append(ENV::cs_key(pr, path, ch), share, level - share, level);  // :599-601
     }
-    env.heap_push(key, pack_service(pr, path, share, ch, i, level));  // "n" = position in service.channels
+#pragma unroll
+    for (int q = 0; q < PHY_ADIM - 1; q++)
+      if (q == i) {
+        sv.ch[q] = ch;
+        sv.share[q] = share;
+        sv.cap[q] = level;
+      }
   }
+  env.svc_provision(sv, key);
   env.cnt[CNT_ACC]++;  // _service_acceptance(False) :767-778
   env.cnt[CNT_EP_ACC]++;
   env.fsum[0] += __ldg(p.path_length + (size_t)pr * p.k + path);

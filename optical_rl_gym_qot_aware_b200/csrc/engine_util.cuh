@@ -62,6 +62,27 @@ __global__ void services_kernel(const Params p, int* out, int max_rows, int* cou
   if (e >= p.num_envs) return;
   const ulonglong2* heap = p.heap + (size_t)e * p.heap_stride + HEAP_PAD;
   const int n = p.heap_len[e];
+  if (p.kind == ORLG_ENV_PHYRMSA) {  // one queue entry per service: its channels are in the service's record
+    int rows = 0;
+    for (int i = 0; i < n; i++) {
+      const uint4* r = p.phy_svc + ((size_t)e * p.phy_svc_cap + (size_t)heap[i].y) * 3;
+      const uint4 a = r[0], b = r[1], c = r[2];
+      const int nch = (int)(a.z >> 24);
+      const uint32_t cw[4] = {b.x, b.y, b.z, b.w}, sw[2] = {c.x, c.y}, pw[2] = {c.z, c.w};
+      for (int q = 0; q < nch; q++, rows++) {
+        if (rows >= max_rows) continue;
+        int* o = out + ((size_t)e * max_rows + rows) * 6;
+        o[0] = (int)(a.z & 0xFFFFu);
+        o[1] = (int)((a.z >> 16) & 0xFFu);
+        o[2] = (int)((sw[q >> 2] >> (8 * (q & 3))) & 0xFFu);
+        o[3] = (int)((cw[q >> 1] >> (16 * (q & 1))) & 0xFFFFu);
+        o[4] = q;
+        o[5] = (int)((pw[q >> 2] >> (8 * (q & 3))) & 0xFFu);
+      }
+    }
+    count[e] = rows;
+    return;
+  }
   for (int i = 0; i < n && i < max_rows; i++) {
     const unsigned long long s = heap[i].y;
     int* o = out + ((size_t)e * max_rows + i) * 6;
@@ -73,6 +94,12 @@ __global__ void services_kernel(const Params p, int* out, int max_rows, int* cou
     o[5] = svc_se(s);
   }
   count[e] = n;
+}
+
+__global__ void phy_moves_kernel(const Params p, long long* out) {
+  int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= p.num_envs) return;
+  for (int i = 0; i < 3; i++) out[(size_t)e * 3 + i] = p.phy_moves ? p.phy_moves[(size_t)i * p.NP + e] : 0;
 }
 
 // PhyRMSA-v0 channel_state without the tombstones, thread per env

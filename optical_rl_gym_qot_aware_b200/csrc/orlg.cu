@@ -269,19 +269,20 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   }
   if (c->request_source == ORLG_SRC_REPLAY || min_br < 1) min_br = 1;
   int min_slots = (int)std::ceil((double)min_br / ((double)max_se * c->channel_width)) + 1;
-  if (phy) min_slots = 1;  // one queue entry per occupied channel
+  if (phy) min_slots = 1;  // a service holds >= 1 channel on >= 1 link
   long long bound = (long long)cores * p.E * (p.S / min_slots);
   const long long lightpaths = bound;  // PhyRMSA: occupied (link, channel) cells
   if (phy && c->phy_grooming) bound *= PHY_LEVELS;  // a level-m channel can carry m groomed 100G services, one entry each
   // Default capacity: the offered load is Poisson (M/G/inf): mean A = holding / inter-arrival services in the
   // system if nothing were blocked, so A + 8 sqrt(A) + 32 entries are never exceeded in practice (8 sigma), and
-  // never more than the provable bound.  PhyRMSA queues one entry per channel: up to 8 per service.  Overflow
-  // raises the sticky fault bit (ORLG_C_FAULT), it never corrupts state silently.
+  // never more than the provable bound.  Overflow raises the sticky fault bit (ORLG_C_FAULT) and the request is
+  // refused; it never corrupts state silently.
   {
     const double A = c->mean_holding / c->mean_iat;
     double est = A + 8.0 * std::sqrt(A) + 32.0;
-    if (phy) est *= (PHY_ADIM - 1);
     if (c->request_source == ORLG_SRC_PHILOX && est < (double)bound) bound = (long long)std::ceil(est);
+    // PhyRMSA addresses a service's row with 16 bits
+    if (phy && bound > 0xFFFE) bound = est < 65534.0 ? (long long)std::ceil(est) : 0xFFFE;
     // engines with the QoT gate address a service's row with 14 bits: sized by load for every request source
     if (c->qot_gate && bound > 0x3FFF) bound = est < 16383.0 ? (long long)std::ceil(est) : 0x3FFF;
   }
@@ -373,6 +374,33 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
   const size_t NP = p.NP;
   if (phy && ((rc = dev_alloc(e, &p.phy_f, 2 * NP)) || (rc = dev_alloc(e, &p.phy_i, 4 * NP))))
     return fail_create(e, rc, e->err);
+  if (phy) {  // service table: one row per running service (= release-queue capacity)
+    if (p.heap_cap > 0xFFFE) return fail_create(e, ORLG_EINVAL, "PhyRMSA: release-queue capacity above 65534 services");
+    p.phy_svc_cap = p.heap_cap;
+    if ((rc = dev_alloc(e, &p.phy_svc, NP * (size_t)p.phy_svc_cap * 3)) ||
+        (rc = dev_alloc(e, &p.phy_free, NP * (size_t)p.phy_svc_cap)) || (rc = dev_alloc(e, &p.phy_free_n, NP)))
+      return fail_create(e, rc, e->err);
+    if (c->phy_defrag_period > 0) {
+      if (!c->phy_grooming) return fail_create(e, ORLG_EINVAL, "phy_defrag_period needs phy_grooming != 0 (channel_state)");
+      if (c->phy_number_moves < 0 || c->phy_metric < 0 || c->phy_metric > 1 || (c->phy_metric == 1 && p.E > 64))
+        return fail_create(e, ORLG_EINVAL, "defragmentation: number_moves >= 0, metric 0 (cut) or 1 (rss, <= 64 links)");
+      p.phy_defrag_period = c->phy_defrag_period;
+      p.phy_number_moves = c->phy_number_moves;
+      p.phy_metric = c->phy_metric;
+      long long rcap = 2ll * p.phy_svc_cap + 4ll * c->phy_number_moves + 64;
+      p.phy_run_cap = (int)(rcap > 65535 ? 65535 : rcap);
+      if (p.phy_run_cap < p.phy_svc_cap + 2 * c->phy_number_moves + 16)
+        return fail_create(e, ORLG_EINVAL, "defragmentation: too many services for the order list");
+      // candidates: every whole channel of every running service, at most the occupied (link, channel) cells
+      long long ccap = (long long)p.phy_svc_cap * (PHY_ADIM - 1);
+      if (ccap > lightpaths) ccap = lightpaths;
+      p.phy_cand_cap = (int)ccap;
+      if ((rc = dev_alloc(e, &p.phy_run, NP * (size_t)p.phy_run_cap)) || (rc = dev_alloc(e, &p.phy_run_len, NP)) ||
+          (rc = dev_alloc(e, &p.phy_moves, 3 * NP)) || (rc = dev_alloc(e, &p.phy_cand, NP * (size_t)p.phy_cand_cap)) ||
+          (rc = dev_alloc(e, &p.phy_cand_id, NP * (size_t)p.phy_cand_cap)))
+        return fail_create(e, rc, e->err);
+    }
+  }
   if (c->info_stats) {
     if (c->env_kind != ORLG_ENV_RMSA && c->env_kind != ORLG_ENV_DEEPRMSA)
       return fail_create(e, ORLG_EINVAL, "info_stats is built for RMSA-v0 / DeepRMSA-v0");
@@ -1052,5 +1080,18 @@ extern "C" int orlg_timed_steps(orlg_engine* e, int mode, int hid, int32_t* dev_
     cudaGetLastError();
     return ORLG_ECUDA;
   }
+  return ORLG_OK;
+}
+
+extern "C" int orlg_phy_get_moves(orlg_engine* e, int64_t* dev_out, void* stream) {
+  if (!e || !dev_out) return ORLG_EINVAL;
+  if (e->p.kind != ORLG_ENV_PHYRMSA) {
+    e->err = "orlg_phy_get_moves needs env_kind PhyRMSA";
+    return ORLG_ESTATE;
+  }
+  cudaSetDevice(e->device);
+  phy_moves_kernel<<<(e->p.num_envs + 127) / 128, 128, 0, (cudaStream_t)stream>>>(e->p, (long long*)dev_out);
+  CK(cudaGetLastError());
+  e->launches++;
   return ORLG_OK;
 }

@@ -36,7 +36,7 @@ EXPORTS = (
     "orlg_launch_count", "orlg_gsnr_configure", "orlg_gsnr", "orlg_gsnr_for_actions", "orlg_phy_get_stats", "orlg_path_first_fit", "orlg_set_next_action_hint", "orlg_step_host_async", "orlg_step_host_wait", "orlg_set_host_wait",
     "orlg_phy_get_channel_state", "orlg_info_dim", "orlg_set_info_output",
     "orlg_step_auto", "orlg_qot_get", "orlg_qot_check", "orlg_step_auto_noalloc",
-    "orlg_export_services", "orlg_timed_steps",
+    "orlg_export_services", "orlg_timed_steps", "orlg_phy_get_moves",
 )
 
 
@@ -63,6 +63,7 @@ class OrlgConfig(C.Structure):
         ("phy_cut_links", C.c_void_p), ("phy_cut_count", C.c_void_p),
         ("qot_gate", C.c_int32), ("qot_adaptive", C.c_int32), ("qot_n_se", C.c_int32), ("qot_pad", C.c_int32),
         ("qot_se", C.c_int32 * 8), ("qot_thr_db", C.c_double * 16), ("qot_gsnr", C.c_void_p),
+        ("phy_defrag_period", C.c_int32), ("phy_number_moves", C.c_int32), ("phy_metric", C.c_int32), ("phy_pad", C.c_int32),
     ]
 
 
@@ -123,6 +124,7 @@ def load_library():
         L.orlg_step_auto_noalloc.argtypes = [vp, i32, vp, vp, vp, vp, vp]
         L.orlg_export_services.argtypes = [vp, vp, i32, vp, vp]
         L.orlg_timed_steps.argtypes = [vp, i32, i32, vp, vp, vp, vp, i32, vp, C.c_size_t, i32, vp, vp, vp]
+        L.orlg_phy_get_moves.argtypes = [vp, vp, vp]
         L.orlg_qot_get.argtypes = [vp, vp, vp]
         L.orlg_qot_check.argtypes = [vp, vp, vp]
         _lib = L
@@ -175,6 +177,9 @@ class Engine:
         if ph is not None:
             c.phy_n_tables, c.phy_max_terms = ph.n_tables, ph.max_terms
             c.phy_grooming = int(getattr(spec, "phy_grooming", 0))
+            c.phy_defrag_period = int(getattr(spec, "phy_defrag_period", 0) or 0)
+            c.phy_number_moves = int(getattr(spec, "phy_number_moves", 0) or 0)
+            c.phy_metric = int(getattr(spec, "phy_metric", 0) or 0)
         c.abi_version = self.L.orlg_abi_version()
         c.env_kind, c.device, c.num_envs = spec.env_kind, device, self.num_envs
         c.global_env_offset = global_env_offset
@@ -398,6 +403,12 @@ class Engine:
         cnt = torch.zeros(self.num_envs, dtype=torch.int32, device=self.device)
         self._ck(self.L.orlg_phy_get_channel_state(self.h, self._p(out), max_entries, self._p(cnt), self._stream()))
         return out, cnt
+
+    def phy_moves(self):
+        """PhyRMSA-v0 defragmentation: int64 [num_envs, 3] counted_moves, counted_moves_groom, counted_defrag_cycles."""
+        out = self.torch.empty((self.num_envs, 3), dtype=self.torch.int64, device=self.device)
+        self._ck(self.L.orlg_phy_get_moves(self.h, self._p(out), self._stream()))
+        return out
 
     def phy_stats(self):
         """PhyRMSA-v0: f64 [num_envs, 8] (see orlg_phy_get_stats in include/orlg.h)."""

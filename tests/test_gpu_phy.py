@@ -175,3 +175,79 @@ def test_phy_invalid_actions_are_rejections():
     st = eng.export_state().cpu().numpy()
     assert st[:5].min() == 1 and st[5].sum() < st[0].sum()
     eng.close()
+
+
+@pytest.mark.parametrize("case", G.DEFRAG_CASES)
+def test_engine_replays_defragmentation_golden(case):
+    """Periodic defragmentation (phy_rmsa_env.py:355-417, 662-764) inside the step kernel: per step the heuristic's
+    action, accept / block, counters, the cumulative move counters and the checksum of available_channels of the
+    unmodified reference's run - every grooming move and every reallocation lands where the reference put it."""
+    import torch
+
+    from optical_rl_gym_qot_aware_b200.engine import Engine
+
+    g, spec = G.load_case(case)
+    hid = S.H_PHY_BM_FA_RSS if "_rss_" in case else S.H_PHY_BM_FA_CUT
+    n_env = 3
+    eng = Engine(spec, n_env)
+    eng.load_trace(np.repeat(g["requests"][:, None], n_env, axis=1))
+    eng.reset(True)
+    dev = eng.device
+    reward = torch.zeros(n_env, dtype=torch.int32, device=dev)
+    done = torch.zeros(n_env, dtype=torch.uint8, device=dev)
+    alloc = torch.zeros((n_env, 4), dtype=torch.int32, device=dev)
+    hact = torch.zeros((n_env, 9), dtype=torch.int32, device=dev)
+    weights = None
+    for t in range(len(g["actions"])):
+        eng.heuristic(hid, hact)
+        ha = hact.cpu().numpy()
+        assert np.array_equal(ha[0], g["actions"][t]) and np.array_equal(ha[2], g["actions"][t]), (case, t, ha[0], g["actions"][t])
+        eng.step(hact, reward, done, None, alloc)
+        assert alloc.cpu().numpy()[1, 0] == g["accepted"][t] and reward.cpu().numpy()[2] == g["reward"][t], (case, t)
+        mv = eng.phy_moves().cpu().numpy()
+        assert np.array_equal(mv[0], g["moves"][t]) and np.array_equal(mv[2], g["moves"][t]), (case, t, mv[0], g["moves"][t])
+        st = eng.export_state().cpu().numpy().astype(np.int64).reshape(n_env, -1)
+        if weights is None:
+            weights = np.arange(1, st.shape[1] + 1, dtype=np.int64)
+        assert int(st[1] @ weights) == int(g["avail_sum"][t]), (case, t)
+        d = bool(done.cpu().numpy()[0])
+        assert d == bool(g["done"][t]), (case, t)
+        if d:
+            eng.reset(False)
+        assert np.array_equal(eng.counters().cpu().numpy()[1, :8], g["counters"][t]), (case, t)
+    assert np.array_equal(eng.export_state().cpu().numpy()[0], g["final_avail"])
+    assert int(eng.counters()[:, 10].max()) == 0
+
+
+def test_defragmentation_matches_oracle_on_philox_streams():
+    """Philox-driven PhyRMSA envs with grooming and defragmentation, env by env against the CPU oracle."""
+    import torch
+
+    import oracle_binding as OB
+    from optical_rl_gym_qot_aware_b200.engine import Engine
+
+    g, spec0 = G.load_case("defrag_phy_us14_defrag_groom_cut_100ch")
+    kw = dict(load=1800, mean_service_holding_time=25, episode_length=150, number_spectrum_channels=30,
+              number_spectrum_channels_s_band=40, grooming=True, defrag_period=7, number_moves=6, metric="cut",
+              modulation_level=spec0.phy.mod_level, gsnr=spec0.phy.gsnr,
+              connections_detail=np.load(G.GOLDEN + "/phytab_Results_K3SP_FRP_SLC_CBG_USB14.npz")["phy_conn"])
+    spec = S.make_spec("PhyRMSA-v0", spec0.tables, seed=9, auto_reset=True, **kw)
+    n_env, n_steps = 48, 400
+    eng = Engine(spec, n_env)
+    eng.reset(True)
+    eng.rollout(S.H_PHY_BM_FA_CUT, n_steps)
+    cnt = eng.counters().cpu().numpy()
+    mv = eng.phy_moves().cpu().numpy()
+    st = eng.export_state().cpu().numpy()
+    assert int(cnt[:, 10].max()) == 0
+    total_moves = 0
+    for i in range(n_env):
+        o = OB.OracleEnv(spec, i)
+        o.reset(True)
+        for _ in range(n_steps):
+            o.step(o.heuristic(S.H_PHY_BM_FA_CUT))
+        assert np.array_equal(o.counters()[:9], cnt[i, :9]), i
+        assert np.array_equal(o.phy_moves(), mv[i]), (i, o.phy_moves(), mv[i])
+        assert np.array_equal(o.state(), st[i]), i
+        total_moves += int(mv[i, 0])
+    assert total_moves > 0
