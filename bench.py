@@ -80,7 +80,7 @@ WORKLOADS = {
     "c4_phyrmsa_us14_320": dict(
         env="PhyRMSA-v0", topo="us14", hid=S.H_PHY_BM_FA_CUT, obs=S.OBS_PHY_CUTS, step="hint", preroll=6000, bytes=1426,
         cpu_envs=256,
-        kw=dict(load=1400, mean_service_holding_time=25, episode_length=200, number_spectrum_channels=160, s_band=False),
+        kw=dict(load=1400, mean_service_holding_time=25, episode_length=200, number_spectrum_channels=106, number_spectrum_channels_s_band=108),
         what="BASELINE configs[3]: phy-frag RMSA on US14, 320 channels, BM-FA-Cut, cuts reward"),
     "c5_rmsa_spn_100": dict(
         env="RMSA-v0", topo="spn", hid=S.H_SAP_FF, obs=S.OBS_NONE, step="hint", preroll=600, bytes=517, cpu_envs=8192,

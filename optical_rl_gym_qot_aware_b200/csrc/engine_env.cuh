@@ -31,6 +31,11 @@ __device__ __forceinline__ int svc_slot(unsigned long long s) { return (int)((s 
 // created with info_stats carry that code)
 template <int W, int BD, bool PHY = false, bool INFO = false>
 struct Env {
+  // the INFO instantiations keep RMSAEnv's info-dict state; for PhyRMSA the same flag selects the kernels that carry
+  // the periodic defragmentation (engine_phy.cuh), so engines without it run kernels whose env context never
+  // leaves the registers
+  static constexpr bool INFO_STATS = INFO && !PHY;
+  static constexpr bool PHY_DEFRAG = INFO && PHY;
   const Params& p;
   Tile<W, BD> tile;
   int e;  // local env index
@@ -68,7 +73,7 @@ struct Env {
     for (int i = 0; i < CNT_N; i++) cnt[i] = p.counters[(size_t)i * p.NP + e];
     slot_hops = 0;
     rel_n = p.qot ? p.qot_rel_n[e] : 0;  // releases not yet seen by qot_kernel survive an episode reset
-    if constexpr (INFO) slot_hops = p.slot_hops[e];
+    if constexpr (INFO_STATS) slot_hops = p.slot_hops[e];
     if constexpr (PHY) {
       fsum[0] = p.phy_f[e];
       fsum[1] = p.phy_f[(size_t)p.NP + e];
@@ -208,7 +213,7 @@ struct Env {
     p.heap_len[e] = heap_len;
 #pragma unroll
     for (int i = 0; i < CNT_N; i++) p.counters[(size_t)i * p.NP + e] = cnt[i];
-    if constexpr (INFO) p.slot_hops[e] = slot_hops;
+    if constexpr (INFO_STATS) p.slot_hops[e] = slot_hops;
     if (p.qot) p.qot_rel_n[e] = rel_n;
     if constexpr (PHY) {
       p.phy_f[e] = fsum[0];
@@ -370,9 +375,18 @@ struct Env {
   __device__ void phy_release(int slot) {
     const PhySvc v = svc_load(slot);
     PathRec rec = load_path(p, v.pair, v.path);
+    // the record's fields are only ever indexed statically (the arrays stay in registers); the loop body is
+    // selected per iteration instead
 #pragma unroll 1
     for (int i = 0; i < v.nch; i++) {
-      const int share = v.share[i], cap = v.cap[i], ch = v.ch[i];
+      int share = v.share[0], cap = v.cap[0], ch = v.ch[0];
+#pragma unroll
+      for (int q = 1; q < 8; q++)
+        if (q == i) {
+          share = v.share[q];
+          cap = v.cap[q];
+          ch = v.ch[q];
+        }
       bool free_it = !p.phy_grooming || share == cap;  // :784 channel[1] == channel[3]
       if (!free_it) {
         const uint32_t key = cs_key(v.pair, v.path, ch);
@@ -521,7 +535,7 @@ struct Env {
     }
     cnt[CNT_BR_REQ] += bit_rate;  // rmsa_env.py:677-678, rmcsa_env.py:730-731
     cnt[CNT_EP_BR_REQ] += bit_rate;
-    if constexpr (INFO) info_count(0, bit_rate);  // bit_rate_requested_histogram :680
+    if constexpr (INFO_STATS) info_count(0, bit_rate);  // bit_rate_requested_histogram :680
     while (next_rel <= now) {  // rmsa_env.py:689-695
       unsigned long long s = heap_pop();
       if constexpr (PHY) {
@@ -533,7 +547,7 @@ struct Env {
           if (rel_n < QOT_REL_CAP_) p.qot_rel[(size_t)e * QOT_REL_CAP_ + rel_n++] = s;
           else cnt[CNT_FAULT] |= 16;
         }
-        if constexpr (INFO) {  // _release_path :531-535 (current_time is already the new arrival)
+        if constexpr (INFO_STATS) {  // _release_path :531-535 (current_time is already the new arrival)
           for_each_link(rec, [&](int l) { info_update_link(l); });
           slot_hops -= (long long)svc_slots(s) * rec.hops();
         }
@@ -571,7 +585,7 @@ struct Env {
   // _provision_path + _add_release (state and counters only)
   __device__ __forceinline__ void provision(const PathRec& rec, int path, int core, int start, int n, int se, int row = 0) {
     tile.clear_range(rec, core, start, n);
-    if constexpr (INFO) {  // _provision_path :494, :510
+    if constexpr (INFO_STATS) {  // _provision_path :494, :510
       for_each_link(rec, [&](int l) { info_update_link(l); });
       slot_hops += (long long)n * rec.hops();
       info_count(1, bit_rate);

@@ -103,7 +103,7 @@ __global__ void ORLG_LAUNCH_BOUNDS(BD) env_kernel(const Params p, const StepIO i
     env.heap_len = 0;
     env.cs_len = env.cs_dead = 0;  // channel_state phy_rmsa_env.py:455-461
     env.slot_hops = 0;
-    if (INFO && active) {  // optical_network_env.py:257-260, rmsa_env.py:444-452
+    if (INFO && !PHY && active) {  // optical_network_env.py:257-260, rmsa_env.py:444-452
       for (int l = 0; l < p.E; l++) env.lnk(0, l) = env.lnk(1, l) = env.lnk(2, l) = 0.0;
       for (int i = 0; i < 2 * p.n_bit_rates; i++) p.br_hist[(size_t)i * p.NP + env.e] = 0;
     }
@@ -189,8 +189,8 @@ __global__ void ORLG_LAUNCH_BOUNDS(BD) env_kernel(const Params p, const StepIO i
         }
         Decision d;
         double prev_compactness = 0.0;
-        const bool want_info = INFO && mode == MODE_STEP && io.info != nullptr;
-        if constexpr (INFO)
+        const bool want_info = INFO && !PHY && mode == MODE_STEP && io.info != nullptr;
+        if constexpr (INFO && !PHY)
           if (want_info) prev_compactness = env.info_network_compactness();  // rmsa_env.py:227-229
         if constexpr (PHY) {
           d = phy_decide<W, PS>(env, a);
@@ -215,7 +215,7 @@ __global__ void ORLG_LAUNCH_BOUNDS(BD) env_kernel(const Params p, const StepIO i
           else if (p.kind == ORLG_ENV_DEEPRMSA) d = deeprmsa_decide<W, PS>(env, a[0]);
           else d = rmcsa_decide<W, PS>(env, a[0], a[1], a[2], a[3]);
         }
-        if constexpr (INFO)
+        if constexpr (INFO && !PHY)
           if (want_info) env.info_write(io.info + (size_t)e * (9 + p.n_bit_rates), prev_compactness);
         if (p.kind == ORLG_ENV_RMCSA) {  // rmcsa_env.py:292-295
           env.cnt[CNT_PROC]++;
@@ -226,7 +226,7 @@ __global__ void ORLG_LAUNCH_BOUNDS(BD) env_kernel(const Params p, const StepIO i
         // reward: optical_network_env.py:213-214 ; deeprmsa_env.py:123-124
         int r = (p.kind == ORLG_ENV_DEEPRMSA) ? (d.accepted ? 1 : -1) : (d.accepted ? 1 : 0);
         env.commit_request(nx);
-        if constexpr (PHY)  // periodic defragmentation, after _next_service (phy_rmsa_env.py:355-417)
+        if constexpr (PHY && INFO)  // periodic defragmentation, after _next_service (phy_rmsa_env.py:355-417)
           if (p.phy_defrag_period > 0 && env.cnt[CNT_PROC] % p.phy_defrag_period == 0) phy_defragmentation<W, PS>(env);
         int dn = env.cnt[CNT_EP_PROC] == (long long)p.episode_length;  // rmsa_env.py:339
         if (dn) {

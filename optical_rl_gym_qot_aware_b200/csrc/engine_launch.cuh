@@ -76,8 +76,20 @@ cudaError_t launch_w(const LaunchGeom& g, const Params& p, const StepIO& io, cud
 template cudaError_t launch_w<ORLG_INSTANTIATE_W>(const LaunchGeom&, const Params&, const StepIO&, cudaStream_t);
 #endif
 #ifdef ORLG_INSTANTIATE_PHY
+// PhyRMSA engines with periodic defragmentation: the modes that step carry it (INFO flag of the PHY kernels)
+template <int W, int BD, bool DIRECT>
+static cudaError_t launch_phy_defrag(const LaunchGeom& g, const Params& p, const StepIO& io, cudaStream_t st) {
+  switch (io.mode) {
+    case MODE_STEP: return launch_t<W, BD, MODE_STEP, true, DIRECT, true>(g, p, io, st);
+    case MODE_ROLLOUT: return launch_t<W, BD, MODE_ROLLOUT, true, DIRECT, true>(g, p, io, st);
+    case MODE_HEURISTIC: return launch_t<W, BD, MODE_HEURISTIC, true, DIRECT>(g, p, io, st);
+    default: return launch_t<W, BD, -1, true, DIRECT>(g, p, io, st);
+  }
+}
 template <int W>
 cudaError_t launch_phy(const LaunchGeom& g, const Params& p, const StepIO& io, cudaStream_t st) {
+  if (p.phy_defrag_period > 0)
+    return g.direct ? launch_phy_defrag<W, DIRECT_CTA, true>(g, p, io, st) : launch_phy_defrag<W, 32, false>(g, p, io, st);
   if (g.direct) return launch_m<W, DIRECT_CTA, true, true>(g, p, io, st);
   return launch_m<W, 32, true>(g, p, io, st);
 }

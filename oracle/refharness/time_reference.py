@@ -37,7 +37,7 @@ CONFIGS = {
     "c3_rmcsa_jpn12_320_gn": ("RMCSA-v0", JPN, dict(load=250, mean_service_holding_time=25, num_spectrum_resources=320,
                                                     num_spatial_resources=7, worst_xt=-84.7, episode_length=1000), "gn"),
     "c4_phyrmsa_us14_320": ("PhyRMSA-v0", US, dict(load=1400, mean_service_holding_time=25, episode_length=200,
-                                                   number_spectrum_channels=160, s_band=False, num_spectrum_resources=64,
+                                                   number_spectrum_channels=106, number_spectrum_channels_s_band=108, num_spectrum_resources=64,
                                                    bit_rate_selection="discrete", grooming=False), "bmfa"),
     "c5_rmsa_spn_100": ("RMSA-v0", SPN, dict(load=100, mean_service_holding_time=25, num_spectrum_resources=100,
                                              episode_length=1000), "sapff"),
@@ -49,6 +49,14 @@ CONFIGS = {
 
 
 def worker(name, seed, seconds, warm_steps, out):
+    try:
+        _worker(name, seed, seconds, warm_steps, out)
+    except BaseException as ex:  # a dead worker must not hang the parent
+        out.put((0, 1.0))
+        raise ex
+
+
+def _worker(name, seed, seconds, warm_steps, out):
     import numpy as np
 
     env_id, topo_file, kw, pol = CONFIGS[name]
