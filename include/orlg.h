@@ -295,9 +295,11 @@ int orlg_heuristic(orlg_engine* e, int heuristic_id, int32_t* dev_actions, void*
  * dev_actions buffer of the same orlg_step call (an env reads its action before it writes its hint). */
 int orlg_set_next_action_hint(orlg_engine* e, int heuristic_id, int32_t* dev_next_actions);
 
-/* PathOnlyFirstFitAction.action (rmsa_env.py:982-1005), RMSA-v0 only: dev_paths int32[num_envs]
- * (path index or k_paths = reject) -> dev_actions int32[num_envs][2] = (path, first-fit slot) or
- * (k_paths, num_slots). */
+/* PathOnlyFirstFitAction.action (rmsa_env.py:982-1005): dev_paths int32[num_envs] (path index or k_paths =
+ * reject) -> RMSA-v0: dev_actions int32[num_envs][2] = (path, first-fit slot) or (k_paths, num_slots).
+ * RMCSA-v0 (rmcsa_env.py:950-982; as shipped that wrapper calls get_number_slots / is_path_free with RMSA's
+ * signatures and raises, so its intent is built): int32[num_envs][4] = (path, best modulation by reach, first core
+ * with room, first-fit slot) or the reject action. */
 int orlg_path_first_fit(orlg_engine* e, const int32_t* dev_paths, int32_t* dev_actions, void* stream);
 
 /* nsteps x (heuristic -> step) in one launch, state staged on chip between steps.
@@ -307,6 +309,13 @@ int orlg_rollout(orlg_engine* e, int heuristic_id, int nsteps, int64_t* dev_rewa
 
 int orlg_get_counters(orlg_engine* e, int64_t* dev_out /* [num_envs][ORLG_NUM_COUNTERS] */,
                       void* stream);
+
+/* With a non-NULL dev_snapshot (int64 [num_envs][8], kept by the engine until replaced or cleared with NULL) every
+ * following orlg_step also writes the counters ORLG_C_SERVICES_PROCESSED .. ORLG_C_EP_BIT_RATE_PROVISIONED as they are
+ * where the reference builds its info dict: after the decision, before _next_service counts the next request and
+ * before an episode reset (rmsa_env.py:293-307 precede :334-335) - the values behind service_blocking_rate,
+ * episode_service_blocking_rate, bit_rate_blocking_rate and episode_bit_rate_blocking_rate. */
+int orlg_set_counter_snapshot(orlg_engine* e, int64_t* dev_snapshot);
 
 /* PhyRMSA-v0 per-env statistics, f64 [num_envs][8]: total_path_length_episode, total_gsnr_episode,
  * total_path_index_episode, total_modulation_level_episode, channels_accepted_episode,

@@ -135,6 +135,7 @@ struct StepIO {
   int* alloc;
   long long* reward_sum;
   double* info;        // optional f64 [num_envs][9 + n_bit_rates]: the step's info dict (needs info_stats)
+  long long* snap;     // optional int64 [num_envs][8]: the first eight counters at the info dict's point in the step
   int* hint_actions;   // optional: the heuristic's action for the NEW pending request (fused next-action hint)
   int hint_heuristic;
 };

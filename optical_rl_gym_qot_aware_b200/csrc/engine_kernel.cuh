@@ -223,6 +223,13 @@ __global__ void ORLG_LAUNCH_BOUNDS(BD) env_kernel(const Params p, const StepIO i
           env.cnt[CNT_BR_REQ] += env.bit_rate;
           env.cnt[CNT_EP_BR_REQ] += env.bit_rate;
         }
+        if (mode == MODE_STEP && io.snap != nullptr) {
+          // the counters as the reference's info dict reads them: after the decision, before _next_service counts
+          // the next request and before an episode reset (rmsa_env.py:293-307 precede :334-335)
+          long long* o = io.snap + (size_t)e * 8;
+#pragma unroll
+          for (int i = 0; i < 8; i++) o[i] = env.cnt[i];
+        }
         // reward: optical_network_env.py:213-214 ; deeprmsa_env.py:123-124
         int r = (p.kind == ORLG_ENV_DEEPRMSA) ? (d.accepted ? 1 : -1) : (d.accepted ? 1 : 0);
         env.commit_request(nx);

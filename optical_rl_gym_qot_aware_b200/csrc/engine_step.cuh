@@ -158,7 +158,11 @@ __device__ __forceinline__ void heuristic_action(ENV& env, int hid, int* a, int 
     a[1] = p.n_mods;
     a[2] = p.cores;
     a[3] = p.S;
-    for (int path = 0; path < p.k; path++) {
+    // ORLG_H_PATH_FF: the walk restricted to the given path (the device form of rmcsa_env.py:950-982, which as
+    // shipped calls get_number_slots / is_path_free with RMSA's signatures and cannot run)
+    const bool one = hid == ORLG_H_PATH_FF;
+    if (one && (in_path < 0 || in_path >= p.k)) return;
+    for (int path = one ? in_path : 0; path < (one ? in_path + 1 : p.k); path++) {
       PathRec rec = load_path(p, pr, path);
       int mod = rec.best_mod();
       if (rec.hops() <= 0 || mod >= p.n_mods) continue;

@@ -46,6 +46,7 @@ struct orlg_engine {
   int hint_heuristic = 0;
   int* auto_actions = nullptr;          // orlg_step_auto without a caller buffer
   long long* auto_reward_sum = nullptr; // set by orlg_rollout around its orlg_step_auto loop
+  long long* snap = nullptr;            // orlg_set_counter_snapshot
   int qot_cap = 64;                     // services staged per window by qot_kernel (64 / 128 / 256)
   cudaEvent_t mid_ev = nullptr;         // orlg_timed_steps: recorded between the launches of a multi-launch step
   bool mid_external = false;
@@ -361,6 +362,18 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
         }
     for (size_t i = 0; i < npairs; i++)
       if (c->phy_table_id[i] >= c->phy_n_tables) return fail_create(e, ORLG_EINVAL, "phy_table_id out of range");
+    {  // an action carries at most 8 channels; the reference's greedy take has no cap (phy_rmsa_env.py:1425-1432), so a
+       // bit-rate table that could need more is refused here instead of diverging silently
+      int min_level = PHY_LEVELS, max_br = c->bit_rate_hi;
+      for (size_t i = 0; i < T * S * K; i++) min_level = c->phy_mod_level[i] < min_level ? c->phy_mod_level[i] : min_level;
+      if (c->n_bit_rates > 0 && c->bit_rates) {
+        max_br = 0;
+        for (int i = 0; i < c->n_bit_rates; i++) max_br = c->bit_rates[i] > max_br ? c->bit_rates[i] : max_br;
+      }
+      if (max_br > (PHY_ADIM - 1) * 100 * min_level)
+        return fail_create(e, ORLG_EINVAL, "PhyRMSA: the largest bit rate could need more than 8 channels of the lowest "
+                                           "modulation level in the table (action format: 8 channels)");
+    }
     if ((rc = dev_upload(e, &p.phy_table_id, c->phy_table_id, npairs)) ||
         (rc = dev_upload(e, &p.phy_mod, c->phy_mod_level, T * S * K)) ||
         (rc = dev_upload(e, &p.phy_gsnr, c->phy_gsnr, T * S * K)) ||
@@ -581,6 +594,7 @@ static StepIO make_io(orlg_engine* e, int mode) {
   io.obs_es = e->obs_es ? e->obs_es : e->obs_dim;
   io.obs_fs = e->obs_es ? e->obs_fs : 1;
   io.nsteps = 1;
+  io.snap = e->snap;
   return io;
 }
 
@@ -672,8 +686,8 @@ extern "C" int orlg_heuristic(orlg_engine* e, int hid, int32_t* dev_actions, voi
 
 extern "C" int orlg_path_first_fit(orlg_engine* e, const int32_t* dev_paths, int32_t* dev_actions, void* stream) {
   if (!e || !dev_paths || !dev_actions) return ORLG_EINVAL;
-  if (e->p.kind != ORLG_ENV_RMSA) {
-    e->err = "orlg_path_first_fit is defined for RMSA-v0 (rmsa_env.py:974-1008)";
+  if (e->p.kind != ORLG_ENV_RMSA && e->p.kind != ORLG_ENV_RMCSA) {
+    e->err = "orlg_path_first_fit is defined for RMSA-v0 (rmsa_env.py:974-1008) and RMCSA-v0 (rmcsa_env.py:950-982)";
     return ORLG_ESTATE;
   }
   cudaSetDevice(e->device);
@@ -1093,5 +1107,11 @@ extern "C" int orlg_phy_get_moves(orlg_engine* e, int64_t* dev_out, void* stream
   phy_moves_kernel<<<(e->p.num_envs + 127) / 128, 128, 0, (cudaStream_t)stream>>>(e->p, (long long*)dev_out);
   CK(cudaGetLastError());
   e->launches++;
+  return ORLG_OK;
+}
+
+extern "C" int orlg_set_counter_snapshot(orlg_engine* e, int64_t* dev_snapshot) {
+  if (!e) return ORLG_EINVAL;
+  e->snap = (long long*)dev_snapshot;
   return ORLG_OK;
 }

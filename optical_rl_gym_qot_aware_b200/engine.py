@@ -37,6 +37,7 @@ EXPORTS = (
     "orlg_phy_get_channel_state", "orlg_info_dim", "orlg_set_info_output",
     "orlg_step_auto", "orlg_qot_get", "orlg_qot_check", "orlg_step_auto_noalloc",
     "orlg_export_services", "orlg_timed_steps", "orlg_phy_get_moves",
+    "orlg_set_counter_snapshot",
 )
 
 
@@ -125,6 +126,7 @@ def load_library():
         L.orlg_export_services.argtypes = [vp, vp, i32, vp, vp]
         L.orlg_timed_steps.argtypes = [vp, i32, i32, vp, vp, vp, vp, i32, vp, C.c_size_t, i32, vp, vp, vp]
         L.orlg_phy_get_moves.argtypes = [vp, vp, vp]
+        L.orlg_set_counter_snapshot.argtypes = [vp, vp]
         L.orlg_qot_get.argtypes = [vp, vp, vp]
         L.orlg_qot_check.argtypes = [vp, vp, vp]
         _lib = L
@@ -403,6 +405,17 @@ class Engine:
         cnt = torch.zeros(self.num_envs, dtype=torch.int32, device=self.device)
         self._ck(self.L.orlg_phy_get_channel_state(self.h, self._p(out), max_entries, self._p(cnt), self._stream()))
         return out, cnt
+
+    def set_counter_snapshot(self, enable: bool = True):
+        """Every following step also writes the first eight counters at the info dict's point in the step (before
+        the next request is counted and before an episode reset); returns the int64 [num_envs, 8] tensor."""
+        if not enable:
+            self._snap = None
+            self._ck(self.L.orlg_set_counter_snapshot(self.h, None))
+            return None
+        self._snap = self.torch.zeros((self.num_envs, 8), dtype=self.torch.int64, device=self.device)
+        self._ck(self.L.orlg_set_counter_snapshot(self.h, self._p(self._snap)))
+        return self._snap
 
     def phy_moves(self):
         """PhyRMSA-v0 defragmentation: int64 [num_envs, 3] counted_moves, counted_moves_groom, counted_defrag_cycles."""

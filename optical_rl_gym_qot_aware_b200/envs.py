@@ -116,6 +116,10 @@ class BatchedEnv:
         self.device = self.engine.device
         # info_stats=True: the step's info dict of rmsa_env.py:293-332 comes from the step kernel itself
         self._info = self.engine.set_info_output() if self.spec.info_stats else None
+        # the counters behind the four blocking rates, as they are where the reference builds its info dict (after the
+        # decision, before the next request is counted and before an episode reset)
+        self._snap = self.engine.set_counter_snapshot()
+        self._stepped = False
         t = tables
         # attributes the reference's drivers and heuristics read
         self.k_paths = t.k_paths
@@ -186,6 +190,7 @@ class BatchedEnv:
             a = torch.as_tensor(np.asarray(a), device=self.device)
         a = a.to(device=self.device, dtype=torch.int32).reshape(self.num_envs, self.engine.action_dim).contiguous()
         self.engine.step(a, self._reward, self._done, self._obs, self._alloc)
+        self._stepped = True
         info = {"accepted": self._alloc[:, 0], "path": self._alloc[:, 1] & 0xFFFF, "core": self._alloc[:, 1] >> 16,
                 "initial_slot": self._alloc[:, 2], "number_slots": self._alloc[:, 3]}
         return self._obs, self._reward, self._done, info
@@ -222,9 +227,12 @@ class BatchedEnv:
             "total_path_length": st[:, 0] / (st[:, 5] + 1), "avrage_gsnr": st[:, 1] / (st[:, 4] + 1),
             "average_mod_level": st[:, 3] / (st[:, 4] + 1), "average_path_index": st[:, 2] / (st[:, 5] + 1),
             "path_index": st[:, 2], "physical_paths": st[:, 5],
-            # defrag_period=None (the only mode built): the reference's move counters stay 0
-            "num_moves": st[:, 0] * 0.0, "num_moves_groom": st[:, 0] * 0.0, "num_defrag_cycle": st[:, 0] * 0.0,
+            **self._phy_moves(),
         }
+
+    def _phy_moves(self):
+        mv = self.engine.phy_moves().to(self.torch.float64)  # phy_rmsa_env.py:340-342
+        return {"num_moves": mv[:, 0] / 2 + mv[:, 1], "num_moves_groom": mv[:, 1], "num_defrag_cycle": mv[:, 2]}
 
     def available_channels(self):
         """PhyRMSA-v0: topology.graph["available_channels"] of every env, uint8 [num_envs, E, C]."""
@@ -246,7 +254,9 @@ class BatchedEnv:
             for i, b in enumerate(np.asarray(self.spec.bit_rates).tolist()):
                 out[f"bit_rate_blocking_{b}"] = self._info[:, 9 + i]
             return out
-        c = self.counters().to(self.torch.float64)
+        # after a step: the snapshot the step kernel took at the reference's point (rmsa_env.py:293-307); before the
+        # first step there is no info dict in the reference either - the current counters stand in
+        c = (self._snap if self._stepped else self.counters()[:, :8]).to(self.torch.float64)
         safe = lambda x: self.torch.clamp(x, min=1.0)  # noqa: E731
         return {
             "service_blocking_rate": (c[:, 0] - c[:, 1]) / safe(c[:, 0]),
@@ -303,6 +313,7 @@ class OrlgVecEnv:
         a = np.asarray(actions, dtype=np.int32).reshape(self.num_envs, -1)
         self._h_act.numpy()[:] = a
         self._pending = True
+        self.env._stepped = True  # info() now reads the step kernel's counter snapshot
         self._stream.wait_stream(self.env.torch.cuda.current_stream(self.env.device))
         self.env.engine.step_host_async(self._h_act, self._h_rew, self._h_done, self._h_obs, self._h_alloc,
                                         stream=self._stream)
@@ -314,14 +325,21 @@ class OrlgVecEnv:
         rew = self._h_rew.numpy().astype(np.float32)
         done = self._h_done.numpy().astype(bool)
         al = self._h_alloc.numpy()
-        infos = [{"accepted": bool(al[i, 0])} for i in range(self.num_envs)] if self.num_envs <= 64 else \
-            {"accepted": al[:, 0].astype(bool), "path": al[:, 1] & 0xFFFF, "core": al[:, 1] >> 16,
-             "initial_slot": al[:, 2], "number_slots": al[:, 3]}
+        # SB3 indexes infos[i]: always one dict per env; the same columns as arrays are kept in `last_info_arrays`
+        cols = {"accepted": al[:, 0].astype(bool), "path": al[:, 1] & 0xFFFF, "core": al[:, 1] >> 16,
+                "initial_slot": al[:, 2], "number_slots": al[:, 3]}
+        self.last_info_arrays = cols
+        lists = {k: v.tolist() for k, v in cols.items()}
+        infos = [{k: lists[k][i] for k in lists} for i in range(self.num_envs)]
         return self._obs_view(), rew, done, infos
 
     def step(self, actions):
         self.step_async(actions)
         return self.step_wait()
+
+    def info(self):
+        """The info dict of the last step, per env (arrays): what Monitor / VecMonitor log at an episode's end."""
+        return self.env.info()
 
     def seed(self, seed=None):
         return [None] * self.num_envs
@@ -353,7 +371,87 @@ class GymEnv:
                      "action_space", "observation_space", "spec"):
             setattr(self, name, getattr(self._b, name))
         self.tables = self._b.spec.tables
-        self.topology = SimpleNamespace(graph=_GraphView(self))
+        self.topology = _TopologyView(self)
+        self.k_shortest_paths = _KspView(self.tables)
+        self.channel_width = self._b.spec.channel_width
+        self.grooming = self._b.spec.phy_grooming == 1
+        self._state_cache = None
+        if self._phy:  # phy_rmsa_env.py:51-53,93-95
+            ph = self._b.spec.phy
+            self.modulation_level, self.gsnr = ph.mod_level.astype(np.int64), ph.gsnr
+            self.connections_detail = np.asarray(kwargs.get("connections_detail"))
+
+    # -- read-only views of the network state for code written against the reference env (its module-level
+    # heuristics rmsa_env.py:854-937, deeprmsa_env.py:135-155 read these); every call works on a host copy of the
+    # occupancy fetched once per step --
+    def _state(self):
+        if self._state_cache is None:
+            self._state_cache = self._b.available_slots()[0].cpu().numpy().astype(np.int64)  # [cores, E, S]
+        return self._state_cache
+
+    def _links(self, path):
+        return [self.topology[path.node_list[i]][path.node_list[i + 1]]["index"] for i in range(len(path.node_list) - 1)]
+
+    def get_number_slots(self, path, modulation_format=None):
+        """rmsa_env.py:708-719 / rmcsa_env.py:753-765"""
+        import math
+
+        se = (modulation_format or path.best_modulation).spectral_efficiency
+        return math.ceil(self.current_service.bit_rate / (se * self.channel_width)) + 1
+
+    def is_path_free(self, path, *args):
+        """rmsa_env.py:721-734 (path, initial_slot, number_slots) / rmcsa_env.py:767-794 (path, core, initial_slot,
+        number_slots)"""
+        core, slot, n = (args if len(args) == 3 else (0,) + tuple(args))
+        if slot + n > self.num_spectrum_resources:
+            return False
+        st = self._state()
+        return all(not np.any(st[core, l, slot:slot + n] == 0) for l in self._links(path))
+
+    def get_available_slots(self, path):
+        """rmsa_env.py:745-756: AND of the path's link rows"""
+        st = self._state()
+        out = np.ones(self.num_spectrum_resources, np.int64)
+        for l in self._links(path):
+            out = out * st[0, l]
+        return out
+
+    @staticmethod
+    def rle(inarray):
+        """rmsa_env.py:758-772: (initial indices, values, lengths)"""
+        ia = np.asarray(inarray)
+        n = len(ia)
+        if n == 0:
+            return None, None, None
+        y = np.array(ia[1:] != ia[:-1])
+        i = np.append(np.where(y), n - 1)
+        z = np.diff(np.append(-1, i))
+        return np.cumsum(np.append(0, z))[:-1], ia[i], z
+
+    def get_available_blocks(self, path_index):
+        """rmsa_env.py:774-804: the first j blocks of >= the required slots on path `path_index`"""
+        cs = self.current_service
+        path = self.k_shortest_paths[cs.source, cs.destination][path_index]
+        slots = self.get_number_slots(path)
+        starts, values, lengths = self.rle(self.get_available_slots(path))
+        ok = [i for i in range(len(values)) if values[i] == 1 and lengths[i] >= slots][: self.j]
+        return starts[ok], lengths[ok]
+
+    def is_channel_free(self, path, channel_number):
+        """phy_rmsa_env.py:1029-1035"""
+        st = self._state()
+        return all(st[0, l, channel_number] != 0 for l in self._links(path))
+
+    @property
+    def channel_state(self):
+        """phy_rmsa_env.py:158-166: {(src_id, dst_id, idp): [(channel, used, free, capacity), ...]} in append order"""
+        n, k = self.tables.n_nodes, self.k_paths
+        out = {(a, b, i): [] for a in range(n) for b in range(n) for i in range(k)}
+        if self._b.spec.phy_grooming:
+            rows, cnt = self._b.engine.phy_channel_state(4096)
+            for r in rows[0, : int(cnt[0])].cpu().numpy():
+                out[(int(r[0]) // n, int(r[0]) % n, int(r[1]))].append((int(r[2]), int(r[3]), int(r[4]), int(r[5])))
+        return out
 
     # -- the attributes reference heuristics read (rmsa_env.py:854-937, deeprmsa_env.py:135-155) --
     @property
@@ -398,6 +496,7 @@ class GymEnv:
         return a
 
     def reset(self, only_episode_counters: bool = True):
+        self._state_cache = None
         return self._obs_np(self._b.reset(only_episode_counters))
 
     def observation(self):
@@ -408,6 +507,7 @@ class GymEnv:
         (obs, reward, done, False, info) of phy_rmsa_env.py:418-424."""
         if self._phy:
             action = self._phy_action(action)
+        self._state_cache = None
         obs, rew, done, info = self._b.step(np.atleast_1d(np.asarray(action, dtype=np.int64))[None])
         i = {k: (float(v[0]) if v.dtype.is_floating_point else int(v[0])) for k, v in self._b.info().items()}
         i.update({k: int(v[0]) for k, v in info.items()})
@@ -447,6 +547,7 @@ class GymEnv:
         return int(a[0]) if a.size == 1 else tuple(int(x) for x in a)
 
     def load_trace(self, trace):
+        self._state_cache = None
         self._b.load_trace(np.asarray(trace).reshape(-1, 1))
 
     def render(self, mode="human"):
@@ -454,6 +555,55 @@ class GymEnv:
 
     def close(self):
         self._b.close()
+
+
+class _KspView:
+    """``env.k_shortest_paths[src, dst]`` -> list of path objects with the fields of utils.Path (utils.py:27-36)."""
+
+    def __init__(self, t: TopologyTables):
+        self._t, self._cache = t, {}
+        self._nid = {name: i for i, name in enumerate(t.node_names)}
+
+    def __getitem__(self, key):
+        a, b = key
+        if key not in self._cache:
+            t = self._t
+            pr = self._nid[a] * t.n_nodes + self._nid[b]
+            out = []
+            for ip in range(t.k_paths):
+                h = int(t.path_hops[pr, ip])
+                if h <= 0:
+                    continue
+                m = int(t.path_mod[pr, ip])
+                mod = SimpleNamespace(name=t.mod_names[m] if m >= 0 else None, spectral_efficiency=int(t.path_se[pr, ip]),
+                                      maximum_length=float(t.mod_max_length[m]) if m >= 0 else None)
+                out.append(SimpleNamespace(path_id=pr * t.k_paths + ip, idp=ip, hops=h, length=float(t.path_length[pr, ip]),
+                                           node_list=tuple(t.node_names[int(x)] for x in t.path_nodes[pr, ip, : h + 1]),
+                                           best_modulation=mod, current_modulation=None))
+            self._cache[key] = out
+        return self._cache[key]
+
+
+class _TopologyView:
+    """``env.topology``: ``.graph`` (see _GraphView) and ``topology[n1][n2]["index" | "id" | "length"]``."""
+
+    def __init__(self, env: "GymEnv"):
+        self.graph = _GraphView(env)
+        t = env.tables
+        self._adj: Dict[str, Dict[str, Dict[str, Any]]] = {n: {} for n in t.node_names}
+        for e, (a, b) in enumerate(t.edge_nodes):
+            d = {"index": e, "id": e, "length": float(t.edge_length[e])}
+            self._adj[t.node_names[int(a)]][t.node_names[int(b)]] = d
+            self._adj[t.node_names[int(b)]][t.node_names[int(a)]] = d
+
+    def __getitem__(self, node):
+        return self._adj[node]
+
+    def nodes(self):
+        return list(self._adj)
+
+    def number_of_edges(self):
+        return sum(len(v) for v in self._adj.values()) // 2
 
 
 class _GraphView(dict):
@@ -489,11 +639,12 @@ def make(env_id: str, topology=None, num_envs: Optional[int] = None, vec_env: bo
 
 
 class PathOnlyFirstFitAction:
-    """rmsa_env.py:974-1008: the agent picks only the path; the first fitting slot is found on
-    the device (``orlg_path_first_fit``).  Wraps a :class:`BatchedEnv` of RMSA-v0."""
+    """rmsa_env.py:974-1008 / rmcsa_env.py:950-982: the agent picks only the path; the first fitting slot is found on
+    the device (``orlg_path_first_fit``).  Wraps a :class:`BatchedEnv` of RMSA-v0 or RMCSA-v0."""
 
     def __init__(self, env: BatchedEnv):
-        assert env.spec.env_kind == S.ENV_RMSA
+        # RMCSA-v0 (rmcsa_env.py:950-982): the path's best modulation by reach, first core with room, first fit
+        assert env.spec.env_kind in (S.ENV_RMSA, S.ENV_RMCSA)
         self.env = env
         self.action_space = Discrete(env.k_paths + (1 if env.allow_rejection else 0))
         self.observation_space = env.observation_space

@@ -78,7 +78,7 @@ def test_vecenv_matches_device_path_and_oracle():
         assert np.array_equal(obs_h, obs_d.cpu().numpy()), t
         assert np.array_equal(rew_h, rew_d.cpu().numpy().astype(np.float32))
         assert np.array_equal(done_h, done_d.cpu().numpy().astype(bool))
-        assert np.array_equal(infos["accepted"], info_d["accepted"].cpu().numpy().astype(bool))
+        assert np.array_equal([i["accepted"] for i in infos], info_d["accepted"].cpu().numpy().astype(bool))
         rsum += rew_d.cpu().numpy()
         episodes += int(done_h.sum())
     assert episodes == n_env * (n_steps // 29)
@@ -280,3 +280,92 @@ def test_host_wait_modes_give_the_same_step():
         eng.close()
     for a, b in zip(*outs):
         assert all(np.array_equal(x, y) for x, y in zip(a, b))
+
+
+@pytest.mark.gpu
+def test_gymenv_views_carry_reference_style_heuristics():
+    """Code written against the reference env's attribute surface (env.k_shortest_paths, current_service,
+    get_number_slots, is_path_free, get_available_blocks, topology[n1][n2]["index"], topology.graph[...]) runs on a
+    GymEnv: a test-local restatement of shortest-available-path first-fit (rmsa_env.py:901-913) and of DeepRMSA's
+    K-SP-FF (deeprmsa_env.py:146-155) over those views picks the device heuristic's action at every step; the info
+    dict's blocking rates are the reference's (counted before the next request)."""
+    import golden_util as G
+    from optical_rl_gym_qot_aware_b200 import make
+
+    def sap_ff(env):  # the walk of rmsa_env.py:901-913 over the env's public surface
+        cs = env.current_service
+        for idp, path in enumerate(env.k_shortest_paths[cs.source, cs.destination]):
+            n = env.get_number_slots(path)
+            for s0 in range(0, env.topology.graph["num_spectrum_resources"] - n):
+                if env.is_path_free(path, s0, n):
+                    return (idp, s0)
+        return (env.topology.graph["k_paths"], env.topology.graph["num_spectrum_resources"])
+
+    env = make("RMSA-v0", topology=G.topology("nsfnet"), seed=5, load=60, num_spectrum_resources=100, episode_length=40)
+    acc = 0
+    for t in range(120):
+        a = sap_ff(env)
+        assert a == env.heuristic("sap_ff"), (t, a)
+        proc, accepted = env.services_processed, env.services_accepted
+        _, r, d, info = env.step(a)
+        acc += r
+        # rmsa_env.py:293-296: rates from the counters before _next_service counts the next request
+        assert info["service_blocking_rate"] == (proc - (accepted + r)) / proc, (t, info)
+        if d:
+            env.reset()
+    assert 0 < acc < 120
+    avail = env.topology.graph["available_slots"]
+    assert avail.shape == (22, 100) and env.get_available_slots(env.k_shortest_paths["1", "2"][0]).shape == (100,)
+    env.close()
+
+    def ksp_ff(env):  # deeprmsa_env.py:146-155
+        for idp in range(env.k_paths):
+            starts, _ = env.get_available_blocks(idp)
+            if len(starts) > 0:
+                return idp * env.j
+        return env.k_paths * env.j
+
+    env = make("DeepRMSA-v0", topology=G.topology("nsfnet"), seed=6, mean_service_holding_time=7.5,
+               mean_service_inter_arrival_time=1 / 12.0, episode_length=50, j=1)
+    for t in range(100):
+        a = ksp_ff(env)
+        assert a == env.heuristic("ksp_ff"), (t, a)
+        _, _, d, _ = env.step(a)
+        if d:
+            env.reset()
+    env.close()
+
+
+@pytest.mark.gpu
+def test_vecenv_infos_and_monitor_rates_under_auto_reset(tmp_path):
+    """SB3 indexes infos[i]: one dict per env whatever the env count; the episode_* rates VecMonitor logs when an
+    episode ends under auto-reset are those of the finished episode (the reference's info dict), not the counters
+    after the in-kernel reset."""
+    import golden_util as G
+    import oracle_binding as OB
+    from optical_rl_gym_qot_aware_b200 import make, spec as S
+    from optical_rl_gym_qot_aware_b200.monitor import VecMonitor, load_results
+
+    n = 130
+    venv = make("RMSA-v0", topology=G.topology("nsfnet"), num_envs=n, vec_env=True, seed=7, load=60,
+                num_spectrum_resources=100, episode_length=30)
+    mon = VecMonitor(venv, str(tmp_path / "m"), info_keywords=("episode_service_blocking_rate",))
+    mon.reset()
+    ora = OB.OracleEnv(S.make_spec("RMSA-v0", G.topology("nsfnet"), seed=7, load=60, num_spectrum_resources=100,
+                                   episode_length=30, auto_reset=True), 3)
+    ora.reset(True)
+    want = []
+    for t in range(65):
+        act = venv.env.heuristic("sap_ff").cpu().numpy()
+        _, _, done, infos = mon.step(act)
+        assert isinstance(infos, list) and len(infos) == n and {"accepted", "path", "initial_slot"} <= set(infos[3])
+        c = ora.counters()
+        _, r, d, _ = ora.step(ora.heuristic(S.H_SAP_FF))
+        if d:  # the finished episode's rate, from the counters before the next request was counted
+            want.append((c[2] - (c[3] + r)) / c[2])
+        assert d == bool(done[3])
+    mon.close()
+    _, cols = load_results(str(tmp_path / "m") + ".monitor.csv")
+    got = cols["episode_service_blocking_rate"]
+    assert len(want) == 2 and len(got) == 2 * n
+    assert 0.0 <= got.min() and got.max() < 1.0 and abs(got[3] - want[0]) < 1e-6 and abs(got[n + 3] - want[1]) < 1e-6
