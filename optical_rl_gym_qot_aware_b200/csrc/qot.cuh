@@ -23,7 +23,13 @@
 namespace orlg {
 
 enum { QOT_VERDICT = 0, QOT_HEUR_VERDICT = 1, QOT_HEURISTIC = 2 };
-constexpr int QOT_WARPS = 4;
+#ifndef QOT_WARPS_N  // envs (warps) per CTA (A/B knob)
+#define QOT_WARPS_N 4
+#endif
+constexpr int QOT_WARPS = QOT_WARPS_N;
+#ifndef QOT_LINKS_SMEM
+#define QOT_LINKS_SMEM 128
+#endif
 constexpr int QOT_REL_CAP = 32;  // services released by one step (overflow: sticky fault bit 16)
 constexpr double QOT_SCALE = 17592186044416.0;  // 2^44
 constexpr double QOT_INV_SCALE = 1.0 / 17592186044416.0;
@@ -302,7 +308,7 @@ __device__ __forceinline__ bool qot_alone_ok_lane(const Params& p, const GsnrPar
 template <int W, int QOT_CAP>
 __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const Params p_, const GsnrParams g_, const QotIO io) {
   __shared__ QotWarpSmem<QOT_CAP> smem[QOT_WARPS];
-  __shared__ double4 s_link[128];
+  __shared__ double4 s_link[QOT_LINKS_SMEM];
   // the parameter blocks are handed to non-inlined helpers by reference: one shared copy per CTA instead of a
   // local-memory copy per thread
   __shared__ Params p;
