@@ -117,6 +117,8 @@ struct Params {
   int* qot_free_n;                      // [NP]
   unsigned long long* qot_rel;          // [NP][QOT_REL_CAP] payloads of the services the last step released
   int* qot_rel_n;                       // [NP]
+  unsigned long long* qot_add;          // [NP] payload of the lightpath the last qot_kernel launch accepted (0: none); it enters its
+                                        // neighbours' sums at the start of the next launch
   int4* qot_verdict;                    // [NP][2] (accept, path | core << 16, first slot, slots), (se, row, modulation, 0)
   double* qot_g;                        // [NP][2] 1 / GSNR (linear) of the last candidate evaluated and of its worst neighbour with it present; < 0 = none
   const double2* qot_chan;              // [S + 1] per slot count: (B h NF / P, (P / B)^3 8 / (27 pi |b2|) g^2 B / P)

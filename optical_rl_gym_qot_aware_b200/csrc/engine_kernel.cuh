@@ -119,6 +119,7 @@ __global__ void ORLG_LAUNCH_BOUNDS(BD) env_kernel(const Params p, const StepIO i
       for (int i = 0; i < p.qot_slot_cap; i++)
         p.qot_free[(size_t)env.e * p.qot_slot_cap + i] = (unsigned short)(p.qot_slot_cap - 1 - i);
       p.qot_free_n[env.e] = p.qot_slot_cap;
+      p.qot_add[env.e] = 0ull;
     }
 #pragma unroll
     for (int i = 0; i < CNT_N; i++) env.cnt[i] = 0;

@@ -488,7 +488,7 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
     p.qot_slot_cap = p.heap_cap;
     if ((rc = dev_alloc(e, &p.qot_sums, NP * (size_t)p.qot_slot_cap * p.qot_hops)) ||
         (rc = dev_alloc(e, &p.qot_free, NP * (size_t)p.qot_slot_cap)) || (rc = dev_alloc(e, &p.qot_free_n, NP)) ||
-        (rc = dev_alloc(e, &p.qot_rel, NP * (size_t)QOT_REL_CAP)) || (rc = dev_alloc(e, &p.qot_rel_n, NP)) ||
+        (rc = dev_alloc(e, &p.qot_rel, NP * (size_t)QOT_REL_CAP)) || (rc = dev_alloc(e, &p.qot_rel_n, NP)) || (rc = dev_alloc(e, &p.qot_add, NP)) ||
         (rc = dev_alloc(e, &p.qot_verdict, NP * 2)) || (rc = dev_alloc(e, &p.qot_g, NP * 2)))
       return fail_create(e, rc, e->err);
   }

@@ -165,7 +165,7 @@ struct QotCtx {
   // The gate for one candidate; warp-collective.  Returns pass / fail; acc_c = 1 / GSNR of the candidate,
   // acc_w = the largest 1 / GSNR among its neighbours with the candidate present (0 without neighbours).
   // Leaves the candidate's sums in sm.cSA / sm.cSX.
-  __device__ __noinline__ bool gate(const PathRec& rec, int path, int core, int start, int n, int se, double& acc_c, double& acc_w) {
+  __device__ __forceinline__ bool gate(const PathRec& rec, int path, int core, int start, int n, int se, double& acc_c, double& acc_w) {
     const int cpos2 = 2 * start + n;
     const ulonglong2 cmask = __ldg(g.path_mask + (size_t)pair * p.k + path);
     const int hops = rec.hops();
@@ -240,12 +240,14 @@ struct QotCtx {
     return acc_c <= p.qot_thr_lin[se] && !fail;
   }
 
-  // add (sign = +1) or remove (-1) lightpath (path mask, core, start, n, se) from the sums of its neighbours
-  __device__ __noinline__ void apply_to_neighbours(ulonglong2 mask, int core, int start, int n, int se, int sign) {
+  // add (sign = +1) or remove (-1) lightpath (path mask, core, start, n, se) from the sums of its neighbours; the
+  // service in row `skip_row` is the lightpath itself
+  __device__ __forceinline__ void apply_to_neighbours(ulonglong2 mask, int core, int start, int n, int se, int sign, int skip_row) {
     const int cols = 4 * g.tab_S + 1;
     const int pos2 = 2 * start + n;
     const double pm = phi_mod(se);
     for_neighbours(core, mask, [&](unsigned long long s, ulonglong2 common) {
+      if (svc_slot(s) == skip_row) return;
       const int d = (2 * svc_start(s) + svc_slots(s)) - pos2;
       const double2 t = __ldg(g.xci_tab + (size_t)n * cols + (-d + 2 * g.tab_S));  // this lightpath seen by service i
       const long long qa = sign * qot_q(t.x), qx = sign * qot_q(pm * t.y);
@@ -306,20 +308,10 @@ __device__ __forceinline__ bool qot_alone_ok_lane(const Params& p, const GsnrPar
 // first-fit heuristics walk them, (3) an accepted candidate gets a row of the service table and enters its
 // neighbours' sums; the verdict tells the step kernel what to provision.
 template <int W, int QOT_CAP>
-__global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const Params p_, const GsnrParams g_, const QotIO io) {
+__global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const __grid_constant__ Params p, const __grid_constant__ GsnrParams g, const QotIO io) {
   __shared__ QotWarpSmem<QOT_CAP> smem[QOT_WARPS];
   __shared__ double4 s_link[QOT_LINKS_SMEM];
-  // the parameter blocks are handed to non-inlined helpers by reference: one shared copy per CTA instead of a
-  // local-memory copy per thread
-  __shared__ Params p;
-  __shared__ GsnrParams g;
-  {
-    const int* src = reinterpret_cast<const int*>(&p_);
-    int* dst = reinterpret_cast<int*>(&p);
-    for (int i = threadIdx.x; i < (int)(sizeof(Params) / 4); i += blockDim.x) dst[i] = src[i];
-    if (threadIdx.x == 0) g = g_;
-  }
-  for (int l = threadIdx.x; l < p_.E; l += blockDim.x) s_link[l] = g_.link_c[l];
+  for (int l = threadIdx.x; l < p.E; l += blockDim.x) s_link[l] = g.link_c[l];
   __syncthreads();
   const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (e >= p.num_envs) return;
@@ -331,14 +323,20 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
   int free_n = p.qot_free_n[e];
   if (cx.heap_len > 0) cx.stage(0);
 
-  // (1) releases of the last step (the services are out of the queue already)
-  const int nrel = p.qot_rel_n[e];
-  for (int r = 0; r < nrel; r++) {
-    const unsigned long long s = p.qot_rel[(size_t)e * QOT_REL_CAP + r];
-    const ulonglong2 rm = __ldg(g.path_mask + (size_t)svc_pair(s) * p.k + svc_path(s));
-    cx.apply_to_neighbours(rm, svc_core(s), svc_start(s), svc_slots(s), svc_se(s), -1);
-    if (lane == 0) free_stack[free_n] = (unsigned short)svc_slot(s);
-    free_n++;
+  // (1) the lightpath the last launch accepted enters its neighbours' sums (it is in the queue by now - unless the
+  // step released it at once), the services the last step released leave theirs.  Integer sums: any order gives the
+  // same table.
+  const unsigned long long added = p.qot_add[e];
+  const int nrel = p.qot_rel_n[e], nadd = added != 0ull ? 1 : 0;
+  for (int ev = 0; ev < nadd + nrel; ev++) {
+    const bool is_add = ev < nadd;
+    const unsigned long long s = is_add ? added : p.qot_rel[(size_t)e * QOT_REL_CAP + (ev - nadd)];
+    const ulonglong2 em = __ldg(g.path_mask + (size_t)svc_pair(s) * p.k + svc_path(s));
+    cx.apply_to_neighbours(em, svc_core(s), svc_start(s), svc_slots(s), svc_se(s), is_add ? 1 : -1, is_add ? svc_slot(s) : -1);
+    if (!is_add) {
+      if (lane == 0) free_stack[free_n] = (unsigned short)svc_slot(s);
+      free_n++;
+    }
   }
   __syncwarp();
 
@@ -362,92 +360,100 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
       act_ok = a.x >= 0 && a.y >= 0 && a.z >= 0 && a.w >= 0 && a.x < p.k && a.y < p.n_mods && a.z < p.cores && a.w < p.S;
     }
   }
-  const int n_paths = verdict ? 1 : p.k;
+  const int n_paths = (verdict ? 1 : p.k) * (act_ok ? 1 : 0);
   const int ppr = max(1, 32 / nt);  // whole paths per round of 32 lanes
   double gc = -1.0, gmin = 0.0;  // 1 / GSNR (linear) of the last candidate evaluated (< 0: none) and of its worst neighbour
   bool accept = false;
   QotCand A{-1, 0, -1, 0, 0, 0};  // the last candidate evaluated
-  for (int p0 = 0; p0 < n_paths && !accept && act_ok; p0 += ppr) {
-    // ---- generation, one candidate per lane ----
-    QotCand c{-1, 0, -1, 0, 0, 0};
-    bool ok = false;
-    const int pl = lane / nt, t = lane - pl * nt;
-    if (pl < ppr && p0 + pl < n_paths) {
-      c.path = verdict ? act[0] : p0 + pl;
-      const PathRec rec = load_path(p, cx.pair, c.path);
-      if (rec.hops() > 0) {
-        if (!rmcsa) {
-          c.se = p.qot_adaptive ? p.qot_se[t] : rec.se();
-          c.n = number_slots(bit_rate, c.se, p);
-          const Row<W> av = tile.path_avail(rec, 0);
-          if (verdict) {  // RMSAEnv.step: the slot is given
-            c.start = act[3];
-            ok = c.start + c.n <= p.S && range_is_free<W>(av, c.start, c.n);
-          } else {  // walk of rmsa_env.py:901-913
-            c.start = first_fit<W>(av, c.n, p.S);
-            ok = c.start >= 0;
-          }
-        } else {
-          c.mod = verdict ? act[1] : p.qot_adaptive ? p.qot_mod_order[t] : rec.best_mod();
-          if (c.mod < p.n_mods) {  // else: no modulation reaches (get_best_modulation_format raises)
-            c.se = __ldg(p.mod_se + c.mod);
+  // One loop, one gate evaluation per trip (a single inlined copy of the gate).  phase 0: the walk of the heuristic,
+  // candidates generated one per lane, a round of whole paths at a time, the viable ones gated in order.  phase 1
+  // (RMSA-v0, QOT_HEUR_VERDICT): the action (path, slot) does not name the modulation - the step assigns the most
+  // efficient one that passes AT THIS SLOT, which can be better than the one that passed at its own first-fit slot;
+  // walk the step's search over the more efficient ones.  phase 2: none passed, the chosen one is evaluated again.
+  QotCand c{-1, 0, -1, 0, 0, 0}, chosen{-1, 0, -1, 0, 0, 0};
+  unsigned viable = 0u;
+  int p0 = 0, phase = 0, cur_t = 0;
+  while (true) {
+    if (phase == 0 && !viable) {
+      if (p0 >= n_paths) break;
+      // ---- generation, one candidate per lane ----
+      c = QotCand{-1, 0, -1, 0, 0, 0};
+      bool ok = false;
+      const int pl = lane / nt, t = lane - pl * nt;
+      if (pl < ppr && p0 + pl < n_paths) {
+        c.path = verdict ? act[0] : p0 + pl;
+        const PathRec rec = load_path(p, cx.pair, c.path);
+        if (rec.hops() > 0) {
+          if (!rmcsa) {
+            c.se = p.qot_adaptive ? p.qot_se[t] : rec.se();
             c.n = number_slots(bit_rate, c.se, p);
-            if (verdict) {  // RMCSAEnv.step: core and slot are given
-              c.core = act[2], c.start = act[3];
-              ok = c.start + c.n <= p.S && range_is_free<W>(tile.path_avail(rec, c.core), c.start, c.n);
-            } else {  // walk of rmcsa_env.py:882-911: the first core with room
-              for (int core = 0; core < p.cores && !ok; core++) {
-                c.start = first_fit<W>(tile.path_avail(rec, core), c.n, p.S);
-                c.core = core;
-                ok = c.start >= 0;
-              }
+            const Row<W> av = tile.path_avail(rec, 0);
+            if (verdict) {  // RMSAEnv.step: the slot is given
+              c.start = act[3];
+              ok = c.start + c.n <= p.S && range_is_free<W>(av, c.start, c.n);
+            } else {  // walk of rmsa_env.py:901-913
+              c.start = first_fit<W>(av, c.n, p.S);
+              ok = c.start >= 0;
             }
-            ok = ok && qot_crosstalk_ok(p, bit_rate, c.mod, __ldg(p.path_length + (size_t)cx.pair * p.k + c.path));
+          } else {
+            c.mod = verdict ? act[1] : p.qot_adaptive ? p.qot_mod_order[t] : rec.best_mod();
+            if (c.mod < p.n_mods) {  // else: no modulation reaches (get_best_modulation_format raises)
+              c.se = __ldg(p.mod_se + c.mod);
+              c.n = number_slots(bit_rate, c.se, p);
+              // RMCSAEnv.step: core and slot are given; else the walk of rmcsa_env.py:882-911: the first core with room
+              for (int core = verdict ? act[2] : 0; core < (verdict ? act[2] + 1 : p.cores) && !ok; core++) {
+                const Row<W> av = tile.path_avail(rec, core);
+                c.core = core;
+                if (verdict) {
+                  c.start = act[3];
+                  ok = c.start + c.n <= p.S && range_is_free<W>(av, c.start, c.n);
+                } else {
+                  c.start = first_fit<W>(av, c.n, p.S);
+                  ok = c.start >= 0;
+                }
+              }
+              ok = ok && qot_crosstalk_ok(p, bit_rate, c.mod, __ldg(p.path_length + (size_t)cx.pair * p.k + c.path));
+            }
           }
+          // a slot count that does not fit ends a path's search in the reference walk; wider channels (later t) fit even
+          // less, so dropping every candidate without room is the same thing
+          if (ok && p.qot_adaptive) ok = qot_alone_ok_lane(p, g, s_link, rec, c.start, c.n, c.se, cx.invP);
         }
-        // a slot count that does not fit ends a path's search in the reference walk; wider channels (later t) fit even
-        // less, so dropping every candidate without room is the same thing
-        if (ok && p.qot_adaptive) ok = qot_alone_ok_lane(p, g, s_link, rec, c.start, c.n, c.se, cx.invP);
       }
+      viable = __ballot_sync(0xFFFFFFFFu, ok);
+      p0 += ppr;
+      continue;
     }
-    // ---- the gate, in candidate order, until one passes ----
-    unsigned viable = __ballot_sync(0xFFFFFFFFu, ok);
-    while (viable && !accept) {
+    if (phase == 1 && !viable) {
+      phase = 2;
+      A = chosen;
+    } else if (phase < 2) {
       const int L = __ffs((int)viable) - 1;
       viable &= viable - 1;
       A = qot_cand_from(c, L);
-      const PathRec rec = load_path(p, cx.pair, A.path);
-      accept = cx.gate(rec, A.path, A.core, A.start, A.n, A.se, gc, gmin);
-      if (accept && !rmcsa && io.mode == QOT_HEUR_VERDICT && (L % nt) > 0) {
-        // The RMSA-v0 action (path, slot) does not name the modulation: the step assigns the most efficient one that
-        // passes AT THIS SLOT, which can be better than the one that passed at its own first-fit slot.  Walk the
-        // step's search over the more efficient ones; the chosen one is evaluated again last if none passes.
-        const QotCand chosen = A;
-        const int tc = L % nt;
-        QotCand c2 = chosen;
-        bool ok2 = false;
-        if (lane < tc) {
-          c2.se = p.qot_se[lane];
-          c2.n = number_slots(bit_rate, c2.se, p);  // narrower than the chosen channel: it fits where that one fits
-          ok2 = qot_alone_ok_lane(p, g, s_link, rec, c2.start, c2.n, c2.se, cx.invP);
-        }
-        unsigned v2 = __ballot_sync(0xFFFFFFFFu, ok2);
-        accept = false;
-        while (v2 && !accept) {
-          const int L2 = __ffs((int)v2) - 1;
-          v2 &= v2 - 1;
-          A = qot_cand_from(c2, L2);
-          accept = cx.gate(rec, A.path, A.core, A.start, A.n, A.se, gc, gmin);
-        }
-        if (!accept) {
-          A = chosen;
-          accept = cx.gate(rec, A.path, A.core, A.start, A.n, A.se, gc, gmin);
-        }
-      }
+      cur_t = L % nt;
     }
+    // ---- the gate ----
+    const PathRec rec = load_path(p, cx.pair, A.path);
+    accept = cx.gate(rec, A.path, A.core, A.start, A.n, A.se, gc, gmin);
+    if (phase == 2) break;
+    if (phase == 0 && accept && !rmcsa && io.mode == QOT_HEUR_VERDICT && cur_t > 0) {
+      chosen = A;
+      c = chosen;
+      bool ok2 = false;
+      if (lane < cur_t) {
+        c.se = p.qot_se[lane];
+        c.n = number_slots(bit_rate, c.se, p);  // narrower than the chosen channel: it fits where that one fits
+        ok2 = qot_alone_ok_lane(p, g, s_link, rec, c.start, c.n, c.se, cx.invP);
+      }
+      viable = __ballot_sync(0xFFFFFFFFu, ok2);
+      phase = 1;
+      accept = false;
+      continue;
+    }
+    if (accept) break;
   }
 
-  const double nan = __longlong_as_double(0x7FF8000000000000ll);
   if (!verdict && io.actions_out != nullptr && lane == 0) {
     if (!rmcsa)
       reinterpret_cast<int2*>(io.actions_out)[e] = accept ? make_int2(A.path, A.start) : make_int2(p.k, p.S);
@@ -472,7 +478,6 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
       const PathRec rec = load_path(p, cx.pair, A.path);
       if (lane < rec.hops())
         cx.row(slot)[lane] = make_longlong2((long long)cx.sm.cSA[lane], (long long)cx.sm.cSX[lane]);
-      cx.apply_to_neighbours(__ldg(g.path_mask + (size_t)cx.pair * p.k + A.path), A.core, A.start, A.n, A.se, +1);
     }
     if (lane == 0) {
       p.qot_verdict[2 * (size_t)e] = make_int4(accept ? 1 : 0, A.path | (A.core << 16), A.start, A.n);
@@ -482,6 +487,8 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
   if (lane == 0) {
     p.qot_free_n[e] = free_n;
     p.qot_rel_n[e] = 0;
+    // the accepted lightpath enters its neighbours' sums at the start of the next launch (one copy of that code)
+    p.qot_add[e] = (accept && io.mode != QOT_HEURISTIC) ? pack_service(cx.pair, A.path, A.core, A.start, A.n, A.se, slot) : 0ull;
   }
 }
 

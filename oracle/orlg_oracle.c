@@ -1670,13 +1670,16 @@ int64_t oracle_services(const oracle_env* e, int32_t* out6, int64_t max_rows) {
  * re-evaluated with the candidate present, still meets its own.  Each GSNR is one literal call of
  * calculate_osnr; nothing is cached.  qot_last = (candidate, lowest neighbour; NaN when the candidate
  * itself failed and the neighbours were not looked at). */
+static long long g_qot_stat[4]; /* workload statistics for DESIGN.md: gate calls, candidate misses, neighbours, neighbour hops */
+void oracle_qot_stats(long long* out4) { for (int i = 0; i < 4; i++) out4[i] = __atomic_load_n(&g_qot_stat[i], __ATOMIC_RELAXED); }
 static int qot_gate_eval(oracle_env* e, int pair, int path, int core, int start, int n, int se) {
   const oracle_gsnr_params* g = e->c.qot_gsnr;
   gn_service cand = gn_service_of(g, -1, start, n, se);
   double gc = gsnr_of(e, g, pair, path, core, &cand, 0, pair, path, core, &cand);
   e->qot_last[0] = gc;
   e->qot_last[1] = NAN;
-  if (!(gc >= e->c.qot_thr_db[se])) return 0;
+  __atomic_fetch_add(&g_qot_stat[0], 1, __ATOMIC_RELAXED);
+  if (!(gc >= e->c.qot_thr_db[se])) { __atomic_fetch_add(&g_qot_stat[1], 1, __ATOMIC_RELAXED); return 0; }
   int ok = 1;
   double mn = INFINITY;
   const int16_t* CL = links_of(e, pair, path, 0);
@@ -1688,6 +1691,8 @@ static int qot_gate_eval(oracle_env* e, int pair, int path, int core, int start,
     if (!shares) continue;
     gn_service t = gn_service_of(g, (int)i, s->initial_slot, s->number_slots, s->se);
     double v = gsnr_of(e, g, s->pair, s->path, s->core, &t, 1, pair, path, core, &cand);
+    __atomic_fetch_add(&g_qot_stat[2], 1, __ATOMIC_RELAXED);
+    __atomic_fetch_add(&g_qot_stat[3], hops_of(e, s->pair, s->path), __ATOMIC_RELAXED);
     if (v < mn) mn = v;
     if (!(v >= e->c.qot_thr_db[s->se])) ok = 0;
   }

@@ -146,6 +146,7 @@ void oracle_gsnr(const oracle_env* e, const oracle_gsnr_params* g, const int32_t
 int64_t oracle_services(const oracle_env* e, int32_t* out6, int64_t max_rows);
 /* QoT gate of the last step / heuristic call: out2 = (candidate GSNR dB, lowest neighbour GSNR dB with the
  * candidate present) of the last candidate evaluated; NaN where nothing was evaluated */
+void oracle_qot_stats(long long* out4); /* process-wide: gate calls, candidate misses, neighbours, neighbour hops */
 void oracle_qot_last(const oracle_env* e, double* out2);
 
 /* persistent pool of envs stepped with a heuristic on host threads (the envs keep
