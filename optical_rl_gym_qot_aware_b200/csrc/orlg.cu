@@ -566,11 +566,12 @@ static int launch_qot(orlg_engine* e, int mode, const int32_t* actions, int32_t*
   cudaStream_t st = (cudaStream_t)stream;
   QotIO q{mode, actions, actions_out};
   const int grid = (e->p.num_envs + QOT_WARPS - 1) / QOT_WARPS;
+  const size_t dsm = (size_t)e->p.E * sizeof(double4);  // the per-link factors staged by every CTA
 #define ORLG_QOT_LAUNCH(WW)                                                                         \
   do {                                                                                              \
-    if (e->qot_cap <= 64) qot_kernel<WW, 64><<<grid, QOT_WARPS * 32, 0, st>>>(e->p, e->gp, q);       \
-    else if (e->qot_cap <= 128) qot_kernel<WW, 128><<<grid, QOT_WARPS * 32, 0, st>>>(e->p, e->gp, q); \
-    else qot_kernel<WW, 256><<<grid, QOT_WARPS * 32, 0, st>>>(e->p, e->gp, q);                        \
+    if (e->qot_cap <= 64) qot_kernel<WW, 64><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q);       \
+    else if (e->qot_cap <= 128) qot_kernel<WW, 128><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q); \
+    else qot_kernel<WW, 256><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q);                        \
   } while (0)
   switch (e->W) {
     case 2: ORLG_QOT_LAUNCH(2); break;

@@ -23,13 +23,10 @@
 namespace orlg {
 
 enum { QOT_VERDICT = 0, QOT_HEUR_VERDICT = 1, QOT_HEURISTIC = 2 };
-#ifndef QOT_WARPS_N  // envs (warps) per CTA (A/B knob)
-#define QOT_WARPS_N 4
+#ifndef QOT_WARPS_N  // envs (warps) per CTA (A/B knob): a one-warp CTA gives its SM slot back the moment its env is done
+#define QOT_WARPS_N 1
 #endif
 constexpr int QOT_WARPS = QOT_WARPS_N;
-#ifndef QOT_LINKS_SMEM
-#define QOT_LINKS_SMEM 128
-#endif
 constexpr int QOT_REL_CAP = 32;  // services released by one step (overflow: sticky fault bit 16)
 constexpr double QOT_SCALE = 17592186044416.0;  // 2^44
 constexpr double QOT_INV_SCALE = 1.0 / 17592186044416.0;
@@ -41,7 +38,7 @@ struct QotIO {
 };
 
 #ifndef QOT_MIN_CTAS  // resident CTAs per SM the register allocation must allow (A/B knob)
-#define QOT_MIN_CTAS 8
+#define QOT_MIN_CTAS 32
 #endif
 // QOT_CAP = running services staged per window (an env with more is walked window by window); the kernel is
 // instantiated for 64 / 128 / 256 and the launch picks the smallest that covers the offered load + 1 sigma, because
@@ -310,7 +307,7 @@ __device__ __forceinline__ bool qot_alone_ok_lane(const Params& p, const GsnrPar
 template <int W, int QOT_CAP>
 __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const __grid_constant__ Params p, const __grid_constant__ GsnrParams g, const QotIO io) {
   __shared__ QotWarpSmem<QOT_CAP> smem[QOT_WARPS];
-  __shared__ double4 s_link[QOT_LINKS_SMEM];
+  extern __shared__ double4 s_link[];  // per-link factors, p.E entries (sized at launch)
   for (int l = threadIdx.x; l < p.E; l += blockDim.x) s_link[l] = g.link_c[l];
   __syncthreads();
   const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
