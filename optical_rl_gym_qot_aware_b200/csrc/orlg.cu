@@ -567,11 +567,16 @@ static int launch_qot(orlg_engine* e, int mode, const int32_t* actions, int32_t*
   QotIO q{mode, actions, actions_out};
   const int grid = (e->p.num_envs + QOT_WARPS - 1) / QOT_WARPS;
   const size_t dsm = (size_t)e->p.E * sizeof(double4);  // the per-link factors staged by every CTA
-#define ORLG_QOT_LAUNCH(WW)                                                                         \
-  do {                                                                                              \
-    if (e->qot_cap <= 64) qot_kernel<WW, 64><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q);       \
-    else if (e->qot_cap <= 128) qot_kernel<WW, 128><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q); \
-    else qot_kernel<WW, 256><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q);                        \
+#define ORLG_QOT_LAUNCH_K(WW, RM)                                                                          \
+  do {                                                                                                     \
+    if (e->qot_cap <= 64) qot_kernel<WW, 64, RM><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q);       \
+    else if (e->qot_cap <= 128) qot_kernel<WW, 128, RM><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q); \
+    else qot_kernel<WW, 256, RM><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q);                        \
+  } while (0)
+#define ORLG_QOT_LAUNCH(WW)                                   \
+  do {                                                        \
+    if (e->p.kind == ORLG_ENV_RMCSA) ORLG_QOT_LAUNCH_K(WW, true); \
+    else ORLG_QOT_LAUNCH_K(WW, false);                        \
   } while (0)
   switch (e->W) {
     case 2: ORLG_QOT_LAUNCH(2); break;
@@ -579,6 +584,7 @@ static int launch_qot(orlg_engine* e, int mode, const int32_t* actions, int32_t*
     default: ORLG_QOT_LAUNCH(10); break;
   }
 #undef ORLG_QOT_LAUNCH
+#undef ORLG_QOT_LAUNCH_K
   cudaError_t rc = cudaGetLastError();
   if (rc != cudaSuccess) {
     e->err = std::string("qot_kernel launch: ") + cudaGetErrorString(rc);

@@ -304,7 +304,7 @@ __device__ __forceinline__ bool qot_alone_ok_lane(const Params& p, const GsnrPar
 // closed-form gate, interference-free GSNR - and the viable ones put through the gate in the order the reference's
 // first-fit heuristics walk them, (3) an accepted candidate gets a row of the service table and enters its
 // neighbours' sums; the verdict tells the step kernel what to provision.
-template <int W, int QOT_CAP>
+template <int W, int QOT_CAP, bool RMCSA>
 __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const __grid_constant__ Params p, const __grid_constant__ GsnrParams g, const QotIO io) {
   __shared__ QotWarpSmem<QOT_CAP> smem[QOT_WARPS];
   extern __shared__ double4 s_link[];  // per-link factors, p.E entries (sized at launch)
@@ -339,7 +339,7 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
 
   // (2) candidates
   Tile<W, 1> tile{p.occ + (size_t)e * p.planes, 0, p.E};
-  const bool rmcsa = p.kind == ORLG_ENV_RMCSA;
+  constexpr bool rmcsa = RMCSA;  // p.kind == ORLG_ENV_RMCSA (else RMSA-v0): each instantiation carries one env's code only
   const bool verdict = io.mode == QOT_VERDICT;
   // modulations tried per path, most efficient first: RMSA-v0 adaptive qot_se[], RMCSA-v0 adaptive qot_mod_order[],
   // else the path's best modulation; a verdict on an RMCSA action names its modulation
