@@ -567,11 +567,17 @@ static int launch_qot(orlg_engine* e, int mode, const int32_t* actions, int32_t*
   QotIO q{mode, actions, actions_out};
   const int grid = (e->p.num_envs + QOT_WARPS - 1) / QOT_WARPS;
   const size_t dsm = (size_t)e->p.E * sizeof(double4);  // the per-link factors staged by every CTA
-#define ORLG_QOT_LAUNCH_K(WW, RM)                                                                          \
-  do {                                                                                                     \
-    if (e->qot_cap <= 64) qot_kernel<WW, 64, RM><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q);       \
-    else if (e->qot_cap <= 128) qot_kernel<WW, 128, RM><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q); \
-    else qot_kernel<WW, 256, RM><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q);                        \
+#define ORLG_QOT_LAUNCH_M(WW, RM, MD)                                                                          \
+  do {                                                                                                         \
+    if (e->qot_cap <= 64) qot_kernel<WW, 64, RM, MD><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q);       \
+    else if (e->qot_cap <= 128) qot_kernel<WW, 128, RM, MD><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q); \
+    else qot_kernel<WW, 256, RM, MD><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q);                        \
+  } while (0)
+#define ORLG_QOT_LAUNCH_K(WW, RM)                                          \
+  do {                                                                     \
+    if (mode == QOT_VERDICT) ORLG_QOT_LAUNCH_M(WW, RM, QOT_VERDICT);       \
+    else if (mode == QOT_HEUR_VERDICT) ORLG_QOT_LAUNCH_M(WW, RM, QOT_HEUR_VERDICT); \
+    else ORLG_QOT_LAUNCH_M(WW, RM, QOT_HEURISTIC);                         \
   } while (0)
 #define ORLG_QOT_LAUNCH(WW)                                   \
   do {                                                        \
@@ -585,6 +591,7 @@ static int launch_qot(orlg_engine* e, int mode, const int32_t* actions, int32_t*
   }
 #undef ORLG_QOT_LAUNCH
 #undef ORLG_QOT_LAUNCH_K
+#undef ORLG_QOT_LAUNCH_M
   cudaError_t rc = cudaGetLastError();
   if (rc != cudaSuccess) {
     e->err = std::string("qot_kernel launch: ") + cudaGetErrorString(rc);

@@ -304,7 +304,7 @@ __device__ __forceinline__ bool qot_alone_ok_lane(const Params& p, const GsnrPar
 // closed-form gate, interference-free GSNR - and the viable ones put through the gate in the order the reference's
 // first-fit heuristics walk them, (3) an accepted candidate gets a row of the service table and enters its
 // neighbours' sums; the verdict tells the step kernel what to provision.
-template <int W, int QOT_CAP, bool RMCSA>
+template <int W, int QOT_CAP, bool RMCSA, int MODE>
 __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const __grid_constant__ Params p, const __grid_constant__ GsnrParams g, const QotIO io) {
   __shared__ QotWarpSmem<QOT_CAP> smem[QOT_WARPS];
   extern __shared__ double4 s_link[];  // per-link factors, p.E entries (sized at launch)
@@ -340,7 +340,7 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
   // (2) candidates
   Tile<W, 1> tile{p.occ + (size_t)e * p.planes, 0, p.E};
   constexpr bool rmcsa = RMCSA;  // p.kind == ORLG_ENV_RMCSA (else RMSA-v0): each instantiation carries one env's code only
-  const bool verdict = io.mode == QOT_VERDICT;
+  constexpr bool verdict = MODE == QOT_VERDICT;  // MODE == io.mode: each instantiation carries one mode's code only
   // modulations tried per path, most efficient first: RMSA-v0 adaptive qot_se[], RMCSA-v0 adaptive qot_mod_order[],
   // else the path's best modulation; a verdict on an RMCSA action names its modulation
   const int nt = (rmcsa && verdict) ? 1 : !p.qot_adaptive ? 1 : rmcsa ? p.n_mods : p.qot_n_se;
@@ -434,7 +434,7 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
     const PathRec rec = load_path(p, cx.pair, A.path);
     accept = cx.gate(rec, A.path, A.core, A.start, A.n, A.se, gc, gmin);
     if (phase == 2) break;
-    if (phase == 0 && accept && !rmcsa && io.mode == QOT_HEUR_VERDICT && cur_t > 0) {
+    if (phase == 0 && accept && !rmcsa && MODE == QOT_HEUR_VERDICT && cur_t > 0) {
       chosen = A;
       c = chosen;
       bool ok2 = false;
@@ -465,7 +465,7 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
 
   // (3) the accepted candidate enters the service table
   int slot = 0;
-  if (io.mode != QOT_HEURISTIC) {
+  if (MODE != QOT_HEURISTIC) {
     if (accept && free_n == 0) {  // more running services than rows (the release queue is as full): refuse
       accept = false;
       if (lane == 0) atomicOr((unsigned long long*)&p.counters[(size_t)CNT_FAULT * p.NP + e], 32ull);
@@ -485,7 +485,7 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
     p.qot_free_n[e] = free_n;
     p.qot_rel_n[e] = 0;
     // the accepted lightpath enters its neighbours' sums at the start of the next launch (one copy of that code)
-    p.qot_add[e] = (accept && io.mode != QOT_HEURISTIC) ? pack_service(cx.pair, A.path, A.core, A.start, A.n, A.se, slot) : 0ull;
+    p.qot_add[e] = (accept && MODE != QOT_HEURISTIC) ? pack_service(cx.pair, A.path, A.core, A.start, A.n, A.se, slot) : 0ull;
   }
 }
 
