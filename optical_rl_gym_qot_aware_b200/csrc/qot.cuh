@@ -203,22 +203,21 @@ struct QotCtx {
       const double sci = __ldg(g.sci_tab + ni);
       double acc = 0.0;
       const int hi = __ldg(ri);
-      for (int h0 = 0; h0 < hi; h0 += 4) {  // four independent row loads in flight
-        longlong2 sv[4];
+      for (int h0 = 0; h0 < hi; h0 += 4) {  // four independent row loads in flight; no branch per hop (a hop past
+        longlong2 sv[4];                     // the end reads link 0 of the record's padding and adds +0.0)
 #pragma unroll
         for (int u = 0; u < 4; u++) sv[u] = (h0 + u < hi) ? rw[h0 + u] : make_longlong2(0, 0);
 #pragma unroll
-        for (int u = 0; u < 4; u++)
-          if (h0 + u < hi) {
-            const int l = __ldg(ri + 4 + h0 + u);
-            const double4 lc = link_c[l];
-            if (mask_has(common, l)) {
-              sv[u].x += qa_ic;
-              sv[u].y += qx_ic;
-            }
-            const double sum_phi = sci + ((double)sv[u].x * QOT_INV_SCALE - ((double)sv[u].y * QOT_INV_SCALE) * lc.y);
-            acc += lc.w * (ci.ase * lc.z + ci.nli * lc.x * sum_phi);
-          }
+        for (int u = 0; u < 4; u++) {
+          const int l = __ldg(ri + 4 + h0 + u);
+          const double4 lc = link_c[l];
+          const bool shared = mask_has(common, l);
+          sv[u].x += shared ? qa_ic : 0ll;
+          sv[u].y += shared ? qx_ic : 0ll;
+          const double sum_phi = sci + ((double)sv[u].x * QOT_INV_SCALE - ((double)sv[u].y * QOT_INV_SCALE) * lc.y);
+          const double t = lc.w * (ci.ase * lc.z + ci.nli * lc.x * sum_phi);
+          acc += (h0 + u < hi) ? t : 0.0;
+        }
       }
       worst = fmax(worst, acc);
       if (!(acc <= p.qot_thr_lin[sei])) fail = true;
@@ -292,10 +291,25 @@ __device__ __forceinline__ bool qot_alone_ok_lane(const Params& p, const GsnrPar
   const QotChan c = qot_chan(p, g, start, n);
   const double sci = __ldg(g.sci_tab + n);
   double acc = 0.0;
-  for_each_link(rec, [&](int l) {
-    const double4 lc = link_c[l];
+  // lanes hold paths of different lengths: the hops of a group of four are computed without branches (a hop past the
+  // end reads link 0 and adds +0.0, which leaves the sum as it is), only the groups are skipped
+  const int h = rec.hops();
+#pragma unroll
+  for (int gq = 0; gq < 3; gq++) {
+    if (4 * gq < h) {
+      const uint32_t wd = rec.w[gq + 1];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const double4 lc = link_c[(wd >> (8 * u)) & 0xFFu];
+        const double t = lc.w * (c.ase * lc.z + c.nli * lc.x * sci);
+        acc += (4 * gq + u < h) ? t : 0.0;
+      }
+    }
+  }
+  for (int i = 12; i < h; i++) {  // long paths (32-byte records)
+    const double4 lc = link_c[rec.link(i)];
     acc += lc.w * (c.ase * lc.z + c.nli * lc.x * sci);
-  });
+  }
   return acc <= p.qot_thr_lin[se];
 }
 
