@@ -63,7 +63,26 @@ struct CutPlanes {
   Row<W> b[PHY_PLANES];
 };
 
-// per-channel number of r_cut terms whose neighbour link has the channel free
+// carry[] enters the counters at plane q0; before it every counter is < 2^np, so the ripple stops at plane np - 1
+template <int W>
+__device__ __forceinline__ void ripple_add(CutPlanes<W>& c, uint32_t (&carry)[W], int q0, int np) {
+#pragma unroll
+  for (int q = 0; q < PHY_PLANES; q++) {
+    if (q >= q0 && q < np) {
+#pragma unroll
+      for (int i = 0; i < W; i++) {
+        uint32_t t2 = c.b[q].w[i] & carry[i];
+        c.b[q].w[i] ^= carry[i];
+        carry[i] = t2;
+      }
+    }
+  }
+}
+
+// per-channel number of r_cut terms whose neighbour link has the channel free.  Bit-sliced counters; the rows of
+// four terms at a time go through carry-save adders (two 3:2 steps into the ones, one into the twos), so only one
+// carry row per four terms ripples through the planes above - about half the word operations of adding row by row.
+// np bounds the planes that can hold a bit after t terms: it depends on the loop counter only.
 template <int W, int BD, typename ENV>
 __device__ __forceinline__ void count_terms(ENV& env, int pathg, CutPlanes<W>& c) {
   const Params& p = env.p;
@@ -73,25 +92,48 @@ __device__ __forceinline__ void count_terms(ENV& env, int pathg, CutPlanes<W>& c
     for (int i = 0; i < W; i++) c.b[q].w[i] = 0u;
   const int T = __ldg(p.phy_cut_count + pathg);
   const unsigned char* links = p.phy_cut_links + (size_t)pathg * p.phy_max_terms;
-  for (int t = 0; t < T; t++) {
+  int t = 0;
+  for (; t + 4 <= T; t += 4) {
+    const int l0 = __ldg(links + t), l1 = __ldg(links + t + 1), l2 = __ldg(links + t + 2), l3 = __ldg(links + t + 3);
+    uint32_t carry[W];
+#pragma unroll
+    for (int i = 0; i < W; i++) {
+      const uint32_t x0 = env.tile.word(0, l0, i), x1 = env.tile.word(0, l1, i), x2 = env.tile.word(0, l2, i),
+                     x3 = env.tile.word(0, l3, i);
+      uint32_t ones = c.b[0].w[i], twos = c.b[1].w[i];
+      uint32_t u = ones ^ x0;
+      const uint32_t ha = (ones & x0) | (u & x1);
+      ones = u ^ x1;
+      u = ones ^ x2;
+      const uint32_t hb = (ones & x2) | (u & x3);
+      ones = u ^ x3;
+      u = twos ^ ha;
+      carry[i] = (twos & ha) | (u & hb);
+      twos = u ^ hb;
+      c.b[0].w[i] = ones;
+      c.b[1].w[i] = twos;
+    }
+    ripple_add<W>(c, carry, 2, 32 - __clz(t + 4));
+  }
+  if (t + 2 <= T) {
+    const int l0 = __ldg(links + t), l1 = __ldg(links + t + 1);
+    uint32_t carry[W];
+#pragma unroll
+    for (int i = 0; i < W; i++) {
+      const uint32_t x0 = env.tile.word(0, l0, i), x1 = env.tile.word(0, l1, i);
+      const uint32_t ones = c.b[0].w[i], u = ones ^ x0;
+      carry[i] = (ones & x0) | (u & x1);
+      c.b[0].w[i] = u ^ x1;
+    }
+    t += 2;
+    ripple_add<W>(c, carry, 1, 32 - __clz(t));
+  }
+  if (t < T) {
     const int l = __ldg(links + t);
-    // before term t every counter is <= t, so only planes 0 .. bits(t + 1) - 1 can change: the ripple stops
-    // there (t is the loop counter, hence the bound is the same for every lane still in the loop)
-    const int np = 32 - __clz(t + 1);
     uint32_t carry[W];
 #pragma unroll
     for (int i = 0; i < W; i++) carry[i] = env.tile.word(0, l, i);
-#pragma unroll
-    for (int q = 0; q < PHY_PLANES; q++) {
-      if (q < np) {
-#pragma unroll
-        for (int i = 0; i < W; i++) {
-          uint32_t t2 = c.b[q].w[i] & carry[i];
-          c.b[q].w[i] ^= carry[i];
-          carry[i] = t2;
-        }
-      }
-    }
+    ripple_add<W>(c, carry, 0, 32 - __clz(t + 1));
   }
 }
 
@@ -306,6 +348,11 @@ __device__ void phy_heuristic(ENV& env, int hid, int* a) {
   const int table = __ldg(p.phy_table_id + pr);
   if (table < 0) return;
   int best = -1, best_mod = -1, best_frag = -(1 << 30);
+  CutPlanes<W> cp_best;  // the counters of the best row so far (BM-FA-Cut, FA-FF): the channel walk below needs them again
+#pragma unroll
+  for (int q = 0; q < PHY_PLANES; q++)
+#pragma unroll
+    for (int i = 0; i < W; i++) cp_best.b[q].w[i] = 0u;
   for (int idp = 0; idp < p.k; idp++) {
     PathRec rec = load_path(p, pr, idp);
     if (rec.hops() <= 0) continue;
@@ -350,6 +397,7 @@ __device__ void phy_heuristic(ENV& env, int hid, int* a) {
       best = idp;
       best_mod = head;
       best_frag = frag;
+      cp_best = cp;
     }
   }
   if (best < 0) return;
@@ -360,25 +408,21 @@ __device__ void phy_heuristic(ENV& env, int hid, int* a) {
   if (hid == ORLG_H_PHY_SAP_FF || hid == ORLG_H_PHY_FA_FF) {
     // SAP-FF: ascending channel number, whatever the level (:1704); FA-FF: descending r_cut, then
     // ascending channel (:1537); each channel counts with its own level
-    CutPlanes<W> cp;
-    if (hid == ORLG_H_PHY_FA_FF) count_terms<W, BD>(env, pr * p.k + best, cp);
     while (need > 0 && n < PHY_ADIM - 1) {
-      int ch = lowest_set<W>(hid == ORLG_H_PHY_FA_FF ? min_count_subset<W>(A, cp) : A);
+      int ch = lowest_set<W>(hid == ORLG_H_PHY_FA_FF ? min_count_subset<W>(A, cp_best) : A);
       if (ch < 0) break;
       row_clear_bit<W>(A, ch);
       a[1 + n++] = ch;
       need -= (int)__ldg(p.phy_mod + ((size_t)table * p.S + ch) * p.k + best) * 100;
     }
   } else {
-    CutPlanes<W> cp;
-    if (hid == ORLG_H_PHY_BM_FA_CUT) count_terms<W, BD>(env, pr * p.k + best, cp);
 #pragma unroll 1
     for (int m = PHY_LEVELS; m >= 1 && need > 0; m--) {
       Row<W> cand = level_mask<W>(p, table, best, m);
       and_into(cand, A);
       while (need > 0 && n < PHY_ADIM - 1 && row_any<W>(cand)) {
         Row<W> s = cand;
-        if (hid == ORLG_H_PHY_BM_FA_CUT) s = min_count_subset<W>(cand, cp);
+        if (hid == ORLG_H_PHY_BM_FA_CUT) s = min_count_subset<W>(cand, cp_best);
         int ch = lowest_set<W>(s);
         row_clear_bit<W>(cand, ch);
         a[1 + n++] = ch;
@@ -730,12 +774,15 @@ __device__ void phy_info(ENV& env, double* o, long long fs, bool want_rss) {
   const Params& p = env.p;
   // _calculate_total_cuts :1195-1203: runs of free links (in link-index order) per channel
   long long cuts = 0;
+  uint32_t prev[W];
+#pragma unroll
+  for (int i = 0; i < W; i++) prev[i] = 0u;
   for (int l = 0; l < p.E; l++) {
 #pragma unroll
     for (int i = 0; i < W; i++) {
-      uint32_t cur = env.tile.word(0, l, i);
-      uint32_t prev = l > 0 ? env.tile.word(0, l - 1, i) : 0u;
-      cuts += __popc(cur & ~prev);
+      const uint32_t cur = env.tile.word(0, l, i);
+      cuts += __popc(cur & ~prev[i]);
+      prev[i] = cur;
     }
   }
   o[0] = (double)cuts / (double)p.S;

@@ -42,8 +42,11 @@ def disasm_lines(obj, kernel):
 
 
 def ncu_rows(report, kernel_idx):
-    txt = subprocess.run(["ncu", "-i", report, "--page", "source", "--csv", "--print-source", "sass"],
-                         capture_output=True, text=True).stdout
+    if report.endswith(".csv"):  # the source page exported on the GPU box (the .ncu-rep itself is too big to bring back)
+        txt = open(report).read()
+    else:
+        txt = subprocess.run(["ncu", "-i", report, "--page", "source", "--csv", "--print-source", "sass"],
+                             capture_output=True, text=True).stdout
     sections, cur = [], None
     for row in csv.reader(io.StringIO(txt)):
         if row and row[0] == "Kernel Name":
