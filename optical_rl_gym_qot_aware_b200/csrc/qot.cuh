@@ -46,7 +46,9 @@ struct QotIO {
 template <int QOT_CAP>
 struct QotWarpSmem {
   unsigned long long pay[QOT_CAP];      // release-queue payloads of the staged window
+#ifdef QOT_STAGE_MASKS
   ulonglong2 mask[QOT_CAP];             // their paths as link sets
+#endif
   unsigned long long cSA[32], cSX[32];  // the candidate's own sums, per hop
   unsigned short nb[QOT_CAP];           // compacted neighbour list of the current pass
   unsigned char hop_of[128];            // link -> hop of the candidate
@@ -94,13 +96,23 @@ struct QotCtx {
     return reinterpret_cast<const unsigned char*>(p.path_rec + ((size_t)pr * p.k + path) * p.rec_u4);
   }
 
+  // link set of a staged service: from the path table (a few KB, L1 resident) unless the build stages it
+  __device__ __forceinline__ ulonglong2 svc_mask(unsigned long long s, int i) const {
+#ifdef QOT_STAGE_MASKS
+    return sm.mask[i];
+#else
+    return __ldg(g.path_mask + (size_t)svc_pair(s) * p.k + svc_path(s));
+#endif
+  }
   __device__ __forceinline__ void stage(int w) {
     __syncwarp();
     const int base = w * QOT_CAP, n = min(QOT_CAP, heap_len - base);
     for (int i = lane; i < n; i += 32) {
       const unsigned long long s = heap[base + i].y;
       sm.pay[i] = s;
+#ifdef QOT_STAGE_MASKS
       sm.mask[i] = __ldg(g.path_mask + (size_t)svc_pair(s) * p.k + svc_path(s));
+#endif
     }
     win = w;
     __syncwarp();
@@ -120,7 +132,7 @@ struct QotCtx {
         const int i = base + lane;
         bool hit = false;
         if (i < n && svc_core(sm.pay[i]) == core) {
-          const ulonglong2 im = sm.mask[i];
+          const ulonglong2 im = svc_mask(sm.pay[i], i);
           hit = ((im.x & mask.x) | (im.y & mask.y)) != 0ull;
         }
         const unsigned bal = __ballot_sync(0xFFFFFFFFu, hit);
@@ -130,7 +142,7 @@ struct QotCtx {
       __syncwarp();
       for (int j = lane; j < cnt; j += 32) {
         const int i = sm.nb[j];
-        const ulonglong2 im = sm.mask[i];
+        const ulonglong2 im = svc_mask(sm.pay[i], i);
         f(sm.pay[i], make_ulonglong2(im.x & mask.x, im.y & mask.y));
       }
       __syncwarp();
