@@ -117,6 +117,7 @@ struct Params {
   int* qot_free_n;                      // [NP]
   unsigned long long* qot_rel;          // [NP][QOT_REL_CAP] payloads of the services the last step released
   int* qot_rel_n;                       // [NP]
+  double* qot_gp;                       // [NP][2] GSNR pair of a heuristic launch's proposal (qot.cuh)
   unsigned long long* qot_add;          // [NP] payload of the lightpath the last qot_kernel launch accepted (0: none); it enters its
                                         // neighbours' sums at the start of the next launch
   int4* qot_verdict;                    // [NP][2] (accept, path | core << 16, first slot, slots), (se, row, modulation, 0)

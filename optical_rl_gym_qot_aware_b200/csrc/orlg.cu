@@ -47,6 +47,7 @@ struct orlg_engine {
   int* auto_actions = nullptr;          // orlg_step_auto without a caller buffer
   long long* auto_reward_sum = nullptr; // set by orlg_rollout around its orlg_step_auto loop
   long long* snap = nullptr;            // orlg_set_counter_snapshot
+  bool qot_proposal_valid = false;      // the last state-touching call was a heuristic-13 launch (launch_qot)
   int qot_cap = 64;                     // services staged per window by qot_kernel (64 / 128 / 256)
   cudaEvent_t mid_ev = nullptr;         // orlg_timed_steps: recorded between the launches of a multi-launch step
   bool mid_external = false;
@@ -488,7 +489,7 @@ extern "C" int orlg_create(const orlg_config* c, orlg_engine** out) {
     p.qot_slot_cap = p.heap_cap;
     if ((rc = dev_alloc(e, &p.qot_sums, NP * (size_t)p.qot_slot_cap * p.qot_hops)) ||
         (rc = dev_alloc(e, &p.qot_free, NP * (size_t)p.qot_slot_cap)) || (rc = dev_alloc(e, &p.qot_free_n, NP)) ||
-        (rc = dev_alloc(e, &p.qot_rel, NP * (size_t)QOT_REL_CAP)) || (rc = dev_alloc(e, &p.qot_rel_n, NP)) || (rc = dev_alloc(e, &p.qot_add, NP)) ||
+        (rc = dev_alloc(e, &p.qot_rel, NP * (size_t)QOT_REL_CAP)) || (rc = dev_alloc(e, &p.qot_rel_n, NP)) || (rc = dev_alloc(e, &p.qot_add, NP)) || (rc = dev_alloc(e, &p.qot_gp, NP * 2)) ||
         (rc = dev_alloc(e, &p.qot_verdict, NP * 2)) || (rc = dev_alloc(e, &p.qot_g, NP * 2)))
       return fail_create(e, rc, e->err);
   }
@@ -537,6 +538,7 @@ extern "C" int orlg_load_trace(orlg_engine* e, const orlg_request* dev_trace, in
   if (!e || !dev_trace || n < 1) return ORLG_EINVAL;
   e->p.trace = dev_trace;
   e->p.trace_len = n;
+  e->qot_proposal_valid = false;
   return ORLG_OK;
 }
 
@@ -564,7 +566,10 @@ static void record_mid(orlg_engine* e, void* stream) {
 // qot_kernel launch (engines with the QoT gate): one warp per env
 static int launch_qot(orlg_engine* e, int mode, const int32_t* actions, int32_t* actions_out, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
-  QotIO q{mode, actions, actions_out};
+  // the verdict launch that follows a heuristic-13 launch on the same state may take its verdict (qot.cuh); any
+  // other launch of this function, a reset or a new trace ends that
+  QotIO q{mode, actions, actions_out, (mode == QOT_VERDICT && e->qot_proposal_valid) ? 1 : 0};
+  e->qot_proposal_valid = (mode == QOT_HEURISTIC);
   const int grid = (e->p.num_envs + QOT_WARPS - 1) / QOT_WARPS;
   const size_t dsm = (size_t)e->p.E * sizeof(double4);  // the per-link factors staged by every CTA
 #define ORLG_QOT_LAUNCH_M(WW, RM, MD)                                                                          \
@@ -618,6 +623,7 @@ extern "C" int orlg_reset(orlg_engine* e, int full, void* stream) {
   cudaSetDevice(e->device);
   StepIO io = make_io(e, full ? MODE_RESET_FULL : MODE_RESET_EPISODE);
   io.obs = nullptr;
+  e->qot_proposal_valid = false;
   return launch(e, io, stream);
 }
 

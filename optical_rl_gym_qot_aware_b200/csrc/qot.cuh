@@ -35,6 +35,8 @@ struct QotIO {
   int mode;
   const int* actions;  // QOT_VERDICT: the step's action tensor
   int* actions_out;    // heuristic modes: the action chosen (may be null in QOT_HEUR_VERDICT)
+  int use_proposal;    // QOT_VERDICT: the last launch was QOT_HEURISTIC on this very state - an action equal to its
+                       // proposal takes that launch's verdict (and the sums it left in the next free row)
 };
 
 #ifndef QOT_MIN_CTAS  // resident CTAs per SM the register allocation must allow (A/B knob)
@@ -383,11 +385,21 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
       act_ok = a.x >= 0 && a.y >= 0 && a.z >= 0 && a.w >= 0 && a.x < p.k && a.y < p.n_mods && a.z < p.cores && a.w < p.S;
     }
   }
-  const int n_paths = (verdict ? 1 : p.k) * (act_ok ? 1 : 0);
+  // An agent loop asks the heuristic and steps with its answer: the verdict launch would repeat the heuristic launch's
+  // gate.  When the host says nothing changed in between (io.use_proposal) and the action is the proposal, its verdict
+  // stands: the lightpath, its modulation, and its sums, which that launch left in the next free row.
+  bool cached = false;
+  QotCand A{-1, 0, -1, 0, 0, 0};  // the last candidate evaluated
+  if (verdict && io.use_proposal && act_ok) {
+    const int4 v0 = p.qot_verdict[2 * (size_t)e], v1 = p.qot_verdict[2 * (size_t)e + 1];
+    const int vp = v0.y & 0xFFFF, vc = v0.y >> 16;
+    cached = v0.x != 0 && act[0] == vp && act[3] == v0.z && (!rmcsa || (act[1] == v1.z && act[2] == vc));
+    if (cached) A = QotCand{vp, vc, v0.z, v0.w, v1.x, v1.z};
+  }
+  const int n_paths = (verdict ? 1 : p.k) * ((act_ok && !cached) ? 1 : 0);
   const int ppr = max(1, 32 / nt);  // whole paths per round of 32 lanes
   double gc = -1.0, gmin = 0.0;  // 1 / GSNR (linear) of the last candidate evaluated (< 0: none) and of its worst neighbour
-  bool accept = false;
-  QotCand A{-1, 0, -1, 0, 0, 0};  // the last candidate evaluated
+  bool accept = cached;
   // One loop, one gate evaluation per trip (a single inlined copy of the gate).  phase 0: the walk of the heuristic,
   // candidates generated one per lane, a round of whole paths at a time, the viable ones gated in order.  phase 1
   // (RMSA-v0, QOT_HEUR_VERDICT): the action (path, slot) does not name the modulation - the step assigns the most
@@ -396,6 +408,7 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
   QotCand c{-1, 0, -1, 0, 0, 0}, chosen{-1, 0, -1, 0, 0, 0};
   unsigned viable = 0u;
   int p0 = 0, phase = 0, cur_t = 0;
+  double gc0 = -1.0, gmin0 = 0.0;
   while (true) {
     if (phase == 0 && !viable) {
       if (p0 >= n_paths) break;
@@ -460,8 +473,9 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
     const PathRec rec = load_path(p, cx.pair, A.path);
     accept = cx.gate(rec, A.path, A.core, A.start, A.n, A.se, gc, gmin);
     if (phase == 2) break;
-    if (phase == 0 && accept && !rmcsa && MODE == QOT_HEUR_VERDICT && cur_t > 0) {
+    if (phase == 0 && accept && !rmcsa && MODE != QOT_VERDICT && cur_t > 0) {
       chosen = A;
+      gc0 = gc, gmin0 = gmin;  // what the heuristic's own walk evaluated last (QOT_HEURISTIC reports that)
       c = chosen;
       bool ok2 = false;
       if (lane < cur_t) {
@@ -485,27 +499,42 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
           accept ? make_int4(A.path, A.mod, A.core, A.start) : make_int4(p.k, p.n_mods, p.cores, p.S);
   }
   if (lane == 0) {  // 1 / GSNR (linear); orlg_qot_get converts to dB on demand (no log10 on the step path)
-    p.qot_g[2 * (size_t)e] = gc;  // < 0: nothing evaluated
-    p.qot_g[2 * (size_t)e + 1] = (gc >= 0.0 && gc <= p.qot_thr_lin[A.se]) ? gmin : -1.0;  // not reported when the candidate failed
+    double* q = p.qot_g + 2 * (size_t)e;   // the pair orlg_qot_get reports
+    double* qp = p.qot_gp + 2 * (size_t)e; // the pair of a QOT_HEURISTIC launch's proposal, for the verdict launch that takes it
+    if (cached) {
+      q[0] = qp[0], q[1] = qp[1];
+    } else {
+      const double fc = gc;  // < 0: nothing evaluated
+      const double fw = (gc >= 0.0 && gc <= p.qot_thr_lin[A.se]) ? gmin : -1.0;  // not reported when the candidate failed
+      if (MODE == QOT_HEURISTIC) {
+        qp[0] = fc, qp[1] = fw;
+        // the heuristic's own walk ended at its first-fit candidate; the modulation search at that slot came after
+        q[0] = gc0 >= 0.0 ? gc0 : fc, q[1] = gc0 >= 0.0 ? gmin0 : fw;
+      } else {
+        q[0] = fc, q[1] = fw;
+      }
+    }
   }
 
-  // (3) the accepted candidate enters the service table
+  // (3) the accepted candidate enters the service table (QOT_HEURISTIC: its sums are left in the row the next pop
+  // would return and the verdict is recorded as the proposal; nothing is taken)
   int slot = 0;
-  if (MODE != QOT_HEURISTIC) {
-    if (accept && free_n == 0) {  // more running services than rows (the release queue is as full): refuse
-      accept = false;
-      if (lane == 0) atomicOr((unsigned long long*)&p.counters[(size_t)CNT_FAULT * p.NP + e], 32ull);
-    }
-    if (accept) {
-      slot = free_stack[--free_n];
+  if (accept && free_n == 0) {  // more running services than rows (the release queue is as full): refuse
+    accept = false;
+    if (MODE != QOT_HEURISTIC && lane == 0) atomicOr((unsigned long long*)&p.counters[(size_t)CNT_FAULT * p.NP + e], 32ull);
+  }
+  if (accept) {
+    slot = free_stack[free_n - 1];
+    if (MODE != QOT_HEURISTIC) free_n--;
+    if (!cached) {
       const PathRec rec = load_path(p, cx.pair, A.path);
       if (lane < rec.hops())
         cx.row(slot)[lane] = make_longlong2((long long)cx.sm.cSA[lane], (long long)cx.sm.cSX[lane]);
     }
-    if (lane == 0) {
-      p.qot_verdict[2 * (size_t)e] = make_int4(accept ? 1 : 0, A.path | (A.core << 16), A.start, A.n);
-      p.qot_verdict[2 * (size_t)e + 1] = make_int4(A.se, slot, A.mod, 0);
-    }
+  }
+  if (lane == 0) {
+    p.qot_verdict[2 * (size_t)e] = make_int4(accept ? 1 : 0, A.path | (A.core << 16), A.start, A.n);
+    p.qot_verdict[2 * (size_t)e + 1] = make_int4(A.se, slot, A.mod, 0);
   }
   if (lane == 0) {
     p.qot_free_n[e] = free_n;

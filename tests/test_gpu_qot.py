@@ -138,3 +138,46 @@ def test_gate_with_another_policy_and_rollout():
     r0 = torch.zeros(n_env, dtype=torch.int64, device=eng.device)
     e0.rollout(S.H_SAP_FF, n_steps, r0)
     assert int(r0.sum()) > int(rsum.sum())
+
+
+@pytest.mark.parametrize("env_id,topo,kw,adaptive", CONFIGS)
+def test_heuristic_then_step_takes_the_proposal(env_id, topo, kw, adaptive):
+    """The agent loop (orlg_heuristic 13, then orlg_step with its answer) gives what orlg_step_auto gives: the verdict
+    launch takes the heuristic launch's verdict.  A different action, a reset or another step in between do not."""
+    import torch
+
+    from optical_rl_gym_qot_aware_b200.engine import Engine
+
+    spec = S.make_spec(env_id, G.topology(topo), seed=91, auto_reset=True, qot="gn", qot_adaptive=adaptive, **kw)
+    n_env, n_steps = 48, 220
+    a_eng, b_eng = Engine(spec, n_env), Engine(spec, n_env)
+    a_eng.reset(True)
+    b_eng.reset(True)
+    dev = a_eng.device
+    mk = lambda *s, dt=torch.int32: torch.zeros(s, dtype=dt, device=dev)  # noqa: E731
+    act_a, act_b, rew_a, rew_b = mk(n_env, a_eng.action_dim), mk(n_env, a_eng.action_dim), mk(n_env), mk(n_env)
+    al_a, al_b = mk(n_env, 4), mk(n_env, 4)
+    rng = np.random.default_rng(3)
+    for t in range(n_steps):
+        a_eng.step_auto(S.H_SAP_GN_FF, act_a, rew_a, None, None, al_a)
+        b_eng.heuristic(S.H_SAP_GN_FF, act_b)
+        assert torch.equal(act_a, act_b), t
+        if t % 7 == 3:  # some envs get another action than the proposal: evaluated afresh (the twin steps it too)
+            other = act_b.clone()
+            pick = torch.from_numpy(rng.random(n_env) < 0.3).to(dev)
+            other[pick, -1] = (other[pick, -1] + 1) % spec.num_slots
+            b_eng.step(other, rew_b, None, None, al_b)
+            assert int(b_eng.qot_check().abs().sum()) == 0
+            # the twin cannot follow a diverged history: both start again (a reset also ends a proposal)
+            a_eng.reset(True)
+            b_eng.reset(True)
+            continue
+        if t % 11 == 5:  # a heuristic launch that is not followed by its step: the next proposal must be recomputed
+            b_eng.heuristic(S.H_SAP_GN_FF, act_b)
+        b_eng.step(act_b, rew_b, None, None, al_b)
+        assert torch.equal(rew_a, rew_b) and torch.equal(al_a, al_b), t
+        ok = al_a[:, 0].cpu().numpy() == 1  # a blocked request: the fused form reports the heuristic's last candidate, the step nothing
+        assert close(a_eng.qot_last().cpu().numpy()[ok], b_eng.qot_last().cpu().numpy()[ok]), t
+    assert torch.equal(a_eng.export_state(), b_eng.export_state())
+    assert torch.equal(a_eng.counters(), b_eng.counters())
+    assert int(a_eng.qot_check().abs().sum()) == 0 and int(b_eng.qot_check().abs().sum()) == 0

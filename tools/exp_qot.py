@@ -32,3 +32,14 @@ for g in (True, False, True):
 ms, first = eng.timed_steps(20, heuristic_id=S.H_SAP_GN_FF, flush=None, use_graph=True)
 print("warm", np.median(ms), np.median(first))
 print("check", int(eng.qot_check().abs().sum()), "fault", int(eng.counters()[:, 10].max()))
+# the agent loop: heuristic launch, then the step with its answer (verdict launch takes the proposal)
+act = torch.zeros((n, eng.action_dim), dtype=torch.int32, device=eng.device)
+rew = torch.zeros(n, dtype=torch.int32, device=eng.device)
+ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+th, ts = [], []
+for k in range(20):
+    ev[0].record(); eng.heuristic(S.H_SAP_GN_FF, act); ev[1].record(); eng.step(act, rew, None, None, None); ev[2].record()
+    torch.cuda.synchronize()
+    th.append(ev[0].elapsed_time(ev[1])); ts.append(ev[1].elapsed_time(ev[2]))
+print("agent loop: heuristic ms", np.median(th), "step (verdict + step kernel) ms", np.median(ts))
+print("check", int(eng.qot_check().abs().sum()), "fault", int(eng.counters()[:, 10].max()))
