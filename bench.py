@@ -351,15 +351,19 @@ def run_e2e(spec, w, n_env, parts, steps, local, rank, heap_capacity, block_wait
     torch.cuda.synchronize()
     policy_s = [0.0]
 
+    def propose(h):
+        """Device policies: the heuristic launch and the copy of its proposal to pinned memory, not waited for."""
+        if not obs_policy:
+            with torch.cuda.stream(h["st"]):
+                h["e"].heuristic(hid, h["d_act"])
+                h["act"].copy_(h["d_act"], non_blocking=True)
+
     def submit(h):
         he, st = h["e"], h["st"]
         p0 = time.perf_counter()
         if obs_policy:
             host_policy_kspff(h["obs"].numpy(), t.n_nodes, t.k_paths, spec.j, out=h["act"].numpy())
         else:
-            with torch.cuda.stream(st):
-                he.heuristic(hid, h["d_act"])
-                h["act"].copy_(h["d_act"], non_blocking=True)
             st.synchronize()  # the host "policy" has the proposal in hand before it answers
         policy_s[0] += time.perf_counter() - p0
         he.step_host_async(h["act"], h["rew"], h["done"], h["obs"], h["alloc"], stream=st)
@@ -369,14 +373,17 @@ def run_e2e(spec, w, n_env, parts, steps, local, rank, heap_capacity, block_wait
                 h["gs"].copy_(h["d_gs"], non_blocking=True)
 
     def run(nsteps):
+        # two sweeps over the shards per step, so that the shards' proposal launches run side by side on the GPU and
+        # so do their steps, instead of the host waiting for one shard's small launch at a time
         for h in shards:
-            submit(h)
-        for _ in range(nsteps - 1):
+            propose(h)
+        for it in range(nsteps):
+            for h in shards:
+                submit(h)
             for h in shards:
                 h["e"].step_host_wait(stream=h["st"])
-                submit(h)
-        for h in shards:
-            h["e"].step_host_wait(stream=h["st"])
+                if it + 1 < nsteps:
+                    propose(h)
 
     run(min(5, steps))
     barrier()
@@ -397,7 +404,8 @@ def run_e2e(spec, w, n_env, parts, steps, local, rank, heap_capacity, block_wait
         h["e"].close()
     return dict(ms=ms, steps=steps, h2d=h2d, d2h=d2h, policy_ms=policy_s[0] * 1e3 / steps,
                 mode=(f"{parts} VecEnv shard(s) of {nh} envs on their own streams, orlg_step_host_async / _wait"
-                      + (" (a shard's host work overlaps the copies and kernels of the others)" if parts > 1 else "")),
+                      + (" (a shard's host work overlaps the copies and kernels of the others; per step one sweep"
+                         " submits every shard's step, one waits for it and launches the next proposal)" if parts > 1 else "")),
                 policy=("numpy K-SP-FF from the host observation" if obs_policy
                         else "device heuristic -> pinned host (D2H) -> orlg_step_host (H2D)"))
 
