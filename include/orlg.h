@@ -284,7 +284,12 @@ int orlg_set_obs_layout(orlg_engine* e, int64_t env_stride, int64_t feat_stride)
 /* Observation of the pending request without stepping. */
 int orlg_observation(orlg_engine* e, int obs_kind, void* dev_obs, void* stream);
 
-/* Device-side heuristic: writes the action the reference heuristic would return. */
+/* Device-side heuristic: writes the action the reference heuristic would return.
+ * QoT-gated engines, ORLG_H_SAP_GN_FF: the launch also records its verdict (lightpath, modulation, running sums) as a
+ * proposal.  If the next state-touching call on the engine is orlg_step (or orlg_step_host*), every env whose action
+ * equals the proposal takes that verdict instead of evaluating the gate a second time - the reference's agent loop
+ * `action = heuristic(env); env.step(action)` costs one gate evaluation, not two.  Any other action is evaluated as
+ * usual; orlg_reset, orlg_load_trace or another step in between end the proposal.  Results are identical either way. */
 int orlg_heuristic(orlg_engine* e, int heuristic_id, int32_t* dev_actions, void* stream);
 
 /* Fused next-action hint.  With a non-NULL dev_next_actions (int32 [num_envs][action_dim], kept by
