@@ -264,12 +264,12 @@ struct QotCtx {
       const unsigned char* ri = path_bytes(svc_pair(s), svc_path(s));
       longlong2* rw = row(svc_slot(s));
       const int hi = __ldg(ri);
+      // reductions without a return value: nothing waits for the rows.  This env's rows are read (by the gate, below
+      // in the same warp, after a __syncwarp) only after every event has been issued, and nobody else touches them.
       for (int h = 0; h < hi; h++)
         if (mask_has(common, __ldg(ri + 4 + h))) {
-          longlong2 sv = rw[h];
-          sv.x += qa;
-          sv.y += qx;
-          rw[h] = sv;
+          atomicAdd(reinterpret_cast<unsigned long long*>(&rw[h].x), (unsigned long long)qa);
+          atomicAdd(reinterpret_cast<unsigned long long*>(&rw[h].y), (unsigned long long)qx);
         }
     });
   }
