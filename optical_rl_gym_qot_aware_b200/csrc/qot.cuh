@@ -51,7 +51,17 @@ struct QotWarpSmem {
 #ifdef QOT_STAGE_MASKS
   ulonglong2 mask[QOT_CAP];             // their paths as link sets
 #endif
-  unsigned long long cSA[32], cSX[32];  // the candidate's own sums, per hop
+  // the candidate's own sums, per hop, as (low, high) 32-bit halves: shared memory has native 32-bit adds only (a
+  // 64-bit atomicAdd is a compare-and-swap loop); the carry out of the low half is seen by the add that causes it
+  unsigned cSA_lo[32], cSA_hi[32], cSX_lo[32], cSX_hi[32];
+  __device__ __forceinline__ static void add64(unsigned* lo, unsigned* hi, unsigned long long x) {
+    const unsigned xl = (unsigned)x, xh = (unsigned)(x >> 32);
+    const unsigned old = atomicAdd(lo, xl);
+    const unsigned up = xh + ((unsigned)(old + xl) < xl ? 1u : 0u);
+    if (up) atomicAdd(hi, up);
+  }
+  __device__ __forceinline__ long long SA(int h) const { return (long long)(((unsigned long long)cSA_hi[h] << 32) | cSA_lo[h]); }
+  __device__ __forceinline__ long long SX(int h) const { return (long long)(((unsigned long long)cSX_hi[h] << 32) | cSX_lo[h]); }
   unsigned short nb[QOT_CAP];           // compacted neighbour list of the current pass
   unsigned char hop_of[128];            // link -> hop of the candidate
 };
@@ -175,14 +185,13 @@ struct QotCtx {
 
   // The gate for one candidate; warp-collective.  Returns pass / fail; acc_c = 1 / GSNR of the candidate,
   // acc_w = the largest 1 / GSNR among its neighbours with the candidate present (0 without neighbours).
-  // Leaves the candidate's sums in sm.cSA / sm.cSX.
+  // Leaves the candidate's sums in sm.cSA_* / sm.cSX_*.
   __device__ __forceinline__ bool gate(const PathRec& rec, int path, int core, int start, int n, int se, double& acc_c, double& acc_w) {
     const int cpos2 = 2 * start + n;
     const ulonglong2 cmask = __ldg(g.path_mask + (size_t)pair * p.k + path);
     const int hops = rec.hops();
     __syncwarp();
-    sm.cSA[lane] = 0ull;
-    sm.cSX[lane] = 0ull;
+    sm.cSA_lo[lane] = sm.cSA_hi[lane] = sm.cSX_lo[lane] = sm.cSX_hi[lane] = 0u;
     if (lane < hops) sm.hop_of[rec.link(lane)] = (unsigned char)lane;
     __syncwarp();
     const int cols = 4 * g.tab_S + 1;
@@ -202,14 +211,14 @@ struct QotCtx {
       unsigned long long c0 = common.x, c1 = common.y;
       while (c0) {
         const int h = sm.hop_of[__ffsll((long long)c0) - 1];
-        atomicAdd(&sm.cSA[h], qa_ci);
-        atomicAdd(&sm.cSX[h], qx_ci);
+        sm.add64(&sm.cSA_lo[h], &sm.cSA_hi[h], qa_ci);
+        sm.add64(&sm.cSX_lo[h], &sm.cSX_hi[h], qx_ci);
         c0 &= c0 - 1;
       }
       while (c1) {
         const int h = sm.hop_of[64 + __ffsll((long long)c1) - 1];
-        atomicAdd(&sm.cSA[h], qa_ci);
-        atomicAdd(&sm.cSX[h], qx_ci);
+        sm.add64(&sm.cSA_lo[h], &sm.cSA_hi[h], qa_ci);
+        sm.add64(&sm.cSX_lo[h], &sm.cSX_hi[h], qx_ci);
         c1 &= c1 - 1;
       }
       // the neighbour with the candidate present: its stored sums + the candidate's term on the shared links
@@ -243,7 +252,7 @@ struct QotCtx {
     double v = 0.0;
     if (lane < hops) {
       const double4 lc = link_c[rec.link(lane)];
-      v = lc.w * (cc.ase * lc.z + cc.nli * lc.x * qot_sum_phi(g, n, (long long)sm.cSA[lane], (long long)sm.cSX[lane], lc.y));
+      v = lc.w * (cc.ase * lc.z + cc.nli * lc.x * qot_sum_phi(g, n, sm.SA(lane), sm.SX(lane), lc.y));
     }
     acc_c = hop_sum(v, hops);
     acc_w = worst;
@@ -529,7 +538,7 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
     if (!cached) {
       const PathRec rec = load_path(p, cx.pair, A.path);
       if (lane < rec.hops())
-        cx.row(slot)[lane] = make_longlong2((long long)cx.sm.cSA[lane], (long long)cx.sm.cSX[lane]);
+        cx.row(slot)[lane] = make_longlong2(cx.sm.SA(lane), cx.sm.SX(lane));
     }
   }
   if (lane == 0) {
