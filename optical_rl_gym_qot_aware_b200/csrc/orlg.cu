@@ -572,11 +572,16 @@ static int launch_qot(orlg_engine* e, int mode, const int32_t* actions, int32_t*
   e->qot_proposal_valid = (mode == QOT_HEURISTIC);
   const int grid = (e->p.num_envs + QOT_WARPS - 1) / QOT_WARPS;
   const size_t dsm = (size_t)e->p.E * sizeof(double4);  // the per-link factors staged by every CTA
-#define ORLG_QOT_LAUNCH_M(WW, RM, MD)                                                                          \
-  do {                                                                                                         \
-    if (e->qot_cap <= 64) qot_kernel<WW, 64, RM, MD><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q);       \
-    else if (e->qot_cap <= 128) qot_kernel<WW, 128, RM, MD><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q); \
-    else qot_kernel<WW, 256, RM, MD><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q);                        \
+#define ORLG_QOT_LAUNCH_N(WW, RM, MD, NR)                                                                          \
+  do {                                                                                                             \
+    if (e->qot_cap <= 64) qot_kernel<WW, 64, RM, MD, NR><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q);       \
+    else if (e->qot_cap <= 128) qot_kernel<WW, 128, RM, MD, NR><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q); \
+    else qot_kernel<WW, 256, RM, MD, NR><<<grid, QOT_WARPS * 32, dsm, st>>>(e->p, e->gp, q);                        \
+  } while (0)
+#define ORLG_QOT_LAUNCH_M(WW, RM, MD)                         \
+  do {                                                        \
+    if (e->p.E <= 64) ORLG_QOT_LAUNCH_N(WW, RM, MD, true);    \
+    else ORLG_QOT_LAUNCH_N(WW, RM, MD, false);                \
   } while (0)
 #define ORLG_QOT_LAUNCH_K(WW, RM)                                          \
   do {                                                                     \
@@ -597,6 +602,7 @@ static int launch_qot(orlg_engine* e, int mode, const int32_t* actions, int32_t*
 #undef ORLG_QOT_LAUNCH
 #undef ORLG_QOT_LAUNCH_K
 #undef ORLG_QOT_LAUNCH_M
+#undef ORLG_QOT_LAUNCH_N
   cudaError_t rc = cudaGetLastError();
   if (rc != cudaSuccess) {
     e->err = std::string("qot_kernel launch: ") + cudaGetErrorString(rc);

@@ -45,12 +45,13 @@ struct QotIO {
 // QOT_CAP = running services staged per window (an env with more is walked window by window); the kernel is
 // instantiated for 64 / 128 / 256 and the launch picks the smallest that covers the offered load + 1 sigma, because
 // shared memory per CTA is what bounds the resident warps here
-template <int QOT_CAP>
+template <int QOT_CAP, bool NARROW>
 struct QotWarpSmem {
   unsigned long long pay[QOT_CAP];      // release-queue payloads of the staged window
-#ifdef QOT_STAGE_MASKS
-  ulonglong2 mask[QOT_CAP];             // their paths as link sets
-#endif
+  // their paths as link sets, staged when the topology has at most 64 links (NARROW) and the window is small; wider
+  // sets and the 256-entry window (where the shared memory is worth more as L1) take them from the path table
+  static constexpr bool STAGED = NARROW && QOT_CAP <= 128;
+  unsigned long long mask[STAGED ? QOT_CAP : 1];
   // the candidate's own sums, per hop, as (low, high) 32-bit halves: shared memory has native 32-bit adds only (a
   // 64-bit atomicAdd is a compare-and-swap loop); the carry out of the low half is seen by the add that causes it
   unsigned cSA_lo[32], cSA_hi[32], cSX_lo[32], cSX_hi[32];
@@ -89,11 +90,11 @@ __device__ __forceinline__ double qot_sum_phi(const GsnrParams& g, int n, long l
   return __ldg(g.sci_tab + n) + ((double)SA * QOT_INV_SCALE - ((double)SX * QOT_INV_SCALE) * lol);
 }
 
-template <int QOT_CAP>
+template <int QOT_CAP, bool NARROW>
 struct QotCtx {
   const Params& p;
   const GsnrParams& g;
-  QotWarpSmem<QOT_CAP>& sm;
+  QotWarpSmem<QOT_CAP, NARROW>& sm;
   const double4* link_c;  // per-link factors (l_eff, l_eff / L, exp(2 a L) - 1, spans), staged in shared memory
   int e, lane;
   const ulonglong2* heap;
@@ -108,13 +109,10 @@ struct QotCtx {
     return reinterpret_cast<const unsigned char*>(p.path_rec + ((size_t)pr * p.k + path) * p.rec_u4);
   }
 
-  // link set of a staged service: from the path table (a few KB, L1 resident) unless the build stages it
+  // link set of a staged service: staged (NARROW) or from the path table (a few KB, L1 resident)
   __device__ __forceinline__ ulonglong2 svc_mask(unsigned long long s, int i) const {
-#ifdef QOT_STAGE_MASKS
-    return sm.mask[i];
-#else
-    return __ldg(g.path_mask + (size_t)svc_pair(s) * p.k + svc_path(s));
-#endif
+    if constexpr (QotWarpSmem<QOT_CAP, NARROW>::STAGED) return make_ulonglong2(sm.mask[i], 0ull);
+    else return __ldg(g.path_mask + (size_t)svc_pair(s) * p.k + svc_path(s));
   }
   __device__ __forceinline__ void stage(int w) {
     __syncwarp();
@@ -122,9 +120,8 @@ struct QotCtx {
     for (int i = lane; i < n; i += 32) {
       const unsigned long long s = heap[base + i].y;
       sm.pay[i] = s;
-#ifdef QOT_STAGE_MASKS
-      sm.mask[i] = __ldg(g.path_mask + (size_t)svc_pair(s) * p.k + svc_path(s));
-#endif
+      if constexpr (QotWarpSmem<QOT_CAP, NARROW>::STAGED)
+        sm.mask[i] = __ldg(reinterpret_cast<const unsigned long long*>(g.path_mask + (size_t)svc_pair(s) * p.k + svc_path(s)));
     }
     win = w;
     __syncwarp();
@@ -341,9 +338,9 @@ __device__ __forceinline__ bool qot_alone_ok_lane(const Params& p, const GsnrPar
 // closed-form gate, interference-free GSNR - and the viable ones put through the gate in the order the reference's
 // first-fit heuristics walk them, (3) an accepted candidate gets a row of the service table and enters its
 // neighbours' sums; the verdict tells the step kernel what to provision.
-template <int W, int QOT_CAP, bool RMCSA, int MODE>
+template <int W, int QOT_CAP, bool RMCSA, int MODE, bool NARROW>
 __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const __grid_constant__ Params p, const __grid_constant__ GsnrParams g, const QotIO io) {
-  __shared__ QotWarpSmem<QOT_CAP> smem[QOT_WARPS];
+  __shared__ QotWarpSmem<QOT_CAP, NARROW> smem[QOT_WARPS];
   extern __shared__ double4 s_link[];  // per-link factors, p.E entries (sized at launch)
   for (int l = threadIdx.x; l < p.E; l += blockDim.x) s_link[l] = g.link_c[l];
   __syncthreads();
@@ -351,7 +348,7 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
   if (e >= p.num_envs) return;
   const uint32_t m = p.meta[e];
   const int bit_rate = (int)(m & 0xFFFFu), src = (int)((m >> 16) & 0xFFu), dst = (int)(m >> 24);
-  QotCtx<QOT_CAP> cx{p, g, smem[threadIdx.x >> 5], s_link, e, lane, p.heap + (size_t)e * p.heap_stride + HEAP_PAD, p.heap_len[e],
+  QotCtx<QOT_CAP, NARROW> cx{p, g, smem[threadIdx.x >> 5], s_link, e, lane, p.heap + (size_t)e * p.heap_stride + HEAP_PAD, p.heap_len[e],
             p.qot_sums + (size_t)e * p.qot_slot_cap * p.qot_hops, bit_rate, src * p.n_nodes + dst, 1.0 / g.P, -1};
   unsigned short* free_stack = p.qot_free + (size_t)e * p.qot_slot_cap;
   int free_n = p.qot_free_n[e];
