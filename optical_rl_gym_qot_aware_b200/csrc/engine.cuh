@@ -260,7 +260,14 @@ struct Tile {
       uint32_t* q = base + l * (W * BD);
 #pragma unroll
       for (int wi = 0; wi < W; wi++)
-        if (m[wi]) q[wi * BD] = set ? (q[wi * BD] | m[wi]) : (q[wi * BD] & ~m[wi]);
+        if (m[wi]) {
+          if constexpr (BD == 1) {  // rows in HBM: a reduction that returns nothing, so no hop waits for its row
+            if (set) atomicOr(q + wi, m[wi]);
+            else atomicAnd(q + wi, ~m[wi]);
+          } else {
+            q[wi * BD] = set ? (q[wi * BD] | m[wi]) : (q[wi * BD] & ~m[wi]);
+          }
+        }
     });
   }
   // one slot / channel on every link of the path (PhyRMSA allocates whole channels): one word per link
@@ -269,7 +276,12 @@ struct Tile {
     uint32_t* base = s + (size_t)core * E * W * BD + tid + (pos >> 5) * BD;
     for_each_link(r, [&](int l) {
       uint32_t* q = base + l * (W * BD);
-      *q = set ? (*q | m) : (*q & ~m);
+      if constexpr (BD == 1) {
+        if (set) atomicOr(q, m);
+        else atomicAnd(q, ~m);
+      } else {
+        *q = set ? (*q | m) : (*q & ~m);
+      }
     });
   }
   __device__ __forceinline__ void clear_range(const PathRec& r, int core, int start, int n) {
