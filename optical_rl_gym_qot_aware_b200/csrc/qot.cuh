@@ -28,6 +28,7 @@ enum { QOT_VERDICT = 0, QOT_HEUR_VERDICT = 1, QOT_HEURISTIC = 2 };
 #endif
 constexpr int QOT_WARPS = QOT_WARPS_N;
 constexpr int QOT_REL_CAP = 32;  // services released by one step (overflow: sticky fault bit 16)
+static_assert(QOT_REL_CAP == 32, "qot_kernel keeps one released payload per lane");
 constexpr double QOT_SCALE = 17592186044416.0;  // 2^44
 constexpr double QOT_INV_SCALE = 1.0 / 17592186044416.0;
 
@@ -117,11 +118,19 @@ struct QotCtx {
   __device__ __forceinline__ void stage(int w) {
     __syncwarp();
     const int base = w * QOT_CAP, n = min(QOT_CAP, heap_len - base);
-    for (int i = lane; i < n; i += 32) {
-      const unsigned long long s = heap[base + i].y;
-      sm.pay[i] = s;
-      if constexpr (QotWarpSmem<QOT_CAP, NARROW>::STAGED)
-        sm.mask[i] = __ldg(reinterpret_cast<const unsigned long long*>(g.path_mask + (size_t)svc_pair(s) * p.k + svc_path(s)));
+    // every round's payload is asked for before the first one is used: one memory round trip per window, not one per
+    // 32 services
+    unsigned long long s[QOT_CAP / 32];
+#pragma unroll
+    for (int u = 0; u < QOT_CAP / 32; u++) s[u] = (lane + 32 * u < n) ? heap[base + lane + 32 * u].y : 0ull;
+#pragma unroll
+    for (int u = 0; u < QOT_CAP / 32; u++) {
+      const int i = lane + 32 * u;
+      if (i < n) {
+        sm.pay[i] = s[u];
+        if constexpr (QotWarpSmem<QOT_CAP, NARROW>::STAGED)
+          sm.mask[i] = __ldg(reinterpret_cast<const unsigned long long*>(g.path_mask + (size_t)svc_pair(s[u]) * p.k + svc_path(s[u])));
+      }
     }
     win = w;
     __syncwarp();
@@ -359,14 +368,20 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
   // same table.
   const unsigned long long added = p.qot_add[e];
   const int nrel = p.qot_rel_n[e], nadd = added != 0ull ? 1 : 0;
+  // lane r holds released payload r (QOT_REL_CAP = 32 = one per lane), fetched before the loop needs them; the row an
+  // accept will take is on top of the free stack now unless a release pushes one
+  const unsigned long long my_rel = lane < nrel ? p.qot_rel[(size_t)e * QOT_REL_CAP + lane] : 0ull;
+  int top_row = (nrel == 0 && free_n > 0) ? (int)free_stack[free_n - 1] : 0;
   for (int ev = 0; ev < nadd + nrel; ev++) {
     const bool is_add = ev < nadd;
-    const unsigned long long s = is_add ? added : p.qot_rel[(size_t)e * QOT_REL_CAP + (ev - nadd)];
+    const unsigned long long rs = __shfl_sync(0xFFFFFFFFu, my_rel, (ev - nadd) & 31);
+    const unsigned long long s = is_add ? added : rs;
     const ulonglong2 em = __ldg(g.path_mask + (size_t)svc_pair(s) * p.k + svc_path(s));
     cx.apply_to_neighbours(em, svc_core(s), svc_start(s), svc_slots(s), svc_se(s), is_add ? 1 : -1, is_add ? svc_slot(s) : -1);
     if (!is_add) {
       if (lane == 0) free_stack[free_n] = (unsigned short)svc_slot(s);
       free_n++;
+      top_row = svc_slot(s);
     }
   }
   __syncwarp();
@@ -530,7 +545,7 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
     if (MODE != QOT_HEURISTIC && lane == 0) atomicOr((unsigned long long*)&p.counters[(size_t)CNT_FAULT * p.NP + e], 32ull);
   }
   if (accept) {
-    slot = free_stack[free_n - 1];
+    slot = top_row;  // == free_stack[free_n - 1]
     if (MODE != QOT_HEURISTIC) free_n--;
     if (!cached) {
       const PathRec rec = load_path(p, cx.pair, A.path);
