@@ -55,6 +55,7 @@ DEEPRMSA_NODE_PROBS = [0.01801802, 0.04004004, 0.05305305, 0.01901902, 0.0450450
 WORKLOADS = {
     "c6_rmsa_us14_320_gn": dict(
         env="RMSA-v0", topo="us14", hid=S.H_SAP_GN_FF, obs=S.OBS_NONE, step="auto", preroll=600, bytes=None, cpu_envs=512,
+        envs=262144,  # the target names no batch size; the gate kernel is still filling up at 65 536 envs (profiles/r02b_env_sweep.md)
         kw=dict(load=100, mean_service_holding_time=25, num_spectrum_resources=320, episode_length=1000, qot="gn",
                 qot_adaptive=True),
         what="BASELINE target config: 320-slot RMSA on the US topology, GN-model GSNR of the candidate and its "
@@ -91,8 +92,11 @@ WORKLOADS = {
         kw=dict(load=400, mean_service_holding_time=25, num_spectrum_resources=320, episode_length=1000),
         what="BASELINE configs[4] (SPN, 320 slots)"),
 }
+WORKLOADS["c6_rmsa_us14_320_gn_64k"] = dict(WORKLOADS["c6_rmsa_us14_320_gn"], envs=65536, ref="c6_rmsa_us14_320_gn",
+                                             what="the headline workload at 65 536 envs per GPU (the batch of BASELINE configs[1])")
 HEADLINE = "c6_rmsa_us14_320_gn"
-BLOCK = ["c1_rmsa_nsfnet_100", "c2_deeprmsa_nsfnet_100", "c3_rmcsa_jpn12_320_gn", "c3_rmcsa_jpn12_320",
+DEFAULT_ENVS = 65536  # BASELINE configs[1]; a workload may name its own (`envs`)
+BLOCK = ["c6_rmsa_us14_320_gn_64k", "c1_rmsa_nsfnet_100", "c2_deeprmsa_nsfnet_100", "c3_rmcsa_jpn12_320_gn", "c3_rmcsa_jpn12_320",
          "c4_phyrmsa_us14_320", "c5_rmsa_spn_100", "c5_rmsa_spn_320"]
 DATA = "synthetic (Philox request streams, seed 0x5eed, keyed by global env id)"
 OBS_NAME = {0: "none", 1: "f64", 2: "f32", 3: "matrix_u8", 4: "phy cuts+rss f64", 5: "phy cuts f64"}
@@ -229,12 +233,16 @@ def cpu_arm(spec, w, n_sample, threads, seconds=None, steps=None, warmup=0):
     return done_steps / dt, dt * 1e3 / max(1, passes), passes, float(blocking)
 
 
+def envs_of(name, args):
+    return int(args.envs or WORKLOADS[name].get("envs", DEFAULT_ENVS))
+
+
 def python_reference(name):
     """The unmodified Python reference timed in the build container (oracle/refharness/time_reference.py writes
     profiles/python_reference.json; it cannot travel to the GPU box)."""
     p = os.path.join(REPO, "profiles", "python_reference.json")
     try:
-        return json.load(open(p)).get(name)
+        return json.load(open(p)).get(WORKLOADS.get(name, {}).get("ref", name))
     except Exception:
         return None
 
@@ -421,7 +429,7 @@ def measure(name, args, ctx, full):
     dev = torch.device("cuda", local)
     spec, w = make_workload(name)
     hid, auto = w["hid"], w["step"] == "auto"
-    n_env, K, W = args.envs, args.steps, args.warmup
+    n_env, K, W = envs_of(name, args), args.steps, args.warmup
     eng = Engine(spec, n_env, device=local, global_env_offset=rank * n_env, heap_capacity=args.heap_capacity)
     eng.reset(True)
     eng.rollout(hid, w["preroll"])
@@ -497,7 +505,7 @@ def workload_record(r, n_total, K, peak):
     ach = r["bytes"] * (n_total) / kern_s / 1e9
     st = [int(x) for x in r["stats"].cpu()]
     e = r["e2e"]
-    return {"what": r["w"]["what"], "env": r["w"]["env"], "value": n_total * K / (r["step_ms"] * 1e-3),
+    return {"what": r["w"]["what"], "env": r["w"]["env"], "envs_per_gpu": n_total, "value": n_total * K / (r["step_ms"] * 1e-3),
             "ms_per_step": r["step_ms"] / K, "median_ms_per_step": r["median_ms"], "launches_per_step": r["launches"] / K,
             "kernel": r["kern_name"], "kernel_us": kern_s * 1e6, "bytes_per_env_step": r["bytes"],
             "roofline_frac": ach / peak, "achieved_gbs": ach, "blocking": 1.0 - st[1] / max(1, st[0]),
@@ -514,7 +522,7 @@ def run_reference(args, name):
     threads = os.cpu_count() or 1
     n_sample = args.ref_envs or w["cpu_envs"]
     v, ms, passes, blocking = cpu_arm(spec, w, n_sample, threads, steps=args.steps, warmup=args.warmup)
-    sample = (f"{n_sample} envs of the {args.envs}-env batch x {passes} steps in one pool call, oracle C port "
+    sample = (f"{n_sample} envs of the {envs_of(name, args)}-env batch x {passes} steps in one pool call, oracle C port "
               f"(oracle/orlg_oracle.c) with its own heuristic, {threads} pthreads, {w['preroll']} pre-roll steps")
     line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": "env-steps/s", "n_gpus": args.gpus, "steps": args.steps,
@@ -581,7 +589,7 @@ def run_b200(args, name):
             dist.destroy_process_group()
         return
 
-    n_env = args.envs
+    n_env = envs_of(name, args)
     total = n_env * world
     peak, peak_src = measured_peaks()
     kern_s = kern_ms * 1e-3 / K
@@ -645,7 +653,7 @@ def run_b200(args, name):
             rr = measure(nm, blockargs, ctx, full=False)
             if int(rr["stats"][5]) != 0:
                 raise RuntimeError(f"device fault bits set in workload {nm}")
-            rec = workload_record(rr, n_env, K, peak)
+            rec = workload_record(rr, envs_of(nm, blockargs), K, peak)
             if not args.no_cpu_baseline:
                 v, _, passes, _ = cpu_arm(rr["spec"], rr["w"], rr["w"]["cpu_envs"], os.cpu_count() or 1,
                                           seconds=args.block_cpu_seconds)
@@ -665,7 +673,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=HEADLINE, choices=sorted(WORKLOADS))
-    ap.add_argument("--envs", type=int, default=65536, help="envs per GPU")
+    ap.add_argument("--envs", type=int, default=0, help="envs per GPU (0 = the workload's own: 65 536 unless it names another)")
     ap.add_argument("--ref-envs", type=int, default=0, help="envs in the CPU arm's bounded sample (0 = the workload's default)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--block-cpu-seconds", type=float, default=2.5)
