@@ -91,7 +91,7 @@ __device__ __forceinline__ double qot_sum_phi(const GsnrParams& g, int n, long l
   return __ldg(g.sci_tab + n) + ((double)SA * QOT_INV_SCALE - ((double)SX * QOT_INV_SCALE) * lol);
 }
 
-template <int QOT_CAP, bool NARROW>
+template <int QOT_CAP, bool NARROW, bool MULTICORE>
 struct QotCtx {
   const Params& p;
   const GsnrParams& g;
@@ -149,7 +149,7 @@ struct QotCtx {
       for (int base = 0; base < n; base += 32) {
         const int i = base + lane;
         bool hit = false;
-        if (i < n && svc_core(sm.pay[i]) == core) {
+        if (i < n && (!MULTICORE || svc_core(sm.pay[i]) == core)) {  // RMSA-v0: one core, nothing to compare
           const ulonglong2 im = svc_mask(sm.pay[i], i);
           hit = ((im.x & mask.x) | (im.y & mask.y)) != 0ull;
         }
@@ -357,7 +357,7 @@ __global__ void __launch_bounds__(QOT_WARPS * 32, QOT_MIN_CTAS) qot_kernel(const
   if (e >= p.num_envs) return;
   const uint32_t m = p.meta[e];
   const int bit_rate = (int)(m & 0xFFFFu), src = (int)((m >> 16) & 0xFFu), dst = (int)(m >> 24);
-  QotCtx<QOT_CAP, NARROW> cx{p, g, smem[threadIdx.x >> 5], s_link, e, lane, p.heap + (size_t)e * p.heap_stride + HEAP_PAD, p.heap_len[e],
+  QotCtx<QOT_CAP, NARROW, RMCSA> cx{p, g, smem[threadIdx.x >> 5], s_link, e, lane, p.heap + (size_t)e * p.heap_stride + HEAP_PAD, p.heap_len[e],
             p.qot_sums + (size_t)e * p.qot_slot_cap * p.qot_hops, bit_rate, src * p.n_nodes + dst, 1.0 / g.P, -1};
   unsigned short* free_stack = p.qot_free + (size_t)e * p.qot_slot_cap;
   int free_n = p.qot_free_n[e];
