@@ -359,13 +359,19 @@ __device__ void phy_heuristic(ENV& env, int hid, int* a) {
     Row<W> A = env.tile.path_avail(rec, 0);
     if (!row_any<W>(A)) continue;
     int cap = 0, head = 0;
+    static_assert(PHY_LEVELS % 4 == 0, "the level masks are fetched four at a time");
 #pragma unroll 1
-    for (int m = PHY_LEVELS; m >= 1; m--) {
-      Row<W> L = level_mask<W>(p, table, idp, m);
-      and_into(L, A);
-      int c = popcount<W>(L);
-      cap += m * c;
-      if (head == 0 && c > 0) head = m;
+    for (int m = PHY_LEVELS; m >= 1; m -= 4) {  // four masks in flight: one trip to L2 per four levels
+      Row<W> L[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) L[u] = level_mask<W>(p, table, idp, m - u);
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        and_into(L[u], A);
+        const int c = popcount<W>(L[u]);
+        cap += (m - u) * c;
+        if (head == 0 && c > 0) head = m - u;
+      }
     }
     if (cap * 100 < env.bit_rate) continue;  // the row would be tried, found short and popped
     if (hid == ORLG_H_PHY_SAP_FF || hid == ORLG_H_PHY_SAP_BM) {  // first row that can carry the request
