@@ -157,6 +157,13 @@ def main():
         episode_length=170, grooming=True, **tiny)
     run("phy_us14_cstate_sapff_100ch", us, US, ref.sapff_rmsa, False, 1500, seed=21, load=1900, episode_length=210,
         **small)
+    # the heuristics of the stubbed fixtures above once more as shipped (no stub: they look at the virtual layer first)
+    run("phy_us14_cstate_bmff_100ch", us, US, ref.phy_aware_bmff_rmsa, False, 1500, seed=25, load=1800, episode_length=260,
+        **small)
+    run("phy_us14_cstate_faff_100ch", us, US, ref.phy_aware_faff_rmsa, False, 1500, seed=26, load=1800, episode_length=270,
+        **small)
+    run("phy_jpn12_cstate_sapbm_64ch", jpn, JPN, ref.phy_aware_sapbm_rmsa, False, 1500, seed=27, load=1400,
+        episode_length=120, **tiny)
     # periodic defragmentation: targets for the round-2 kernel; no engine path consumes them yet
     run("defrag_phy_us14_defrag_cut_100ch", us, US, ref.phy_aware_bmfa_rmsa, False, 1200, seed=22, load=1700,
         episode_length=240, defrag_period=10, number_moves=10, metric="cut", **small)
