@@ -40,7 +40,7 @@ CASES = {
     "ms_phy_us14_bmfa_cut_320ch": ("PhyRMSA-v0", US, dict(load=1400, mean_service_holding_time=25, episode_length=200,
                                                           number_spectrum_channels=106, number_spectrum_channels_s_band=108,
                                                           num_spectrum_resources=64, bit_rate_selection="discrete",
-                                                          grooming=False), "bmfa", 16, 2000),  # the C4 bench shape
+                                                          grooming=False), "bmfa", 16, 4000),  # the C4 bench shape; steady state (and blocking) from ~2 000 steps on
 }
 
 
