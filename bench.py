@@ -490,7 +490,10 @@ def measure(name, args, ctx, full):
     # ---- e2e ----
     ncpu = os.cpu_count() or 1
     block_wait = {"spin": False, "block": True}.get(args.host_wait, world * 2 > ncpu)
-    parts = max(1, args.e2e_parts) if full else 1
+    # shards pay off when a step is long against the host's per-call work, or when the host computes the policy; the
+    # 40-80 us step kernels of the workloads block are host bound with four times the calls
+    slow_step = r["step_ms"] / K > 0.15 or (spec.env_kind == S.ENV_DEEPRMSA and spec.obs_dim > 0)
+    parts = max(1, args.e2e_parts) if (full or slow_step) else 1
     while n_env % parts:
         parts -= 1
     r["e2e"] = run_e2e(spec, w, n_env, parts, max(1, min(K, args.e2e_steps if full else 10)), local, rank,
