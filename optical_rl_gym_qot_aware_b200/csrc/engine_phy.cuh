@@ -422,8 +422,9 @@ __device__ void phy_heuristic(ENV& env, int hid, int* a) {
       need -= (int)__ldg(p.phy_mod + ((size_t)table * p.S + ch) * p.k + best) * 100;
     }
   } else {
+    // the scan above knows the highest level the row offers (BM-FF, BM-FA-Cut): the levels above it are empty
 #pragma unroll 1
-    for (int m = PHY_LEVELS; m >= 1 && need > 0; m--) {
+    for (int m = best_mod > 0 ? best_mod : PHY_LEVELS; m >= 1 && need > 0; m--) {
       Row<W> cand = level_mask<W>(p, table, best, m);
       and_into(cand, A);
       while (need > 0 && n < PHY_ADIM - 1 && row_any<W>(cand)) {
