@@ -53,8 +53,17 @@ template <int W>
 __device__ __forceinline__ Row<W> level_mask(const Params& p, int table, int idp, int m) {
   const uint32_t* a = p.phy_level_mask + (((size_t)table * p.k + idp) * PHY_LEVELS + (m - 1)) * W;
   Row<W> r;
+  if constexpr (W % 2 == 0) {  // rows are W words apart: 8-byte aligned for even W
 #pragma unroll
-  for (int i = 0; i < W; i++) r.w[i] = __ldg(a + i);
+    for (int i = 0; i < W; i += 2) {
+      const uint2 v = __ldg(reinterpret_cast<const uint2*>(a + i));
+      r.w[i] = v.x;
+      r.w[i + 1] = v.y;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < W; i++) r.w[i] = __ldg(a + i);
+  }
   return r;
 }
 
