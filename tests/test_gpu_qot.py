@@ -181,3 +181,19 @@ def test_heuristic_then_step_takes_the_proposal(env_id, topo, kw, adaptive):
     assert torch.equal(a_eng.export_state(), b_eng.export_state())
     assert torch.equal(a_eng.counters(), b_eng.counters())
     assert int(a_eng.qot_check().abs().sum()) == 0 and int(b_eng.qot_check().abs().sum()) == 0
+
+
+@pytest.mark.parametrize("env_id,topo,kw,adaptive", [CONFIGS[0], CONFIGS[2]])
+def test_running_sums_survive_a_long_run(env_id, topo, kw, adaptive):
+    """Thousands of provisions and releases per env (events applied with reductions that return nothing, accepted
+    lightpaths handed from launch to launch): every running sum still equals a from-scratch evaluation, bit for bit."""
+    from optical_rl_gym_qot_aware_b200.engine import Engine
+
+    spec = S.make_spec(env_id, G.topology(topo), seed=1234, auto_reset=True, qot="gn", qot_adaptive=adaptive, **kw)
+    eng = Engine(spec, 4096)
+    eng.reset(True)
+    for _ in range(3):
+        eng.rollout(S.H_SAP_GN_FF, 1500)
+        assert int(eng.qot_check().abs().sum()) == 0
+    cnt = eng.counters()
+    assert int(cnt[:, 10].max()) == 0 and int(cnt[0, 0]) >= 4500  # the pending request is counted on arrival
